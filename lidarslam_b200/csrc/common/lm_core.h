@@ -1,0 +1,311 @@
+// Gauss-Newton / Levenberg-Marquardt core replacing Ceres on the ICP path
+// (reference slam_lib/src/LocalOptimizer.cxx:74-102 configures ceres::Solve with
+// TRUST_REGION + LEVENBERG_MARQUARDT + DENSE_QR, max_num_iterations = LMMaxIter,
+// every other option default; the residual is CeresCostFunctions.h:105-152 with
+// ScaledLoss(TukeyLoss) from KeypointsMatcher.cxx:78-103).
+//
+// Ceres is NOT under /root/reference.  This restates the published Ceres 2.x
+// algorithm (trust_region_minimizer.cc, levenberg_marquardt_strategy.cc,
+// corrector.cc, loss_function.cc): Jacobi column scaling frozen at iteration 0,
+// LM diagonal clamp [1e-6, 1e32], step-quality radius update, function /
+// parameter / gradient tolerances 1e-6 / 1e-8 / 1e-10.  Deviation: the damped
+// system is solved by Cholesky on the 6x6 normal equations instead of QR on the
+// stacked Jacobian (same minimiser, different rounding), and the Jacobian is
+// analytic instead of autodiff Jets (same values up to rounding).
+//
+// Shared by the CUDA LM kernel and the CPU oracle so that both take identical
+// accept/reject decisions; compiled with -fmad=false / -ffp-contract=off.
+#pragma once
+#include "linalg.h"
+
+namespace lsb {
+
+// 28 reduced quantities of one cost/Jacobian evaluation:
+// [0..20] upper triangle of J~^T J~ (row-major: 00 01 02 03 04 05 11 12 ...),
+// [21..26] J~^T r~, [27] cost = sum 0.5*rho.
+#define LSB_LM_NSUM 28
+// Canonical reduction order (GPU and oracle): records in chunks of 256; inside a
+// chunk each group of 32 consecutive records is folded with offsets 16,8,4,2,1,
+// the 8 group sums are added in order, and chunk sums are combined by a
+// binary tree over adjacent chunks.
+#define LSB_LM_CHUNK 256
+
+// One residual record, 16 doubles (A row-major, P, X, weight).  weight < 0 marks
+// "no residual" (match failed): contributes exactly zero.
+struct LmRecord {
+  double A[9];
+  double P[3];
+  double X[3];
+  double w;
+};
+
+struct LmPoint {   // quantities that depend only on the current parameters
+  Mat3d R, dRx, dRy, dRz;
+  Vec3d t;
+};
+
+LSB_HD void lm_make_point(const double* x, LmPoint& p)
+{
+  const double cx = dm::cos(x[3]), sx = dm::sin(x[3]);
+  const double cy = dm::cos(x[4]), sy = dm::sin(x[4]);
+  const double cz = dm::cos(x[5]), sz = dm::sin(x[5]);
+  p.t = Vec3d(x[0], x[1], x[2]);
+  Mat3d& R = p.R;
+  R(0, 0) = cy * cz; R(0, 1) = sx * sy * cz - cx * sz; R(0, 2) = cx * sy * cz + sx * sz;
+  R(1, 0) = cy * sz; R(1, 1) = sx * sy * sz + cx * cz; R(1, 2) = cx * sy * sz - sx * cz;
+  R(2, 0) = -sy;     R(2, 1) = sx * cy;                R(2, 2) = cx * cy;
+  Mat3d& A = p.dRx;  // d/drx
+  A(0, 0) = 0.0; A(0, 1) = cx * sy * cz + sx * sz; A(0, 2) = -sx * sy * cz + cx * sz;
+  A(1, 0) = 0.0; A(1, 1) = cx * sy * sz - sx * cz; A(1, 2) = -sx * sy * sz - cx * cz;
+  A(2, 0) = 0.0; A(2, 1) = cx * cy;                A(2, 2) = -sx * cy;
+  Mat3d& B = p.dRy;  // d/dry
+  B(0, 0) = -sy * cz; B(0, 1) = sx * cy * cz; B(0, 2) = cx * cy * cz;
+  B(1, 0) = -sy * sz; B(1, 1) = sx * cy * sz; B(1, 2) = cx * cy * sz;
+  B(2, 0) = -cy;      B(2, 1) = -sx * sy;     B(2, 2) = -cx * sy;
+  Mat3d& C = p.dRz;  // d/drz
+  C(0, 0) = -cy * sz; C(0, 1) = -sx * sy * sz - cx * cz; C(0, 2) = -cx * sy * sz + sx * cz;
+  C(1, 0) = cy * cz;  C(1, 1) = sx * sy * cz - cx * sz;  C(1, 2) = cx * sy * cz + sx * sz;
+  C(2, 0) = 0.0;      C(2, 1) = 0.0;                     C(2, 2) = 0.0;
+}
+
+// Adds nothing: WRITES the 28 terms of one record into out[] (zeros if w < 0).
+LSB_HD void lm_eval_record(const LmRecord& rec, const LmPoint& pt, double sat, double* out)
+{
+  if (!(rec.w >= 0.0)) {
+    for (int i = 0; i < LSB_LM_NSUM; ++i) out[i] = 0.0;
+    return;
+  }
+  Mat3d A;
+  for (int i = 0; i < 9; ++i) A.m[i] = rec.A[i];
+  const Vec3d X(rec.X[0], rec.X[1], rec.X[2]);
+  const Vec3d P(rec.P[0], rec.P[1], rec.P[2]);
+  const Vec3d Y = pt.R * X + pt.t;
+  const Vec3d r = A * (Y - P);
+  const double s = dot(r, r);
+  // TukeyLoss(sat) scaled by w (Ceres >= 2.0 form, KeypointsMatcher.cxx:96-101)
+  const double a2 = sat * sat;
+  double rho0, rho1;
+  if (s <= a2) {
+    const double v = 1.0 - s / a2;
+    const double v2 = v * v;
+    rho0 = a2 / 3.0 * (1.0 - v2 * v);
+    rho1 = v2;
+  } else {
+    rho0 = a2 / 3.0;
+    rho1 = 0.0;
+  }
+  rho0 = rec.w * rho0;
+  rho1 = rec.w * rho1;
+  // Ceres corrector with rho'' <= 0: residual and Jacobian scaled by sqrt(rho')
+  const double sr = ::sqrt(rho1);
+  const Vec3d rt = sr * r;
+  // J~ columns: translation = A columns, rotation = A * (dR_k * X)
+  Vec3d J[6];
+  J[0] = sr * A.col(0); J[1] = sr * A.col(1); J[2] = sr * A.col(2);
+  J[3] = sr * (A * (pt.dRx * X));
+  J[4] = sr * (A * (pt.dRy * X));
+  J[5] = sr * (A * (pt.dRz * X));
+  int o = 0;
+  for (int i = 0; i < 6; ++i)
+    for (int j = i; j < 6; ++j) out[o++] = dot(J[i], J[j]);
+  for (int i = 0; i < 6; ++i) out[21 + i] = dot(J[i], rt);
+  out[27] = 0.5 * rho0;
+}
+
+// Cholesky solve of the symmetric 6x6 system M y = b (M full, row-major).
+// Returns false if M is not positive definite or the result is not finite.
+LSB_HD bool lm_chol_solve6(const double* M, const double* b, double* y)
+{
+  double L[36];
+  for (int i = 0; i < 36; ++i) L[i] = 0.0;
+  for (int j = 0; j < 6; ++j) {
+    double d = M[j * 6 + j];
+    for (int k = 0; k < j; ++k) d = d - L[j * 6 + k] * L[j * 6 + k];
+    if (!(d > 0.0)) return false;
+    const double ljj = ::sqrt(d);
+    L[j * 6 + j] = ljj;
+    for (int i = j + 1; i < 6; ++i) {
+      double s = M[i * 6 + j];
+      for (int k = 0; k < j; ++k) s = s - L[i * 6 + k] * L[j * 6 + k];
+      L[i * 6 + j] = s / ljj;
+    }
+  }
+  double z[6];
+  for (int i = 0; i < 6; ++i) {
+    double s = b[i];
+    for (int k = 0; k < i; ++k) s = s - L[i * 6 + k] * z[k];
+    z[i] = s / L[i * 6 + i];
+  }
+  for (int i = 5; i >= 0; --i) {
+    double s = z[i];
+    for (int k = i + 1; k < 6; ++k) s = s - L[k * 6 + i] * y[k];
+    y[i] = s / L[i * 6 + i];
+  }
+  for (int i = 0; i < 6; ++i)
+    if (!(y[i] - y[i] == 0.0)) return false;   // NaN / inf
+  return true;
+}
+
+enum { LSB_LM_RUNNING = 0, LSB_LM_CONV_GRADIENT, LSB_LM_CONV_PARAMETER, LSB_LM_CONV_FUNCTION, LSB_LM_CONV_RADIUS,
+       LSB_LM_MAX_ITER, LSB_LM_FAIL_INVALID };
+
+// Trust-region LM state machine.  Driver:
+//   lm_begin(s, x0, max_iter, two_d); E = evaluate(s.x); lm_first_eval(s, E);
+//   while (!s.done) { E = evaluate(s.xc); lm_next_eval(s, E); }
+// The solution is s.x; s.H/s.g/s.cost always describe s.x.
+struct LmState {
+  double x[6];
+  double xc[6];           // candidate point awaiting evaluation
+  double cost;
+  double H[21];           // J~^T J~ at x (upper, row-major)
+  double g[6];            // J~^T r~ at x
+  double S[6];            // Jacobi scaling, frozen at iteration 0
+  double radius, decrease_factor;
+  double model_cost_change;
+  double step_norm;
+  int iter;               // LM iterations started (Ceres iteration index)
+  int max_iter;
+  int num_successful;     // accepted steps (iteration 0 NOT counted)
+  int num_invalid;        // consecutive invalid steps
+  int two_d;              // hold z, rx, ry (LocalOptimizer.cxx:89-90)
+  int done;
+  int term;
+};
+
+LSB_HD bool lm_free(const LmState& s, int i) { return !(s.two_d && (i == 2 || i == 3 || i == 4)); }
+
+LSB_HD int lm_hidx(int i, int j)  // index in the 21-entry upper triangle, i <= j
+{
+  return i * 6 - (i * (i - 1)) / 2 + (j - i);
+}
+
+// Computes the next candidate (or terminates).  Loops over invalid steps, which
+// consume iterations without needing an evaluation.
+LSB_HD void lm_propose(LmState& s)
+{
+  while (true) {
+    if (s.iter >= s.max_iter) { s.done = 1; s.term = LSB_LM_MAX_ITER; return; }
+    if (s.radius < 1e-32) { s.done = 1; s.term = LSB_LM_CONV_RADIUS; return; }
+    s.iter += 1;
+    double M[36], b[6], Hs[36], gs[6];
+    for (int i = 0; i < 6; ++i) {
+      for (int j = 0; j < 6; ++j) {
+        const double h = (i <= j) ? s.H[lm_hidx(i, j)] : s.H[lm_hidx(j, i)];
+        Hs[i * 6 + j] = (lm_free(s, i) && lm_free(s, j)) ? h * s.S[i] * s.S[j] : 0.0;
+        M[i * 6 + j] = Hs[i * 6 + j];
+      }
+      gs[i] = lm_free(s, i) ? s.g[i] * s.S[i] : 0.0;
+      b[i] = -gs[i];
+    }
+    for (int i = 0; i < 6; ++i) {
+      if (!lm_free(s, i)) { M[i * 6 + i] = 1.0; continue; }   // decoupled dummy row -> delta_i = 0
+      double d = Hs[i * 6 + i];
+      d = (d < 1e-6) ? 1e-6 : d;
+      d = (d > 1e32) ? 1e32 : d;
+      M[i * 6 + i] = Hs[i * 6 + i] + d / s.radius;
+    }
+    double db[6];
+    bool ok = lm_chol_solve6(M, b, db);
+    double mcc = 0.0;
+    if (ok) {
+      // model_cost_change = -delta^T (g + 0.5 H delta)   (scaled quantities)
+      for (int i = 0; i < 6; ++i) {
+        double hd = 0.0;
+        for (int j = 0; j < 6; ++j) hd += Hs[i * 6 + j] * db[j];
+        mcc -= db[i] * (gs[i] + 0.5 * hd);
+      }
+      ok = (mcc > 0.0);
+    }
+    if (!ok) {
+      s.num_invalid += 1;
+      if (s.num_invalid >= 5) { s.done = 1; s.term = LSB_LM_FAIL_INVALID; return; }
+      s.radius = s.radius / s.decrease_factor;
+      s.decrease_factor *= 2.0;
+      continue;
+    }
+    s.num_invalid = 0;
+    s.model_cost_change = mcc;
+    double sn = 0.0;
+    for (int i = 0; i < 6; ++i) {
+      const double d = db[i] * s.S[i];
+      s.xc[i] = s.x[i] + d;
+      const double e = s.x[i] - s.xc[i];
+      sn += e * e;
+    }
+    s.step_norm = ::sqrt(sn);
+    return;
+  }
+}
+
+LSB_HD void lm_begin(LmState& s, const double* x0, int max_iter, int two_d)
+{
+  for (int i = 0; i < 6; ++i) { s.x[i] = x0[i]; s.xc[i] = x0[i]; s.g[i] = 0.0; s.S[i] = 1.0; }
+  for (int i = 0; i < 21; ++i) s.H[i] = 0.0;
+  s.cost = 0.0;
+  s.radius = 1e4;
+  s.decrease_factor = 2.0;
+  s.model_cost_change = 0.0;
+  s.step_norm = 0.0;
+  s.iter = 0;
+  s.max_iter = max_iter;
+  s.num_successful = 0;
+  s.num_invalid = 0;
+  s.two_d = two_d;
+  s.done = 0;
+  s.term = LSB_LM_RUNNING;
+}
+
+LSB_HD double lm_grad_max(const LmState& s)
+{
+  double m = 0.0;
+  for (int i = 0; i < 6; ++i) {
+    if (!lm_free(s, i)) continue;
+    const double a = (s.g[i] < 0.0) ? -s.g[i] : s.g[i];
+    m = (a > m) ? a : m;
+  }
+  return m;
+}
+
+// E = the 28 sums evaluated at s.x (iteration 0)
+LSB_HD void lm_first_eval(LmState& s, const double* E)
+{
+  for (int i = 0; i < 21; ++i) s.H[i] = E[i];
+  for (int i = 0; i < 6; ++i) s.g[i] = E[21 + i];
+  s.cost = E[27];
+  for (int i = 0; i < 6; ++i) s.S[i] = 1.0 / (1.0 + ::sqrt(s.H[lm_hidx(i, i)]));
+  if (lm_grad_max(s) <= 1e-10) { s.done = 1; s.term = LSB_LM_CONV_GRADIENT; return; }
+  lm_propose(s);
+}
+
+// E = the 28 sums evaluated at s.xc
+LSB_HD void lm_next_eval(LmState& s, const double* E)
+{
+  const double cost_c = E[27];
+  double xn = 0.0;
+  for (int i = 0; i < 6; ++i) xn += s.x[i] * s.x[i];
+  xn = ::sqrt(xn);
+  if (s.step_norm <= 1e-8 * (xn + 1e-8)) { s.done = 1; s.term = LSB_LM_CONV_PARAMETER; return; }
+  const double cost_change = s.cost - cost_c;
+  const double acc = (cost_change < 0.0) ? -cost_change : cost_change;
+  if (acc <= 1e-6 * s.cost) { s.done = 1; s.term = LSB_LM_CONV_FUNCTION; return; }
+  const double rho = cost_change / s.model_cost_change;
+  if (rho > 1e-3) {
+    for (int i = 0; i < 6; ++i) { s.x[i] = s.xc[i]; s.g[i] = E[21 + i]; }
+    for (int i = 0; i < 21; ++i) s.H[i] = E[i];
+    s.cost = cost_c;
+    s.num_successful += 1;
+    const double q = 2.0 * rho - 1.0;
+    double den = 1.0 - q * q * q;
+    den = (den < 1.0 / 3.0) ? 1.0 / 3.0 : den;
+    s.radius = s.radius / den;
+    s.radius = (s.radius > 1e16) ? 1e16 : s.radius;
+    s.decrease_factor = 2.0;
+    if (lm_grad_max(s) <= 1e-10) { s.done = 1; s.term = LSB_LM_CONV_GRADIENT; return; }
+  } else {
+    s.radius = s.radius / s.decrease_factor;
+    s.decrease_factor *= 2.0;
+  }
+  lm_propose(s);
+}
+
+}  // namespace lsb

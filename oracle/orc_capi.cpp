@@ -1,0 +1,230 @@
+// CPU ORACLE (test infrastructure) — C entry points for ctypes, mirroring the
+// lsb_* C ABI (include/lidarslam_b200.h) one to one with an orc_ prefix so the
+// parity tests call both sides the same way.
+#include "orc_slam.h"
+#include <cstring>
+#include <omp.h>
+
+using namespace orc;
+
+static Iso3d FromRowMajor(const double* T)
+{
+  Iso3d r;
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) r.R(i, j) = T[i * 4 + j];
+  }
+  r.t = Vec3d(T[3], T[7], T[11]);
+  return r;
+}
+static void ToRowMajor(const Iso3d& a, double* T)
+{
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) T[i * 4 + j] = a.R(i, j);
+    T[i * 4 + 3] = a.t[i];
+  }
+  T[12] = T[13] = T[14] = 0.; T[15] = 1.;
+}
+static long CopyCloud(const Cloud& c, lsb_point* out, long cap)
+{
+  if (out) std::memcpy(out, c.data(), sizeof(lsb_point) * (size_t)std::min<long>(cap, (long)c.size()));
+  return (long)c.size();
+}
+
+extern "C" {
+
+#define ORC_API __attribute__((visibility("default")))
+
+ORC_API int orc_max_threads() { return omp_get_max_threads(); }
+ORC_API Slam* orc_create() { return new Slam(); }
+ORC_API void orc_destroy(Slam* h) { delete h; }
+ORC_API int orc_reset(Slam* h, int resetLog) { h->Reset(resetLog != 0); return 0; }
+ORC_API int orc_set_params(Slam* h, const lsb_params* p) { h->P = *p; return 0; }
+ORC_API int orc_get_params(const Slam* h, lsb_params* p) { *p = h->P; return 0; }
+ORC_API int orc_set_extractor_params(Slam* h, int dev, const lsb_ke_params* p) { h->KeyPointsExtractors[dev].P = *p; return 0; }
+ORC_API int orc_get_extractor_params(Slam* h, int dev, lsb_ke_params* p)
+{
+  if (!h->KeyPointsExtractors.count(dev)) return LSB_E_INVALID;
+  *p = h->KeyPointsExtractors[dev].P;
+  return 0;
+}
+ORC_API int orc_set_base_to_lidar(Slam* h, int dev, const double* T) { h->BaseToLidarOffsets[dev] = FromRowMajor(T); return 0; }
+ORC_API int orc_set_voxel_grid_leaf_size(Slam* h, int k, double s) { h->SetVoxelGridLeafSize(k, s); return 0; }
+ORC_API int orc_set_voxel_grid_size(Slam* h, int s) { h->SetVoxelGridSize(s); return 0; }
+ORC_API int orc_set_voxel_grid_resolution(Slam* h, double r) { h->SetVoxelGridResolution(r); return 0; }
+ORC_API int orc_set_voxel_grid_min_frames_per_voxel(Slam* h, unsigned n) { for (auto& m : h->LocalMaps) m.MinFramesPerVoxel = n; return 0; }
+ORC_API int orc_set_voxel_grid_decaying_threshold(Slam* h, double s) { for (auto& m : h->LocalMaps) m.DecayingThreshold = s; return 0; }
+ORC_API int orc_set_voxel_grid_sampling_mode(Slam* h, int k, int mode) { h->LocalMaps[k].Sampling = mode; return 0; }
+
+ORC_API int orc_add_frames(Slam* h, int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq)
+{
+  std::vector<Frame> f;
+  for (int i = 0; i < n_frames; ++i) f.push_back(Frame{frames[i], n[i], stamp_us[i], seq ? seq[i] : 0u});
+  return h->AddFrames(f);
+}
+
+ORC_API int orc_get_world_transform(const Slam* h, double* T, double* time)
+{
+  if (h->LogTrajectory.empty()) { ToRowMajor(Iso3d::identity(), T); if (time) *time = 0.; return 0; }
+  ToRowMajor(h->LogTrajectory.back().T, T);
+  if (time) *time = h->LogTrajectory.back().time;
+  return 0;
+}
+ORC_API int orc_get_relative_transform(const Slam* h, double* T) { ToRowMajor(h->Trelative, T); return 0; }
+ORC_API int orc_get_registration_error(const Slam* h, lsb_registration_error* e) { *e = h->LocalizationUncertainty; return 0; }
+ORC_API int orc_get_covariance(const Slam* h, double* c) { std::memcpy(c, h->LocalizationUncertainty.covariance, 36 * sizeof(double)); return 0; }
+ORC_API long orc_get_keypoints(Slam* h, int type, int world, lsb_point* out, long cap)
+{
+  if (!world) return CopyCloud(h->CurrentKeypoints[type], out, cap);
+  Cloud c = h->CurrentKeypoints[type];
+  for (auto& p : c) lsb::transform_point_f(h->Tworld, p.x, p.y, p.z);
+  return CopyCloud(c, out, cap);
+}
+ORC_API long orc_get_map(Slam* h, int type, int clean, lsb_point* out, long cap) { return CopyCloud(h->LocalMaps[type].Get(clean != 0), out, cap); }
+ORC_API long orc_get_submap(Slam* h, int type, lsb_point* out, long cap) { return CopyCloud(h->LocalMaps[type].SubMap, out, cap); }
+ORC_API long orc_get_registered_frame(Slam* h, lsb_point* out, long cap) { return CopyCloud(h->GetRegisteredFrame(), out, cap); }
+ORC_API long orc_get_match_debug(Slam* h, int stage, int type, uint8_t* status, double* weight, long cap)
+{
+  const MatchingResults& m = stage == 0 ? h->EgoMotionMatchingResults[type] : h->LocalizationMatchingResults[type];
+  const long n = (long)m.Rejections.size();
+  for (long i = 0; i < std::min(n, cap); ++i) { if (status) status[i] = m.Rejections[i]; if (weight) weight[i] = m.Weights[i]; }
+  return n;
+}
+ORC_API long orc_get_ke_debug(Slam* h, int dev, int field, float* out, long cap)
+{
+  if (!h->KeyPointsExtractors.count(dev)) return LSB_E_INVALID;
+  const std::vector<float> v = h->KeyPointsExtractors[dev].DebugArray(field);
+  if (out) std::memcpy(out, v.data(), sizeof(float) * (size_t)std::min<long>(cap, (long)v.size()));
+  return (long)v.size();
+}
+ORC_API int orc_get_frame_stats(const Slam* h, lsb_frame_stats* s) { *s = h->Stats; return 0; }
+ORC_API unsigned orc_get_total_matched_keypoints(const Slam* h) { return h->TotalMatchedKeypoints; }
+ORC_API int orc_set_world_transform_from_guess(Slam* h, const double* T) { h->SetWorldTransformFromGuess(FromRowMajor(T)); return 0; }
+ORC_API int orc_clear_maps(Slam* h) { h->ClearMaps(); return 0; }
+ORC_API int orc_map_load_points(Slam* h, int type, const lsb_point* pts, long n, int fixed)
+{
+  Cloud c(pts, pts + n);
+  h->LocalMaps[type].Add(c, fixed != 0, 0.);
+  return 0;
+}
+
+// ---- kernel-level entry points ------------------------------------------------
+ORC_API int orc_extract_keypoints(Slam* h, const lsb_point* pts, size_t n, uint8_t* label_out, uint32_t* counts)
+{
+  Extractor& ke = h->KeyPointsExtractors[0];
+  ke.NbThreads = h->P.nb_threads;
+  ke.ComputeKeyPoints(pts, n);
+  const std::vector<uint8_t> l = ke.LabelsInputOrder();
+  if (label_out) std::memcpy(label_out, l.data(), n);
+  for (int k = 0; k < 3; ++k) counts[k] = (uint32_t)ke.Keypoints[k].size();
+  return 0;
+}
+ORC_API long orc_get_extracted_keypoints(Slam* h, int type, lsb_point* out, long cap) { return CopyCloud(h->KeyPointsExtractors[0].Keypoints[type], out, cap); }
+
+ORC_API int orc_knn_search(Slam* h, const lsb_point* cloud, size_t m, const float* q, size_t nq, int k, int32_t* idx_out, float* d2_out)
+{
+  Cloud c(cloud, cloud + m);
+  KdTree t;
+  t.Reset(&c);
+#pragma omp parallel for num_threads(h->P.nb_threads) schedule(guided, 8)
+  for (long i = 0; i < (long)nq; ++i) {
+    int* id = idx_out + i * k;
+    float* d = d2_out + i * k;
+    const int n = t.Knn(q + 3 * i, k, id, d);
+    for (int j = n; j < k; ++j) { id[j] = -1; d[j] = std::numeric_limits<float>::infinity(); }
+  }
+  return 0;
+}
+
+ORC_API int orc_match_and_solve(Slam* h, const lsb_point* const* keypoints, const size_t* nk, const lsb_point* const* target, const size_t* nt,
+                                const lsb_match_params* mp, int lm_max_iter, const double* prior, uint8_t* status_out, double* weight_out,
+                                double* pose_out, int* lm_accepted_steps, int* lm_iterations, double* final_cost, lsb_registration_error* err_out)
+{
+  const Iso3d T = FromRowMajor(prior);
+  Matcher matcher(*mp, T, h->P.nb_threads);
+  Optimizer opt;
+  opt.TwoDMode = h->P.two_d_mode != 0;
+  opt.SetPosePrior(T);
+  opt.LMMaxIter = (unsigned)lm_max_iter;
+  opt.NbThreads = h->P.nb_threads;
+  opt.Sat = mp->saturation_distance;
+  size_t off = 0;
+  unsigned total = 0;
+  for (int k = 0; k < 3; ++k) {
+    Cloud kp(keypoints[k], keypoints[k] + nk[k]), tg(target[k], target[k] + nt[k]);
+    KdTree tree;
+    tree.Reset(&tg);
+    MatchingResults r = matcher.BuildMatchResiduals(kp, tree, k);
+    for (size_t i = 0; i < nk[k]; ++i) { status_out[off + i] = r.Rejections[i]; weight_out[off + i] = r.Weights[i]; }
+    off += nk[k];
+    total += r.NbMatches();
+    opt.AddResiduals(r);
+  }
+  if (total == 0) {
+    ToRowMajor(T, pose_out);
+    *lm_accepted_steps = 0; *lm_iterations = 0; *final_cost = 0.;
+    if (err_out) std::memset(err_out, 0, sizeof(*err_out));
+    return LSB_W_LOC_SKIPPED;
+  }
+  opt.Solve();
+  ToRowMajor(opt.GetOptimizedPose(), pose_out);
+  *lm_accepted_steps = opt.State.num_successful;
+  *lm_iterations = opt.State.iter;
+  *final_cost = opt.State.cost;
+  if (err_out) *err_out = opt.EstimateRegistrationError();
+  return 0;
+}
+
+ORC_API int orc_map_add(Slam* h, int type, const lsb_point* pts, size_t n, int fixed, double current_time)
+{
+  Cloud c(pts, pts + n);
+  h->LocalMaps[type].Add(c, fixed != 0, current_time);
+  return 0;
+}
+
+ORC_API int orc_undistort(Slam*, lsb_point* pts, size_t n, const double* H0, const double* H1, double t0, double t1)
+{
+  lsb::Interpolator it;
+  it.t0 = t0; it.t1 = t1;
+  it.set_transforms(FromRowMajor(H0), FromRowMajor(H1));
+  for (size_t i = 0; i < n; ++i) {
+    const Iso3d T = it.at(pts[i].time);
+    lsb::transform_point_f(T, pts[i].x, pts[i].y, pts[i].z);
+  }
+  return 0;
+}
+
+// Exposes the shared deterministic math for tests/test_detmath.py
+ORC_API void orc_detmath(int fn, const double* a, const double* b, double* out, long n)
+{
+  for (long i = 0; i < n; ++i) {
+    switch (fn) {
+      case 0: out[i] = lsb::dm::sin(a[i]); break;
+      case 1: out[i] = lsb::dm::cos(a[i]); break;
+      case 2: out[i] = lsb::dm::atan2(a[i], b[i]); break;
+      case 3: out[i] = lsb::dm::acos(a[i]); break;
+      case 4: out[i] = lsb::dm::asin(a[i]); break;
+      default: out[i] = 0.;
+    }
+  }
+}
+// eigen33 on n symmetric matrices (row-major 9 doubles each): evals ascending + evecs row-major
+ORC_API void orc_eigen33(const double* m9, double* evals3, double* evecs9, long n, int as_float)
+{
+  for (long i = 0; i < n; ++i) {
+    if (as_float) {
+      Mat3f M, V; float ev[3];
+      for (int j = 0; j < 9; ++j) M.m[j] = (float)m9[i * 9 + j];
+      lsb::eigen33(M, V, ev);
+      for (int j = 0; j < 9; ++j) evecs9[i * 9 + j] = V.m[j];
+      for (int j = 0; j < 3; ++j) evals3[i * 3 + j] = ev[j];
+    } else {
+      Mat3d M, V; double ev[3];
+      for (int j = 0; j < 9; ++j) M.m[j] = m9[i * 9 + j];
+      lsb::eigen33(M, V, ev);
+      for (int j = 0; j < 9; ++j) evecs9[i * 9 + j] = V.m[j];
+      for (int j = 0; j < 3; ++j) evals3[i * 3 + j] = ev[j];
+    }
+  }
+}
+
+}  // extern "C"

@@ -1,0 +1,102 @@
+// CPU ORACLE (test infrastructure) — LocalOptimizer restatement
+// (reference slam_lib/src/LocalOptimizer.cxx:44-48, 74-102, 105-140).
+// The LM state machine and per-record math come from common/lm_core.h (a
+// restatement of Ceres, shared with the GPU on purpose); this file provides the
+// sequential CPU evaluation in the canonical reduction order.
+#pragma once
+#include "orc_matcher.h"
+#include "../lidarslam_b200/csrc/common/lm_core.h"
+#include "../lidarslam_b200/csrc/common/lm_covariance.h"
+
+namespace orc {
+
+struct Optimizer {
+  bool TwoDMode = false;
+  unsigned LMMaxIter = 15;
+  int NbThreads = 1;
+  double Sat = 1.0;
+  double PoseArray[6] = {0, 0, 0, 0, 0, 0};
+  std::vector<lsb::LmRecord> Records;   // index-aligned with the matcher output, w < 0 = no residual
+  lsb::LmState State;
+  int NumEvaluations = 0;
+
+  void SetPosePrior(const Iso3d& T) { lsb::iso_to_xyzrpy(T, PoseArray); }   // LocalOptimizer.cxx:44-48
+  void AddResiduals(const MatchingResults& m)                                // Slam.cxx:1120-1121
+  {
+    for (size_t i = 0; i < m.Residuals.size(); ++i) {
+      lsb::LmRecord r;
+      const MatchRecord& s = m.Residuals[i];
+      for (int k = 0; k < 9; ++k) r.A[k] = s.A[k];
+      for (int k = 0; k < 3; ++k) { r.P[k] = s.P[k]; r.X[k] = s.X[k]; }
+      r.w = (m.Rejections[i] == LSB_MATCH_SUCCESS) ? s.weight : -1.0;
+      Records.push_back(r);
+    }
+  }
+
+  // 28 sums at x in the canonical order of lm_core.h
+  void Evaluate(const double* x, double* E)
+  {
+    ++NumEvaluations;
+    lsb::LmPoint pt;
+    lsb::lm_make_point(x, pt);
+    const size_t n = Records.size();
+    const size_t nChunks = (n + LSB_LM_CHUNK - 1) / LSB_LM_CHUNK;
+    std::vector<double> part(std::max<size_t>(nChunks, 1) * LSB_LM_NSUM, 0.0);
+#pragma omp parallel for num_threads(NbThreads) schedule(static)
+    for (long c = 0; c < (long)nChunks; ++c) {
+      double chunk[LSB_LM_NSUM];
+      for (int q = 0; q < LSB_LM_NSUM; ++q) chunk[q] = 0.0;
+      for (int w = 0; w < LSB_LM_CHUNK / 32; ++w) {
+        double lane[32][LSB_LM_NSUM];
+        for (int l = 0; l < 32; ++l) {
+          const size_t i = (size_t)c * LSB_LM_CHUNK + w * 32 + l;
+          if (i < n) lsb::lm_eval_record(Records[i], pt, Sat, lane[l]);
+          else for (int q = 0; q < LSB_LM_NSUM; ++q) lane[l][q] = 0.0;
+        }
+        for (int off = 16; off >= 1; off >>= 1)
+          for (int l = 0; l < off; ++l)
+            for (int q = 0; q < LSB_LM_NSUM; ++q) lane[l][q] += lane[l + off][q];
+        for (int q = 0; q < LSB_LM_NSUM; ++q) chunk[q] = (w == 0) ? lane[0][q] : chunk[q] + lane[0][q];
+      }
+      for (int q = 0; q < LSB_LM_NSUM; ++q) part[c * LSB_LM_NSUM + q] = chunk[q];
+    }
+    size_t m = std::max<size_t>(nChunks, 1);
+    while (m > 1) {
+      const size_t h = (m + 1) / 2;
+      for (size_t i = 0; i < h; ++i)
+        for (int q = 0; q < LSB_LM_NSUM; ++q) {
+          const double a = part[(2 * i) * LSB_LM_NSUM + q];
+          part[i * LSB_LM_NSUM + q] = (2 * i + 1 < m) ? a + part[(2 * i + 1) * LSB_LM_NSUM + q] : a;
+        }
+      m = h;
+    }
+    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = part[q];
+  }
+
+  // LocalOptimizer::Solve (:74-102). Returns Ceres' num_successful_steps
+  // (iteration 0 counts as successful).
+  int Solve()
+  {
+    double E[LSB_LM_NSUM];
+    lsb::lm_begin(State, PoseArray, (int)LMMaxIter, TwoDMode ? 1 : 0);
+    Evaluate(State.x, E);
+    lsb::lm_first_eval(State, E);
+    while (!State.done) {
+      Evaluate(State.xc, E);
+      lsb::lm_next_eval(State, E);
+    }
+    for (int i = 0; i < 6; ++i) PoseArray[i] = State.x[i];
+    return State.num_successful + 1;
+  }
+
+  Iso3d GetOptimizedPose() const { return lsb::xyzrpy_to_iso(PoseArray); }   // :105-109
+
+  lsb_registration_error EstimateRegistrationError() const                   // :112-140
+  {
+    lsb_registration_error e;
+    lsb::registration_error_from_normal_matrix(State.H, TwoDMode ? 1 : 0, &e);
+    return e;
+  }
+};
+
+}  // namespace orc

@@ -1,0 +1,67 @@
+"""CPU ORACLE (test infrastructure) — ctypes front-end of oracle/_ref/liborc.so.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this module.  It reuses the product's generic ctypes wrapper
+(lidarslam_b200.capi.CApi) with the symbol prefix "orc_" so both sides are driven
+by identical calls."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from lidarslam_b200 import capi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+def load():
+    global _LIB
+    if _LIB is None:
+        p = os.path.join(_HERE, "_ref", "liborc.so")
+        if not os.path.exists(p):
+            build()
+        _LIB = C.CDLL(p)
+    return _LIB
+
+
+class Oracle(capi.CApi):
+    def __init__(self, nb_threads=None):
+        super().__init__(load(), "orc_")
+        if nb_threads is not None:
+            p = self.GetParams()
+            p.nb_threads = nb_threads
+            self.SetParams(p)
+
+
+def max_threads():
+    return int(load().orc_max_threads())
+
+
+def default_params():
+    return capi.default_params(load())
+
+
+def default_ke_params():
+    return capi.default_ke_params(load())
+
+
+def detmath(fn, a, b=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    b = np.ascontiguousarray(b if b is not None else np.zeros_like(a), dtype=np.float64)
+    out = np.zeros_like(a)
+    load().orc_detmath(C.c_int(fn), capi._ptr(a), capi._ptr(b), capi._ptr(out), C.c_long(a.size))
+    return out
+
+
+def eigen33(mats, as_float=False):
+    m = np.ascontiguousarray(mats, dtype=np.float64).reshape(-1, 9)
+    ev = np.zeros((len(m), 3))
+    vec = np.zeros((len(m), 9))
+    load().orc_eigen33(capi._ptr(m), capi._ptr(ev), capi._ptr(vec), C.c_long(len(m)), C.c_int(1 if as_float else 0))
+    return ev, vec.reshape(-1, 3, 3)
