@@ -189,6 +189,22 @@ LSB_API int lsb_set_voxel_grid_sampling_mode(lsb_slam* h, int keypoint_type, int
 LSB_API int lsb_add_frames(lsb_slam* h, int n_frames, const lsb_point* const* frames, const size_t* n,
                            const uint64_t* stamp_us, const uint32_t* seq);
 
+/* Same entry with the frames already resident in DEVICE memory of the handle's GPU
+ * (frames[i] are device pointers; they must stay valid until the next call, as the
+ * reference retains its input clouds, Slam.cxx:237).  Used to time the path with
+ * inputs in HBM. */
+LSB_API int lsb_add_frames_dev(lsb_slam* h, int n_frames, const lsb_point* const* dev_frames, const size_t* n,
+                               const uint64_t* stamp_us, const uint32_t* seq);
+
+/* Memory helpers for callers without their own CUDA allocator: pinned host
+ * buffers (fast H2D for lsb_add_frames) and device buffers (lsb_add_frames_dev). */
+LSB_API void* lsb_host_alloc(size_t bytes);
+LSB_API void lsb_host_free(void* p);
+LSB_API void* lsb_dev_alloc(lsb_slam* h, size_t bytes);
+LSB_API void lsb_dev_free(lsb_slam* h, void* p);
+LSB_API int lsb_dev_upload(lsb_slam* h, void* dev_dst, const void* host_src, size_t bytes);
+LSB_API int lsb_dev_flush_l2(lsb_slam* h);   /* writes a 256 MiB scratch buffer (benchmark hygiene) */
+
 /* ---- outputs ---------------------------------------------------------------- */
 LSB_API int lsb_get_world_transform(const lsb_slam* h, double T_rowmajor[16], double* time);   /* Slam::GetWorldTransform Slam.cxx:550-553 */
 LSB_API int lsb_get_latency_compensated_world_transform(const lsb_slam* h, double T_rowmajor[16], double* time); /* Slam.cxx:556-591 */

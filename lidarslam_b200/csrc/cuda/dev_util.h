@@ -1,0 +1,85 @@
+// Device-side plumbing shared by the kernels of liblidarslam_b200: error
+// handling, growable device buffers, launch helpers.  No torch types: the
+// library owns its device memory and one CUDA stream per lsb_slam handle.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstddef>
+#include <cstdio>
+#include <string>
+#include <stdexcept>
+#include "../../../include/lidarslam_b200.h"
+
+namespace lsb {
+
+struct CudaError : std::runtime_error {
+  int code;
+  CudaError(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+inline void cuda_check(cudaError_t e, const char* what, const char* file, int line)
+{
+  if (e != cudaSuccess) {
+    char buf[512];
+    std::snprintf(buf, sizeof(buf), "%s failed at %s:%d: %s", what, file, line, cudaGetErrorString(e));
+    throw CudaError(LSB_E_CUDA, buf);
+  }
+}
+#define LSB_CUDA(x) ::lsb::cuda_check((x), #x, __FILE__, __LINE__)
+#define LSB_LAUNCH_CHECK() ::lsb::cuda_check(cudaGetLastError(), "kernel launch", __FILE__, __LINE__)
+
+// Growable device array.  Growth reallocates (content is NOT preserved unless
+// keep=true); steady state never allocates.
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { if (p) cudaFree(p); }
+  void reserve(size_t n, cudaStream_t s = 0, bool keep = false, size_t keep_n = 0)
+  {
+    if (n <= cap) return;
+    size_t ncap = cap ? cap : 1024;
+    while (ncap < n) ncap = ncap + ncap / 2 + 1024;
+    T* q = nullptr;
+    LSB_CUDA(cudaMalloc(&q, ncap * sizeof(T)));
+    if (p) {
+      if (keep && keep_n) LSB_CUDA(cudaMemcpyAsync(q, p, keep_n * sizeof(T), cudaMemcpyDeviceToDevice, s));
+      LSB_CUDA(cudaStreamSynchronize(s));
+      cudaFree(p);
+    }
+    p = q;
+    cap = ncap;
+  }
+  void swap(DevBuf& o) { T* tp = p; p = o.p; o.p = tp; size_t tc = cap; cap = o.cap; o.cap = tc; }
+};
+
+// Pinned host staging buffer (results read back by the host driver).
+template <typename T>
+struct PinnedBuf {
+  T* p = nullptr;
+  size_t cap = 0;
+  PinnedBuf() = default;
+  PinnedBuf(const PinnedBuf&) = delete;
+  PinnedBuf& operator=(const PinnedBuf&) = delete;
+  ~PinnedBuf() { if (p) cudaFreeHost(p); }
+  void reserve(size_t n)
+  {
+    if (n <= cap) return;
+    if (p) cudaFreeHost(p);
+    LSB_CUDA(cudaMallocHost(&p, n * sizeof(T)));
+    cap = n;
+  }
+};
+
+inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+// Launch counter of one handle (lsb_frame_stats.kernel_launches).
+struct LaunchCounter {
+  unsigned n = 0;
+  void add(unsigned k = 1) { n += k; }
+};
+
+}  // namespace lsb

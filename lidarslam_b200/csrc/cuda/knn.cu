@@ -1,0 +1,308 @@
+// Exact kNN on a uniform grid — see knn.cuh.  Hand-written search kernel; CUB is
+// used only for the radix sort that orders the target points by cell.
+//
+// Search (one thread per query): the cube of cells of Chebyshev radius r around
+// the query's cell is scanned shell by shell.  Cells of one (z, y) row are
+// contiguous in the cell-major point array, so a row of a shell is ONE index range
+// (two cell_start loads), which makes empty space cheap.  After the cube of radius
+// r is complete every unvisited point is farther than
+//   bound(r) = r * cell + min over axes of the query's distance to its cell faces,
+// so the search stops as soon as the k-th best distance is strictly below
+// bound(r) (minus a rounding margin) or the cube covers the whole grid: exact,
+// with ties at equal d2 resolved by the smaller cloud index.
+#include "knn.cuh"
+#include <cub/cub.cuh>
+#include <cfloat>
+#include <climits>
+#include <algorithm>
+#include <cmath>
+
+namespace lsb {
+
+namespace {
+
+constexpr int TPB = 256;
+constexpr long long KNN_MAX_CELLS = 4ll << 20;
+
+__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return (i >= 0) ? i : (i ^ 0x7fffffff); }
+__host__ __device__ __forceinline__ float ord2f(int i) { const int j = (i >= 0) ? i : (i ^ 0x7fffffff);
+#ifdef __CUDA_ARCH__
+  return __int_as_float(j);
+#else
+  float f; memcpy(&f, &j, 4); return f;
+#endif
+}
+
+__global__ void k_bbox_init(int* bb) { if (threadIdx.x < 3) bb[threadIdx.x] = INT_MAX; else if (threadIdx.x < 6) bb[threadIdx.x] = INT_MIN; }
+
+__global__ void k_bbox(const lsb_point* __restrict__ pts, int n, int* __restrict__ bb)
+{
+  int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 p = reinterpret_cast<const float4*>(pts)[2 * i];
+    const int v[3] = {f2ord(p.x), f2ord(p.y), f2ord(p.z)};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = min(mn[a], v[a]); mx[a] = max(mx[a], v[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    for (int off = 16; off; off >>= 1) {
+      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], off));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], off));
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(bb + a, mn[a]); atomicMax(bb + 3 + a, mx[a]); }
+  }
+}
+
+__device__ __forceinline__ int cell_coord(float v, float o, float cell, int n)
+{
+  float f = floorf((v - o) / cell);
+  f = fminf(fmaxf(f, 0.f), (float)(n - 1));
+  return (int)f;
+}
+
+__global__ void k_cell_keys(const lsb_point* __restrict__ pts, int m, KnnGridParams gp, uint32_t* __restrict__ key, uint32_t* __restrict__ idx)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const float4 p = reinterpret_cast<const float4*>(pts)[2 * i];
+  const int cx = cell_coord(p.x, gp.ox, gp.cell, gp.nx), cy = cell_coord(p.y, gp.oy, gp.cell, gp.ny), cz = cell_coord(p.z, gp.oz, gp.cell, gp.nz);
+  key[i] = (uint32_t)((cz * gp.ny + cy) * gp.nx + cx);
+  idx[i] = (uint32_t)i;
+}
+
+__global__ void k_cell_gather(const lsb_point* __restrict__ pts, int m, const uint32_t* __restrict__ idx, float4* __restrict__ sorted)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  const uint32_t o = idx[i];
+  const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)o];
+  sorted[i] = make_float4(p.x, p.y, p.z, __int_as_float((int)o));
+}
+
+// cell_start[c] = number of points whose cell key is < c  (c in [0, ncells])
+__global__ void k_cell_start(const uint32_t* __restrict__ key_sorted, int m, int ncells, uint32_t* __restrict__ cell_start)
+{
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c > ncells) return;
+  int lo = 0, hi = m;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (key_sorted[mid] < (uint32_t)c) lo = mid + 1; else hi = mid;
+  }
+  cell_start[c] = (uint32_t)lo;
+}
+
+// ------------------------------------------------------------------ search ---
+template <int KMAX>
+struct TopK {
+  float d[KMAX];
+  int id[KMAX];
+  __device__ __forceinline__ void init()
+  {
+#pragma unroll
+    for (int t = 0; t < KMAX; ++t) { d[t] = INFINITY; id[t] = INT_MAX; }
+  }
+  __device__ __forceinline__ void offer(float dd, int ii)
+  {
+    if (dd < d[KMAX - 1] || (dd == d[KMAX - 1] && ii < id[KMAX - 1])) {
+      d[KMAX - 1] = dd; id[KMAX - 1] = ii;
+#pragma unroll
+      for (int t = KMAX - 1; t > 0; --t) {
+        const bool sw = d[t] < d[t - 1] || (d[t] == d[t - 1] && id[t] < id[t - 1]);
+        const float td = d[t]; const int ti = id[t];
+        d[t] = sw ? d[t - 1] : td; id[t] = sw ? id[t - 1] : ti;
+        d[t - 1] = sw ? td : d[t - 1]; id[t - 1] = sw ? ti : id[t - 1];
+      }
+    }
+  }
+};
+
+template <int KMAX>
+__device__ __forceinline__ void scan_range(TopK<KMAX>& tk, const float4* __restrict__ sorted, uint32_t b, uint32_t e, float qx, float qy, float qz)
+{
+  for (uint32_t p = b; p < e; ++p) {
+    const float4 s = __ldg(sorted + p);
+    const float dx = qx - s.x, dy = qy - s.y, dz = qz - s.z;
+    const float d = (dx * dx + dy * dy) + dz * dz;
+    tk.offer(d, __float_as_int(s.w));
+  }
+}
+
+template <int KMAX, bool FROM_POINTS>
+__global__ void __launch_bounds__(128)
+k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
+      const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, int32_t* __restrict__ idx_out,
+      float* __restrict__ d2_out, int32_t* __restrict__ nfound_out)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  float qx, qy, qz;
+  if (FROM_POINTS) {
+    const float4 p = reinterpret_cast<const float4*>(kp)[2 * (size_t)i];
+    const Vec3d w = apply(prior, Vec3d((double)p.x, (double)p.y, (double)p.z));
+    qx = (float)w.x; qy = (float)w.y; qz = (float)w.z;
+  } else {
+    qx = q_xyz[3 * (size_t)i]; qy = q_xyz[3 * (size_t)i + 1]; qz = q_xyz[3 * (size_t)i + 2];
+  }
+  TopK<KMAX> tk;
+  tk.init();
+  const float cell = gp.cell;
+  // unclamped cell coordinates of the query (bounded so that the int conversion is defined)
+  const float fx = fminf(fmaxf(floorf((qx - gp.ox) / cell), -1.0e6f), 1.0e6f);
+  const float fy = fminf(fmaxf(floorf((qy - gp.oy) / cell), -1.0e6f), 1.0e6f);
+  const float fz = fminf(fmaxf(floorf((qz - gp.oz) / cell), -1.0e6f), 1.0e6f);
+  const int cx = (int)fx, cy = (int)fy, cz = (int)fz;
+  float minoff;
+  {
+    const float lx = gp.ox + fx * cell, ly = gp.oy + fy * cell, lz = gp.oz + fz * cell;
+    minoff = fminf(fminf(fminf(qx - lx, lx + cell - qx), fminf(qy - ly, ly + cell - qy)), fminf(qz - lz, lz + cell - qz));
+    minoff = fmaxf(minoff, 0.f);
+  }
+  // radius at which the cube covers the whole grid / first touches it
+  const int rcover = max(max(max(cx, gp.nx - 1 - cx), max(cy, gp.ny - 1 - cy)), max(cz, gp.nz - 1 - cz));
+  const int rfirst = max(max(max(-cx, cx - (gp.nx - 1)), max(-cy, cy - (gp.ny - 1))), max(max(-cz, cz - (gp.nz - 1)), 0));
+  int r = max(1, rfirst);
+  bool first = true;
+  if (qx == qx && qy == qy && qz == qz) {
+    while (true) {
+      const int z0 = max(0, cz - r), z1 = min(gp.nz - 1, cz + r);
+      const int y0 = max(0, cy - r), y1 = min(gp.ny - 1, cy + r);
+      const int x0 = max(0, cx - r), x1 = min(gp.nx - 1, cx + r);
+      for (int z = z0; z <= z1; ++z) {
+        const bool zface = (z == cz - r) || (z == cz + r);
+        for (int y = y0; y <= y1; ++y) {
+          const int base = (z * gp.ny + y) * gp.nx;
+          if (first || zface || y == cy - r || y == cy + r) {
+            if (x0 <= x1) scan_range(tk, sorted, cell_start[base + x0], cell_start[base + x1 + 1], qx, qy, qz);
+          } else {
+            if (cx - r >= 0 && cx - r < gp.nx) scan_range(tk, sorted, cell_start[base + cx - r], cell_start[base + cx - r + 1], qx, qy, qz);
+            if (cx + r >= 0 && cx + r < gp.nx) scan_range(tk, sorted, cell_start[base + cx + r], cell_start[base + cx + r + 1], qx, qy, qz);
+          }
+        }
+      }
+      first = false;
+      if (r >= rcover) break;
+      if (tk.d[KMAX - 1] < INFINITY) {
+        const float reach = (float)r * cell + minoff;
+        const float bound = reach - (1.0e-3f + 1.0e-4f * (reach + cell));
+        if (bound > 0.f && tk.d[KMAX - 1] < bound * bound) break;
+      }
+      ++r;
+    }
+  }
+  int nf = 0;
+#pragma unroll
+  for (int t = 0; t < KMAX; ++t) {
+    if (t < k) {
+      const bool ok = tk.d[t] < INFINITY;
+      idx_out[(size_t)i * k + t] = ok ? tk.id[t] : -1;
+      d2_out[(size_t)i * k + t] = ok ? tk.d[t] : INFINITY;
+      nf += ok ? 1 : 0;
+    }
+  }
+  if (nfound_out) nfound_out[i] = nf;
+}
+
+template <bool FROM_POINTS>
+void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso3d& prior, size_t nq, int k, int32_t* idx, float* d2,
+                int32_t* nf, cudaStream_t s)
+{
+  const unsigned G = div_up(nq, 128);
+  const int NQ = (int)nq;
+#define LSB_KNN_CASE(KM) k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, idx, d2, nf)
+  if (k <= 1) LSB_KNN_CASE(1);
+  else if (k <= 5) LSB_KNN_CASE(5);
+  else if (k <= 8) LSB_KNN_CASE(8);
+  else if (k <= 10) LSB_KNN_CASE(10);
+  else if (k <= 16) LSB_KNN_CASE(16);
+  else LSB_KNN_CASE(32);
+#undef LSB_KNN_CASE
+  LSB_LAUNCH_CHECK();
+}
+
+__global__ void k_fill_empty(int32_t* idx, float* d2, int32_t* nf, size_t total, size_t nq)
+{
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < total) { idx[i] = -1; d2[i] = INFINITY; }
+  if (nf && i < nq) nf[i] = 0;
+}
+
+}  // namespace
+
+void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc)
+{
+  cloud = d_cloud;
+  m = m_;
+  if (m == 0) return;
+  const int M = (int)m;
+  float bmin[3], bmax[3];
+  if (lo && hi) {
+    for (int a = 0; a < 3; ++a) { bmin[a] = lo[a]; bmax[a] = hi[a]; }
+  } else {
+    d_bbox.reserve(8, s); h_bbox.reserve(8);
+    k_bbox_init<<<1, 32, 0, s>>>((int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
+    k_bbox<<<std::min(div_up(m, TPB), 592u), TPB, 0, s>>>(d_cloud, M, (int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
+    LSB_CUDA(cudaMemcpyAsync(h_bbox.p, d_bbox.p, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    LSB_CUDA(cudaStreamSynchronize(s));
+    for (int a = 0; a < 3; ++a) {
+      int v; memcpy(&v, h_bbox.p + a, 4); bmin[a] = ord2f(v);
+      memcpy(&v, h_bbox.p + 3 + a, 4); bmax[a] = ord2f(v);
+    }
+  }
+  for (int a = 0; a < 3; ++a) {
+    if (!(bmin[a] <= bmax[a]) || !std::isfinite(bmin[a]) || !std::isfinite(bmax[a])) throw CudaError(LSB_E_INVALID, "kNN target cloud has non-finite coordinates");
+  }
+  // one cell of margin on each side; enlarge the cell until the grid fits the budget
+  float c = cell;
+  long long nx, ny, nz;
+  while (true) {
+    nx = (long long)std::floor((bmax[0] - bmin[0]) / c) + 3;
+    ny = (long long)std::floor((bmax[1] - bmin[1]) / c) + 3;
+    nz = (long long)std::floor((bmax[2] - bmin[2]) / c) + 3;
+    if (nx * ny * nz <= KNN_MAX_CELLS) break;
+    c *= 1.25f;
+  }
+  gp.cell = c;
+  gp.ox = bmin[0] - c; gp.oy = bmin[1] - c; gp.oz = bmin[2] - c;
+  gp.nx = (int)nx; gp.ny = (int)ny; gp.nz = (int)nz;
+  const int ncells = gp.nx * gp.ny * gp.nz;
+  key_a.reserve(m, s); key_b.reserve(m, s); idx_a.reserve(m, s); idx_b.reserve(m, s);
+  sorted.reserve(m, s); cell_start.reserve((size_t)ncells + 1, s);
+  const unsigned G = div_up(m, TPB);
+  k_cell_keys<<<G, TPB, 0, s>>>(d_cloud, M, gp, key_a.p, idx_a.p); LSB_LAUNCH_CHECK(); lc.add();
+  int bits = 1;
+  while ((1ll << bits) < ncells) ++bits;
+  size_t tmp = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp, key_a.p, key_b.p, idx_a.p, idx_b.p, M, 0, bits, s);
+  cub_tmp.reserve(tmp + 256, s);
+  size_t tb = cub_tmp.cap;
+  LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, key_a.p, key_b.p, idx_a.p, idx_b.p, M, 0, bits, s)); lc.add(3);
+  k_cell_gather<<<G, TPB, 0, s>>>(d_cloud, M, idx_b.p, sorted.p); LSB_LAUNCH_CHECK(); lc.add();
+  k_cell_start<<<div_up((size_t)ncells + 1, TPB), TPB, 0, s>>>(key_b.p, M, ncells, cell_start.p); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void KnnGrid::search(const float* d_q, size_t nq, int k, int32_t* d_idx, float* d_d2, int32_t* d_nf, cudaStream_t s, LaunchCounter& lc) const
+{
+  if (nq == 0) return;
+  if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
+  if (m == 0) {
+    k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
+    return;
+  }
+  launch_knn<false>(*this, d_q, nullptr, Iso3d::identity(), nq, k, d_idx, d_d2, d_nf, s); lc.add();
+}
+
+void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, int32_t* d_idx, float* d_d2, int32_t* d_nf,
+                            cudaStream_t s, LaunchCounter& lc) const
+{
+  if (nq == 0) return;
+  if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
+  if (m == 0) {
+    k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
+    return;
+  }
+  launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, d_idx, d_d2, d_nf, s); lc.add();
+}
+
+}  // namespace lsb

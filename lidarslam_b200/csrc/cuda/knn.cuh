@@ -1,0 +1,48 @@
+// Exact k-nearest-neighbour search on a uniform grid (kernels K7b/K8 of DESIGN.md).
+// Replaces KDTreePCLAdaptor (reference slam_lib/include/LidarSlam/KDTreePCLAdaptor.h:57-105,
+// nanoflann KDTreeSingleIndexAdaptor<L2_Simple_Adaptor<float>, 3>, leaf 16).
+// Semantics kept: exact search, float distance d2 = ((dx^2 + dy^2) + dz^2), query
+// = double world point cast to float (:96-101), results ascending, min(k, size)
+// found.  Canonical tie order (north star): ascending (d2, index in the cloud).
+#pragma once
+#include "dev_util.h"
+#include "../common/linalg.h"
+
+namespace lsb {
+
+constexpr int KNN_MAX_K = 32;
+
+struct KnnGridParams {
+  float ox, oy, oz;     // origin (min corner)
+  float cell;           // cell edge
+  int nx, ny, nz;
+};
+
+struct KnnGrid {
+  const lsb_point* cloud = nullptr;   // device, not owned; indices refer to this order
+  size_t m = 0;
+  KnnGridParams gp{};
+  DevBuf<uint32_t> key_a, key_b, idx_a, idx_b;
+  DevBuf<float4> sorted;          // cell-major points: (x, y, z, bits of the cloud index)
+  DevBuf<uint32_t> cell_start;    // [ncells + 1] prefix offsets into sorted
+  DevBuf<unsigned char> cub_tmp;
+  DevBuf<float> d_bbox;           // [6]
+  PinnedBuf<float> h_bbox;
+
+  bool empty() const { return m == 0; }
+  void clear() { cloud = nullptr; m = 0; }
+  // Builds the grid over d_cloud[0..m).  lo/hi: host-known bounds containing every
+  // point (nullptr => computed on the device, one stream sync).
+  void build(const lsb_point* d_cloud, size_t m, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc);
+
+  // kNN of nq float queries (xyz packed).  idx_out/d2_out: [nq * k], missing
+  // entries -1 / +inf.  nfound_out may be nullptr.
+  void search(const float* d_queries_xyz, size_t nq, int k, int32_t* d_idx_out, float* d_d2_out, int32_t* d_nfound_out,
+              cudaStream_t s, LaunchCounter& lc) const;
+  // kNN of the keypoints kp[0..nq) moved by `prior` in double then cast to float
+  // (KeypointsMatcher.cxx:118 + KDTreePCLAdaptor.h:96-101).
+  void search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, int32_t* d_idx_out, float* d_d2_out,
+                     int32_t* d_nfound_out, cudaStream_t s, LaunchCounter& lc) const;
+};
+
+}  // namespace lsb

@@ -1,0 +1,511 @@
+// GPU RollingGrid — see map.cuh.  The per-point serial hash inserts of the
+// reference (RollingGrid.cxx:188-313) become: key computation -> stable radix sort
+// by leaf key -> one thread per touched leaf replays the reference's sequential
+// rule over its (short, arrival-ordered) segment -> binary-search join with the
+// sorted map: existing leaves are updated in place, new leaves are merged by rank.
+#include "map.cuh"
+#include "../common/linalg.h"
+#include <cub/cub.cuh>
+#include <climits>
+#include <cmath>
+#include <cstring>
+#include <algorithm>
+
+namespace lsb {
+
+namespace {
+
+constexpr int TPB = 256;
+constexpr unsigned long long INVALID_KEY = ~0ull;
+
+struct GridGeom {
+  int G;                 // GridSize
+  float ox, oy, oz;      // voxelGridOrigin (RollingGrid.cxx:177)
+  float res;             // (float)VoxelResolution
+  float leaf;            // (float)LeafSize
+};
+
+__host__ __device__ __forceinline__ int to1d(int x, int y, int z, int G) { return z * G * G + y * G + x; }   // :449-452
+__host__ __device__ __forceinline__ void to3d(int id, int G, int& x, int& y, int& z)                           // :455-463
+{
+  z = id / (G * G);
+  id -= z * G * G;
+  y = id / G;
+  x = id - y * G;
+}
+// Utils::PositionToVoxel (RollingGrid.h:38-42): float arithmetic, round half away from zero
+__host__ __device__ __forceinline__ int pos2vox(float p, float o, float r) { return (int)roundf((p - o) / r); }
+
+__device__ __forceinline__ unsigned long long make_key(int idxOut, int idxIn)
+{
+  return ((unsigned long long)(unsigned)idxOut << 32) | (unsigned long long)((unsigned)idxIn ^ 0x80000000u);
+}
+
+__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return (i >= 0) ? i : (i ^ 0x7fffffff); }
+
+__global__ void k_bbox_init(int* bb) { if (threadIdx.x < 3) bb[threadIdx.x] = INT_MAX; else if (threadIdx.x < 6) bb[threadIdx.x] = INT_MIN; }
+__global__ void k_bbox(const lsb_point* __restrict__ pts, int n, int* __restrict__ bb)
+{
+  int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)i];
+    const int v[3] = {f2ord(p.x), f2ord(p.y), f2ord(p.z)};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = min(mn[a], v[a]); mx[a] = max(mx[a], v[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    for (int off = 16; off; off >>= 1) {
+      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], off));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], off));
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(bb + a, mn[a]); atomicMax(bb + 3 + a, mx[a]); }
+  }
+}
+
+// leaf key of every incoming point (RollingGrid.cxx:190-202)
+__global__ void k_point_keys(const lsb_point* __restrict__ pts, int n, GridGeom g, unsigned long long* __restrict__ key, uint32_t* __restrict__ idx)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)i];
+  const int vx = pos2vox(p.x, g.ox, g.res), vy = pos2vox(p.y, g.oy, g.res), vz = pos2vox(p.z, g.oz, g.res);
+  unsigned long long k = INVALID_KEY;
+  if (vx >= 0 && vx < g.G && vy >= 0 && vy < g.G && vz >= 0 && vz < g.G) {
+    const float cx = (float)vx * g.res + g.ox, cy = (float)vy * g.res + g.oy, cz = (float)vz * g.res + g.oz;
+    const int ix = pos2vox(p.x, cx, g.leaf), iy = pos2vox(p.y, cy, g.leaf), iz = pos2vox(p.z, cz, g.leaf);
+    k = make_key(to1d(vx, vy, vz, g.G), to1d(ix, iy, iz, g.G));
+  }
+  key[i] = k;
+  idx[i] = (uint32_t)i;
+}
+
+__device__ __forceinline__ int lower_bound_key(const unsigned long long* __restrict__ keys, int n, unsigned long long k)
+{
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (keys[mid] < k) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+struct PointRaw { uint4 a, b; };
+__device__ __forceinline__ PointRaw load_raw(const lsb_point* p) { PointRaw r; r.a = reinterpret_cast<const uint4*>(p)[0]; r.b = reinterpret_cast<const uint4*>(p)[1]; return r; }
+__device__ __forceinline__ void store_raw(lsb_point* p, const PointRaw& r) { reinterpret_cast<uint4*>(p)[0] = r.a; reinterpret_cast<uint4*>(p)[1] = r.b; }
+__device__ __forceinline__ float raw_intensity(const PointRaw& r) { return __uint_as_float(r.b.z); }
+__device__ __forceinline__ unsigned raw_label(const PointRaw& r) { return r.b.w >> 24; }
+__device__ __forceinline__ void raw_set_time_label(PointRaw& r, double t, unsigned label)
+{
+  const unsigned long long u = (unsigned long long)__double_as_longlong(t);
+  r.b.x = (unsigned)(u & 0xffffffffull); r.b.y = (unsigned)(u >> 32);
+  r.b.w = (r.b.w & 0x00ffffffu) | (label << 24);
+}
+
+// One thread per segment head of the sorted incoming keys: replays the sequential
+// insertion rule of RollingGrid::Add for that leaf (:203-311).
+// info[0] |= updated, flags[i] = 1 for heads that create a NEW leaf.
+__global__ void k_apply_segments(const unsigned long long* __restrict__ skey, const uint32_t* __restrict__ sidx, int n,
+                                 const lsb_point* __restrict__ cloud, unsigned long long* __restrict__ map_keys,
+                                 lsb_point* __restrict__ map_pts, uint32_t* __restrict__ map_counts, int n_map, GridGeom g, int sampling,
+                                 unsigned fixed, double currentTime, uint32_t* __restrict__ flags, lsb_point* __restrict__ seg_pts,
+                                 uint32_t* __restrict__ seg_counts, uint32_t* __restrict__ info)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  flags[i] = 0;
+  const unsigned long long k = skey[i];
+  if (k == INVALID_KEY) return;
+  if (i > 0 && skey[i - 1] == k) return;   // not a segment head
+  const int pos = lower_bound_key(map_keys, n_map, k);
+  bool exists = pos < n_map && map_keys[pos] == k;
+  const bool existed = exists;
+  PointRaw cur;
+  uint32_t count = 0;
+  if (exists) { cur = load_raw(map_pts + pos); count = map_counts[pos]; }
+  bool updated = false, seen = false;
+  for (int j = i; j < n && skey[j] == k; ++j) {
+    const PointRaw p = load_raw(cloud + sidx[j]);
+    if (!exists) { cur = p; exists = true; updated = true; }
+    else {
+      if (raw_label(cur) == 1) continue;
+      if (sampling == LSB_SAMPLING_LAST) { cur = p; updated = true; }
+      else if (sampling == LSB_SAMPLING_MAX_INTENSITY) {
+        if (raw_intensity(p) > raw_intensity(cur)) { cur = p; updated = true; }
+      } else if (sampling == LSB_SAMPLING_CENTER_POINT) {
+        int vx, vy, vz, ix, iy, iz;
+        to3d((int)(k >> 32), g.G, vx, vy, vz);
+        // inverse of to1d for the inner key is ambiguous; recompute from the stored point instead
+        const float px = __uint_as_float(p.a.x), py = __uint_as_float(p.a.y), pz = __uint_as_float(p.a.z);
+        const float cx = (float)vx * g.res + g.ox, cy = (float)vy * g.res + g.oy, cz = (float)vz * g.res + g.oz;
+        ix = pos2vox(px, cx, g.leaf); iy = pos2vox(py, cy, g.leaf); iz = pos2vox(pz, cz, g.leaf);
+        const float half = g.res / 2.f;
+        const Vec3f ctr(cx - half + g.leaf * (float)ix, cy - half + g.leaf * (float)iy, cz - half + g.leaf * (float)iz);
+        const Vec3f pn(px, py, pz), po(__uint_as_float(cur.a.x), __uint_as_float(cur.a.y), __uint_as_float(cur.a.z));
+        if (norm(pn - ctr) < norm(po - ctr)) { cur = p; updated = true; }
+      }
+      // LSB_SAMPLING_FIRST: keep the stored point
+    }
+    raw_set_time_label(cur, currentTime, fixed);
+    if (!seen) { ++count; seen = true; }
+  }
+  if (existed) { store_raw(map_pts + pos, cur); map_counts[pos] = count; }
+  else { flags[i] = 1; store_raw(seg_pts + i, cur); seg_counts[i] = count; }
+  if (updated) atomicOr(info, 1u);
+}
+
+// compaction of flagged segment heads into the (sorted) insert list
+__global__ void k_gather_inserts(const uint32_t* __restrict__ flags, const uint32_t* __restrict__ scan, int n,
+                                 const unsigned long long* __restrict__ skey, const lsb_point* __restrict__ seg_pts,
+                                 const uint32_t* __restrict__ seg_counts, unsigned long long* __restrict__ ins_keys,
+                                 lsb_point* __restrict__ ins_pts, uint32_t* __restrict__ ins_counts, uint32_t* __restrict__ info)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (flags[i]) {
+    const uint32_t o = scan[i];
+    ins_keys[o] = skey[i];
+    store_raw(ins_pts + o, load_raw(seg_pts + i));
+    ins_counts[o] = seg_counts[i];
+  }
+  if (i == n - 1) info[1] = scan[i] + flags[i];
+}
+
+// merge by rank: both key lists are sorted and disjoint
+__global__ void k_merge(const unsigned long long* __restrict__ ka, const lsb_point* __restrict__ pa, const uint32_t* __restrict__ ca, int na,
+                        const unsigned long long* __restrict__ kb, const lsb_point* __restrict__ pb, const uint32_t* __restrict__ cb, int nb,
+                        unsigned long long* __restrict__ ko, lsb_point* __restrict__ po, uint32_t* __restrict__ co)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < na) {
+    const unsigned long long k = ka[i];
+    const int o = i + lower_bound_key(kb, nb, k);
+    ko[o] = k; store_raw(po + o, load_raw(pa + i)); co[o] = ca[i];
+  } else if (i < na + nb) {
+    const int j = i - na;
+    const unsigned long long k = kb[j];
+    const int o = j + lower_bound_key(ka, na, k);
+    ko[o] = k; store_raw(po + o, load_raw(pb + j)); co[o] = cb[j];
+  }
+}
+
+// Roll (:136-156): shift the outer index, flag survivors
+__global__ void k_roll_keys(unsigned long long* __restrict__ keys, int n, int G, int ox, int oy, int oz, uint32_t* __restrict__ flags)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long k = keys[i];
+  int x, y, z;
+  to3d((int)(k >> 32), G, x, y, z);
+  x -= ox; y -= oy; z -= oz;
+  const bool in = x >= 0 && x < G && y >= 0 && y < G && z >= 0 && z < G;
+  flags[i] = in ? 1u : 0u;
+  if (in) keys[i] = ((unsigned long long)(unsigned)to1d(x, y, z, G) << 32) | (k & 0xffffffffull);
+}
+
+__global__ void k_compact(const uint32_t* __restrict__ flags, const uint32_t* __restrict__ scan, int n,
+                          const unsigned long long* __restrict__ ki, const lsb_point* __restrict__ pi, const uint32_t* __restrict__ ci,
+                          unsigned long long* __restrict__ ko, lsb_point* __restrict__ po, uint32_t* __restrict__ co, uint32_t* __restrict__ info)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (flags[i]) {
+    const uint32_t o = scan[i];
+    if (ko) ko[o] = ki[i];
+    store_raw(po + o, load_raw(pi + i));
+    if (co) co[o] = ci[i];
+  }
+  if (i == n - 1) info[2] = scan[i] + flags[i];
+}
+
+// submap / Get flags.  mode 0: inside bbox; 1: inside && (count >= minFrames || label == 1);
+// 2: inside && (count < minFrames && label != 1); 3: all; 4: count > minFrames
+__global__ void k_flag_entries(const unsigned long long* __restrict__ keys, const lsb_point* __restrict__ pts, const uint32_t* __restrict__ counts,
+                               int n, int G, int lx, int ly, int lz, int hx, int hy, int hz, int mode, unsigned minFrames, uint32_t* __restrict__ flags)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  bool f = true;
+  if (mode <= 2) {
+    int x, y, z;
+    to3d((int)(keys[i] >> 32), G, x, y, z);
+    f = lx <= x && x <= hx && ly <= y && y <= hy && lz <= z && z <= hz;
+  }
+  if (f && mode != 0 && mode != 3) {
+    const unsigned c = counts[i];
+    if (mode == 4) f = c > minFrames;
+    else {
+      const unsigned label = reinterpret_cast<const uint4*>(pts)[2 * (size_t)i + 1].w >> 24;
+      const bool keep = c >= minFrames || label == 1;
+      f = (mode == 1) ? keep : !keep;
+    }
+  }
+  flags[i] = f ? 1u : 0u;
+}
+
+// ClearOldPoints (:325-350)
+__global__ void k_flag_old(const lsb_point* __restrict__ pts, int n, double currentTime, double threshold, uint32_t* __restrict__ flags)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 h = reinterpret_cast<const uint4*>(pts)[2 * (size_t)i + 1];
+  const double t = __longlong_as_double((long long)(((unsigned long long)h.y << 32) | h.x));
+  const unsigned label = h.w >> 24;
+  flags[i] = (!label && currentTime - t > threshold) ? 0u : 1u;
+}
+
+}  // namespace
+
+// ============================================================== host side ====
+static inline float ord2f_host(int i) { const int j = (i >= 0) ? i : (i ^ 0x7fffffff); float f; std::memcpy(&f, &j, 4); return f; }
+
+void cloud_bbox(const lsb_point* d_cloud, size_t n, float mn[3], float mx[3], DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
+                cudaStream_t s, LaunchCounter& lc)
+{
+  d_bbox.reserve(8, s); h_bbox.reserve(8);
+  k_bbox_init<<<1, 32, 0, s>>>((int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
+  k_bbox<<<std::min(div_up(n, TPB), 592u), TPB, 0, s>>>(d_cloud, (int)n, (int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
+  LSB_CUDA(cudaMemcpyAsync(h_bbox.p, d_bbox.p, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaStreamSynchronize(s));
+  for (int a = 0; a < 3; ++a) {
+    int v;
+    std::memcpy(&v, h_bbox.p + a, 4); mn[a] = ord2f_host(v);
+    std::memcpy(&v, h_bbox.p + 3 + a, 4); mx[a] = ord2f_host(v);
+  }
+}
+
+static GridGeom make_geom(const RollingGridGpu& m)
+{
+  GridGeom g;
+  g.G = m.GridSize;
+  const float shift = (float)(int(m.GridSize / 2) * m.VoxelResolution);
+  g.ox = m.Position[0] - shift; g.oy = m.Position[1] - shift; g.oz = m.Position[2] - shift;
+  g.res = (float)m.VoxelResolution;
+  g.leaf = (float)m.LeafSize;
+  return g;
+}
+
+void RollingGridGpu::ensure_scratch(size_t n, cudaStream_t s)
+{
+  flags.reserve(n + 1, s); scan.reserve(n + 1, s);
+  d_info.reserve(8, s); h_info.reserve(8);
+  size_t tmp = 0, tmp2 = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp, flags.p, scan.p, (int)n, s);
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp2, nk_a.p, nk_b.p, ni_a.p, ni_b.p, (int)n, 0, 64, s);
+  cub_tmp.reserve(std::max(tmp, tmp2) + 256, s);
+}
+
+void RollingGridGpu::Clear()
+{
+  NbPoints = 0;
+  n_entries = 0;
+  ResetTree();
+}
+
+void RollingGridGpu::Reset(const float p[3], cudaStream_t)
+{
+  Clear();
+  const float r = (float)VoxelResolution;
+  for (int a = 0; a < 3; ++a) Position[a] = std::floor(p[a] / r) * r;
+}
+
+// keeps map entries with flags != 0 (order preserved); returns the new count (one sync)
+size_t RollingGridGpu::compact_entries(cudaStream_t s, LaunchCounter& lc)
+{
+  const int n = (int)n_entries;
+  if (n == 0) return 0;
+  keys_b.reserve(n_entries, s); pts_b.reserve(n_entries, s); counts_b.reserve(n_entries, s);
+  size_t tb = cub_tmp.cap;
+  LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, n, s)); lc.add(2);
+  k_compact<<<div_up(n_entries, TPB), TPB, 0, s>>>(flags.p, scan.p, n, keys.p, pts.p, counts.p, keys_b.p, pts_b.p, counts_b.p, d_info.p);
+  LSB_LAUNCH_CHECK(); lc.add();
+  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaStreamSynchronize(s));
+  keys.swap(keys_b); pts.swap(pts_b); counts.swap(counts_b);
+  n_entries = h_info.p[2];
+  return n_entries;
+}
+
+void RollingGridGpu::Roll(const float mn[3], const float mx[3], cudaStream_t s, LaunchCounter& lc)
+{
+  const double halfGridSize = static_cast<double>(GridSize) / 2 * VoxelResolution;
+  const float h = (float)halfGridSize;
+  const float r = (float)VoxelResolution;
+  int vo[3];
+  for (int a = 0; a < 3; ++a) {
+    const float down = mn[a] - (Position[a] - h);
+    const float up = mx[a] - (Position[a] + h);
+    float off = (up + down) / 2.f;
+    const float dmin0 = (down < 0.f) ? down : 0.f;
+    const float umax0 = (up > 0.f) ? up : 0.f;
+    off = (off < dmin0) ? dmin0 : off;
+    off = (off > umax0) ? umax0 : off;
+    vo[a] = (int)std::round(off / r);
+  }
+  if (vo[0] == 0 && vo[1] == 0 && vo[2] == 0) return;
+  if (n_entries) {
+    ensure_scratch(n_entries, s);
+    k_roll_keys<<<div_up(n_entries, TPB), TPB, 0, s>>>(keys.p, (int)n_entries, GridSize, vo[0], vo[1], vo[2], flags.p); LSB_LAUNCH_CHECK(); lc.add();
+    NbPoints = (unsigned)compact_entries(s, lc);
+  } else NbPoints = 0;
+  for (int a = 0; a < 3; ++a) Position[a] += (float)vo[a] * r;
+}
+
+void RollingGridGpu::Add(const lsb_point* d_cloud, size_t n, bool fixed, double currentTime, bool roll, cudaStream_t s, LaunchCounter& lc)
+{
+  if (n == 0) return;
+  if (Sampling == LSB_SAMPLING_CENTROID) throw CudaError(LSB_E_INVALID, "SamplingMode::CENTROID is not implemented on the GPU map");
+  if (roll) {
+    float mn[3], mx[3];
+    cloud_bbox(d_cloud, n, mn, mx, d_bbox, h_bbox, s, lc);
+    Roll(mn, mx, s, lc);
+  }
+  const GridGeom g = make_geom(*this);
+  const int N = (int)n;
+  nk_a.reserve(n, s); nk_b.reserve(n, s); ni_a.reserve(n, s); ni_b.reserve(n, s);
+  ins_keys.reserve(n, s); ins_pts.reserve(n, s); ins_counts.reserve(n, s);
+  pts_b.reserve(n, s); counts_b.reserve(n, s);      // per-segment scratch (seg_pts / seg_counts)
+  ensure_scratch(std::max(n, n_entries), s);
+  const unsigned G = div_up(n, TPB);
+  k_point_keys<<<G, TPB, 0, s>>>(d_cloud, N, g, nk_a.p, ni_a.p); LSB_LAUNCH_CHECK(); lc.add();
+  size_t tb = cub_tmp.cap;
+  LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, nk_a.p, nk_b.p, ni_a.p, ni_b.p, N, 0, 64, s)); lc.add(9);
+  LSB_CUDA(cudaMemsetAsync(d_info.p, 0, 8 * sizeof(uint32_t), s));
+  k_apply_segments<<<G, TPB, 0, s>>>(nk_b.p, ni_b.p, N, d_cloud, keys.p, pts.p, counts.p, (int)n_entries, g, Sampling, fixed ? 1u : 0u,
+                                     currentTime, flags.p, pts_b.p, counts_b.p, d_info.p);
+  LSB_LAUNCH_CHECK(); lc.add();
+  tb = cub_tmp.cap;
+  LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, N, s)); lc.add(2);
+  k_gather_inserts<<<G, TPB, 0, s>>>(flags.p, scan.p, N, nk_b.p, pts_b.p, counts_b.p, ins_keys.p, ins_pts.p, ins_counts.p, d_info.p);
+  LSB_LAUNCH_CHECK(); lc.add();
+  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaStreamSynchronize(s));
+  const bool updated = h_info.p[0] != 0;
+  const size_t n_ins = h_info.p[1];
+  if (n_ins) {
+    const size_t total = n_entries + n_ins;
+    keys_b.reserve(total, s); pts_b.reserve(total, s); counts_b.reserve(total, s);
+    // pts_b / counts_b were the segment scratch: the inserts were already gathered out of them
+    k_merge<<<div_up(total, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, (int)n_entries, ins_keys.p, ins_pts.p, ins_counts.p, (int)n_ins,
+                                               keys_b.p, pts_b.p, counts_b.p);
+    LSB_LAUNCH_CHECK(); lc.add();
+    keys.swap(keys_b); pts.swap(pts_b); counts.swap(counts_b);
+    n_entries = total;
+    NbPoints += (unsigned)n_ins;
+  }
+  if (updated) ResetTree();
+}
+
+void RollingGridGpu::ClearOldPoints(double currentTime, cudaStream_t s, LaunchCounter& lc)
+{
+  if (!n_entries) return;
+  ensure_scratch(n_entries, s);
+  k_flag_old<<<div_up(n_entries, TPB), TPB, 0, s>>>(pts.p, (int)n_entries, currentTime, DecayingThreshold, flags.p); LSB_LAUNCH_CHECK(); lc.add();
+  compact_entries(s, lc);   // NbPoints is NOT decremented (reference behaviour, :325-350)
+}
+
+size_t RollingGridGpu::Get(bool clean, lsb_point* d_out, cudaStream_t s, LaunchCounter& lc)
+{
+  if (!n_entries) return 0;
+  const int n = (int)n_entries;
+  if (!clean) {
+    LSB_CUDA(cudaMemcpyAsync(d_out, pts.p, n_entries * sizeof(lsb_point), cudaMemcpyDeviceToDevice, s));
+    return n_entries;
+  }
+  ensure_scratch(n_entries, s);
+  k_flag_entries<<<div_up(n_entries, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, 0, 0, 0, 0, 0, 0, 4, MinFramesPerVoxel, flags.p);
+  LSB_LAUNCH_CHECK(); lc.add();
+  size_t tb = cub_tmp.cap;
+  LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, n, s)); lc.add(2);
+  k_compact<<<div_up(n_entries, TPB), TPB, 0, s>>>(flags.p, scan.p, n, nullptr, pts.p, nullptr, nullptr, d_out, nullptr, d_info.p);
+  LSB_LAUNCH_CHECK(); lc.add();
+  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaStreamSynchronize(s));
+  return h_info.p[2];
+}
+
+void RollingGridGpu::build_grid(const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc)
+{
+  tree_valid = true;
+  if (n_submap == 0) { grid.clear(); return; }
+  grid.build(submap.p, n_submap, knn_cell_factor * (float)LeafSize, lo, hi, s, lc);
+}
+
+void RollingGridGpu::BuildSubMapKdTree(cudaStream_t s, LaunchCounter& lc)
+{
+  submap.reserve(std::max<size_t>(n_entries, 1), s);
+  n_submap = Get(false, submap.p, s, lc);
+  build_grid(nullptr, nullptr, s, lc);
+}
+
+void RollingGridGpu::BuildSubMapKdTree(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc)
+{
+  const GridGeom g = make_geom(*this);
+  int lo[3], hi[3];
+  const float o[3] = {g.ox, g.oy, g.oz};
+  for (int a = 0; a < 3; ++a) {
+    lo[a] = std::max(pos2vox(mn[a], o[a], g.res), 0);
+    hi[a] = std::min(pos2vox(mx[a], o[a], g.res), GridSize - 1);
+  }
+  n_submap = 0;
+  submap.reserve(std::max<size_t>(n_entries, 1), s);
+  if (n_entries) {
+    const int n = (int)n_entries;
+    ensure_scratch(n_entries, s);
+    const bool filter = !(minNbPoints < 0 || MinFramesPerVoxel <= 1);
+    auto pass = [&](int mode, size_t offset) -> size_t {
+      k_flag_entries<<<div_up(n_entries, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], mode,
+                                                            MinFramesPerVoxel, flags.p);
+      LSB_LAUNCH_CHECK(); lc.add();
+      size_t tb = cub_tmp.cap;
+      LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, n, s)); lc.add(2);
+      k_compact<<<div_up(n_entries, TPB), TPB, 0, s>>>(flags.p, scan.p, n, nullptr, pts.p, nullptr, nullptr, submap.p + offset, nullptr, d_info.p);
+      LSB_LAUNCH_CHECK(); lc.add();
+      LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+      LSB_CUDA(cudaStreamSynchronize(s));
+      return h_info.p[2];
+    };
+    n_submap = pass(filter ? 1 : 0, 0);
+    if (filter && (int)n_submap < minNbPoints) n_submap += pass(2, n_submap);
+  }
+  // every submap point lies in an outer voxel of [lo, hi]: host-known kNN grid bounds (with slack)
+  float blo[3], bhi[3];
+  for (int a = 0; a < 3; ++a) {
+    blo[a] = o[a] + ((float)lo[a] - 0.5f) * g.res - 0.01f * g.res;
+    bhi[a] = o[a] + ((float)hi[a] + 0.5f) * g.res + 0.01f * g.res;
+  }
+  const bool bounded = lo[0] <= hi[0] && lo[1] <= hi[1] && lo[2] <= hi[2];
+  build_grid(bounded ? blo : nullptr, bounded ? bhi : nullptr, s, lc);
+}
+
+void RollingGridGpu::SetGridSize(int size, cudaStream_t s, LaunchCounter& lc)
+{
+  GridSize = size;
+  const size_t n = n_entries;
+  if (n) {
+    DevBuf<lsb_point> prev;
+    prev.reserve(n, s);
+    Get(false, prev.p, s, lc);
+    Clear();
+    Add(prev.p, n, false, -1., true, s, lc);
+    LSB_CUDA(cudaStreamSynchronize(s));
+  } else Clear();
+}
+
+void RollingGridGpu::SetVoxelResolution(double resolution, cudaStream_t s, LaunchCounter& lc)
+{
+  VoxelResolution = int(resolution / LeafSize) * LeafSize;
+  const float r = (float)VoxelResolution;
+  for (int a = 0; a < 3; ++a) Position[a] = std::floor(Position[a] / r) * r;
+  const size_t n = n_entries;
+  if (n) {
+    DevBuf<lsb_point> prev;
+    prev.reserve(n, s);
+    Get(false, prev.p, s, lc);
+    Clear();
+    Add(prev.p, n, false, -1., true, s, lc);
+    LSB_CUDA(cudaStreamSynchronize(s));
+  } else Clear();
+}
+
+}  // namespace lsb

@@ -1,0 +1,347 @@
+// K9 model fit + K10/K11 device LM — see match.cuh.
+// Per keypoint (one thread): neighbourhood selection (per-ring pick or inlier-line
+// vote, KeypointsMatcher.cxx:349-480), 3x3 FP64 covariance + closed-form eigen
+// (common/pca.h), model checks and the residual record (A, P, X, w)
+// (KeypointsMatcher.cxx:106-346).  Plain IEEE arithmetic, no FMA contraction.
+#include "match.cuh"
+#include "../common/pca.h"
+#include <cfloat>
+#include <cmath>
+
+namespace lsb {
+
+namespace {
+
+constexpr int FIT_TPB = 128;
+
+struct FitParams {
+  int single_edge_per_ring;
+  double sq_max_neighbors_distance;
+  unsigned edge_nb, edge_min_nb;
+  double edge_max_model_error, sq_edge_max_model_error;
+  float sq_edge_inlier;          // (float)(EdgeMaxModelError^2)  (KeypointsMatcher.cxx:423)
+  unsigned plane_nb;
+  double planarity_threshold, plane_max_model_error, sq_plane_max_model_error;
+  unsigned blob_nb;
+};
+
+__device__ __forceinline__ Vec3f cloud_xyz(const lsb_point* __restrict__ cloud, int i)
+{
+  const float4 p = __ldg(reinterpret_cast<const float4*>(cloud) + 2 * (size_t)i);
+  return Vec3f(p.x, p.y, p.z);
+}
+__device__ __forceinline__ int cloud_ring(const lsb_point* __restrict__ cloud, int i)
+{
+  const uint4 h = __ldg(reinterpret_cast<const uint4*>(cloud) + 2 * (size_t)i + 1);
+  return (int)(h.w & 0xffffu);
+}
+
+__device__ __forceinline__ bool dev_isfinite(double v) { return (v - v) == 0.0; }
+
+__device__ __forceinline__ void write_record(LmRecord* __restrict__ rec, const Mat3d& A, const Vec3d& mean, const Vec3d& X, double w)
+{
+#pragma unroll
+  for (int t = 0; t < 9; ++t) rec->A[t] = A.m[t];
+  rec->P[0] = mean.x; rec->P[1] = mean.y; rec->P[2] = mean.z;
+  rec->X[0] = X.x; rec->X[1] = X.y; rec->X[2] = X.z;
+  rec->w = w;
+}
+
+// One thread per keypoint.  sel[] holds positions in the kNN list, in list order.
+template <int TYPE>
+__global__ void __launch_bounds__(FIT_TPB)
+k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cloud, const int32_t* __restrict__ nn_idx,
+      const float* __restrict__ nn_d2, const int32_t* __restrict__ nn_found, int k, FitParams fp, LmRecord* __restrict__ records,
+      uint8_t* __restrict__ status, double* __restrict__ weight, int* __restrict__ hist)
+{
+  __shared__ int s_hist[LSB_MATCH_N_STATUS];
+  if (threadIdx.x < LSB_MATCH_N_STATUS) s_hist[threadIdx.x] = 0;
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nq) {
+    int st = LSB_MATCH_SUCCESS;
+    double w = 0.0;
+    const int32_t* idx = nn_idx + (size_t)i * k;
+    const float* d2 = nn_d2 + (size_t)i * k;
+    const int n = nn_found[i];
+    int sel[KNN_MAX_K];
+    int nsel = 0;
+    if (TYPE == LSB_EDGE) {
+      if (fp.edge_nb < 2 || fp.edge_min_nb < 2) st = LSB_MATCH_BAD_MODEL_PARAMETRIZATION;
+      else if (fp.single_edge_per_ring) {
+        // GetPerRingLineNeighbors (:349-405): the nearest's ring and rings farther than 4
+        // from it are excluded; then the first hit of each remaining ring, in list order.
+        if (n > 0) {
+          const int closest = cloud_ring(cloud, idx[0]);
+          int rings[KNN_MAX_K];
+          for (int t = 0; t < n; ++t) rings[t] = cloud_ring(cloud, idx[t]);
+          for (int t = 0; t < n; ++t) {
+            const int r = rings[t];
+            if (r == closest || abs(closest - r) > 4) continue;
+            bool seen = false;
+            for (int u = 0; u < nsel; ++u) seen |= (rings[sel[u]] == r);
+            if (!seen) sel[nsel++] = t;
+          }
+        }
+      } else {
+        // GetRansacLineNeighbors (:408-480)
+        if (n >= 2) {
+          Vec3f nb[KNN_MAX_K];
+          for (int t = 0; t < n; ++t) nb[t] = cloud_xyz(cloud, idx[t]);
+          const Vec3f P1 = nb[0];
+          unsigned bestMask = 0;
+          int bestCount = 0;
+          for (int pt = 1; pt < n; ++pt) {
+            const Vec3f dir = normalized(nb[pt] - P1);
+            unsigned mask = 0;
+            for (int cd = 1; cd < n; ++cd) {
+              if (cd == pt) mask |= 1u << cd;
+              else if (sqnorm(cross(nb[cd] - P1, dir)) < fp.sq_edge_inlier) mask |= 1u << cd;
+            }
+            const int cnt = __popc(mask);
+            if (cnt > bestCount) { bestCount = cnt; bestMask = mask; }
+          }
+          sel[nsel++] = 0;
+          for (int cd = 1; cd < n; ++cd)
+            if (bestMask & (1u << cd)) sel[nsel++] = cd;
+        }
+      }
+      if (st == LSB_MATCH_SUCCESS && (unsigned)nsel < fp.edge_min_nb) st = LSB_MATCH_NOT_ENOUGH_NEIGHBORS;
+    } else {
+      const unsigned need = (TYPE == LSB_PLANE) ? fp.plane_nb : fp.blob_nb;
+      if (need < ((TYPE == LSB_PLANE) ? 3u : 4u)) st = LSB_MATCH_BAD_MODEL_PARAMETRIZATION;
+      else if ((unsigned)n < need) st = LSB_MATCH_NOT_ENOUGH_NEIGHBORS;
+      else { nsel = n; for (int t = 0; t < n; ++t) sel[t] = t; }
+    }
+    if (st == LSB_MATCH_SUCCESS && (double)d2[sel[nsel - 1]] > fp.sq_max_neighbors_distance) st = LSB_MATCH_NEIGHBORS_TOO_FAR;
+    if (st == LSB_MATCH_SUCCESS) {
+      // Utils::ComputeMeanAndPCA in double over the selected neighbours, in order
+      CovAccum<double> acc;
+      for (int t = 0; t < nsel; ++t) { const Vec3f p = cloud_xyz(cloud, idx[sel[t]]); acc.add(p.x, p.y, p.z); }
+      Vec3d mean;
+      Mat3d cov, V;
+      double ev[3];
+      acc.finish(mean, cov);
+      eigen33(cov, V, ev);
+      const float4 q = reinterpret_cast<const float4*>(kp)[2 * (size_t)i];
+      const Vec3d base((double)q.x, (double)q.y, (double)q.z);
+      Mat3d A;
+      if (TYPE == LSB_EDGE) {
+        const Vec3d nn = V.col(2);
+        for (int r = 0; r < 3; ++r)
+          for (int c = 0; c < 3; ++c) A(r, c) = ((r == c) ? 1.0 : 0.0) - nn[r] * nn[c];
+        const double mse = ev[0] + ev[1];
+        if (!dev_isfinite(A(0, 0))) st = LSB_MATCH_INVALID_NUMERICAL;
+        else if (mse >= fp.sq_edge_max_model_error) st = LSB_MATCH_MSE_TOO_LARGE;
+        else w = (mse <= 1e-6) ? 1. : 1. - ::sqrt(mse) / fp.edge_max_model_error;
+      } else if (TYPE == LSB_PLANE) {
+        if (ev[1] / ev[2] < fp.planarity_threshold) st = LSB_MATCH_BAD_PCA_STRUCTURE;
+        else {
+          const Vec3d nn = V.col(0);
+          for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) A(r, c) = nn[r] * nn[c];
+          const double mse = ev[0];
+          if (!dev_isfinite(A(0, 0))) st = LSB_MATCH_INVALID_NUMERICAL;
+          else if (mse >= fp.sq_plane_max_model_error) st = LSB_MATCH_MSE_TOO_LARGE;
+          else w = (mse <= 1e-6) ? 1. : 1. - ::sqrt(mse) / fp.plane_max_model_error;
+        }
+      } else {
+        if (ev[0] <= 0. || ev[1] <= 0.) st = LSB_MATCH_BAD_PCA_STRUCTURE;
+        else {
+          const double s0 = 1.0 / ::sqrt(ev[0]), s1 = 1.0 / ::sqrt(ev[1]), s2 = 1.0 / ::sqrt(ev[2]);
+          for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c)
+              A(r, c) = sum3((V(r, 0) * s0) * V(c, 0), (V(r, 1) * s1) * V(c, 1), (V(r, 2) * s2) * V(c, 2));
+          if (!dev_isfinite(A(0, 0)) || !dev_isfinite(s0 * (s1 * s2))) st = LSB_MATCH_INVALID_NUMERICAL;
+          else w = 1.0;
+        }
+      }
+      if (st == LSB_MATCH_SUCCESS) write_record(records + i, A, mean, base, w);
+    }
+    if (st != LSB_MATCH_SUCCESS) { w = 0.0; records[i].w = -1.0; }
+    status[i] = (uint8_t)st;
+    weight[i] = w;
+    atomicAdd(&s_hist[st], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x < LSB_MATCH_N_STATUS && s_hist[threadIdx.x]) atomicAdd(hist + threadIdx.x, s_hist[threadIdx.x]);
+}
+
+// target empty: MatchingResults::Reset values (KeypointsMatcher.h:108-118)
+__global__ void k_fit_empty(int nq, LmRecord* __restrict__ records, uint8_t* __restrict__ status, double* __restrict__ weight)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  records[i].w = -1.0;
+  status[i] = LSB_MATCH_UNKNOWN;
+  weight[i] = 0.0;
+}
+
+// ---------------------------------------------------------------- K10/K11 ----
+// One launch = one cost/Jacobian evaluation of the whole problem + one step of
+// the trust-region state machine (common/lm_core.h).  Each CTA reduces one
+// canonical chunk of 256 records (warp shuffles, offsets 16..1, the 8 warp sums
+// added in order); the last CTA to finish folds the chunk sums with the
+// canonical adjacent-pair tree and advances the LM state.  A launch whose state
+// is already `done` exits at once, so the host enqueues 1 + max_iter launches
+// back to back without reading anything back.
+__global__ void __launch_bounds__(LSB_LM_CHUNK)
+k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, LmState* __restrict__ state,
+          double* __restrict__ part_a, double* __restrict__ part_b, unsigned* __restrict__ counter, int first)
+{
+  __shared__ __align__(16) unsigned char s_pt_raw[sizeof(LmPoint)];
+  LmPoint& s_pt = *reinterpret_cast<LmPoint*>(s_pt_raw);
+  __shared__ double s_warp[LSB_LM_CHUNK / 32][LSB_LM_NSUM];
+  __shared__ int s_last;
+  __shared__ int s_done;
+  if (threadIdx.x == 0) {
+    s_done = state->done;
+    if (!s_done) lm_make_point(first ? state->x : state->xc, s_pt);
+  }
+  __syncthreads();
+  if (s_done) return;
+  const int i = blockIdx.x * LSB_LM_CHUNK + threadIdx.x;
+  double out[LSB_LM_NSUM];
+  if (i < n) lm_eval_record(records[i], s_pt, sat, out);
+  else {
+#pragma unroll
+    for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
+  }
+#pragma unroll
+  for (int q = 0; q < LSB_LM_NSUM; ++q) {
+    double v = out[q];
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+    out[q] = v;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+#pragma unroll
+    for (int q = 0; q < LSB_LM_NSUM; ++q) s_warp[warp][q] = out[q];
+  }
+  __syncthreads();
+  if (threadIdx.x < LSB_LM_NSUM) {
+    double c = s_warp[0][threadIdx.x];
+    for (int w = 1; w < LSB_LM_CHUNK / 32; ++w) c = c + s_warp[w][threadIdx.x];
+    part_a[(size_t)blockIdx.x * LSB_LM_NSUM + threadIdx.x] = c;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(counter, 1u);
+    s_last = (t == (unsigned)(nchunks - 1));
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // canonical tree over adjacent chunks (ping-pong between the two buffers)
+  double* src = part_a;
+  double* dst = part_b;
+  int m = nchunks;
+  while (m > 1) {
+    const int h = (m + 1) / 2;
+    for (int t = threadIdx.x; t < h * LSB_LM_NSUM; t += blockDim.x) {
+      const int c = t / LSB_LM_NSUM, q = t - c * LSB_LM_NSUM;
+      const double a = __ldcg(src + (size_t)(2 * c) * LSB_LM_NSUM + q);
+      dst[(size_t)c * LSB_LM_NSUM + q] = (2 * c + 1 < m) ? a + __ldcg(src + (size_t)(2 * c + 1) * LSB_LM_NSUM + q) : a;
+    }
+    __threadfence_block();
+    __syncthreads();
+    double* tmp = src; src = dst; dst = tmp;
+    m = h;
+  }
+  if (threadIdx.x == 0) {
+    double E[LSB_LM_NSUM];
+    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = __ldcg(src + q);
+    LmState s = *state;
+    if (first) lm_first_eval(s, E); else lm_next_eval(s, E);
+    *state = s;
+    *counter = 0u;
+  }
+}
+
+__global__ void k_lm_begin(LmState* state, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5, int max_iter, int two_d)
+{
+  const double x[6] = {x0, x1, x2, x3, x4, x5};
+  LmState s;
+  lm_begin(s, x, max_iter, two_d);
+  *state = s;
+  *counter = 0u;
+}
+
+}  // namespace
+
+// ============================================================== host side ====
+void MatchWorkspace::begin_iteration(const size_t nk[3], cudaStream_t s)
+{
+  off[0] = 0;
+  for (int k = 0; k < 3; ++k) off[k + 1] = off[k] + nk[k];
+  total = off[3];
+  size_t maxq = std::max(nk[0], std::max(nk[1], nk[2]));
+  nn_idx.reserve(maxq * KNN_MAX_K, s); nn_d2.reserve(maxq * KNN_MAX_K, s); nn_found.reserve(maxq, s);
+  records.reserve(total, s); status.reserve(total, s); weight.reserve(total, s);
+  hist.reserve(3 * LSB_MATCH_N_STATUS, s);
+  h_hist.reserve(3 * LSB_MATCH_N_STATUS);
+  LSB_CUDA(cudaMemsetAsync(hist.p, 0, 3 * LSB_MATCH_N_STATUS * sizeof(int), s));
+}
+
+void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, const KnnGrid& target, const Iso3d& prior,
+                                const lsb_match_params& mp, cudaStream_t s, LaunchCounter& lc)
+{
+  if (nk == 0) return;
+  LmRecord* rec = records.p + off[type];
+  uint8_t* st = status.p + off[type];
+  double* wt = weight.p + off[type];
+  int* h = hist.p + type * LSB_MATCH_N_STATUS;
+  const unsigned G = div_up(nk, FIT_TPB);
+  if (target.empty()) {
+    k_fit_empty<<<G, FIT_TPB, 0, s>>>((int)nk, rec, st, wt); LSB_LAUNCH_CHECK(); lc.add();
+    return;
+  }
+  FitParams fp;
+  fp.single_edge_per_ring = mp.single_edge_per_ring;
+  fp.sq_max_neighbors_distance = mp.max_neighbors_distance * mp.max_neighbors_distance;
+  fp.edge_nb = mp.edge_nb_neighbors; fp.edge_min_nb = mp.edge_min_nb_neighbors;
+  fp.edge_max_model_error = mp.edge_max_model_error;
+  fp.sq_edge_max_model_error = mp.edge_max_model_error * mp.edge_max_model_error;
+  fp.sq_edge_inlier = (float)(mp.edge_max_model_error * mp.edge_max_model_error);
+  fp.plane_nb = mp.plane_nb_neighbors; fp.planarity_threshold = mp.planarity_threshold;
+  fp.plane_max_model_error = mp.plane_max_model_error;
+  fp.sq_plane_max_model_error = mp.plane_max_model_error * mp.plane_max_model_error;
+  fp.blob_nb = mp.blob_nb_neighbors;
+  const unsigned kk = (type == LSB_EDGE) ? mp.edge_nb_neighbors : (type == LSB_PLANE ? mp.plane_nb_neighbors : mp.blob_nb_neighbors);
+  if (kk > (unsigned)KNN_MAX_K) throw CudaError(LSB_E_CAPACITY, "more than 32 neighbours requested");
+  const int k = std::max(1, (int)kk);
+  target.search_points(d_kp, nk, prior, k, nn_idx.p, nn_d2.p, nn_found.p, s, lc);
+  const int NQ = (int)nk;
+  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
+  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
+  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
+  LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void MatchWorkspace::read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s)
+{
+  LSB_CUDA(cudaMemcpyAsync(h_hist.p, hist.p, 3 * LSB_MATCH_N_STATUS * sizeof(int), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaStreamSynchronize(s));
+  for (int t = 0; t < 3; ++t)
+    for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) hist_out[t][q] = h_hist.p[t * LSB_MATCH_N_STATUS + q];
+}
+
+LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, double saturation, cudaStream_t s, LaunchCounter& lc)
+{
+  const int n = (int)total;
+  const int nchunks = std::max(1, (int)div_up(total, LSB_LM_CHUNK));
+  part_a.reserve((size_t)nchunks * LSB_LM_NSUM, s); part_b.reserve((size_t)nchunks * LSB_LM_NSUM, s);
+  lm_state.reserve(1, s); lm_counter.reserve(1, s); h_lm.reserve(1);
+  k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d); LSB_LAUNCH_CHECK(); lc.add();
+  for (int e = 0; e <= max_iter; ++e) {
+    k_lm_eval<<<nchunks, LSB_LM_CHUNK, 0, s>>>(records.p, n, nchunks, saturation, lm_state.p, part_a.p, part_b.p, lm_counter.p, e == 0 ? 1 : 0);
+    LSB_LAUNCH_CHECK(); lc.add();
+  }
+  LSB_CUDA(cudaMemcpyAsync(h_lm.p, lm_state.p, sizeof(LmState), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaStreamSynchronize(s));
+  return *h_lm.p;
+}
+
+}  // namespace lsb

@@ -1,0 +1,38 @@
+// Keypoint-to-model matching (K9) and the device Gauss-Newton / LM loop (K10/K11).
+// Replaces reference slam_lib/src/KeypointsMatcher.cxx:33-480 (after the kNN),
+// include/LidarSlam/CeresCostFunctions.h:105-152 and src/LocalOptimizer.cxx:74-102.
+#pragma once
+#include "dev_util.h"
+#include "knn.cuh"
+#include "../common/lm_core.h"
+
+namespace lsb {
+
+// Everything one ICP iteration needs on the device.  Records / status / weight are
+// index-aligned with the keypoints, the three types concatenated EDGE | PLANE | BLOB.
+struct MatchWorkspace {
+  DevBuf<int32_t> nn_idx, nn_found;
+  DevBuf<float> nn_d2;
+  DevBuf<LmRecord> records;
+  DevBuf<uint8_t> status;
+  DevBuf<double> weight;
+  DevBuf<int> hist;                 // [3][LSB_MATCH_N_STATUS]
+  DevBuf<double> part_a, part_b;    // LM chunk partial sums (ping-pong)
+  DevBuf<LmState> lm_state;         // [1]
+  DevBuf<unsigned> lm_counter;      // [1]
+  PinnedBuf<int> h_hist;
+  PinnedBuf<LmState> h_lm;
+  size_t total = 0;                 // records of the current iteration
+  size_t off[4] = {0, 0, 0, 0};     // offsets of the three types
+
+  void begin_iteration(const size_t nk[3], cudaStream_t s);
+  // KeypointsMatcher::BuildMatchResiduals for one keypoint type (kNN + model fit).
+  void match_type(int type, const lsb_point* d_kp, size_t nk, const KnnGrid& target, const Iso3d& prior, const lsb_match_params& mp,
+                  cudaStream_t s, LaunchCounter& lc);
+  // reads the status histograms back (one stream sync); hist_out[3][LSB_MATCH_N_STATUS]
+  void read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s);
+  // LocalOptimizer::Solve on the current records; returns the final state (one stream sync)
+  LmState solve(const double x0[6], int max_iter, int two_d, double saturation, cudaStream_t s, LaunchCounter& lc);
+};
+
+}  // namespace lsb

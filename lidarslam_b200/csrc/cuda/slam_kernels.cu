@@ -1,0 +1,178 @@
+// K6: rigid transform / motion undistortion / small per-cloud reductions.
+// Reference: Utils::TransformPoint (Utilities.h:274-278, FP64 math, FP32 store),
+// LinearTransformInterpolator (MotionModel.h:36-136), Slam::RefineUndistortion
+// (Slam.cxx:1337-1351), Slam::AggregateFrames (Slam.cxx:1512-1578).
+#include "../host/slam.cuh"
+#include <climits>
+#include <cstring>
+
+namespace lsb {
+
+namespace {
+
+constexpr int TPB = 256;
+
+__device__ __forceinline__ void load_xyz(const lsb_point* p, float& x, float& y, float& z)
+{
+  const float4 v = reinterpret_cast<const float4*>(p)[0];
+  x = v.x; y = v.y; z = v.z;
+}
+__device__ __forceinline__ void store_xyz(lsb_point* p, float x, float y, float z)
+{
+  float4 v = reinterpret_cast<float4*>(p)[0];
+  v.x = x; v.y = y; v.z = z;
+  reinterpret_cast<float4*>(p)[0] = v;
+}
+
+__global__ void k_transform(lsb_point* __restrict__ pts, int n, Iso3d T)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float x, y, z;
+  load_xyz(pts + i, x, y, z);
+  transform_point_f(T, x, y, z);
+  store_xyz(pts + i, x, y, z);
+}
+
+__global__ void k_aggregate(lsb_point* __restrict__ pts, int n, double timeOffset, Iso3d T, int applyT)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  pts[i].time += timeOffset;
+  if (applyT) {
+    float x, y, z;
+    load_xyz(pts + i, x, y, z);
+    transform_point_f(T, x, y, z);
+    store_xyz(pts + i, x, y, z);
+  }
+}
+
+__global__ void k_undistort(lsb_point* __restrict__ pts, int n, Interpolator it, double timeOffset)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double t = pts[i].time;
+  if (timeOffset != 0.0) { t += timeOffset; pts[i].time = t; }
+  const Iso3d T = it.at(t);
+  float x, y, z;
+  load_xyz(pts + i, x, y, z);
+  transform_point_f(T, x, y, z);
+  store_xyz(pts + i, x, y, z);
+}
+
+// order-preserving map double -> uint64 for atomicMin/atomicMax
+__host__ __device__ __forceinline__ unsigned long long d2ord(double d)
+{
+  unsigned long long u;
+#ifdef __CUDA_ARCH__
+  u = (unsigned long long)__double_as_longlong(d);
+#else
+  std::memcpy(&u, &d, 8);
+#endif
+  return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+inline double ord2d(unsigned long long u)
+{
+  u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
+  double d;
+  std::memcpy(&d, &u, 8);
+  return d;
+}
+
+__global__ void k_minmax_init(unsigned long long* mm) { mm[0] = ~0ull; mm[1] = 0ull; }
+
+__global__ void k_time_minmax(const lsb_point* __restrict__ pts, int n, unsigned long long* __restrict__ mm)
+{
+  unsigned long long mn = ~0ull, mx = 0ull;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const unsigned long long o = d2ord(pts[i].time);
+    mn = min(mn, o); mx = max(mx, o);
+  }
+  for (int off = 16; off; off >>= 1) {
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, off));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMin(mm, mn); atomicMax(mm + 1, mx); }
+}
+
+__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return (i >= 0) ? i : (i ^ 0x7fffffff); }
+__global__ void k_bbox_init(int* bb) { if (threadIdx.x < 3) bb[threadIdx.x] = INT_MAX; else if (threadIdx.x < 6) bb[threadIdx.x] = INT_MIN; }
+
+// pcl::transformPointCloud (PCL <= 1.10 explicit form) then pcl::getMinMax3D
+__global__ void k_transformed_bbox(const lsb_point* __restrict__ pts, int n, Iso3d T, int* __restrict__ bb)
+{
+  int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    float fx, fy, fz;
+    load_xyz(pts + i, fx, fy, fz);
+    const double x = fx, y = fy, z = fz;
+    const float wx = (float)(T.R.m[0] * x + T.R.m[1] * y + T.R.m[2] * z + T.t.x);
+    const float wy = (float)(T.R.m[3] * x + T.R.m[4] * y + T.R.m[5] * z + T.t.y);
+    const float wz = (float)(T.R.m[6] * x + T.R.m[7] * y + T.R.m[8] * z + T.t.z);
+    const int v[3] = {f2ord(wx), f2ord(wy), f2ord(wz)};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = min(mn[a], v[a]); mx[a] = max(mx[a], v[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    for (int off = 16; off; off >>= 1) {
+      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], off));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], off));
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(bb + a, mn[a]); atomicMax(bb + 3 + a, mx[a]); }
+  }
+}
+
+}  // namespace
+
+void dev_transform(lsb_point* d_pts, size_t n, const Iso3d& T, cudaStream_t s, LaunchCounter& lc)
+{
+  if (!n) return;
+  k_transform<<<div_up(n, TPB), TPB, 0, s>>>(d_pts, (int)n, T); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void dev_aggregate(lsb_point* d_pts, size_t n, double timeOffset, const Iso3d& T, bool applyT, cudaStream_t s, LaunchCounter& lc)
+{
+  if (!n) return;
+  k_aggregate<<<div_up(n, TPB), TPB, 0, s>>>(d_pts, (int)n, timeOffset, T, applyT ? 1 : 0); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void dev_undistort(lsb_point* d_pts, size_t n, const Interpolator& it, double timeOffset, cudaStream_t s, LaunchCounter& lc)
+{
+  if (!n) return;
+  k_undistort<<<div_up(n, TPB), TPB, 0, s>>>(d_pts, (int)n, it, timeOffset); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc)
+{
+  k_minmax_init<<<1, 1, 0, s>>>(d_mm); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc)
+{
+  if (!n) return;
+  k_time_minmax<<<std::min(div_up(n, TPB), 592u), TPB, 0, s>>>(d_pts, (int)n, d_mm); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx)
+{
+  mn = ord2d(h_mm[0]);
+  mx = ord2d(h_mm[1]);
+}
+
+void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,
+                          PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc)
+{
+  d_bbox.reserve(8, s); h_bbox.reserve(8);
+  k_bbox_init<<<1, 32, 0, s>>>((int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
+  if (n) { k_transformed_bbox<<<std::min(div_up(n, TPB), 592u), TPB, 0, s>>>(d_pts, (int)n, T, (int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add(); }
+  LSB_CUDA(cudaMemcpyAsync(h_bbox.p, d_bbox.p, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaStreamSynchronize(s));
+  for (int a = 0; a < 3; ++a) {
+    int v, j;
+    std::memcpy(&v, h_bbox.p + a, 4); j = (v >= 0) ? v : (v ^ 0x7fffffff); std::memcpy(&mn[a], &j, 4);
+    std::memcpy(&v, h_bbox.p + 3 + a, 4); j = (v >= 0) ? v : (v ^ 0x7fffffff); std::memcpy(&mx[a], &j, 4);
+  }
+}
+
+}  // namespace lsb

@@ -1,0 +1,478 @@
+// lsb_slam — host driver of the per-frame pipeline.  Mirrors the control flow of
+// LidarSlam::Slam (reference slam_lib/src/Slam.cxx, line ranges per function);
+// every cloud operation is a kernel on the handle's stream.
+#include "slam.cuh"
+#include <cstring>
+#include <cmath>
+#include <cfloat>
+#include <algorithm>
+
+using namespace lsb;
+
+static inline double StampToSec(uint64_t us) { return us * 1e-6; }   // Utils::PclStampToSec
+
+lsb_slam::lsb_slam(int dev) : device(dev)
+{
+  LSB_CUDA(cudaSetDevice(dev));
+  LSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  for (auto& e : ev) LSB_CUDA(cudaEventCreate(&e));
+  lsb_default_params(&P);
+  KeyPointsExtractors[0].reset(new ExtractorGpu());
+  // Slam.cxx:153-157: resolution is snapped with the leaf size at call time (0.2 -> 10.0)
+  for (auto& m : LocalMaps) m.SetVoxelResolution(10., stream, lc);
+  for (auto& m : LocalMaps) m.SetGridSize(50, stream, lc);
+  LocalMaps[LSB_EDGE].LeafSize = 0.30;
+  LocalMaps[LSB_PLANE].LeafSize = 0.60;
+  LocalMaps[LSB_BLOB].LeafSize = 0.30;
+  // kNN cell edge relative to the leaf size (density of each map differs)
+  LocalMaps[LSB_EDGE].knn_cell_factor = 5.0f;
+  LocalMaps[LSB_PLANE].knn_cell_factor = 2.5f;
+  LocalMaps[LSB_BLOB].knn_cell_factor = 2.5f;
+  d_minmax.reserve(2, stream); h_minmax.reserve(2);
+  Reset(true);
+}
+
+lsb_slam::~lsb_slam()
+{
+  cudaSetDevice(device);
+  if (stream) cudaStreamSynchronize(stream);
+  for (auto& e : ev) if (e) cudaEventDestroy(e);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+void lsb_slam::ClearMaps()
+{
+  const float zero[3] = {0.f, 0.f, 0.f};
+  for (auto& m : LocalMaps) m.Reset(zero, stream);
+}
+
+void lsb_slam::Reset(bool resetLog)
+{
+  ClearMaps();
+  KfLastPose = Iso3d::identity();
+  KfCounter = 0;
+  Tworld = PreviousTworld = Trelative = Iso3d::identity();
+  WithinFrameMotion.reset();
+  std::memset(&LocalizationUncertainty, 0, sizeof(LocalizationUncertainty));
+  NbCurrentFrames = 0;
+  CurrentStamp = 0;
+  for (int k = 0; k < 3; ++k) {
+    CurrentKeypoints[k].n = 0; PreviousKeypoints[k].n = 0; CurrentWorldKeypoints[k].n = 0;
+    WorldKeypointsValid[k] = false;
+  }
+  for (StageDebug* d : {&EgoDebug, &LocDebug}) {
+    for (auto& o : d->off) o = 0;
+    std::memset(d->hist, 0, sizeof(d->hist));
+  }
+  TotalMatchedKeypoints = 0;
+  if (resetLog) { NbrFrameProcessed = 0; LogTrajectory.clear(); }
+  std::memset(&Stats, 0, sizeof(Stats));
+}
+
+void lsb_slam::SetWorldTransformFromGuess(const Iso3d& T)
+{
+  Tworld = T;
+  PreviousTworld = T;
+  for (int k = 0; k < 3; ++k) CurrentKeypoints[k].n = 0;
+}
+
+Iso3d lsb_slam::GetBaseToLidarOffset(int dev) const
+{
+  auto it = BaseToLidarOffsets.find(dev);
+  return it != BaseToLidarOffsets.end() ? it->second : Iso3d::identity();
+}
+
+ExtractorGpu& lsb_slam::Extractor(int dev)
+{
+  auto& p = KeyPointsExtractors[dev];
+  if (!p) p.reset(new ExtractorGpu());
+  return *p;
+}
+
+//-----------------------------------------------------------------------------
+int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq, bool on_device)
+{
+  LSB_CUDA(cudaSetDevice(device));
+  Warnings = 0;
+  if (!CheckFrames(n_frames, n, stamp_us, seq)) return LSB_W_FRAME_IGNORED;
+  const unsigned launches0 = lc.n;
+  LSB_CUDA(cudaEventRecord(ev[0], stream));
+  // host -> device copy of the input frames (skipped for device-resident input)
+  while (FramePool.size() < (size_t)n_frames) FramePool.emplace_back(new DFrame());
+  NbCurrentFrames = (size_t)n_frames;
+  std::memset(&Stats, 0, sizeof(Stats));
+  for (int i = 0; i < n_frames; ++i) {
+    DFrame& f = *FramePool[i];
+    f.n = n[i]; f.stamp_us = stamp_us[i]; f.seq = seq ? seq[i] : 0u;
+    Stats.n_points += (uint32_t)n[i];
+    if (on_device) f.d = frames[i];
+    else {
+      f.own.buf.reserve(std::max<size_t>(n[i], 1), stream);
+      if (n[i]) LSB_CUDA(cudaMemcpyAsync(f.own.buf.p, frames[i], n[i] * sizeof(lsb_point), cudaMemcpyHostToDevice, stream));
+      f.d = f.own.buf.p;
+    }
+    f.device_id = 0;
+    if (n[i]) {
+      if (on_device) {
+        lsb_point first;
+        LSB_CUDA(cudaMemcpyAsync(&first, frames[i], sizeof(lsb_point), cudaMemcpyDeviceToHost, stream));
+        LSB_CUDA(cudaStreamSynchronize(stream));
+        f.device_id = first.device_id;
+      } else f.device_id = frames[i][0].device_id;
+    }
+  }
+  CurrentStamp = stamp_us[0];
+  CurrentTime = StampToSec(CurrentStamp);
+  for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
+
+  ExtractKeypoints();
+  LSB_CUDA(cudaEventRecord(ev[1], stream));
+  ComputeEgoMotion();
+  LSB_CUDA(cudaEventRecord(ev[2], stream));
+  Localization();
+  LSB_CUDA(cudaEventRecord(ev[3], stream));
+  if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
+  LSB_CUDA(cudaEventRecord(ev[4], stream));
+  LSB_CUDA(cudaEventSynchronize(ev[4]));
+  LogCurrentFrameState(CurrentTime);
+  for (int k = 0; k < 3; ++k) {
+    Stats.n_keypoints[k] = (uint32_t)CurrentKeypoints[k].n;
+    Stats.n_submap[k] = (uint32_t)LocalMaps[k].n_submap;
+    Stats.n_map[k] = LocalMaps[k].Size();
+    Stats.n_matches[k] = (uint32_t)LocDebug.hist[k][LSB_MATCH_SUCCESS];
+    Stats.ego_n_matches[k] = (uint32_t)EgoDebug.hist[k][LSB_MATCH_SUCCESS];
+  }
+  cudaEventElapsedTime(&Stats.ms_extract, ev[0], ev[1]);
+  cudaEventElapsedTime(&Stats.ms_ego, ev[1], ev[2]);
+  cudaEventElapsedTime(&Stats.ms_localization, ev[2], ev[3]);
+  cudaEventElapsedTime(&Stats.ms_map_update, ev[3], ev[4]);
+  cudaEventElapsedTime(&Stats.ms_total, ev[0], ev[4]);
+  Stats.kernel_launches = lc.n - launches0;
+  Latency = Stats.ms_total * 1e-3;
+  NbrFrameProcessed++;
+  return Warnings;
+}
+
+//-----------------------------------------------------------------------------
+bool lsb_slam::CheckFrames(int n_frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq)
+{
+  bool allEmpty = true;
+  for (int i = 0; i < n_frames; ++i) if (n[i] > 0) allEmpty = false;
+  if (n_frames <= 0 || allEmpty) return false;                 // :720-724
+  if (stamp_us[0] == CurrentStamp) return false;               // :727-731 (stamp 0 after Reset, as the reference)
+  for (int i = 0; i < n_frames; ++i) {                         // :734-740
+    const unsigned sq = seq ? seq[i] : 0u;
+    const unsigned dropped = sq - PreviousFramesSeq[i] - 1;
+    if (PreviousFramesSeq[i] > 0 && dropped > 0) Warnings |= LSB_W_FRAMES_DROPPED;
+    PreviousFramesSeq[i] = sq;
+  }
+  return true;
+}
+
+//-----------------------------------------------------------------------------
+void lsb_slam::ExtractKeypoints()
+{
+  for (int k = 0; k < 3; ++k) { PreviousKeypoints[k].swap(CurrentKeypoints[k]); CurrentKeypoints[k].n = 0; }   // :751
+  // With several input frames the extractor buffers are reused, so keypoints are
+  // appended to the aggregate right after each extraction.
+  for (size_t fi = 0; fi < NbCurrentFrames; ++fi) {
+    DFrame& f = *FramePool[fi];
+    if (f.n == 0) continue;
+    int dev = f.device_id;
+    if (!KeyPointsExtractors.count(dev) || !KeyPointsExtractors[dev]) {   // :764-780
+      if (KeyPointsExtractors.size() == 1) dev = KeyPointsExtractors.begin()->first;
+      else continue;
+    }
+    ExtractorGpu& ke = *KeyPointsExtractors[dev];
+    ke.compute(f.d, f.n, stream, lc);
+    // AggregateFrames(keypoints[k], false)  (:1512-1578)
+    for (int k = 0; k < 3; ++k) {
+      if (!P.use_keypoints[k] || ke.counts[k] == 0) continue;
+      DCloud& agg = CurrentKeypoints[k];
+      const size_t start = agg.n, cnt = ke.counts[k];
+      agg.buf.reserve(start + cnt, stream, true, start);
+      LSB_CUDA(cudaMemcpyAsync(agg.buf.p + start, ke.kp[k].p, cnt * sizeof(lsb_point), cudaMemcpyDeviceToDevice, stream));
+      agg.n = start + cnt;
+      const double timeOffset = StampToSec(f.stamp_us) - StampToSec(CurrentStamp);
+      const Iso3d tf = GetBaseToLidarOffset(f.device_id);
+      const bool ident = iso_is_approx(tf, Iso3d::identity());
+      if (!ident || timeOffset != 0.0) dev_aggregate(agg.buf.p + start, cnt, timeOffset, tf, !ident, stream, lc);
+    }
+  }
+}
+
+//-----------------------------------------------------------------------------
+static lsb_match_params EgoParams(const lsb_params& P)
+{
+  lsb_match_params m;
+  m.single_edge_per_ring = 1;                                    // Slam.cxx:879
+  m.max_neighbors_distance = P.ego_motion_max_neighbors_distance;
+  m.edge_nb_neighbors = P.ego_motion_edge_nb_neighbors;
+  m.edge_min_nb_neighbors = P.ego_motion_edge_min_nb_neighbors;
+  m.edge_max_model_error = P.ego_motion_edge_max_model_error;
+  m.plane_nb_neighbors = P.ego_motion_plane_nb_neighbors;
+  m.planarity_threshold = P.ego_motion_planarity_threshold;
+  m.plane_max_model_error = P.ego_motion_plane_max_model_error;
+  m.blob_nb_neighbors = 10;                                      // KeypointsMatcher.h:70 (unused by ego-motion)
+  m.saturation_distance = 1.;
+  return m;
+}
+static lsb_match_params LocParams(const lsb_params& P)
+{
+  lsb_match_params m;
+  m.single_edge_per_ring = 0;
+  m.max_neighbors_distance = P.localization_max_neighbors_distance;
+  m.edge_nb_neighbors = P.localization_edge_nb_neighbors;
+  m.edge_min_nb_neighbors = P.localization_edge_min_nb_neighbors;
+  m.edge_max_model_error = P.localization_edge_max_model_error;
+  m.plane_nb_neighbors = P.localization_plane_nb_neighbors;
+  m.planarity_threshold = P.localization_planarity_threshold;
+  m.plane_max_model_error = P.localization_plane_max_model_error;
+  m.blob_nb_neighbors = P.localization_blob_nb_neighbors;
+  m.saturation_distance = 1.;
+  return m;
+}
+
+// keeps the per-keypoint status / weight of the last matching of a stage
+void lsb_slam::SaveDebug(StageDebug& d)
+{
+  for (int k = 0; k < 4; ++k) d.off[k] = mw.off[k];
+  if (&d == &LocDebug) return;   // localization results stay in the workspace until the next frame
+  d.status.reserve(std::max<size_t>(mw.total, 1), stream);
+  d.weight.reserve(std::max<size_t>(mw.total, 1), stream);
+  if (mw.total) {
+    LSB_CUDA(cudaMemcpyAsync(d.status.p, mw.status.p, mw.total, cudaMemcpyDeviceToDevice, stream));
+    LSB_CUDA(cudaMemcpyAsync(d.weight.p, mw.weight.p, mw.total * sizeof(double), cudaMemcpyDeviceToDevice, stream));
+  }
+}
+
+void lsb_slam::ComputeEgoMotion()
+{
+  Trelative = Iso3d::identity();
+  std::memset(EgoDebug.hist, 0, sizeof(EgoDebug.hist));
+  for (auto& o : EgoDebug.off) o = 0;
+  // Linearly extrapolate the previous motion (:821-836)
+  if (LogTrajectory.size() >= 2 && (P.ego_motion == LSB_EGO_MOTION_EXTRAPOLATION || P.ego_motion == LSB_EGO_MOTION_EXTRAPOLATION_AND_REGISTRATION)) {
+    const double t = StampToSec(CurrentStamp);
+    const double t1 = LogTrajectory[LogTrajectory.size() - 1].time;
+    const double t0 = LogTrajectory[LogTrajectory.size() - 2].time;
+    if (std::abs((t - t1) / (t1 - t0)) > P.max_extrapolation_ratio) Warnings |= LSB_W_EXTRAPOLATION;
+    else {
+      const Iso3d next = linear_interpolation(PreviousTworld, Tworld, t, t0, t1);
+      Trelative = inverse(Tworld) * next;
+    }
+  }
+  // Frame-to-frame registration (:839-964)
+  if (P.ego_motion == LSB_EGO_REGISTRATION || P.ego_motion == LSB_EGO_MOTION_EXTRAPOLATION_AND_REGISTRATION) {
+    for (int k = 0; k < 2; ++k) {
+      if (PreviousKeypoints[k].n) EgoGrids[k].build(PreviousKeypoints[k].buf.p, PreviousKeypoints[k].n, 1.0f, nullptr, nullptr, stream, lc);
+      else EgoGrids[k].clear();
+    }
+    TotalMatchedKeypoints = 0;
+    lsb_match_params mp = EgoParams(P);
+    const size_t nk[3] = {CurrentKeypoints[0].n, CurrentKeypoints[1].n, 0};
+    for (unsigned icpIter = 0; icpIter < P.ego_motion_icp_max_iter; ++icpIter) {
+      const double iterRatio = icpIter / static_cast<double>(P.ego_motion_icp_max_iter - 1);
+      mp.saturation_distance = (1 - iterRatio) * P.ego_motion_init_saturation_distance + iterRatio * P.ego_motion_final_saturation_distance;
+      mw.begin_iteration(nk, stream);
+      for (int k = 0; k < 2; ++k) {
+        mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], EgoGrids[k], Trelative, mp, stream, lc);
+        Stats.knn_queries += (uint32_t)nk[k];
+      }
+      mw.read_histograms(EgoDebug.hist, stream);
+      Stats.ego_icp_iters++;
+      TotalMatchedKeypoints = 0;
+      for (int k = 0; k < 2; ++k) TotalMatchedKeypoints += (unsigned)EgoDebug.hist[k][LSB_MATCH_SUCCESS];
+      if (TotalMatchedKeypoints < P.min_nb_matched_keypoints) { Warnings |= LSB_W_EGO_SKIPPED; break; }   // :919-923
+      double x0[6];
+      iso_to_xyzrpy(Trelative, x0);
+      const LmState st = mw.solve(x0, (int)P.ego_motion_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance, stream, lc);
+      Stats.ego_lm_iters += (uint32_t)st.iter;
+      Trelative = xyzrpy_to_iso(st.x);
+      if (st.num_successful + 1 == 1) break;   // summary.num_successful_steps == 1 (:950)
+    }
+    SaveDebug(EgoDebug);
+  }
+}
+
+//-----------------------------------------------------------------------------
+void lsb_slam::Localization()
+{
+  PreviousTworld = Tworld;                     // :980-981
+  Tworld = PreviousTworld * Trelative;
+  std::memset(LocDebug.hist, 0, sizeof(LocDebug.hist));
+  for (auto& o : LocDebug.off) o = 0;
+  if (P.undistortion) { InitUndistortion(); RefineUndistortion(); }   // :986-995
+
+  // Submaps (:1003-1037)
+  for (int k = 0; k < 3; ++k) {
+    RollingGridGpu& map = LocalMaps[k];
+    if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) continue;
+    if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(stream, lc); continue; }
+    if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, stream, lc);
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (CurrentKeypoints[k].n) dev_transformed_bbox(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, mn, mx, d_bbox, h_bbox, stream, lc);
+    map.BuildSubMapKdTree(mn, mx, (int)(CurrentKeypoints[k].n / 2), stream, lc);
+  }
+
+  // ICP - LM loop (:1051-1156)
+  TotalMatchedKeypoints = 0;
+  lsb_match_params mp = LocParams(P);
+  const size_t nk[3] = {CurrentKeypoints[0].n, CurrentKeypoints[1].n, CurrentKeypoints[2].n};
+  for (unsigned icpIter = 0; icpIter < P.localization_icp_max_iter; ++icpIter) {
+    const double iterRatio = icpIter / static_cast<double>(P.localization_icp_max_iter - 1);
+    mp.saturation_distance = (1 - iterRatio) * P.localization_init_saturation_distance + iterRatio * P.localization_final_saturation_distance;
+    mw.begin_iteration(nk, stream);
+    for (int k = 0; k < 3; ++k) {
+      mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], LocalMaps[k].grid, Tworld, mp, stream, lc);
+      Stats.knn_queries += (uint32_t)nk[k];
+    }
+    mw.read_histograms(LocDebug.hist, stream);
+    SaveDebug(LocDebug);
+    Stats.loc_icp_iters++;
+    TotalMatchedKeypoints = 0;
+    for (int k = 0; k < 3; ++k) TotalMatchedKeypoints += (unsigned)LocDebug.hist[k][LSB_MATCH_SUCCESS];
+    if (TotalMatchedKeypoints < P.min_nb_matched_keypoints) {   // :1098-1107
+      Trelative = Iso3d::identity();
+      Tworld = PreviousTworld;
+      if (P.undistortion) WithinFrameMotion.set_transforms(Iso3d::identity(), Iso3d::identity());
+      Warnings |= LSB_W_LOC_SKIPPED;
+      break;
+    }
+    double x0[6];
+    iso_to_xyzrpy(Tworld, x0);
+    const LmState st = mw.solve(x0, (int)P.localization_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance, stream, lc);
+    Stats.loc_lm_iters += (uint32_t)st.iter;
+    Tworld = xyzrpy_to_iso(st.x);
+    Trelative = inverse(PreviousTworld) * Tworld;
+    if (P.undistortion == LSB_UNDISTORTION_REFINED) RefineUndistortion();
+    if (st.num_successful + 1 == 1 || icpIter == P.localization_icp_max_iter - 1) {   // :1151-1155
+      registration_error_from_normal_matrix(st.H, P.two_d_mode != 0, &LocalizationUncertainty);
+      break;
+    }
+  }
+}
+
+//-----------------------------------------------------------------------------
+void lsb_slam::UpdateMapsUsingTworld()
+{
+  const Iso3d motion = inverse(KfLastPose) * Tworld;
+  const double trans = norm(motion.t);
+  const double rot = rotation_angle(motion.R);
+  const double thresholdCoef = std::min(KfCounter / 10., 1.);
+  unsigned nbMapKpts = 0;
+  for (const auto& m : LocalMaps) nbMapKpts += m.Size();
+  const bool isNewKeyFrame = nbMapKpts < P.min_nb_matched_keypoints * 10 || trans >= thresholdCoef * P.kf_distance_threshold ||
+                             rot >= (thresholdCoef * P.kf_angle_threshold) / 180. * M_PI;
+  if (!isNewKeyFrame) return;
+  Stats.is_keyframe = 1;
+  KfCounter++;
+  KfLastPose = Tworld;
+  for (int k = 0; k < 3; ++k) {
+    if (!P.use_keypoints[k]) continue;
+    const DCloud& w = WorldKeypoints(k);
+    LocalMaps[k].Add(w.buf.p, w.n, false, CurrentTime, true, stream, lc);
+  }
+}
+
+// GetKeypoints(k, true) -> TransformPointCloud (:690-702, :1491-1509), cached per frame
+const DCloud& lsb_slam::WorldKeypoints(int k)
+{
+  DCloud& w = CurrentWorldKeypoints[k];
+  if (!WorldKeypointsValid[k]) {
+    const DCloud& c = CurrentKeypoints[k];
+    w.buf.reserve(std::max<size_t>(c.n, 1), stream);
+    w.n = c.n;
+    if (c.n) {
+      LSB_CUDA(cudaMemcpyAsync(w.buf.p, c.buf.p, c.n * sizeof(lsb_point), cudaMemcpyDeviceToDevice, stream));
+      dev_transform(w.buf.p, w.n, Tworld, stream, lc);
+    }
+    WorldKeypointsValid[k] = true;
+  }
+  return w;
+}
+
+//-----------------------------------------------------------------------------
+void lsb_slam::LogCurrentFrameState(double time)
+{
+  LogTrajectory.push_back(LoggedPose{Tworld, time});
+  if (P.logging_timeout != 0.) {
+    if (P.logging_timeout > 0)
+      while (time - LogTrajectory.front().time > P.logging_timeout && LogTrajectory.size() > 2) LogTrajectory.pop_front();
+  } else {
+    while (LogTrajectory.size() > 2) LogTrajectory.pop_front();
+  }
+}
+
+//-----------------------------------------------------------------------------
+Iso3d lsb_slam::InterpolateScanPose(double time)
+{
+  if (LogTrajectory.empty()) return Tworld;
+  const double prevPoseTime = LogTrajectory.back().time;
+  const double currPoseTime = StampToSec(CurrentStamp);
+  if (std::abs(time / (currPoseTime - prevPoseTime)) > P.max_extrapolation_ratio) { Warnings |= LSB_W_EXTRAPOLATION; return Tworld; }
+  return linear_interpolation(PreviousTworld, Tworld, currPoseTime + time, prevPoseTime, currPoseTime);
+}
+
+void lsb_slam::InitUndistortion()
+{
+  // time range over ALL keypoint clouds (:1293-1300)
+  double first = std::numeric_limits<double>::max(), last = std::numeric_limits<double>::lowest();
+  size_t total = 0;
+  for (int k = 0; k < 3; ++k) total += CurrentKeypoints[k].n;
+  if (total) {
+    dev_time_minmax_begin(d_minmax.p, stream, lc);
+    for (int k = 0; k < 3; ++k) dev_time_minmax(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_minmax.p, stream, lc);
+    LSB_CUDA(cudaMemcpyAsync(h_minmax.p, d_minmax.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    LSB_CUDA(cudaStreamSynchronize(stream));
+    time_minmax_decode(h_minmax.p, first, last);
+  }
+  WithinFrameMotion.set_times(first, last);
+  WithinFrameMotion.set_transforms(Iso3d::identity(), Iso3d::identity());
+  if (WithinFrameMotion.t1 - WithinFrameMotion.t0 < 1e-6) { Warnings |= LSB_W_TIME_FIELD; WithinFrameMotion.set_times(0., 0.); }
+  else if (WithinFrameMotion.t1 - WithinFrameMotion.t0 > 10.) Warnings |= LSB_W_TIME_FIELD;
+}
+
+void lsb_slam::RefineUndistortion()
+{
+  const Iso3d prevBegin = WithinFrameMotion.H0(), prevEnd = WithinFrameMotion.H1();
+  const Iso3d wBegin = InterpolateScanPose(WithinFrameMotion.t0);
+  const Iso3d wEnd = InterpolateScanPose(WithinFrameMotion.t1);
+  const Iso3d baseToWorld = inverse(Tworld);
+  const Iso3d newBegin = baseToWorld * wBegin, newEnd = baseToWorld * wEnd;
+  WithinFrameMotion.set_transforms(newBegin, newEnd);
+  Interpolator interp = WithinFrameMotion;
+  interp.set_transforms(newBegin * inverse(prevBegin), newEnd * inverse(prevEnd));
+  for (int k = 0; k < 3; ++k) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, interp, 0.0, stream, lc);
+  for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
+}
+
+//-----------------------------------------------------------------------------
+// AggregateFrames(CurrentFrames, true)  (:1512-1578)
+size_t lsb_slam::RegisteredFrame(DevBuf<lsb_point>& out)
+{
+  size_t total = 0;
+  for (size_t i = 0; i < NbCurrentFrames; ++i) total += FramePool[i]->n;
+  out.reserve(std::max<size_t>(total, 1), stream);
+  size_t start = 0;
+  for (size_t i = 0; i < NbCurrentFrames; ++i) {
+    DFrame& f = *FramePool[i];
+    if (f.n == 0) continue;
+    LSB_CUDA(cudaMemcpyAsync(out.p + start, f.d, f.n * sizeof(lsb_point), cudaMemcpyDeviceToDevice, stream));
+    const double timeOffset = StampToSec(f.stamp_us) - StampToSec(CurrentStamp);
+    const Iso3d baseToLidar = GetBaseToLidarOffset(f.device_id);
+    if (P.undistortion) {
+      Interpolator interp = WithinFrameMotion;
+      interp.set_transforms(Tworld * WithinFrameMotion.H0() * baseToLidar, Tworld * WithinFrameMotion.H1() * baseToLidar);
+      // point.time += timeOffset, then interpolator(point.time)
+      if (timeOffset != 0.0) dev_aggregate(out.p + start, f.n, timeOffset, Iso3d::identity(), false, stream, lc);
+      dev_undistort(out.p + start, f.n, interp, 0.0, stream, lc);
+    } else {
+      const Iso3d tf = Tworld * baseToLidar;
+      const bool ident = iso_is_approx(tf, Iso3d::identity());
+      if (!ident || timeOffset != 0.0) dev_aggregate(out.p + start, f.n, timeOffset, tf, !ident, stream, lc);
+    }
+    start += f.n;
+  }
+  return total;
+}

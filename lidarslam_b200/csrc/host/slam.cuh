@@ -1,0 +1,113 @@
+// lsb_slam: the per-sequence state machine behind the C ABI = LidarSlam::Slam's
+// per-frame pipeline (reference slam_lib/src/Slam.cxx:230-344 and the steps it
+// calls), with every cloud resident in device memory.  Pose bookkeeping (a few
+// 4x4 products per frame) stays on the host in FP64 (common/linalg.h).
+#pragma once
+#include <deque>
+#include <map>
+#include <memory>
+#include <vector>
+#include "../cuda/dev_util.h"
+#include "../cuda/extract.cuh"
+#include "../cuda/knn.cuh"
+#include "../cuda/match.cuh"
+#include "../cuda/map.cuh"
+#include "../common/linalg.h"
+#include "../common/lm_covariance.h"
+
+struct DCloud {
+  lsb::DevBuf<lsb_point> buf;
+  size_t n = 0;
+  void swap(DCloud& o) { buf.swap(o.buf); size_t t = n; n = o.n; o.n = t; }
+};
+
+struct lsb_slam {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  lsb::LaunchCounter lc;
+  lsb_params P;
+
+  std::map<int, std::unique_ptr<lsb::ExtractorGpu>> KeyPointsExtractors;   // Slam.h:500
+  std::map<int, lsb::Iso3d> BaseToLidarOffsets;                            // Slam.h:505
+  lsb::RollingGridGpu LocalMaps[3];                                        // Slam.h:553
+
+  lsb::Iso3d Tworld, PreviousTworld, Trelative;                            // Slam.h:461-467
+  lsb::Interpolator WithinFrameMotion;                                     // Slam.h:481
+  struct LoggedPose { lsb::Iso3d T; double time; };
+  std::deque<LoggedPose> LogTrajectory;                                    // Slam.h:487
+  lsb::Iso3d KfLastPose;
+  int KfCounter = 0;
+  unsigned NbrFrameProcessed = 0;
+  double CurrentTime = 0.;
+  uint64_t CurrentStamp = 0;
+  std::map<int, unsigned> PreviousFramesSeq;
+  double Latency = 0.;
+
+  // CurrentRawKeypoints and CurrentUndistortedKeypoints alias each other in the
+  // reference (Slam.cxx:984): one device storage.
+  DCloud CurrentKeypoints[3], PreviousKeypoints[3], CurrentWorldKeypoints[3];
+  bool WorldKeypointsValid[3] = {false, false, false};
+
+  // device copies of the input frames (the reference retains the input clouds, Slam.cxx:237)
+  struct DFrame { DCloud own; const lsb_point* d = nullptr; size_t n = 0; uint64_t stamp_us = 0; uint32_t seq = 0; int device_id = 0; };
+  std::vector<std::unique_ptr<DFrame>> FramePool;
+  size_t NbCurrentFrames = 0;
+
+  lsb::MatchWorkspace mw;
+  lsb::KnnGrid EgoGrids[2];
+  // match results kept for GetDebugArray (Slam.cxx:635-657)
+  struct StageDebug { lsb::DevBuf<uint8_t> status; lsb::DevBuf<double> weight; size_t off[4] = {0, 0, 0, 0}; int hist[3][LSB_MATCH_N_STATUS] = {}; };
+  StageDebug EgoDebug, LocDebug;
+  lsb_registration_error LocalizationUncertainty;
+  unsigned TotalMatchedKeypoints = 0;
+  float OverlapEstimation = -1.f;
+  lsb_frame_stats Stats;
+  int Warnings = 0;
+
+  // scratch
+  lsb::DevBuf<lsb_point> tmp_cloud;
+  lsb::DevBuf<unsigned long long> d_minmax;
+  lsb::PinnedBuf<unsigned long long> h_minmax;
+  lsb::DevBuf<float> d_bbox;
+  lsb::PinnedBuf<float> h_bbox;
+  lsb::DevBuf<float> tmp_f;
+  lsb::DevBuf<uint8_t> tmp_u8;
+  cudaEvent_t ev[6] = {};
+
+  explicit lsb_slam(int dev);
+  ~lsb_slam();
+  void Reset(bool resetLog);
+  void ClearMaps();
+  int AddFrames(int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq, bool on_device);
+  void SetWorldTransformFromGuess(const lsb::Iso3d& T);
+  lsb::Iso3d GetBaseToLidarOffset(int dev) const;
+  lsb::ExtractorGpu& Extractor(int dev);
+  // device clouds produced on demand
+  const DCloud& WorldKeypoints(int k);
+  size_t RegisteredFrame(lsb::DevBuf<lsb_point>& out);
+
+ private:
+  bool CheckFrames(int n_frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq);   // Slam.cxx:709-743
+  void ExtractKeypoints();                               // :746-810
+  void ComputeEgoMotion();                               // :813-972
+  void Localization();                                   // :975-1175
+  void UpdateMapsUsingTworld();                          // :1178-1222
+  void LogCurrentFrameState(double time);                // :1225-1264
+  lsb::Iso3d InterpolateScanPose(double time);           // :1271-1285
+  void InitUndistortion();                               // :1288-1319
+  void RefineUndistortion();                             // :1322-1352
+  void SaveDebug(StageDebug& d);
+};
+
+namespace lsb {
+// device helpers implemented in slam_kernels.cu
+void dev_transform(lsb_point* d_pts, size_t n, const Iso3d& T, cudaStream_t s, LaunchCounter& lc);                     // Utils::TransformPoint
+void dev_aggregate(lsb_point* d_pts, size_t n, double timeOffset, const Iso3d& T, bool applyT, cudaStream_t s, LaunchCounter& lc);
+void dev_undistort(lsb_point* d_pts, size_t n, const Interpolator& it, double timeOffset, cudaStream_t s, LaunchCounter& lc);   // Slam.cxx:1345-1350
+void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
+void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
+void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx);
+// bbox of (float)(T * p) in the pcl::transformPointCloud arithmetic (Slam.cxx:1026-1029); one sync
+void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,
+                          PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc);
+}  // namespace lsb
