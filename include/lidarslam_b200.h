@@ -155,7 +155,11 @@ typedef struct lsb_frame_stats {
   uint32_t n_map[3];
   uint32_t kernel_launches;            /* our kernels launched for this frame */
   float ms_extract, ms_ego, ms_localization, ms_map_update, ms_total; /* CUDA-event times */
-  float ms_knn;                        /* CUDA-event time inside match kernels (kNN+PCA) */
+  float ms_knn;                        /* CUDA-event time of the kNN kernel launches (needs lsb_set_profiling) */
+  uint32_t knn_launches;               /* kNN kernel launches this frame */
+  float ms_fit, ms_lm;                 /* model-fit kernels / LM evaluation kernels (needs lsb_set_profiling) */
+  uint32_t lm_launches;
+  uint64_t d2h_bytes, h2d_bytes;       /* bytes copied device->host / host->device inside the call */
 } lsb_frame_stats;
 
 typedef struct lsb_slam lsb_slam;      /* opaque: one CUDA stream + all device buffers of one sequence */
@@ -223,6 +227,9 @@ LSB_API long lsb_get_match_debug(lsb_slam* h, int stage, int type, uint8_t* stat
  * field: 0 sin_angle 1 saliency 2 depth_gap 3 intensity_gap 4-6 {edge,plane,blob}_keypoint 7-9 {edge,plane,blob}_validity */
 LSB_API long lsb_get_ke_debug(lsb_slam* h, int device_id, int field, float* out, long cap);
 LSB_API int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s);
+/* When on, CUDA events bracket every kNN / fit / LM kernel launch on the handle's
+ * stream and lsb_frame_stats.ms_knn / ms_fit / ms_lm are filled (small overhead). */
+LSB_API int lsb_set_profiling(lsb_slam* h, int on);
 LSB_API float lsb_get_overlap(const lsb_slam* h);                                              /* Slam::GetOverlapEstimation */
 LSB_API unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h);                       /* Slam.h TotalMatchedKeypoints */
 

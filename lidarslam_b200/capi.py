@@ -75,7 +75,9 @@ class FrameStats(C.Structure):
                 ("knn_queries", C.c_uint32), ("is_keyframe", C.c_uint32), ("n_map", C.c_uint32 * 3),
                 ("kernel_launches", C.c_uint32),
                 ("ms_extract", C.c_float), ("ms_ego", C.c_float), ("ms_localization", C.c_float),
-                ("ms_map_update", C.c_float), ("ms_total", C.c_float), ("ms_knn", C.c_float)]
+                ("ms_map_update", C.c_float), ("ms_total", C.c_float), ("ms_knn", C.c_float),
+                ("knn_launches", C.c_uint32), ("ms_fit", C.c_float), ("ms_lm", C.c_float), ("lm_launches", C.c_uint32),
+                ("d2h_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64)]
 
 
 def _ptr(a):

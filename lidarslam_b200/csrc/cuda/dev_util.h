@@ -7,6 +7,7 @@
 #include <cstddef>
 #include <cstdio>
 #include <string>
+#include <vector>
 #include <stdexcept>
 #include "../../../include/lidarslam_b200.h"
 
@@ -75,6 +76,38 @@ struct PinnedBuf {
 };
 
 inline unsigned div_up(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+// CUDA-event bracket around selected kernel launches (lsb_set_profiling).
+struct KernelTimer {
+  bool enabled = false;
+  std::vector<cudaEvent_t> ev;
+  size_t used = 0;
+  unsigned launches = 0;
+  ~KernelTimer() { for (auto e : ev) cudaEventDestroy(e); }
+  void begin(cudaStream_t s)
+  {
+    ++launches;
+    if (!enabled) return;
+    while (used + 2 > ev.size()) { cudaEvent_t e; LSB_CUDA(cudaEventCreate(&e)); ev.push_back(e); }
+    LSB_CUDA(cudaEventRecord(ev[used], s));
+  }
+  void end(cudaStream_t s)
+  {
+    if (!enabled) return;
+    LSB_CUDA(cudaEventRecord(ev[used + 1], s));
+    used += 2;
+  }
+  // call after the stream is synchronised; returns ms and resets
+  float collect(unsigned* n_launches)
+  {
+    float total = 0.f;
+    for (size_t i = 0; i + 1 < used; i += 2) { float ms = 0.f; cudaEventElapsedTime(&ms, ev[i], ev[i + 1]); total += ms; }
+    used = 0;
+    if (n_launches) *n_launches = launches;
+    launches = 0;
+    return total;
+  }
+};
 
 // Launch counter of one handle (lsb_frame_stats.kernel_launches).
 struct LaunchCounter {

@@ -312,16 +312,21 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
   const unsigned kk = (type == LSB_EDGE) ? mp.edge_nb_neighbors : (type == LSB_PLANE ? mp.plane_nb_neighbors : mp.blob_nb_neighbors);
   if (kk > (unsigned)KNN_MAX_K) throw CudaError(LSB_E_CAPACITY, "more than 32 neighbours requested");
   const int k = std::max(1, (int)kk);
+  t_knn.begin(s);
   target.search_points(d_kp, nk, prior, k, nn_idx.p, nn_d2.p, nn_found.p, s, lc);
+  t_knn.end(s);
   const int NQ = (int)nk;
+  t_fit.begin(s);
   if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
   else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
   else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
   LSB_LAUNCH_CHECK(); lc.add();
+  t_fit.end(s);
 }
 
 void MatchWorkspace::read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s)
 {
+  d2h_bytes += 3 * LSB_MATCH_N_STATUS * sizeof(int);
   LSB_CUDA(cudaMemcpyAsync(h_hist.p, hist.p, 3 * LSB_MATCH_N_STATUS * sizeof(int), cudaMemcpyDeviceToHost, s));
   LSB_CUDA(cudaStreamSynchronize(s));
   for (int t = 0; t < 3; ++t)
@@ -335,10 +340,14 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   part_a.reserve((size_t)nchunks * LSB_LM_NSUM, s); part_b.reserve((size_t)nchunks * LSB_LM_NSUM, s);
   lm_state.reserve(1, s); lm_counter.reserve(1, s); h_lm.reserve(1);
   k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d); LSB_LAUNCH_CHECK(); lc.add();
+  t_lm.begin(s);
   for (int e = 0; e <= max_iter; ++e) {
     k_lm_eval<<<nchunks, LSB_LM_CHUNK, 0, s>>>(records.p, n, nchunks, saturation, lm_state.p, part_a.p, part_b.p, lm_counter.p, e == 0 ? 1 : 0);
     LSB_LAUNCH_CHECK(); lc.add();
   }
+  t_lm.end(s);
+  t_lm.launches += (unsigned)max_iter;
+  d2h_bytes += sizeof(LmState);
   LSB_CUDA(cudaMemcpyAsync(h_lm.p, lm_state.p, sizeof(LmState), cudaMemcpyDeviceToHost, s));
   LSB_CUDA(cudaStreamSynchronize(s));
   return *h_lm.p;

@@ -22,6 +22,8 @@ struct MatchWorkspace {
   DevBuf<unsigned> lm_counter;      // [1]
   PinnedBuf<int> h_hist;
   PinnedBuf<LmState> h_lm;
+  KernelTimer t_knn, t_fit, t_lm;   // lsb_set_profiling
+  size_t d2h_bytes = 0;
   size_t total = 0;                 // records of the current iteration
   size_t off[4] = {0, 0, 0, 0};     // offsets of the three types
 

@@ -148,6 +148,15 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   cudaEventElapsedTime(&Stats.ms_map_update, ev[3], ev[4]);
   cudaEventElapsedTime(&Stats.ms_total, ev[0], ev[4]);
   Stats.kernel_launches = lc.n - launches0;
+  Stats.ms_knn = mw.t_knn.collect(&Stats.knn_launches);
+  Stats.ms_fit = mw.t_fit.collect(nullptr);
+  Stats.ms_lm = mw.t_lm.collect(&Stats.lm_launches);
+  // device->host: match histograms + LM states (counted by the workspace) and the small per-stage
+  // counters (keypoint counts, time range, bboxes, map counters: < 64 B each, bounded here)
+  Stats.d2h_bytes = mw.d2h_bytes + 64 * 16;
+  mw.d2h_bytes = 0;
+  Stats.h2d_bytes = 0;
+  if (!on_device) for (int i = 0; i < n_frames; ++i) Stats.h2d_bytes += n[i] * sizeof(lsb_point);
   Latency = Stats.ms_total * 1e-3;
   NbrFrameProcessed++;
   return Warnings;

@@ -1,0 +1,126 @@
+"""GPU parity tests, stage by stage, through the C ABI (kernel-level entry points)
+against the CPU oracle on identical seeded inputs.  Bit-exact for labels, keypoints,
+neighbour indices, map contents; pose within 1e-6 (north star)."""
+import numpy as np
+import pytest
+
+from lidarslam_b200 import capi
+
+pytestmark = pytest.mark.gpu
+
+
+def _frame(synth, sensor="tiny", idx=0, seed=1234):
+    seq = synth.Sequence(scene_seed=seed)
+    return seq.frame(synth.sensor(sensor), idx)
+
+
+@pytest.mark.parametrize("sensor", ["tiny", "vlp16", "hdl64"])
+def test_extractor_bit_exact(gpu, oracle_lib, synth, sensor):
+    pts, _, _ = _frame(synth, sensor)
+    g, o = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
+    lg, cg, kg = g.ExtractKeypoints(pts)
+    lo, co, ko = o.ExtractKeypoints(pts)
+    assert g.GetExtractorParams().azimuthal_resolution == o.GetExtractorParams().azimuthal_resolution
+    for f, name in enumerate(["sin_angle", "saliency", "depth_gap", "intensity_gap", "edge", "plane", "blob", "edge_valid", "plane_valid", "blob_valid"]):
+        a, b = g.GetKeDebug(f), o.GetKeDebug(f)
+        bad = np.flatnonzero(a.view(np.uint32) != b.view(np.uint32))
+        assert bad.size == 0, "%s differs at %d points, first %s: gpu %s oracle %s" % (name, bad.size, bad[:5], a[bad[:5]], b[bad[:5]])
+    assert cg == co
+    assert np.array_equal(lg, lo)
+    for k in range(3):
+        assert kg[k].tobytes() == ko[k].tobytes()
+    assert co[0] > 0 and co[1] > 0 and co[2] > 0
+
+
+def test_extractor_edge_cases(gpu, oracle_lib, synth):
+    pts, _, _ = _frame(synth, "tiny")
+    g, o = gpu(), oracle_lib.Oracle(nb_threads=2)
+    # ragged rings: drop most of ring 3 (almost empty scan line), shuffle arrival order of ring 5, duplicate points
+    keep = ~((pts["laser_id"] == 3) & (np.arange(len(pts)) % 97 != 0))
+    p2 = pts[keep].copy()
+    p2 = np.concatenate([p2, p2[:40]])
+    lg, cg, kg = g.ExtractKeypoints(p2)
+    lo, co, ko = o.ExtractKeypoints(p2)
+    assert cg == co and np.array_equal(lg, lo)
+    for k in range(3):
+        assert kg[k].tobytes() == ko[k].tobytes()
+    # too small input: every ring is "almost empty"
+    lg, cg, _ = g.ExtractKeypoints(pts[:40])
+    lo, co, _ = o.ExtractKeypoints(pts[:40])
+    assert cg == co == [0, 0, 0] and np.array_equal(lg, lo)
+
+
+@pytest.mark.parametrize("k", [1, 5, 10])
+def test_knn_bit_exact(gpu, oracle_lib, synth, k):
+    pts, _, _ = _frame(synth, "vlp16")
+    rng = np.random.default_rng(7)
+    cloud = pts[rng.permutation(len(pts))[:6000]].copy()
+    q = np.stack([cloud["x"], cloud["y"], cloud["z"]], 1)[:3000] + rng.normal(0, 0.3, (3000, 3)).astype(np.float32)
+    q = np.concatenate([q, [[500., 500., 50.], [-1000., 3., 2.]], q[:5]]).astype(np.float32)   # far outliers + exact duplicates
+    cloud[10:20] = cloud[0]                                                                      # ties at equal distance
+    g, o = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
+    ig, dg = g.KnnSearch(cloud, q, k)
+    io, do = o.KnnSearch(cloud, q, k)
+    assert np.array_equal(ig, io)
+    assert np.array_equal(dg.view(np.uint32), do.view(np.uint32))
+    # fewer points than k
+    ig, dg = g.KnnSearch(cloud[:3], q[:50], 5)
+    io, do = o.KnnSearch(cloud[:3], q[:50], 5)
+    assert np.array_equal(ig, io) and np.array_equal(dg.view(np.uint32), do.view(np.uint32))
+
+
+def test_undistort_bit_exact(gpu, oracle_lib, synth):
+    pts, _, _ = _frame(synth, "tiny")
+    H0 = np.eye(4)
+    c, s = np.cos(0.02), np.sin(0.02)
+    H1 = np.array([[c, -s, 0, 0.8], [s, c, 0, 0.05], [0, 0, 1, -0.01], [0, 0, 0, 1.]])
+    g, o = gpu(), oracle_lib.Oracle()
+    a = g.Undistort(pts, H0, H1, -0.1, 0.0)
+    b = o.Undistort(pts, H0, H1, -0.1, 0.0)
+    assert a.tobytes() == b.tobytes()
+    assert a.tobytes() != pts.tobytes()
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+def test_map_add_bit_exact(gpu, oracle_lib, synth, mode):
+    g, o = gpu(), oracle_lib.Oracle()
+    for s in (g, o):
+        for k in range(3):
+            s.SetVoxelGridSamplingMode(k, mode)
+    seq = synth.Sequence()
+    sens = synth.sensor("vlp16")
+    for i in range(3):
+        pts, T, _ = seq.frame(sens, i * 40)
+        w = pts.copy()
+        xyz = np.stack([pts["x"], pts["y"], pts["z"]], 1).astype(np.float64) @ T[:3, :3].T + T[:3, 3]
+        w["x"], w["y"], w["z"] = xyz[:, 0].astype(np.float32), xyz[:, 1].astype(np.float32), xyz[:, 2].astype(np.float32)
+        for k, leaf in ((0, 0.3), (1, 0.6)):
+            g.MapAdd(k, w[k::2], False, 0.1 * i)
+            o.MapAdd(k, w[k::2], False, 0.1 * i)
+            a, b = g.GetMap(k), o.GetMap(k)
+            assert len(a) == len(b) and len(a) > 1000
+            assert a.tobytes() == b.tobytes(), "map %d differs after add %d" % (k, i)
+
+
+def test_match_and_solve(gpu, oracle_lib, synth):
+    g, o = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
+    seq = synth.Sequence()
+    sens = synth.sensor("vlp16")
+    p0, T0, _ = seq.frame(sens, 0)
+    p1, T1, _ = seq.frame(sens, 1)
+    _, _, k0 = o.ExtractKeypoints(p0)
+    _, _, k1 = o.ExtractKeypoints(p1)
+    prior = np.linalg.inv(T0) @ T1
+    prior[:3, 3] += [0.05, -0.03, 0.01]
+    for single in (0, 1):
+        mp = capi.MatchParams(single, 5.0, 8 if single else 10, 3 if single else 4, 0.2, 5, 0.04, 0.2, 10, 2.0)
+        rg = g.MatchAndSolve(k1, k0, mp, 15, prior)
+        ro = o.MatchAndSolve(k1, k0, mp, 15, prior)
+        assert rg["rc"] == ro["rc"] == 0
+        assert np.array_equal(rg["status"], ro["status"])
+        assert np.array_equal(rg["weight"].view(np.uint64), ro["weight"].view(np.uint64))
+        assert (rg["status"] == 0).sum() > 500
+        assert rg["iterations"] == ro["iterations"] and rg["accepted"] == ro["accepted"]
+        assert np.abs(rg["pose"] - ro["pose"]).max() <= 1e-9
+        assert abs(rg["cost"] - ro["cost"]) <= 1e-9 * max(1.0, abs(ro["cost"]))
+        assert np.allclose(np.array(rg["err"].covariance), np.array(ro["err"].covariance), rtol=1e-6, atol=1e-12)
