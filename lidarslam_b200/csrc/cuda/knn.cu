@@ -132,8 +132,9 @@ __device__ __forceinline__ void scan_range(TopK<KMAX>& tk, const float4* __restr
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
-      const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, int32_t* __restrict__ idx_out,
-      float* __restrict__ d2_out, int32_t* __restrict__ nfound_out)
+      const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped,
+      int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list,
+      unsigned* __restrict__ unres_count)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nq) return;
@@ -164,6 +165,7 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
   const int rfirst = max(max(max(-cx, cx - (gp.nx - 1)), max(-cy, cy - (gp.ny - 1))), max(max(-cz, cz - (gp.nz - 1)), 0));
   int r = max(1, rfirst);
   bool first = true;
+  bool unresolved = false;
   if (qx == qx && qy == qy && qz == qz) {
     while (true) {
       const int z0 = max(0, cz - r), z1 = min(gp.nz - 1, cz + r);
@@ -189,8 +191,16 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
         if (bound > 0.f && tk.d[KMAX - 1] < bound * bound) break;
       }
       ++r;
+      if (r > rcap) { unresolved = true; break; }
     }
   }
+  if (unresolved && !capped) {
+    // exact mode: hand the query to the brute-force kernel (its result overwrites this slot)
+    unres_list[atomicAdd(unres_count, 1u)] = i;
+    return;
+  }
+  // capped mode, unresolved: every point within the cap distance has been visited and the
+  // k-th neighbour is farther than the cap; the caller only needs "k found, too far".
   int nf = 0;
 #pragma unroll
   for (int t = 0; t < KMAX; ++t) {
@@ -201,16 +211,91 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
       nf += ok ? 1 : 0;
     }
   }
+  if (unresolved && m >= k) nf = k;
   if (nfound_out) nfound_out[i] = nf;
 }
 
+// Brute-force exact kNN for the few queries the grid walk gave up on (neighbours far
+// away): one warp per query, each lane keeps the top-K of its strided share of ALL
+// points, then K rounds of warp arg-min merge the 32 sorted lists.
+template <int KMAX, bool FROM_POINTS>
+__global__ void __launch_bounds__(128)
+k_knn_brute(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, const float4* __restrict__ sorted, int m,
+            int k, int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
+            const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
+{
+  const int lane = threadIdx.x & 31;
+  const unsigned count = unres_count[0];
+  while (true) {
+    unsigned slot = 0;
+    if (lane == 0) slot = atomicAdd(unres_count + 1, 1u);
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (slot >= count) break;
+    const int i = unres_list[slot];
+    float qx, qy, qz;
+    if (FROM_POINTS) {
+      const float4 p = reinterpret_cast<const float4*>(kp)[2 * (size_t)i];
+      const Vec3d w = apply(prior, Vec3d((double)p.x, (double)p.y, (double)p.z));
+      qx = (float)w.x; qy = (float)w.y; qz = (float)w.z;
+    } else {
+      qx = q_xyz[3 * (size_t)i]; qy = q_xyz[3 * (size_t)i + 1]; qz = q_xyz[3 * (size_t)i + 2];
+    }
+    TopK<KMAX> tk;
+    tk.init();
+    for (int p = lane; p < m; p += 32) {
+      const float4 s = __ldg(sorted + p);
+      const float dx = qx - s.x, dy = qy - s.y, dz = qz - s.z;
+      tk.offer((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w));
+    }
+    int nf = 0;
+    for (int t = 0; t < k; ++t) {
+      float bd = tk.d[0];
+      int bi = tk.id[0];
+#pragma unroll
+      for (int off = 16; off; off >>= 1) {
+        const float od = __shfl_xor_sync(0xffffffffu, bd, off);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+        if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; }
+      }
+      const bool ok = bd < INFINITY;
+      if (ok && tk.id[0] == bi && tk.d[0] == bd) {   // the winning lane pops its head
+#pragma unroll
+        for (int u = 0; u + 1 < KMAX; ++u) { tk.d[u] = tk.d[u + 1]; tk.id[u] = tk.id[u + 1]; }
+        tk.d[KMAX - 1] = INFINITY; tk.id[KMAX - 1] = INT_MAX;
+      }
+      if (lane == 0) {
+        idx_out[(size_t)i * k + t] = ok ? bi : -1;
+        d2_out[(size_t)i * k + t] = ok ? bd : INFINITY;
+      }
+      nf += ok ? 1 : 0;
+    }
+    if (lane == 0 && nfound_out) nfound_out[i] = nf;
+  }
+}
+
 template <bool FROM_POINTS>
-void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso3d& prior, size_t nq, int k, int32_t* idx, float* d2,
-                int32_t* nf, cudaStream_t s)
+void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso3d& prior, size_t nq, int k, float cap_dist, int32_t* idx,
+                float* d2, int32_t* nf, cudaStream_t s, LaunchCounter& lc)
 {
   const unsigned G = div_up(nq, 128);
-  const int NQ = (int)nq;
-#define LSB_KNN_CASE(KM) k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, idx, d2, nf)
+  const int NQ = (int)nq, M = (int)g.m;
+  const int capped = cap_dist >= 0.f ? 1 : 0;
+  // rings after which the grid walk stops: capped => everything within cap_dist has been visited
+  // (r*cell minus the rounding margin exceeds cap_dist); exact => hand over to brute force
+  const float reach = capped ? cap_dist : 5.0f;
+  const int rcap = std::max(3, (int)std::ceil(reach / g.gp.cell) + 1);
+  g.unres_list.reserve(nq, s); g.unres_count.reserve(2, s);
+  if (!capped) LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 2 * sizeof(unsigned), s));
+#define LSB_KNN_CASE(KM)                                                                                                              \
+  do {                                                                                                                                \
+    k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, idx, d2, nf,       \
+                                             g.unres_list.p, g.unres_count.p);                                                        \
+    LSB_LAUNCH_CHECK(); lc.add();                                                                                                     \
+    if (!capped) {                                                                                                                    \
+      k_knn_brute<KM, FROM_POINTS><<<296, 128, 0, s>>>(q, kp, prior, g.sorted.p, M, k, idx, d2, nf, g.unres_list.p, g.unres_count.p); \
+      LSB_LAUNCH_CHECK(); lc.add();                                                                                                   \
+    }                                                                                                                                 \
+  } while (0)
   if (k <= 1) LSB_KNN_CASE(1);
   else if (k <= 5) LSB_KNN_CASE(5);
   else if (k <= 8) LSB_KNN_CASE(8);
@@ -218,7 +303,6 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   else if (k <= 16) LSB_KNN_CASE(16);
   else LSB_KNN_CASE(32);
 #undef LSB_KNN_CASE
-  LSB_LAUNCH_CHECK();
 }
 
 __global__ void k_fill_empty(int32_t* idx, float* d2, int32_t* nf, size_t total, size_t nq)
@@ -282,7 +366,7 @@ void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float
   k_cell_start<<<div_up((size_t)ncells + 1, TPB), TPB, 0, s>>>(key_b.p, M, ncells, cell_start.p); LSB_LAUNCH_CHECK(); lc.add();
 }
 
-void KnnGrid::search(const float* d_q, size_t nq, int k, int32_t* d_idx, float* d_d2, int32_t* d_nf, cudaStream_t s, LaunchCounter& lc) const
+void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t* d_idx, float* d_d2, int32_t* d_nf, cudaStream_t s, LaunchCounter& lc) const
 {
   if (nq == 0) return;
   if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
@@ -290,11 +374,11 @@ void KnnGrid::search(const float* d_q, size_t nq, int k, int32_t* d_idx, float* 
     k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
-  launch_knn<false>(*this, d_q, nullptr, Iso3d::identity(), nq, k, d_idx, d_d2, d_nf, s); lc.add();
+  launch_knn<false>(*this, d_q, nullptr, Iso3d::identity(), nq, k, cap_dist, d_idx, d_d2, d_nf, s, lc);
 }
 
-void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, int32_t* d_idx, float* d_d2, int32_t* d_nf,
-                            cudaStream_t s, LaunchCounter& lc) const
+void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, float cap_dist, int32_t* d_idx, float* d_d2,
+                            int32_t* d_nf, cudaStream_t s, LaunchCounter& lc) const
 {
   if (nq == 0) return;
   if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
@@ -302,7 +386,7 @@ void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior
     k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
-  launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, d_idx, d_d2, d_nf, s); lc.add();
+  launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, cap_dist, d_idx, d_d2, d_nf, s, lc);
 }
 
 }  // namespace lsb

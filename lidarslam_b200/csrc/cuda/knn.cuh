@@ -26,6 +26,8 @@ struct KnnGrid {
   DevBuf<float4> sorted;          // cell-major points: (x, y, z, bits of the cloud index)
   DevBuf<uint32_t> cell_start;    // [ncells + 1] prefix offsets into sorted
   DevBuf<unsigned char> cub_tmp;
+  mutable DevBuf<int32_t> unres_list;    // queries handed to the brute-force kernel
+  mutable DevBuf<unsigned> unres_count;  // [2]: count, cursor
   DevBuf<float> d_bbox;           // [6]
   PinnedBuf<float> h_bbox;
 
@@ -37,11 +39,15 @@ struct KnnGrid {
 
   // kNN of nq float queries (xyz packed).  idx_out/d2_out: [nq * k], missing
   // entries -1 / +inf.  nfound_out may be nullptr.
-  void search(const float* d_queries_xyz, size_t nq, int k, int32_t* d_idx_out, float* d_d2_out, int32_t* d_nfound_out,
+  // cap_dist < 0: exact for every query (grid walk, then brute force for queries whose
+  // neighbours are far away).  cap_dist >= 0: exact for every query whose k-th neighbour
+  // lies within cap_dist; the others report nfound = min(k, m) with d2[k-1] > cap_dist^2
+  // (possibly +inf), which is all the plane / blob matchers need (NEIGHBORS_TOO_FAR).
+  void search(const float* d_queries_xyz, size_t nq, int k, float cap_dist, int32_t* d_idx_out, float* d_d2_out, int32_t* d_nfound_out,
               cudaStream_t s, LaunchCounter& lc) const;
   // kNN of the keypoints kp[0..nq) moved by `prior` in double then cast to float
   // (KeypointsMatcher.cxx:118 + KDTreePCLAdaptor.h:96-101).
-  void search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, int32_t* d_idx_out, float* d_d2_out,
+  void search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, float cap_dist, int32_t* d_idx_out, float* d_d2_out,
                      int32_t* d_nfound_out, cudaStream_t s, LaunchCounter& lc) const;
 };
 

@@ -313,7 +313,10 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
   if (kk > (unsigned)KNN_MAX_K) throw CudaError(LSB_E_CAPACITY, "more than 32 neighbours requested");
   const int k = std::max(1, (int)kk);
   t_knn.begin(s);
-  target.search_points(d_kp, nk, prior, k, nn_idx.p, nn_d2.p, nn_found.p, s, lc);
+  // planes / blobs only need neighbours within MaxNeighborsDistance (else NEIGHBORS_TOO_FAR);
+  // the line neighbourhood selection needs the exact k nearest whatever their distance
+  const float cap = (type == LSB_EDGE) ? -1.f : (float)mp.max_neighbors_distance * 1.0001f + 1e-3f;
+  target.search_points(d_kp, nk, prior, k, cap, nn_idx.p, nn_d2.p, nn_found.p, s, lc);
   t_knn.end(s);
   const int NQ = (int)nk;
   t_fit.begin(s);

@@ -131,13 +131,15 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   LSB_CUDA(cudaEventRecord(ev[2], stream));
   Localization();
   LSB_CUDA(cudaEventRecord(ev[3], stream));
+  uint32_t n_submap[3];
+  for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // the map update invalidates the submaps
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
   LSB_CUDA(cudaEventRecord(ev[4], stream));
   LSB_CUDA(cudaEventSynchronize(ev[4]));
   LogCurrentFrameState(CurrentTime);
   for (int k = 0; k < 3; ++k) {
     Stats.n_keypoints[k] = (uint32_t)CurrentKeypoints[k].n;
-    Stats.n_submap[k] = (uint32_t)LocalMaps[k].n_submap;
+    Stats.n_submap[k] = n_submap[k];
     Stats.n_map[k] = LocalMaps[k].Size();
     Stats.n_matches[k] = (uint32_t)LocDebug.hist[k][LSB_MATCH_SUCCESS];
     Stats.ego_n_matches[k] = (uint32_t)EgoDebug.hist[k][LSB_MATCH_SUCCESS];
