@@ -26,8 +26,7 @@ namespace lsb {
 #define LSB_LM_NSUM 28
 // Canonical reduction order (GPU and oracle): records in chunks of 256; inside a
 // chunk each group of 32 consecutive records is folded with offsets 16,8,4,2,1,
-// the 8 group sums are added in order, and chunk sums are combined by a
-// binary tree over adjacent chunks.
+// the 8 group sums are added in order, and the chunk sums are added in chunk order.
 #define LSB_LM_CHUNK 256
 
 // One residual record, 16 doubles (A row-major, P, X, weight).  weight < 0 marks

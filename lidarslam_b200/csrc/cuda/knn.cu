@@ -129,78 +129,85 @@ __device__ __forceinline__ void scan_range(TopK<KMAX>& tk, const float4* __restr
   }
 }
 
-template <int KMAX, bool FROM_POINTS>
-__global__ void __launch_bounds__(128)
-k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
-      const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped,
-      int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list,
-      unsigned* __restrict__ unres_count)
-{
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nq) return;
+struct QueryCell {
   float qx, qy, qz;
+  int cx, cy, cz;
+  float minoff;
+  int rcover, rfirst;
+  bool finite;
+};
+
+template <bool FROM_POINTS>
+__device__ __forceinline__ QueryCell make_query(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, const Iso3d& prior, int i,
+                                                const KnnGridParams& gp)
+{
+  QueryCell q;
   if (FROM_POINTS) {
     const float4 p = reinterpret_cast<const float4*>(kp)[2 * (size_t)i];
     const Vec3d w = apply(prior, Vec3d((double)p.x, (double)p.y, (double)p.z));
-    qx = (float)w.x; qy = (float)w.y; qz = (float)w.z;
+    q.qx = (float)w.x; q.qy = (float)w.y; q.qz = (float)w.z;
   } else {
-    qx = q_xyz[3 * (size_t)i]; qy = q_xyz[3 * (size_t)i + 1]; qz = q_xyz[3 * (size_t)i + 2];
+    q.qx = q_xyz[3 * (size_t)i]; q.qy = q_xyz[3 * (size_t)i + 1]; q.qz = q_xyz[3 * (size_t)i + 2];
   }
-  TopK<KMAX> tk;
-  tk.init();
   const float cell = gp.cell;
   // unclamped cell coordinates of the query (bounded so that the int conversion is defined)
-  const float fx = fminf(fmaxf(floorf((qx - gp.ox) / cell), -1.0e6f), 1.0e6f);
-  const float fy = fminf(fmaxf(floorf((qy - gp.oy) / cell), -1.0e6f), 1.0e6f);
-  const float fz = fminf(fmaxf(floorf((qz - gp.oz) / cell), -1.0e6f), 1.0e6f);
-  const int cx = (int)fx, cy = (int)fy, cz = (int)fz;
-  float minoff;
-  {
-    const float lx = gp.ox + fx * cell, ly = gp.oy + fy * cell, lz = gp.oz + fz * cell;
-    minoff = fminf(fminf(fminf(qx - lx, lx + cell - qx), fminf(qy - ly, ly + cell - qy)), fminf(qz - lz, lz + cell - qz));
-    minoff = fmaxf(minoff, 0.f);
-  }
+  const float fx = fminf(fmaxf(floorf((q.qx - gp.ox) / cell), -1.0e6f), 1.0e6f);
+  const float fy = fminf(fmaxf(floorf((q.qy - gp.oy) / cell), -1.0e6f), 1.0e6f);
+  const float fz = fminf(fmaxf(floorf((q.qz - gp.oz) / cell), -1.0e6f), 1.0e6f);
+  q.cx = (int)fx; q.cy = (int)fy; q.cz = (int)fz;
+  const float lx = gp.ox + fx * cell, ly = gp.oy + fy * cell, lz = gp.oz + fz * cell;
+  q.minoff = fminf(fminf(fminf(q.qx - lx, lx + cell - q.qx), fminf(q.qy - ly, ly + cell - q.qy)), fminf(q.qz - lz, lz + cell - q.qz));
+  q.minoff = fmaxf(q.minoff, 0.f);
   // radius at which the cube covers the whole grid / first touches it
-  const int rcover = max(max(max(cx, gp.nx - 1 - cx), max(cy, gp.ny - 1 - cy)), max(cz, gp.nz - 1 - cz));
-  const int rfirst = max(max(max(-cx, cx - (gp.nx - 1)), max(-cy, cy - (gp.ny - 1))), max(max(-cz, cz - (gp.nz - 1)), 0));
-  int r = max(1, rfirst);
-  bool first = true;
-  bool unresolved = false;
-  if (qx == qx && qy == qy && qz == qz) {
-    while (true) {
-      const int z0 = max(0, cz - r), z1 = min(gp.nz - 1, cz + r);
-      const int y0 = max(0, cy - r), y1 = min(gp.ny - 1, cy + r);
-      const int x0 = max(0, cx - r), x1 = min(gp.nx - 1, cx + r);
-      for (int z = z0; z <= z1; ++z) {
-        const bool zface = (z == cz - r) || (z == cz + r);
-        for (int y = y0; y <= y1; ++y) {
-          const int base = (z * gp.ny + y) * gp.nx;
-          if (first || zface || y == cy - r || y == cy + r) {
-            if (x0 <= x1) scan_range(tk, sorted, cell_start[base + x0], cell_start[base + x1 + 1], qx, qy, qz);
-          } else {
-            if (cx - r >= 0 && cx - r < gp.nx) scan_range(tk, sorted, cell_start[base + cx - r], cell_start[base + cx - r + 1], qx, qy, qz);
-            if (cx + r >= 0 && cx + r < gp.nx) scan_range(tk, sorted, cell_start[base + cx + r], cell_start[base + cx + r + 1], qx, qy, qz);
-          }
-        }
-      }
-      first = false;
-      if (r >= rcover) break;
-      if (tk.d[KMAX - 1] < INFINITY) {
-        const float reach = (float)r * cell + minoff;
-        const float bound = reach - (1.0e-3f + 1.0e-4f * (reach + cell));
-        if (bound > 0.f && tk.d[KMAX - 1] < bound * bound) break;
-      }
-      ++r;
-      if (r > rcap) { unresolved = true; break; }
+  q.rcover = max(max(max(q.cx, gp.nx - 1 - q.cx), max(q.cy, gp.ny - 1 - q.cy)), max(q.cz, gp.nz - 1 - q.cz));
+  q.rfirst = max(max(max(-q.cx, q.cx - (gp.nx - 1)), max(-q.cy, q.cy - (gp.ny - 1))), max(max(-q.cz, q.cz - (gp.nz - 1)), 0));
+  q.finite = (q.qx == q.qx) && (q.qy == q.qy) && (q.qz == q.qz);
+  return q;
+}
+
+// every point outside the completed cube of radius r is farther than this (minus a rounding margin)
+__device__ __forceinline__ bool resolved_at(float kth_d2, int r, float cell, float minoff)
+{
+  if (!(kth_d2 < INFINITY)) return false;
+  const float reach = (float)r * cell + minoff;
+  const float bound = reach - (1.0e-3f + 1.0e-4f * (reach + cell));
+  return bound > 0.f && kth_d2 < bound * bound;
+}
+
+// Phase 1: one thread per query scans the 3x3x3 cube around its cell (9 contiguous
+// row ranges, their 18 bounds loaded up front).  Queries it cannot settle go to the
+// warp-per-query kernel below.
+template <int KMAX, bool FROM_POINTS>
+__global__ void __launch_bounds__(128)
+k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
+      const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, int32_t* __restrict__ idx_out,
+      float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nq) return;
+  const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
+  TopK<KMAX> tk;
+  tk.init();
+  bool done = !q.finite;          // NaN query: nothing found, as an exact search would
+  if (q.finite && q.rfirst <= 1) {
+    uint32_t rb[9], re[9];
+    const int x0 = max(0, q.cx - 1), x1 = min(gp.nx - 1, q.cx + 1);
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const int z = q.cz + t / 3 - 1, y = q.cy + t % 3 - 1;
+      const bool in = z >= 0 && z < gp.nz && y >= 0 && y < gp.ny && x0 <= x1;
+      const int base = (z * gp.ny + y) * gp.nx;
+      rb[t] = in ? __ldg(cell_start + base + x0) : 0u;
+      re[t] = in ? __ldg(cell_start + base + x1 + 1) : 0u;
     }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) scan_range(tk, sorted, rb[t], re[t], q.qx, q.qy, q.qz);
+    done = (q.rcover <= 1) || resolved_at(tk.d[KMAX - 1], 1, gp.cell, q.minoff);
   }
-  if (unresolved && !capped) {
-    // exact mode: hand the query to the brute-force kernel (its result overwrites this slot)
+  if (!done) {
     unres_list[atomicAdd(unres_count, 1u)] = i;
     return;
   }
-  // capped mode, unresolved: every point within the cap distance has been visited and the
-  // k-th neighbour is farther than the cap; the caller only needs "k found, too far".
   int nf = 0;
 #pragma unroll
   for (int t = 0; t < KMAX; ++t) {
@@ -211,18 +218,52 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
       nf += ok ? 1 : 0;
     }
   }
-  if (unresolved && m >= k) nf = k;
   if (nfound_out) nfound_out[i] = nf;
 }
 
-// Brute-force exact kNN for the few queries the grid walk gave up on (neighbours far
-// away): one warp per query, each lane keeps the top-K of its strided share of ALL
-// points, then K rounds of warp arg-min merge the 32 sorted lists.
+// merges the 32 per-lane sorted lists: round t yields the t-th smallest (d2, id) of the
+// warp.  Writes the first k; returns the number found and the KMAX-th distance.
+template <int KMAX>
+__device__ __forceinline__ int warp_merge_write(TopK<KMAX>& tk, int k, int lane, int32_t* __restrict__ idx_row, float* __restrict__ d2_row,
+                                                float& kmax_d2)
+{
+  int nf = 0;
+  kmax_d2 = INFINITY;
+#pragma unroll 1
+  for (int t = 0; t < KMAX; ++t) {
+    float bd = tk.d[0];
+    int bi = tk.id[0];
+#pragma unroll
+    for (int off = 16; off; off >>= 1) {
+      const float od = __shfl_xor_sync(0xffffffffu, bd, off);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+      if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; }
+    }
+    const bool ok = bd < INFINITY;
+    if (ok && tk.id[0] == bi && tk.d[0] == bd) {   // the winning lane pops its head
+#pragma unroll
+      for (int u = 0; u + 1 < KMAX; ++u) { tk.d[u] = tk.d[u + 1]; tk.id[u] = tk.id[u + 1]; }
+      tk.d[KMAX - 1] = INFINITY; tk.id[KMAX - 1] = INT_MAX;
+    }
+    if (t < k) {
+      if (lane == 0) { idx_row[t] = ok ? bi : -1; d2_row[t] = ok ? bd : INFINITY; }
+      nf += ok ? 1 : 0;
+    }
+    if (t == KMAX - 1) kmax_d2 = bd;
+  }
+  return nf;
+}
+
+// Phase 2: one warp per unsettled query.  The lanes share the rows of the cube of radius
+// rcap (each row one contiguous range), keep per-lane top-K lists and merge them.  If even
+// that cube does not settle the query: capped mode reports "k-th neighbour beyond the cap",
+// exact mode falls back to a brute-force pass over all m points (rare: isolated queries).
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
-k_knn_brute(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, const float4* __restrict__ sorted, int m,
-            int k, int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
-            const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
+k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
+           const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped,
+           int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
+           const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
 {
   const int lane = threadIdx.x & 31;
   const unsigned count = unres_count[0];
@@ -232,42 +273,40 @@ k_knn_brute(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, I
     slot = __shfl_sync(0xffffffffu, slot, 0);
     if (slot >= count) break;
     const int i = unres_list[slot];
-    float qx, qy, qz;
-    if (FROM_POINTS) {
-      const float4 p = reinterpret_cast<const float4*>(kp)[2 * (size_t)i];
-      const Vec3d w = apply(prior, Vec3d((double)p.x, (double)p.y, (double)p.z));
-      qx = (float)w.x; qy = (float)w.y; qz = (float)w.z;
-    } else {
-      qx = q_xyz[3 * (size_t)i]; qy = q_xyz[3 * (size_t)i + 1]; qz = q_xyz[3 * (size_t)i + 2];
-    }
+    const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
     TopK<KMAX> tk;
     tk.init();
-    for (int p = lane; p < m; p += 32) {
-      const float4 s = __ldg(sorted + p);
-      const float dx = qx - s.x, dy = qy - s.y, dz = qz - s.z;
-      tk.offer((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w));
+    const int R = max(rcap, 1);
+    if (q.rfirst <= R) {
+      const int z0 = max(0, q.cz - R), z1 = min(gp.nz - 1, q.cz + R);
+      const int y0 = max(0, q.cy - R), y1 = min(gp.ny - 1, q.cy + R);
+      const int x0 = max(0, q.cx - R), x1 = min(gp.nx - 1, q.cx + R);
+      const int nyr = y1 - y0 + 1, nrows = (z1 - z0 + 1) * nyr;
+      if (x0 <= x1 && nyr > 0) {
+        for (int t = lane; t < nrows; t += 32) {
+          const int z = z0 + t / nyr, y = y0 + t % nyr;
+          const int base = (z * gp.ny + y) * gp.nx;
+          scan_range(tk, sorted, __ldg(cell_start + base + x0), __ldg(cell_start + base + x1 + 1), q.qx, q.qy, q.qz);
+        }
+      }
     }
-    int nf = 0;
-    for (int t = 0; t < k; ++t) {
-      float bd = tk.d[0];
-      int bi = tk.id[0];
-#pragma unroll
-      for (int off = 16; off; off >>= 1) {
-        const float od = __shfl_xor_sync(0xffffffffu, bd, off);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-        if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; }
+    float kd;
+    int nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * k, d2_out + (size_t)i * k, kd);
+    const bool settled = (q.rcover <= R) || resolved_at(kd, R, gp.cell, q.minoff);
+    if (!settled) {
+      if (capped) {
+        // every point within the cap distance has been visited and the k-th neighbour is
+        // farther than the cap: the caller only needs "k found, too far"
+        if (m >= k) nf = k;
+      } else {
+        tk.init();
+        for (int p = lane; p < m; p += 32) {
+          const float4 s = __ldg(sorted + p);
+          const float dx = q.qx - s.x, dy = q.qy - s.y, dz = q.qz - s.z;
+          tk.offer((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w));
+        }
+        nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * k, d2_out + (size_t)i * k, kd);
       }
-      const bool ok = bd < INFINITY;
-      if (ok && tk.id[0] == bi && tk.d[0] == bd) {   // the winning lane pops its head
-#pragma unroll
-        for (int u = 0; u + 1 < KMAX; ++u) { tk.d[u] = tk.d[u + 1]; tk.id[u] = tk.id[u + 1]; }
-        tk.d[KMAX - 1] = INFINITY; tk.id[KMAX - 1] = INT_MAX;
-      }
-      if (lane == 0) {
-        idx_out[(size_t)i * k + t] = ok ? bi : -1;
-        d2_out[(size_t)i * k + t] = ok ? bd : INFINITY;
-      }
-      nf += ok ? 1 : 0;
     }
     if (lane == 0 && nfound_out) nfound_out[i] = nf;
   }
@@ -280,21 +319,20 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   const unsigned G = div_up(nq, 128);
   const int NQ = (int)nq, M = (int)g.m;
   const int capped = cap_dist >= 0.f ? 1 : 0;
-  // rings after which the grid walk stops: capped => everything within cap_dist has been visited
-  // (r*cell minus the rounding margin exceeds cap_dist); exact => hand over to brute force
+  // radius of the warp kernel's cube: capped => everything within cap_dist is inside it
+  // (r*cell minus the rounding margin exceeds cap_dist); exact => 5 m, then brute force
   const float reach = capped ? cap_dist : 5.0f;
-  const int rcap = std::max(3, (int)std::ceil(reach / g.gp.cell) + 1);
+  const int rcap = std::max(2, (int)std::ceil(reach / g.gp.cell) + 1);
   g.unres_list.reserve(nq, s); g.unres_count.reserve(2, s);
-  if (!capped) LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 2 * sizeof(unsigned), s));
-#define LSB_KNN_CASE(KM)                                                                                                              \
-  do {                                                                                                                                \
-    k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, idx, d2, nf,       \
-                                             g.unres_list.p, g.unres_count.p);                                                        \
-    LSB_LAUNCH_CHECK(); lc.add();                                                                                                     \
-    if (!capped) {                                                                                                                    \
-      k_knn_brute<KM, FROM_POINTS><<<296, 128, 0, s>>>(q, kp, prior, g.sorted.p, M, k, idx, d2, nf, g.unres_list.p, g.unres_count.p); \
-      LSB_LAUNCH_CHECK(); lc.add();                                                                                                   \
-    }                                                                                                                                 \
+  LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 2 * sizeof(unsigned), s));
+#define LSB_KNN_CASE(KM)                                                                                                                   \
+  do {                                                                                                                                     \
+    k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, idx, d2, nf, g.unres_list.p,            \
+                                             g.unres_count.p);                                                                             \
+    LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
+    k_knn_warp<KM, FROM_POINTS><<<148 * 4, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, idx, d2, nf,   \
+                                                        g.unres_list.p, g.unres_count.p);                                                  \
+    LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
   } while (0)
   if (k <= 1) LSB_KNN_CASE(1);
   else if (k <= 5) LSB_KNN_CASE(5);
@@ -304,6 +342,7 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   else LSB_KNN_CASE(32);
 #undef LSB_KNN_CASE
 }
+
 
 __global__ void k_fill_empty(int32_t* idx, float* d2, int32_t* nf, size_t total, size_t nq)
 {

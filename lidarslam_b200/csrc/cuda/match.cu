@@ -181,25 +181,23 @@ __global__ void k_fit_empty(int nq, LmRecord* __restrict__ records, uint8_t* __r
 // One launch = one cost/Jacobian evaluation of the whole problem + one step of
 // the trust-region state machine (common/lm_core.h).  Each CTA reduces one
 // canonical chunk of 256 records (warp shuffles, offsets 16..1, the 8 warp sums
-// added in order); the last CTA to finish folds the chunk sums with the
-// canonical adjacent-pair tree and advances the LM state.  A launch whose state
-// is already `done` exits at once, so the host enqueues 1 + max_iter launches
-// back to back without reading anything back.
+// added in order); the last CTA to finish adds the chunk sums in chunk order
+// (one thread per quantity), advances the LM state and precomputes the rotation
+// and its derivatives for the next evaluation point.  A launch whose state is
+// already `done` exits at once, so the host enqueues 1 + max_iter launches back
+// to back without reading anything back.
 __global__ void __launch_bounds__(LSB_LM_CHUNK)
 k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, LmState* __restrict__ state,
-          double* __restrict__ part_a, double* __restrict__ part_b, unsigned* __restrict__ counter, int first)
+          LmPoint* __restrict__ point, double* __restrict__ part, unsigned* __restrict__ counter, int first)
 {
-  __shared__ __align__(16) unsigned char s_pt_raw[sizeof(LmPoint)];
-  LmPoint& s_pt = *reinterpret_cast<LmPoint*>(s_pt_raw);
+  __shared__ __align__(16) double s_pt_raw[sizeof(LmPoint) / sizeof(double)];
   __shared__ double s_warp[LSB_LM_CHUNK / 32][LSB_LM_NSUM];
+  __shared__ double s_E[LSB_LM_NSUM];
   __shared__ int s_last;
-  __shared__ int s_done;
-  if (threadIdx.x == 0) {
-    s_done = state->done;
-    if (!s_done) lm_make_point(first ? state->x : state->xc, s_pt);
-  }
+  if (state->done) return;   // uniform: written by the previous launch
+  if (threadIdx.x < sizeof(LmPoint) / sizeof(double)) s_pt_raw[threadIdx.x] = reinterpret_cast<const double*>(point)[threadIdx.x];
   __syncthreads();
-  if (s_done) return;
+  const LmPoint& s_pt = *reinterpret_cast<const LmPoint*>(s_pt_raw);
   const int i = blockIdx.x * LSB_LM_CHUNK + threadIdx.x;
   double out[LSB_LM_NSUM];
   if (i < n) lm_eval_record(records[i], s_pt, sat, out);
@@ -223,7 +221,7 @@ k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, 
   if (threadIdx.x < LSB_LM_NSUM) {
     double c = s_warp[0][threadIdx.x];
     for (int w = 1; w < LSB_LM_CHUNK / 32; ++w) c = c + s_warp[w][threadIdx.x];
-    part_a[(size_t)blockIdx.x * LSB_LM_NSUM + threadIdx.x] = c;
+    part[(size_t)blockIdx.x * LSB_LM_NSUM + threadIdx.x] = c;
   }
   __threadfence();
   __syncthreads();
@@ -234,38 +232,43 @@ k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, 
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // canonical tree over adjacent chunks (ping-pong between the two buffers)
-  double* src = part_a;
-  double* dst = part_b;
-  int m = nchunks;
-  while (m > 1) {
-    const int h = (m + 1) / 2;
-    for (int t = threadIdx.x; t < h * LSB_LM_NSUM; t += blockDim.x) {
-      const int c = t / LSB_LM_NSUM, q = t - c * LSB_LM_NSUM;
-      const double a = __ldcg(src + (size_t)(2 * c) * LSB_LM_NSUM + q);
-      dst[(size_t)c * LSB_LM_NSUM + q] = (2 * c + 1 < m) ? a + __ldcg(src + (size_t)(2 * c + 1) * LSB_LM_NSUM + q) : a;
+  // chunk sums added in chunk order, one thread per quantity (loads batched by 8)
+  if (threadIdx.x < LSB_LM_NSUM) {
+    const double* src = part + threadIdx.x;
+    double e = __ldcg(src);
+    int c = 1;
+    for (; c + 8 <= nchunks; c += 8) {
+      double v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcg(src + (size_t)(c + u) * LSB_LM_NSUM);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) e = e + v[u];
     }
-    __threadfence_block();
-    __syncthreads();
-    double* tmp = src; src = dst; dst = tmp;
-    m = h;
+    for (; c < nchunks; ++c) e = e + __ldcg(src + (size_t)c * LSB_LM_NSUM);
+    s_E[threadIdx.x] = e;
   }
+  __syncthreads();
   if (threadIdx.x == 0) {
     double E[LSB_LM_NSUM];
-    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = __ldcg(src + q);
+    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = s_E[q];
     LmState s = *state;
     if (first) lm_first_eval(s, E); else lm_next_eval(s, E);
     *state = s;
+    if (!s.done) { LmPoint pt; lm_make_point(s.xc, pt); *point = pt; }
     *counter = 0u;
   }
 }
 
-__global__ void k_lm_begin(LmState* state, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5, int max_iter, int two_d)
+__global__ void k_lm_begin(LmState* state, LmPoint* point, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5,
+                           int max_iter, int two_d)
 {
   const double x[6] = {x0, x1, x2, x3, x4, x5};
   LmState s;
   lm_begin(s, x, max_iter, two_d);
   *state = s;
+  LmPoint pt;
+  lm_make_point(x, pt);
+  *point = pt;
   *counter = 0u;
 }
 
@@ -340,12 +343,12 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
 {
   const int n = (int)total;
   const int nchunks = std::max(1, (int)div_up(total, LSB_LM_CHUNK));
-  part_a.reserve((size_t)nchunks * LSB_LM_NSUM, s); part_b.reserve((size_t)nchunks * LSB_LM_NSUM, s);
-  lm_state.reserve(1, s); lm_counter.reserve(1, s); h_lm.reserve(1);
-  k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d); LSB_LAUNCH_CHECK(); lc.add();
+  part_a.reserve((size_t)nchunks * LSB_LM_NSUM, s);
+  lm_state.reserve(1, s); lm_point.reserve(1, s); lm_counter.reserve(1, s); h_lm.reserve(1);
+  k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_point.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d); LSB_LAUNCH_CHECK(); lc.add();
   t_lm.begin(s);
   for (int e = 0; e <= max_iter; ++e) {
-    k_lm_eval<<<nchunks, LSB_LM_CHUNK, 0, s>>>(records.p, n, nchunks, saturation, lm_state.p, part_a.p, part_b.p, lm_counter.p, e == 0 ? 1 : 0);
+    k_lm_eval<<<nchunks, LSB_LM_CHUNK, 0, s>>>(records.p, n, nchunks, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
     LSB_LAUNCH_CHECK(); lc.add();
   }
   t_lm.end(s);

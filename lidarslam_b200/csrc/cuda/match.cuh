@@ -17,8 +17,9 @@ struct MatchWorkspace {
   DevBuf<uint8_t> status;
   DevBuf<double> weight;
   DevBuf<int> hist;                 // [3][LSB_MATCH_N_STATUS]
-  DevBuf<double> part_a, part_b;    // LM chunk partial sums (ping-pong)
+  DevBuf<double> part_a;            // LM chunk partial sums
   DevBuf<LmState> lm_state;         // [1]
+  DevBuf<LmPoint> lm_point;         // [1] rotation + derivatives at the next evaluation point
   DevBuf<unsigned> lm_counter;      // [1]
   PinnedBuf<int> h_hist;
   PinnedBuf<LmState> h_lm;

@@ -60,16 +60,8 @@ struct Optimizer {
       }
       for (int q = 0; q < LSB_LM_NSUM; ++q) part[c * LSB_LM_NSUM + q] = chunk[q];
     }
-    size_t m = std::max<size_t>(nChunks, 1);
-    while (m > 1) {
-      const size_t h = (m + 1) / 2;
-      for (size_t i = 0; i < h; ++i)
-        for (int q = 0; q < LSB_LM_NSUM; ++q) {
-          const double a = part[(2 * i) * LSB_LM_NSUM + q];
-          part[i * LSB_LM_NSUM + q] = (2 * i + 1 < m) ? a + part[(2 * i + 1) * LSB_LM_NSUM + q] : a;
-        }
-      m = h;
-    }
+    for (size_t c = 1; c < nChunks; ++c)   // chunk sums in chunk order
+      for (int q = 0; q < LSB_LM_NSUM; ++q) part[q] = part[q] + part[c * LSB_LM_NSUM + q];
     for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = part[q];
   }
 
