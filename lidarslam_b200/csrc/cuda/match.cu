@@ -186,13 +186,29 @@ __global__ void k_fit_empty(int nq, LmRecord* __restrict__ records, uint8_t* __r
 // and its derivatives for the next evaluation point.  A launch whose state is
 // already `done` exits at once, so the host enqueues 1 + max_iter launches back
 // to back without reading anything back.
-__global__ void __launch_bounds__(LSB_LM_CHUNK)
+// the serial trust-region step, kept out of line so that its registers / stack do not
+// weigh on the 256 evaluating threads
+__device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned* counter, const double* sE, int first)
+{
+  double E[LSB_LM_NSUM];
+  for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = sE[q];
+  LmState s = *state;
+  if (first) lm_first_eval(s, E); else lm_next_eval(s, E);
+  *state = s;
+  if (!s.done) { LmPoint pt; lm_make_point(s.xc, pt); *point = pt; }
+  *counter = 0u;
+}
+
+constexpr int LM_TILE = 160;   // chunk partials staged per pass of the final sum (35 KB)
+
+__global__ void __launch_bounds__(LSB_LM_CHUNK, 2)
 k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, LmState* __restrict__ state,
           LmPoint* __restrict__ point, double* __restrict__ part, unsigned* __restrict__ counter, int first)
 {
   __shared__ __align__(16) double s_pt_raw[sizeof(LmPoint) / sizeof(double)];
   __shared__ double s_warp[LSB_LM_CHUNK / 32][LSB_LM_NSUM];
   __shared__ double s_E[LSB_LM_NSUM];
+  __shared__ double s_tile[LM_TILE * LSB_LM_NSUM];
   __shared__ int s_last;
   if (state->done) return;   // uniform: written by the previous launch
   if (threadIdx.x < sizeof(LmPoint) / sizeof(double)) s_pt_raw[threadIdx.x] = reinterpret_cast<const double*>(point)[threadIdx.x];
@@ -232,31 +248,23 @@ k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, 
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // chunk sums added in chunk order, one thread per quantity (loads batched by 8)
-  if (threadIdx.x < LSB_LM_NSUM) {
-    const double* src = part + threadIdx.x;
-    double e = __ldcg(src);
-    int c = 1;
-    for (; c + 8 <= nchunks; c += 8) {
-      double v[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = __ldcg(src + (size_t)(c + u) * LSB_LM_NSUM);
-#pragma unroll
-      for (int u = 0; u < 8; ++u) e = e + v[u];
+  // chunk sums added in chunk order: tiles of the partials are staged in shared memory by
+  // the whole CTA (coalesced, one L2 round trip), then one thread per quantity adds them
+  double e = 0.0;
+  for (int c0 = 0; c0 < nchunks; c0 += LM_TILE) {
+    const int nt = min(LM_TILE, nchunks - c0);
+    for (int t = threadIdx.x; t < nt * LSB_LM_NSUM; t += blockDim.x) s_tile[t] = __ldcg(part + (size_t)c0 * LSB_LM_NSUM + t);
+    __syncthreads();
+    if (threadIdx.x < LSB_LM_NSUM) {
+      int c = 0;
+      if (c0 == 0) { e = s_tile[threadIdx.x]; c = 1; }
+      for (; c < nt; ++c) e = e + s_tile[c * LSB_LM_NSUM + threadIdx.x];
     }
-    for (; c < nchunks; ++c) e = e + __ldcg(src + (size_t)c * LSB_LM_NSUM);
-    s_E[threadIdx.x] = e;
+    __syncthreads();
   }
+  if (threadIdx.x < LSB_LM_NSUM) s_E[threadIdx.x] = e;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    double E[LSB_LM_NSUM];
-    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = s_E[q];
-    LmState s = *state;
-    if (first) lm_first_eval(s, E); else lm_next_eval(s, E);
-    *state = s;
-    if (!s.done) { LmPoint pt; lm_make_point(s.xc, pt); *point = pt; }
-    *counter = 0u;
-  }
+  if (threadIdx.x == 0) lm_control(state, point, counter, s_E, first);
 }
 
 __global__ void k_lm_begin(LmState* state, LmPoint* point, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5,
