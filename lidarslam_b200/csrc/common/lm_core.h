@@ -24,10 +24,10 @@ namespace lsb {
 // [0..20] upper triangle of J~^T J~ (row-major: 00 01 02 03 04 05 11 12 ...),
 // [21..26] J~^T r~, [27] cost = sum 0.5*rho.
 #define LSB_LM_NSUM 28
-// Canonical reduction order (GPU and oracle): records in chunks of 256; inside a
+// Canonical reduction order (GPU and oracle): records in chunks of 1024; inside a
 // chunk each group of 32 consecutive records is folded with offsets 16,8,4,2,1,
-// the 8 group sums are added in order, and the chunk sums are added in chunk order.
-#define LSB_LM_CHUNK 256
+// the 32 group sums are added in order, and the chunk sums are added in chunk order.
+#define LSB_LM_CHUNK 1024
 
 // One residual record, 16 doubles (A row-major, P, X, weight).  weight < 0 marks
 // "no residual" (match failed): contributes exactly zero.
@@ -43,11 +43,18 @@ struct LmPoint {   // quantities that depend only on the current parameters
   Vec3d t;
 };
 
-LSB_HD void lm_make_point(const double* x, LmPoint& p)
+// trig[6] = cos rx, sin rx, cos ry, sin ry, cos rz, sin rz  (entry j: angle x[3 + j/2], cos if j even)
+LSB_HD double lm_point_trig(const double* x, int j)
 {
-  const double cx = dm::cos(x[3]), sx = dm::sin(x[3]);
-  const double cy = dm::cos(x[4]), sy = dm::sin(x[4]);
-  const double cz = dm::cos(x[5]), sz = dm::sin(x[5]);
+  const double a = x[3 + (j >> 1)];
+  return (j & 1) ? dm::sin(a) : dm::cos(a);
+}
+
+LSB_HD void lm_make_point_from_trig(const double* x, const double* trig, LmPoint& p)
+{
+  const double cx = trig[0], sx = trig[1];
+  const double cy = trig[2], sy = trig[3];
+  const double cz = trig[4], sz = trig[5];
   p.t = Vec3d(x[0], x[1], x[2]);
   Mat3d& R = p.R;
   R(0, 0) = cy * cz; R(0, 1) = sx * sy * cz - cx * sz; R(0, 2) = cx * sy * cz + sx * sz;
@@ -65,6 +72,13 @@ LSB_HD void lm_make_point(const double* x, LmPoint& p)
   C(0, 0) = -cy * sz; C(0, 1) = -sx * sy * sz - cx * cz; C(0, 2) = -cx * sy * sz + sx * cz;
   C(1, 0) = cy * cz;  C(1, 1) = sx * sy * cz - cx * sz;  C(1, 2) = cx * sy * cz + sx * sz;
   C(2, 0) = 0.0;      C(2, 1) = 0.0;                     C(2, 2) = 0.0;
+}
+
+LSB_HD void lm_make_point(const double* x, LmPoint& p)
+{
+  double trig[6];
+  for (int j = 0; j < 6; ++j) trig[j] = lm_point_trig(x, j);
+  lm_make_point_from_trig(x, trig, p);
 }
 
 // Adds nothing: WRITES the 28 terms of one record into out[] (zeros if w < 0).
@@ -115,34 +129,47 @@ LSB_HD void lm_eval_record(const LmRecord& rec, const LmPoint& pt, double sat, d
 // Returns false if M is not positive definite or the result is not finite.
 LSB_HD bool lm_chol_solve6(const double* M, const double* b, double* y)
 {
+  // fully unrolled (compile-time indices) so that everything stays in registers on the GPU
   double L[36];
+  bool ok = true;
+#pragma unroll
   for (int i = 0; i < 36; ++i) L[i] = 0.0;
+#pragma unroll
   for (int j = 0; j < 6; ++j) {
     double d = M[j * 6 + j];
+#pragma unroll
     for (int k = 0; k < j; ++k) d = d - L[j * 6 + k] * L[j * 6 + k];
-    if (!(d > 0.0)) return false;
+    if (!(d > 0.0)) ok = false;
     const double ljj = ::sqrt(d);
     L[j * 6 + j] = ljj;
+#pragma unroll
     for (int i = j + 1; i < 6; ++i) {
       double s = M[i * 6 + j];
+#pragma unroll
       for (int k = 0; k < j; ++k) s = s - L[i * 6 + k] * L[j * 6 + k];
       L[i * 6 + j] = s / ljj;
     }
   }
+  if (!ok) return false;
   double z[6];
+#pragma unroll
   for (int i = 0; i < 6; ++i) {
     double s = b[i];
+#pragma unroll
     for (int k = 0; k < i; ++k) s = s - L[i * 6 + k] * z[k];
     z[i] = s / L[i * 6 + i];
   }
+#pragma unroll
   for (int i = 5; i >= 0; --i) {
     double s = z[i];
+#pragma unroll
     for (int k = i + 1; k < 6; ++k) s = s - L[k * 6 + i] * y[k];
     y[i] = s / L[i * 6 + i];
   }
+#pragma unroll
   for (int i = 0; i < 6; ++i)
-    if (!(y[i] - y[i] == 0.0)) return false;   // NaN / inf
-  return true;
+    if (!(y[i] - y[i] == 0.0)) ok = false;   // NaN / inf
+  return ok;
 }
 
 enum { LSB_LM_RUNNING = 0, LSB_LM_CONV_GRADIENT, LSB_LM_CONV_PARAMETER, LSB_LM_CONV_FUNCTION, LSB_LM_CONV_RADIUS,
@@ -187,7 +214,9 @@ LSB_HD void lm_propose(LmState& s)
     if (s.radius < 1e-32) { s.done = 1; s.term = LSB_LM_CONV_RADIUS; return; }
     s.iter += 1;
     double M[36], b[6], Hs[36], gs[6];
+#pragma unroll
     for (int i = 0; i < 6; ++i) {
+#pragma unroll
       for (int j = 0; j < 6; ++j) {
         const double h = (i <= j) ? s.H[lm_hidx(i, j)] : s.H[lm_hidx(j, i)];
         Hs[i * 6 + j] = (lm_free(s, i) && lm_free(s, j)) ? h * s.S[i] * s.S[j] : 0.0;
@@ -196,6 +225,7 @@ LSB_HD void lm_propose(LmState& s)
       gs[i] = lm_free(s, i) ? s.g[i] * s.S[i] : 0.0;
       b[i] = -gs[i];
     }
+#pragma unroll
     for (int i = 0; i < 6; ++i) {
       if (!lm_free(s, i)) { M[i * 6 + i] = 1.0; continue; }   // decoupled dummy row -> delta_i = 0
       double d = Hs[i * 6 + i];
@@ -208,8 +238,10 @@ LSB_HD void lm_propose(LmState& s)
     double mcc = 0.0;
     if (ok) {
       // model_cost_change = -delta^T (g + 0.5 H delta)   (scaled quantities)
+#pragma unroll
       for (int i = 0; i < 6; ++i) {
         double hd = 0.0;
+#pragma unroll
         for (int j = 0; j < 6; ++j) hd += Hs[i * 6 + j] * db[j];
         mcc -= db[i] * (gs[i] + 0.5 * hd);
       }
@@ -225,6 +257,7 @@ LSB_HD void lm_propose(LmState& s)
     s.num_invalid = 0;
     s.model_cost_change = mcc;
     double sn = 0.0;
+#pragma unroll
     for (int i = 0; i < 6; ++i) {
       const double d = db[i] * s.S[i];
       s.xc[i] = s.x[i] + d;

@@ -133,6 +133,7 @@ struct QueryCell {
   float qx, qy, qz;
   int cx, cy, cz;
   float minoff;
+  float ox, oy, oz;      // offset of the query inside its cell, in [0, cell]
   int rcover, rfirst;
   bool finite;
 };
@@ -158,6 +159,7 @@ __device__ __forceinline__ QueryCell make_query(const float* __restrict__ q_xyz,
   const float lx = gp.ox + fx * cell, ly = gp.oy + fy * cell, lz = gp.oz + fz * cell;
   q.minoff = fminf(fminf(fminf(q.qx - lx, lx + cell - q.qx), fminf(q.qy - ly, ly + cell - q.qy)), fminf(q.qz - lz, lz + cell - q.qz));
   q.minoff = fmaxf(q.minoff, 0.f);
+  q.ox = q.qx - lx; q.oy = q.qy - ly; q.oz = q.qz - lz;
   // radius at which the cube covers the whole grid / first touches it
   q.rcover = max(max(max(q.cx, gp.nx - 1 - q.cx), max(q.cy, gp.ny - 1 - q.cy)), max(q.cz, gp.nz - 1 - q.cz));
   q.rfirst = max(max(max(-q.cx, q.cx - (gp.nx - 1)), max(-q.cy, q.cy - (gp.ny - 1))), max(max(-q.cz, q.cz - (gp.nz - 1)), 0));
@@ -174,9 +176,22 @@ __device__ __forceinline__ bool resolved_at(float kth_d2, int r, float cell, flo
   return bound > 0.f && kth_d2 < bound * bound;
 }
 
-// Phase 1: one thread per query scans the 3x3x3 cube around its cell (9 contiguous
-// row ranges, their 18 bounds loaded up front).  Queries it cannot settle go to the
-// warp-per-query kernel below.
+// lower bound (squared, with a rounding margin) of the distance from the query to any point of
+// a cell that lies d cells away along one axis (d = 0: the query's own cell)
+__device__ __forceinline__ float axis_gap(int d, float off, float cell)
+{
+  if (d == 0) return 0.f;
+  const float g = (d > 0) ? ((float)(d - 1) * cell + (cell - off)) : ((float)(-d - 1) * cell + off);
+  return fmaxf(g - (1.0e-3f + 1.0e-4f * cell), 0.f);
+}
+
+// visiting order of the 27 cells of the 3x3x3 cube: the query's cell, the 6 face
+// neighbours, the 12 edge neighbours, the 8 corners (packed (dz+1)*9 + (dy+1)*3 + (dx+1))
+__constant__ unsigned char c_cube_order[27] = {13, 12, 14, 10, 16, 4, 22, 9, 11, 15, 17, 3, 5, 21, 23, 1, 7, 19, 25, 0, 2, 6, 8, 18, 20, 24, 26};
+
+// Phase 1: one thread per query scans the 3x3x3 cube around its cell, nearest cells first;
+// a cell whose lower distance bound is not below the current k-th distance is skipped.
+// Queries it cannot settle go to the warp-per-query kernel below.
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
@@ -190,18 +205,31 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
   tk.init();
   bool done = !q.finite;          // NaN query: nothing found, as an exact search would
   if (q.finite && q.rfirst <= 1) {
-    uint32_t rb[9], re[9];
-    const int x0 = max(0, q.cx - 1), x1 = min(gp.nx - 1, q.cx + 1);
+    // cell boundaries of the 9 rows: cs[row][j] = first point of cell cx-1+j (j = 0..3)
+    uint32_t cs[9][4];
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
       const int z = q.cz + t / 3 - 1, y = q.cy + t % 3 - 1;
-      const bool in = z >= 0 && z < gp.nz && y >= 0 && y < gp.ny && x0 <= x1;
+      const bool in = z >= 0 && z < gp.nz && y >= 0 && y < gp.ny;
       const int base = (z * gp.ny + y) * gp.nx;
-      rb[t] = in ? __ldg(cell_start + base + x0) : 0u;
-      re[t] = in ? __ldg(cell_start + base + x1 + 1) : 0u;
-    }
 #pragma unroll
-    for (int t = 0; t < 9; ++t) scan_range(tk, sorted, rb[t], re[t], q.qx, q.qy, q.qz);
+      for (int j = 0; j < 4; ++j) {
+        const int x = min(max(q.cx - 1 + j, 0), gp.nx);   // clamped: out-of-grid cells become empty ranges
+        cs[t][j] = in ? __ldg(cell_start + base + x) : 0u;
+      }
+    }
+    const float gx[3] = {axis_gap(-1, q.ox, gp.cell), 0.f, axis_gap(1, q.ox, gp.cell)};
+    const float gy[3] = {axis_gap(-1, q.oy, gp.cell), 0.f, axis_gap(1, q.oy, gp.cell)};
+    const float gz[3] = {axis_gap(-1, q.oz, gp.cell), 0.f, axis_gap(1, q.oz, gp.cell)};
+#pragma unroll 1
+    for (int o = 0; o < 27; ++o) {
+      const int c = c_cube_order[o];
+      const int jz = c / 9, jy = (c / 3) % 3, jx = c % 3;
+      const float lb = (gx[jx] * gx[jx] + gy[jy] * gy[jy]) + gz[jz] * gz[jz];
+      if (!(lb < tk.d[KMAX - 1])) continue;
+      const int row = jz * 3 + jy;
+      scan_range(tk, sorted, cs[row][jx], cs[row][jx + 1], q.qx, q.qy, q.qz);
+    }
     done = (q.rcover <= 1) || resolved_at(tk.d[KMAX - 1], 1, gp.cell, q.minoff);
   }
   if (!done) {
@@ -261,7 +289,7 @@ __device__ __forceinline__ int warp_merge_write(TopK<KMAX>& tk, int k, int lane,
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
-           const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped,
+           const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped, float cap2,
            int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
            const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
 {
@@ -285,6 +313,10 @@ k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Is
       if (x0 <= x1 && nyr > 0) {
         for (int t = lane; t < nrows; t += 32) {
           const int z = z0 + t / nyr, y = y0 + t % nyr;
+          // rows that cannot hold anything nearer than this lane's k-th candidate (or than the cap) are skipped
+          const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
+          const float lb = gy * gy + gz * gz;
+          if (!(lb < tk.d[KMAX - 1]) || lb > cap2) continue;
           const int base = (z * gp.ny + y) * gp.nx;
           scan_range(tk, sorted, __ldg(cell_start + base + x0), __ldg(cell_start + base + x1 + 1), q.qx, q.qy, q.qz);
         }
@@ -323,6 +355,7 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   // (r*cell minus the rounding margin exceeds cap_dist); exact => 5 m, then brute force
   const float reach = capped ? cap_dist : 5.0f;
   const int rcap = std::max(2, (int)std::ceil(reach / g.gp.cell) + 1);
+  const float cap2 = capped ? cap_dist * cap_dist : INFINITY;   // rows farther than the cap cannot matter
   g.unres_list.reserve(nq, s); g.unres_count.reserve(2, s);
   LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 2 * sizeof(unsigned), s));
 #define LSB_KNN_CASE(KM)                                                                                                                   \
@@ -330,7 +363,7 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
     k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, idx, d2, nf, g.unres_list.p,            \
                                              g.unres_count.p);                                                                             \
     LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
-    k_knn_warp<KM, FROM_POINTS><<<148 * 4, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, idx, d2, nf,   \
+    k_knn_warp<KM, FROM_POINTS><<<148 * 4, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, cap2, idx, d2, nf, \
                                                         g.unres_list.p, g.unres_count.p);                                                  \
     LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
   } while (0)

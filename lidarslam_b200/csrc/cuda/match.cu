@@ -186,27 +186,51 @@ __global__ void k_fit_empty(int nq, LmRecord* __restrict__ records, uint8_t* __r
 // and its derivatives for the next evaluation point.  A launch whose state is
 // already `done` exits at once, so the host enqueues 1 + max_iter launches back
 // to back without reading anything back.
-// the serial trust-region step, kept out of line so that its registers / stack do not
-// weigh on the 256 evaluating threads
+// The trust-region step, run by warp 0 of the last CTA and kept out of line so that its
+// registers do not weigh on the 256 evaluating threads.  Lane 0 advances the state machine;
+// the six sin/cos of the next evaluation point are computed by six lanes in parallel.
 __device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned* counter, const double* sE, int first)
 {
-  double E[LSB_LM_NSUM];
-  for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = sE[q];
-  LmState s = *state;
-  if (first) lm_first_eval(s, E); else lm_next_eval(s, E);
-  *state = s;
-  if (!s.done) { LmPoint pt; lm_make_point(s.xc, pt); *point = pt; }
-  *counter = 0u;
+  const int lane = threadIdx.x & 31;
+  double xc[6];
+  int done = 1;
+  if (lane == 0) {
+    double E[LSB_LM_NSUM];
+#pragma unroll
+    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = sE[q];
+    LmState s = *state;
+    if (first) lm_first_eval(s, E); else lm_next_eval(s, E);
+    *state = s;
+    *counter = 0u;
+    done = s.done;
+#pragma unroll
+    for (int q = 0; q < 6; ++q) xc[q] = s.xc[q];
+  }
+  done = __shfl_sync(0xffffffffu, done, 0);
+  if (done) return;
+#pragma unroll
+  for (int q = 0; q < 6; ++q) xc[q] = __shfl_sync(0xffffffffu, xc[q], 0);
+  const double tv = (lane < 6) ? lm_point_trig(xc, lane) : 0.0;
+  double trig[6];
+#pragma unroll
+  for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(0xffffffffu, tv, q);
+  if (lane == 0) {
+    LmPoint pt;
+    lm_make_point_from_trig(xc, trig, pt);
+    *point = pt;
+  }
 }
 
-constexpr int LM_TILE = 160;   // chunk partials staged per pass of the final sum (35 KB)
+constexpr int LM_TILE = 160;      // chunk partials staged per pass of the final sum (35 KB)
+constexpr int LM_THREADS = 512;   // 16 warps; each warp folds LSB_LM_CHUNK / 32 / 16 = 2 groups of 32 records
+constexpr int LM_GROUPS = LSB_LM_CHUNK / 32;
 
-__global__ void __launch_bounds__(LSB_LM_CHUNK, 2)
+__global__ void __launch_bounds__(LM_THREADS, 1)
 k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, LmState* __restrict__ state,
           LmPoint* __restrict__ point, double* __restrict__ part, unsigned* __restrict__ counter, int first)
 {
   __shared__ __align__(16) double s_pt_raw[sizeof(LmPoint) / sizeof(double)];
-  __shared__ double s_warp[LSB_LM_CHUNK / 32][LSB_LM_NSUM];
+  __shared__ double s_group[LM_GROUPS][LSB_LM_NSUM];
   __shared__ double s_E[LSB_LM_NSUM];
   __shared__ double s_tile[LM_TILE * LSB_LM_NSUM];
   __shared__ int s_last;
@@ -214,32 +238,32 @@ k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, 
   if (threadIdx.x < sizeof(LmPoint) / sizeof(double)) s_pt_raw[threadIdx.x] = reinterpret_cast<const double*>(point)[threadIdx.x];
   __syncthreads();
   const LmPoint& s_pt = *reinterpret_cast<const LmPoint*>(s_pt_raw);
-  const int i = blockIdx.x * LSB_LM_CHUNK + threadIdx.x;
-  double out[LSB_LM_NSUM];
-  if (i < n) lm_eval_record(records[i], s_pt, sat, out);
-  else {
-#pragma unroll
-    for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
-  }
-#pragma unroll
-  for (int q = 0; q < LSB_LM_NSUM; ++q) {
-    double v = out[q];
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-    out[q] = v;
-  }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) {
+#pragma unroll 1
+  for (int g = warp; g < LM_GROUPS; g += LM_THREADS / 32) {
+    const int i = blockIdx.x * LSB_LM_CHUNK + g * 32 + lane;
+    double out[LSB_LM_NSUM];
+    if (i < n) lm_eval_record(records[i], s_pt, sat, out);
+    else {
 #pragma unroll
-    for (int q = 0; q < LSB_LM_NSUM; ++q) s_warp[warp][q] = out[q];
+      for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
+    }
+#pragma unroll
+    for (int q = 0; q < LSB_LM_NSUM; ++q) {
+      double v = out[q];
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+      if (lane == 0) s_group[g][q] = v;
+    }
   }
   __syncthreads();
   if (threadIdx.x < LSB_LM_NSUM) {
-    double c = s_warp[0][threadIdx.x];
-    for (int w = 1; w < LSB_LM_CHUNK / 32; ++w) c = c + s_warp[w][threadIdx.x];
+    double c = s_group[0][threadIdx.x];
+#pragma unroll 8
+    for (int g = 1; g < LM_GROUPS; ++g) c = c + s_group[g][threadIdx.x];
     part[(size_t)blockIdx.x * LSB_LM_NSUM + threadIdx.x] = c;
+    __threadfence();
   }
-  __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned t = atomicAdd(counter, 1u);
@@ -249,22 +273,29 @@ k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, 
   if (!s_last) return;
   __threadfence();
   // chunk sums added in chunk order: tiles of the partials are staged in shared memory by
-  // the whole CTA (coalesced, one L2 round trip), then one thread per quantity adds them
+  // the whole CTA (independent loads first, one L2 round trip), then one thread per quantity adds them
   double e = 0.0;
   for (int c0 = 0; c0 < nchunks; c0 += LM_TILE) {
-    const int nt = min(LM_TILE, nchunks - c0);
-    for (int t = threadIdx.x; t < nt * LSB_LM_NSUM; t += blockDim.x) s_tile[t] = __ldcg(part + (size_t)c0 * LSB_LM_NSUM + t);
+    const int nt = min(LM_TILE, nchunks - c0) * LSB_LM_NSUM;
+    const double* src = part + (size_t)c0 * LSB_LM_NSUM;
+    for (int t0 = 0; t0 < nt; t0 += LM_THREADS * 4) {
+      double v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { const int t = t0 + u * LM_THREADS + threadIdx.x; v[u] = (t < nt) ? __ldcg(src + t) : 0.0; }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { const int t = t0 + u * LM_THREADS + threadIdx.x; if (t < nt) s_tile[t] = v[u]; }
+    }
     __syncthreads();
     if (threadIdx.x < LSB_LM_NSUM) {
       int c = 0;
       if (c0 == 0) { e = s_tile[threadIdx.x]; c = 1; }
-      for (; c < nt; ++c) e = e + s_tile[c * LSB_LM_NSUM + threadIdx.x];
+      for (; c * LSB_LM_NSUM < nt; ++c) e = e + s_tile[c * LSB_LM_NSUM + threadIdx.x];
     }
     __syncthreads();
   }
   if (threadIdx.x < LSB_LM_NSUM) s_E[threadIdx.x] = e;
   __syncthreads();
-  if (threadIdx.x == 0) lm_control(state, point, counter, s_E, first);
+  if (threadIdx.x < 32) lm_control(state, point, counter, s_E, first);
 }
 
 __global__ void k_lm_begin(LmState* state, LmPoint* point, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5,
@@ -356,7 +387,7 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_point.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d); LSB_LAUNCH_CHECK(); lc.add();
   t_lm.begin(s);
   for (int e = 0; e <= max_iter; ++e) {
-    k_lm_eval<<<nchunks, LSB_LM_CHUNK, 0, s>>>(records.p, n, nchunks, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
+    k_lm_eval<<<nchunks, LM_THREADS, 0, s>>>(records.p, n, nchunks, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
     LSB_LAUNCH_CHECK(); lc.add();
   }
   t_lm.end(s);
