@@ -130,9 +130,8 @@ def run_cpu(frames, warmup, steps, threads=None):
 
 def main():
     a = parse()
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    from lidarslam_b200 import shard
+    rank, world, local = shard.rank_info()
     W, K = max(a.warmup, 3), a.steps
 
     if a.impl == "reference":
@@ -166,7 +165,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    frames = make_frames(a.sensor, W + K, 1234 + rank)   # one independent sequence per rank
+    frames = make_frames(a.sensor, W + K, shard.sequence_seed(rank))   # one independent sequence per rank
     npts = len(frames[0][0])
 
     # ---------------- value: frames resident in HBM -------------------------------------
@@ -212,7 +211,7 @@ def main():
         pin[:] = frames[i][0]
         e.AddFrame(pin, frames[i][1], i + 1)
     barrier()
-    e2e_s, d2h, h2d = 0.0, 0, 0
+    e2e_s, d2h, h2d, e2e_steps = 0.0, 0, 0, []
     for i in range(W, W + K):
         if not a.no_flush:
             e.FlushL2()
@@ -220,7 +219,8 @@ def main():
         t0 = time.perf_counter()
         e.AddFrame(pin, frames[i][1], i + 1)        # H2D + whole path + readbacks
         T, _ = e.GetWorldTransform()                # the step's result on the host
-        e2e_s += time.perf_counter() - t0
+        e2e_steps.append(time.perf_counter() - t0)
+        e2e_s += e2e_steps[-1]
         se = e.GetFrameStats()
         d2h += se.d2h_bytes + 128
         h2d += se.h2d_bytes
@@ -230,14 +230,9 @@ def main():
     pinned_free(pin_ptr)
 
     # ---------------- max over ranks ------------------------------------------------------
-    red = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda:%d" % local)
-    cnt = torch.tensor([launches], dtype=torch.float64, device="cuda:%d" % local)
-    if world > 1:
-        dist.all_reduce(red, op=dist.ReduceOp.MAX)
-        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    max_ms, max_e2e_ms = float(red[0]), float(red[1])
-    value = world * K / (max_ms * 1e-3)
-    e2e_value = world * K / (max_e2e_ms * 1e-3)
+    (max_ms, max_e2e_ms), (n_launches,) = shard.reduce_job([total_ms, e2e_s * 1e3], [launches], device="cuda:%d" % local)
+    value = shard.job_throughput(K, world, max_ms * 1e-3)
+    e2e_value = shard.job_throughput(K, world, max_e2e_ms * 1e-3)
 
     if rank == 0:
         peaks = {}
@@ -250,15 +245,17 @@ def main():
         per_launch_s = knn_ms * 1e-3 / max(knn_launches, 1)
         achieved = per_launch_bytes / per_launch_s / 1e9 if per_launch_s > 0 else 0.0
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": max_ms / K, "p50_ms_per_frame": statistics.median(step_ms), "higher_is_better": True,
+                "ms_per_step": max_ms / K, "p50_ms_per_frame": statistics.median(step_ms), "max_ms_per_frame": max(step_ms),
+                "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64", "data": "synthetic",
                 "points_per_sec": value * npts, "knn_queries_per_sec": knn_queries / (knn_ms * 1e-3) if knn_ms > 0 else None,
                 "config": {"workload": WORKLOAD, "sensor": a.sensor, "sequences": world, "parallelism": "replicas x%d" % world,
                            "l2": "flushed between timed iterations" if not a.no_flush else "not flushed",
                            "timing": "CUDA events on the handle's stream around each lsb_add_frames_dev call"},
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
-                        "same_pose_as_device_arm": same_pose},
-                "gpu_launches": int(cnt[0]),
+                        "same_pose_as_device_arm": same_pose, "p50_ms_per_frame": 1e3 * statistics.median(e2e_steps),
+                        "max_ms_per_frame": 1e3 * max(e2e_steps)},
+                "gpu_launches": int(n_launches),
                 "clocks": sampler.result(),
                 "roofline": {"kernel": "k_knn (exact grid kNN)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak if peak else None, "traffic": None,

@@ -42,8 +42,9 @@ struct DevBuf {
   void reserve(size_t n, cudaStream_t s = 0, bool keep = false, size_t keep_n = 0)
   {
     if (n <= cap) return;
-    size_t ncap = cap ? cap : 1024;
-    while (ncap < n) ncap = ncap + ncap / 2 + 1024;
+    // geometric growth (x2, floor 64 Ki elements) so that a growing map reallocates O(log) times
+    size_t ncap = cap ? cap : 65536;
+    while (ncap < n) ncap = ncap * 2;
     T* q = nullptr;
     LSB_CUDA(cudaMalloc(&q, ncap * sizeof(T)));
     if (p) {

@@ -195,7 +195,7 @@ __constant__ unsigned char c_cube_order[27] = {13, 12, 14, 10, 16, 4, 22, 9, 11,
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
-      const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, int32_t* __restrict__ idx_out,
+      const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, size_t qs, size_t ts, int32_t* __restrict__ idx_out,
       float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -241,8 +241,8 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
   for (int t = 0; t < KMAX; ++t) {
     if (t < k) {
       const bool ok = tk.d[t] < INFINITY;
-      idx_out[(size_t)i * k + t] = ok ? tk.id[t] : -1;
-      d2_out[(size_t)i * k + t] = ok ? tk.d[t] : INFINITY;
+      idx_out[(size_t)i * qs + t * ts] = ok ? tk.id[t] : -1;
+      d2_out[(size_t)i * qs + t * ts] = ok ? tk.d[t] : INFINITY;
       nf += ok ? 1 : 0;
     }
   }
@@ -253,7 +253,7 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
 // warp.  Writes the first k; returns the number found and the KMAX-th distance.
 template <int KMAX>
 __device__ __forceinline__ int warp_merge_write(TopK<KMAX>& tk, int k, int lane, int32_t* __restrict__ idx_row, float* __restrict__ d2_row,
-                                                float& kmax_d2)
+                                                size_t ts, float& kmax_d2)
 {
   int nf = 0;
   kmax_d2 = INFINITY;
@@ -274,7 +274,7 @@ __device__ __forceinline__ int warp_merge_write(TopK<KMAX>& tk, int k, int lane,
       tk.d[KMAX - 1] = INFINITY; tk.id[KMAX - 1] = INT_MAX;
     }
     if (t < k) {
-      if (lane == 0) { idx_row[t] = ok ? bi : -1; d2_row[t] = ok ? bd : INFINITY; }
+      if (lane == 0) { idx_row[t * ts] = ok ? bi : -1; d2_row[t * ts] = ok ? bd : INFINITY; }
       nf += ok ? 1 : 0;
     }
     if (t == KMAX - 1) kmax_d2 = bd;
@@ -290,7 +290,7 @@ template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
            const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped, float cap2,
-           int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
+           size_t qs, size_t ts, int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
            const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
 {
   const int lane = threadIdx.x & 31;
@@ -323,7 +323,7 @@ k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Is
       }
     }
     float kd;
-    int nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * k, d2_out + (size_t)i * k, kd);
+    int nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * qs, d2_out + (size_t)i * qs, ts, kd);
     const bool settled = (q.rcover <= R) || resolved_at(kd, R, gp.cell, q.minoff);
     if (!settled) {
       if (capped) {
@@ -337,7 +337,7 @@ k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Is
           const float dx = q.qx - s.x, dy = q.qy - s.y, dz = q.qz - s.z;
           tk.offer((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w));
         }
-        nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * k, d2_out + (size_t)i * k, kd);
+        nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * qs, d2_out + (size_t)i * qs, ts, kd);
       }
     }
     if (lane == 0 && nfound_out) nfound_out[i] = nf;
@@ -346,8 +346,9 @@ k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Is
 
 template <bool FROM_POINTS>
 void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso3d& prior, size_t nq, int k, float cap_dist, int32_t* idx,
-                float* d2, int32_t* nf, cudaStream_t s, LaunchCounter& lc)
+                float* d2, int32_t* nf, bool entry_major, cudaStream_t s, LaunchCounter& lc)
 {
+  const size_t qs = entry_major ? 1 : (size_t)k, ts = entry_major ? nq : 1;
   const unsigned G = div_up(nq, 128);
   const int NQ = (int)nq, M = (int)g.m;
   const int capped = cap_dist >= 0.f ? 1 : 0;
@@ -360,10 +361,10 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 2 * sizeof(unsigned), s));
 #define LSB_KNN_CASE(KM)                                                                                                                   \
   do {                                                                                                                                     \
-    k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, idx, d2, nf, g.unres_list.p,            \
+    k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, qs, ts, idx, d2, nf, g.unres_list.p,    \
                                              g.unres_count.p);                                                                             \
     LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
-    k_knn_warp<KM, FROM_POINTS><<<148 * 4, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, cap2, idx, d2, nf, \
+    k_knn_warp<KM, FROM_POINTS><<<148 * 4, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, cap2, qs, ts, idx, d2, nf, \
                                                         g.unres_list.p, g.unres_count.p);                                                  \
     LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
   } while (0)
@@ -438,7 +439,7 @@ void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float
   k_cell_start<<<div_up((size_t)ncells + 1, TPB), TPB, 0, s>>>(key_b.p, M, ncells, cell_start.p); LSB_LAUNCH_CHECK(); lc.add();
 }
 
-void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t* d_idx, float* d_d2, int32_t* d_nf, cudaStream_t s, LaunchCounter& lc) const
+void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t* d_idx, float* d_d2, int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc) const
 {
   if (nq == 0) return;
   if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
@@ -446,11 +447,11 @@ void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t
     k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
-  launch_knn<false>(*this, d_q, nullptr, Iso3d::identity(), nq, k, cap_dist, d_idx, d_d2, d_nf, s, lc);
+  launch_knn<false>(*this, d_q, nullptr, Iso3d::identity(), nq, k, cap_dist, d_idx, d_d2, d_nf, entry_major, s, lc);
 }
 
 void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, float cap_dist, int32_t* d_idx, float* d_d2,
-                            int32_t* d_nf, cudaStream_t s, LaunchCounter& lc) const
+                            int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc) const
 {
   if (nq == 0) return;
   if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
@@ -458,7 +459,7 @@ void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior
     k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
-  launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, cap_dist, d_idx, d_d2, d_nf, s, lc);
+  launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, cap_dist, d_idx, d_d2, d_nf, entry_major, s, lc);
 }
 
 }  // namespace lsb

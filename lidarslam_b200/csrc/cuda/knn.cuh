@@ -38,17 +38,18 @@ struct KnnGrid {
   void build(const lsb_point* d_cloud, size_t m, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc);
 
   // kNN of nq float queries (xyz packed).  idx_out/d2_out: [nq * k], missing
-  // entries -1 / +inf.  nfound_out may be nullptr.
+  // entries -1 / +inf.  nfound_out may be nullptr.  Layout: query-major [nq][k], or
+  // entry-major [k][nq] (entry_major, coalesced for one-thread-per-query consumers).
   // cap_dist < 0: exact for every query (grid walk, then brute force for queries whose
   // neighbours are far away).  cap_dist >= 0: exact for every query whose k-th neighbour
   // lies within cap_dist; the others report nfound = min(k, m) with d2[k-1] > cap_dist^2
   // (possibly +inf), which is all the plane / blob matchers need (NEIGHBORS_TOO_FAR).
   void search(const float* d_queries_xyz, size_t nq, int k, float cap_dist, int32_t* d_idx_out, float* d_d2_out, int32_t* d_nfound_out,
-              cudaStream_t s, LaunchCounter& lc) const;
+              bool entry_major, cudaStream_t s, LaunchCounter& lc) const;
   // kNN of the keypoints kp[0..nq) moved by `prior` in double then cast to float
   // (KeypointsMatcher.cxx:118 + KDTreePCLAdaptor.h:96-101).
   void search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, float cap_dist, int32_t* d_idx_out, float* d_d2_out,
-                     int32_t* d_nfound_out, cudaStream_t s, LaunchCounter& lc) const;
+                     int32_t* d_nfound_out, bool entry_major, cudaStream_t s, LaunchCounter& lc) const;
 };
 
 }  // namespace lsb

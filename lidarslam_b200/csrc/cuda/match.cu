@@ -38,20 +38,35 @@ __device__ __forceinline__ int cloud_ring(const lsb_point* __restrict__ cloud, i
 
 __device__ __forceinline__ bool dev_isfinite(double v) { return (v - v) == 0.0; }
 
-__device__ __forceinline__ void write_record(LmRecord* __restrict__ rec, const Mat3d& A, const Vec3d& mean, const Vec3d& X, double w)
+// Residual records live in a structure-of-arrays layout (16 planes of doubles, plane f of
+// record i at rec[f * stride + i]) so that the per-thread accesses of the fit and LM kernels coalesce.
+constexpr int REC_W = 15;   // plane of the weight (w < 0: no residual)
+__device__ __forceinline__ void write_record(double* __restrict__ rec, size_t stride, const Mat3d& A, const Vec3d& mean, const Vec3d& X, double w)
 {
 #pragma unroll
-  for (int t = 0; t < 9; ++t) rec->A[t] = A.m[t];
-  rec->P[0] = mean.x; rec->P[1] = mean.y; rec->P[2] = mean.z;
-  rec->X[0] = X.x; rec->X[1] = X.y; rec->X[2] = X.z;
-  rec->w = w;
+  for (int t = 0; t < 9; ++t) rec[t * stride] = A.m[t];
+  rec[9 * stride] = mean.x; rec[10 * stride] = mean.y; rec[11 * stride] = mean.z;
+  rec[12 * stride] = X.x; rec[13 * stride] = X.y; rec[14 * stride] = X.z;
+  rec[REC_W * stride] = w;
+}
+__device__ __forceinline__ LmRecord load_record(const double* __restrict__ rec, size_t stride)
+{
+  LmRecord r;
+  r.w = rec[REC_W * stride];
+  if (r.w >= 0.0) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t) r.A[t] = rec[t * stride];
+#pragma unroll
+    for (int t = 0; t < 3; ++t) { r.P[t] = rec[(9 + t) * stride]; r.X[t] = rec[(12 + t) * stride]; }
+  }
+  return r;
 }
 
 // One thread per keypoint.  sel[] holds positions in the kNN list, in list order.
 template <int TYPE>
 __global__ void __launch_bounds__(FIT_TPB)
 k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cloud, const int32_t* __restrict__ nn_idx,
-      const float* __restrict__ nn_d2, const int32_t* __restrict__ nn_found, int k, FitParams fp, LmRecord* __restrict__ records,
+      const float* __restrict__ nn_d2, const int32_t* __restrict__ nn_found, int k, FitParams fp, double* __restrict__ records, size_t rec_stride,
       uint8_t* __restrict__ status, double* __restrict__ weight, int* __restrict__ hist)
 {
   __shared__ int s_hist[LSB_MATCH_N_STATUS];
@@ -61,9 +76,11 @@ k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cl
   if (i < nq) {
     int st = LSB_MATCH_SUCCESS;
     double w = 0.0;
-    const int32_t* idx = nn_idx + (size_t)i * k;
-    const float* d2 = nn_d2 + (size_t)i * k;
+    // neighbour lists are stored entry-major (entry t of query i at [t * nq + i]): coalesced
+    int32_t idx[KNN_MAX_K];
+    float d2[KNN_MAX_K];
     const int n = nn_found[i];
+    for (int t = 0; t < k; ++t) { idx[t] = nn_idx[(size_t)t * nq + i]; d2[t] = nn_d2[(size_t)t * nq + i]; }
     int sel[KNN_MAX_K];
     int nsel = 0;
     if (TYPE == LSB_EDGE) {
@@ -156,9 +173,9 @@ k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cl
           else w = 1.0;
         }
       }
-      if (st == LSB_MATCH_SUCCESS) write_record(records + i, A, mean, base, w);
+      if (st == LSB_MATCH_SUCCESS) write_record(records + i, rec_stride, A, mean, base, w);
     }
-    if (st != LSB_MATCH_SUCCESS) { w = 0.0; records[i].w = -1.0; }
+    if (st != LSB_MATCH_SUCCESS) { w = 0.0; records[REC_W * rec_stride + i] = -1.0; }
     status[i] = (uint8_t)st;
     weight[i] = w;
     atomicAdd(&s_hist[st], 1);
@@ -168,11 +185,11 @@ k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cl
 }
 
 // target empty: MatchingResults::Reset values (KeypointsMatcher.h:108-118)
-__global__ void k_fit_empty(int nq, LmRecord* __restrict__ records, uint8_t* __restrict__ status, double* __restrict__ weight)
+__global__ void k_fit_empty(int nq, double* __restrict__ records, size_t rec_stride, uint8_t* __restrict__ status, double* __restrict__ weight)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nq) return;
-  records[i].w = -1.0;
+  records[REC_W * rec_stride + i] = -1.0;
   status[i] = LSB_MATCH_UNKNOWN;
   weight[i] = 0.0;
 }
@@ -226,7 +243,7 @@ constexpr int LM_THREADS = 512;   // 16 warps; each warp folds LSB_LM_CHUNK / 32
 constexpr int LM_GROUPS = LSB_LM_CHUNK / 32;
 
 __global__ void __launch_bounds__(LM_THREADS, 1)
-k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, LmState* __restrict__ state,
+k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, double sat, LmState* __restrict__ state,
           LmPoint* __restrict__ point, double* __restrict__ part, unsigned* __restrict__ counter, int first)
 {
   __shared__ __align__(16) double s_pt_raw[sizeof(LmPoint) / sizeof(double)];
@@ -243,7 +260,7 @@ k_lm_eval(const LmRecord* __restrict__ records, int n, int nchunks, double sat, 
   for (int g = warp; g < LM_GROUPS; g += LM_THREADS / 32) {
     const int i = blockIdx.x * LSB_LM_CHUNK + g * 32 + lane;
     double out[LSB_LM_NSUM];
-    if (i < n) lm_eval_record(records[i], s_pt, sat, out);
+    if (i < n) lm_eval_record(load_record(records + i, rec_stride), s_pt, sat, out);
     else {
 #pragma unroll
       for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
@@ -321,7 +338,8 @@ void MatchWorkspace::begin_iteration(const size_t nk[3], cudaStream_t s)
   total = off[3];
   size_t maxq = std::max(nk[0], std::max(nk[1], nk[2]));
   nn_idx.reserve(maxq * KNN_MAX_K, s); nn_d2.reserve(maxq * KNN_MAX_K, s); nn_found.reserve(maxq, s);
-  records.reserve(total, s); status.reserve(total, s); weight.reserve(total, s);
+  rec_stride = (total + 31) / 32 * 32;
+  records.reserve(std::max<size_t>(16 * rec_stride, 16), s); status.reserve(total, s); weight.reserve(total, s);
   hist.reserve(3 * LSB_MATCH_N_STATUS, s);
   h_hist.reserve(3 * LSB_MATCH_N_STATUS);
   LSB_CUDA(cudaMemsetAsync(hist.p, 0, 3 * LSB_MATCH_N_STATUS * sizeof(int), s));
@@ -331,13 +349,13 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
                                 const lsb_match_params& mp, cudaStream_t s, LaunchCounter& lc)
 {
   if (nk == 0) return;
-  LmRecord* rec = records.p + off[type];
+  double* rec = records.p + off[type];
   uint8_t* st = status.p + off[type];
   double* wt = weight.p + off[type];
   int* h = hist.p + type * LSB_MATCH_N_STATUS;
   const unsigned G = div_up(nk, FIT_TPB);
   if (target.empty()) {
-    k_fit_empty<<<G, FIT_TPB, 0, s>>>((int)nk, rec, st, wt); LSB_LAUNCH_CHECK(); lc.add();
+    k_fit_empty<<<G, FIT_TPB, 0, s>>>((int)nk, rec, rec_stride, st, wt); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
   FitParams fp;
@@ -358,13 +376,13 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
   // planes / blobs only need neighbours within MaxNeighborsDistance (else NEIGHBORS_TOO_FAR);
   // the line neighbourhood selection needs the exact k nearest whatever their distance
   const float cap = (type == LSB_EDGE) ? -1.f : (float)mp.max_neighbors_distance * 1.0001f + 1e-3f;
-  target.search_points(d_kp, nk, prior, k, cap, nn_idx.p, nn_d2.p, nn_found.p, s, lc);
+  target.search_points(d_kp, nk, prior, k, cap, nn_idx.p, nn_d2.p, nn_found.p, /*entry_major=*/true, s, lc);
   t_knn.end(s);
   const int NQ = (int)nk;
   t_fit.begin(s);
-  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
-  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
-  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, st, wt, h);
+  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, rec_stride, st, wt, h);
+  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, rec_stride, st, wt, h);
+  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, rec_stride, st, wt, h);
   LSB_LAUNCH_CHECK(); lc.add();
   t_fit.end(s);
 }
@@ -387,7 +405,7 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_point.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d); LSB_LAUNCH_CHECK(); lc.add();
   t_lm.begin(s);
   for (int e = 0; e <= max_iter; ++e) {
-    k_lm_eval<<<nchunks, LM_THREADS, 0, s>>>(records.p, n, nchunks, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
+    k_lm_eval<<<nchunks, LM_THREADS, 0, s>>>(records.p, rec_stride, n, nchunks, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
     LSB_LAUNCH_CHECK(); lc.add();
   }
   t_lm.end(s);

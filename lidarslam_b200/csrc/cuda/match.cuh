@@ -13,7 +13,8 @@ namespace lsb {
 struct MatchWorkspace {
   DevBuf<int32_t> nn_idx, nn_found;
   DevBuf<float> nn_d2;
-  DevBuf<LmRecord> records;
+  DevBuf<double> records;           // 16 planes x rec_stride (structure of arrays)
+  size_t rec_stride = 0;
   DevBuf<uint8_t> status;
   DevBuf<double> weight;
   DevBuf<int> hist;                 // [3][LSB_MATCH_N_STATUS]

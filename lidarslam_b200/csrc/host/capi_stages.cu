@@ -101,7 +101,7 @@ int lsb_knn_search(lsb_slam* h, const lsb_point* cloud, size_t m, const float* q
     dq.reserve(std::max<size_t>(3 * nq, 1), h->stream); dd2.reserve(std::max<size_t>(nq * k, 1), h->stream); didx.reserve(std::max<size_t>(nq * k, 1), h->stream);
     if (nq) LSB_CUDA(cudaMemcpyAsync(dq.p, queries_xyz, 3 * nq * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     if (m) grid.build(h->tmp_cloud.p, m, 1.0f, nullptr, nullptr, h->stream, h->lc);
-    grid.search(dq.p, nq, k, -1.f, didx.p, dd2.p, nullptr, h->stream, h->lc);
+    grid.search(dq.p, nq, k, -1.f, didx.p, dd2.p, nullptr, /*entry_major=*/false, h->stream, h->lc);
     if (nq) {
       LSB_CUDA(cudaMemcpyAsync(idx_out, didx.p, nq * k * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
       LSB_CUDA(cudaMemcpyAsync(d2_out, dd2.p, nq * k * sizeof(float), cudaMemcpyDeviceToHost, h->stream));

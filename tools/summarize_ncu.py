@@ -1,0 +1,40 @@
+"""Prints the metrics DESIGN.md / profiles/ quote from an `ncu --set full` report:
+   python tools/summarize_ncu.py gpurun_out/prof.ncu-rep > profiles/r01_ncu_full_summary.txt"""
+import csv
+import io
+import subprocess
+import sys
+
+WANT = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg", "smsp__inst_executed.sum",
+        "sm__inst_executed_pipe_fp64.sum", "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sector_hit_rate.pct", "l1tex__t_sector_hit_rate.pct", "lts__t_bytes.sum",
+        "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct", "smsp__warp_issue_stalled_short_scoreboard_per_warp_active.pct",
+        "smsp__warp_issue_stalled_wait_per_warp_active.pct", "smsp__warp_issue_stalled_barrier_per_warp_active.pct",
+        "smsp__warp_issue_stalled_math_pipe_throttle_per_warp_active.pct", "smsp__warp_issue_stalled_branch_resolving_per_warp_active.pct",
+        "smsp__warp_issue_stalled_no_instruction_per_warp_active.pct", "smsp__warp_issue_stalled_lg_throttle_per_warp_active.pct"]
+
+
+def main(path, per_kernel=1):
+    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units = rows[0], rows[1]
+    name_i = hdr.index("Kernel Name")
+    seen = {}
+    for r in rows[2:]:
+        name = r[name_i].split("(")[0].replace("lsb::<unnamed>::", "").replace("void ", "")
+        key = (name, r[hdr.index("launch__grid_size")])
+        if seen.get(key, 0) >= per_kernel:
+            continue
+        seen[key] = seen.get(key, 0) + 1
+        print("==== %s" % name)
+        for w in WANT:
+            if w in hdr:
+                i = hdr.index(w)
+                print("  %-78s %16s %s" % (w, r[i], units[i]))
+
+
+if __name__ == "__main__":
+    main(sys.argv[1], int(sys.argv[2]) if len(sys.argv) > 2 else 1)
