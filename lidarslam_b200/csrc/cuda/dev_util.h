@@ -29,8 +29,10 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 #define LSB_CUDA(x) ::lsb::cuda_check((x), #x, __FILE__, __LINE__)
 #define LSB_LAUNCH_CHECK() ::lsb::cuda_check(cudaGetLastError(), "kernel launch", __FILE__, __LINE__)
 
-// Growable device array.  Growth reallocates (content is NOT preserved unless
-// keep=true); steady state never allocates.
+// Growable device array on the stream-ordered allocator: growth is a cudaMallocAsync /
+// cudaFreeAsync pair ordered on the handle's stream (no device synchronisation); the default
+// memory pool keeps freed blocks (release threshold raised in lsb_slam), so a growing map costs
+// O(log) cheap reallocations and steady state allocates nothing.  Content is kept only when asked.
 template <typename T>
 struct DevBuf {
   T* p = nullptr;
@@ -42,15 +44,14 @@ struct DevBuf {
   void reserve(size_t n, cudaStream_t s = 0, bool keep = false, size_t keep_n = 0)
   {
     if (n <= cap) return;
-    // geometric growth (x2, floor 64 Ki elements) so that a growing map reallocates O(log) times
+    // geometric growth (x2, floor 64 Ki elements)
     size_t ncap = cap ? cap : 65536;
     while (ncap < n) ncap = ncap * 2;
     T* q = nullptr;
-    LSB_CUDA(cudaMalloc(&q, ncap * sizeof(T)));
+    LSB_CUDA(cudaMallocAsync(&q, ncap * sizeof(T), s));
     if (p) {
       if (keep && keep_n) LSB_CUDA(cudaMemcpyAsync(q, p, keep_n * sizeof(T), cudaMemcpyDeviceToDevice, s));
-      LSB_CUDA(cudaStreamSynchronize(s));
-      cudaFree(p);
+      LSB_CUDA(cudaFreeAsync(p, s));
     }
     p = q;
     cap = ncap;

@@ -15,6 +15,12 @@ lsb_slam::lsb_slam(int dev) : device(dev)
 {
   LSB_CUDA(cudaSetDevice(dev));
   LSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  {  // keep freed blocks in the device's default pool: buffer growth must not hit the driver again
+    cudaMemPool_t pool;
+    LSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    unsigned long long keep = ~0ull;
+    LSB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  }
   for (auto& e : ev) LSB_CUDA(cudaEventCreate(&e));
   lsb_default_params(&P);
   KeyPointsExtractors[0].reset(new ExtractorGpu());
