@@ -227,8 +227,10 @@ LSB_API long lsb_get_match_debug(lsb_slam* h, int stage, int type, uint8_t* stat
  * field: 0 sin_angle 1 saliency 2 depth_gap 3 intensity_gap 4-6 {edge,plane,blob}_keypoint 7-9 {edge,plane,blob}_validity */
 LSB_API long lsb_get_ke_debug(lsb_slam* h, int device_id, int field, float* out, long cap);
 LSB_API int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s);
-/* When on, CUDA events bracket every kNN / fit / LM kernel launch on the handle's
- * stream and lsb_frame_stats.ms_knn / ms_fit / ms_lm are filled (small overhead). */
+/* When on, CUDA events bracket every kNN / fit / LM kernel launch and
+ * lsb_frame_stats.ms_knn / ms_fit / ms_lm are filled; the three keypoint types, which
+ * otherwise run on their own streams, are serialised on the handle's stream so that the
+ * durations are those of the kernels alone (slower frames: not for throughput runs). */
 LSB_API int lsb_set_profiling(lsb_slam* h, int on);
 LSB_API float lsb_get_overlap(const lsb_slam* h);                                              /* Slam::GetOverlapEstimation */
 LSB_API unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h);                       /* Slam.h TotalMatchedKeypoints */

@@ -173,7 +173,7 @@ LSB_HD bool lm_chol_solve6(const double* M, const double* b, double* y)
 }
 
 enum { LSB_LM_RUNNING = 0, LSB_LM_CONV_GRADIENT, LSB_LM_CONV_PARAMETER, LSB_LM_CONV_FUNCTION, LSB_LM_CONV_RADIUS,
-       LSB_LM_MAX_ITER, LSB_LM_FAIL_INVALID };
+       LSB_LM_MAX_ITER, LSB_LM_FAIL_INVALID, LSB_LM_SKIPPED /* not enough matches: never started */ };
 
 // Trust-region LM state machine.  Driver:
 //   lm_begin(s, x0, max_iter, two_d); E = evaluate(s.x); lm_first_eval(s, E);

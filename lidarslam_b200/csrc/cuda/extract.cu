@@ -16,6 +16,7 @@
 // All arithmetic is plain IEEE fp32 in the reference's operation order
 // (-fmad=false); trigonometry comes from common/detmath.h.
 #include "extract.cuh"
+#include <cstring>
 #include "../common/pca.h"
 #include <cub/cub.cuh>
 #include <cfloat>
@@ -303,35 +304,63 @@ k_label(const int* __restrict__ ring_start, const int* __restrict__ ring_end, co
 }
 
 // ---------------------------------------------------------------- K5 ---------
-__global__ void k_pack_flags(const uint8_t* __restrict__ label, int n, unsigned long long* __restrict__ out)
+__global__ void k_pack_flags(const uint8_t* __restrict__ label, int n, unsigned long long* __restrict__ out, uint32_t* __restrict__ d_counts)
 {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < 6) reinterpret_cast<unsigned long long*>(d_counts + 8)[j] = (j & 1) ? 0ull : ~0ull;   // time (min, max) per type
   if (j >= n) return;
   const unsigned long long l = label[j];
   out[j] = (l & 1ull) | (((l >> 1) & 1ull) << 21) | (((l >> 2) & 1ull) << 42);
 }
 
+// order-preserving map double -> uint64 (atomicMin / atomicMax on the point times)
+__device__ __forceinline__ unsigned long long time_ord(double d)
+{
+  const unsigned long long u = (unsigned long long)__double_as_longlong(d);
+  return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
+}
+
+// Scatter + per-type time range of the keypoints (Slam::InitUndistortion needs the min / max of the
+// `time` field over the keypoints, Slam.cxx:1293-1300: taken here so that it comes back with the counts).
+// d_counts: [0..2] counts, [3] nb rings, [8..19] = 3 x (min, max) as ordered uint64 (initialised by k_pack_flags).
 __global__ void k_scatter_keypoints(const lsb_point* __restrict__ pts, const uint32_t* __restrict__ src,
                                     const uint8_t* __restrict__ label, const unsigned long long* __restrict__ pos, int n,
                                     lsb_point* __restrict__ out0, lsb_point* __restrict__ out1, lsb_point* __restrict__ out2,
                                     uint32_t* __restrict__ d_counts)
 {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
-  const uint8_t l = label[j];
-  const unsigned long long p = pos[j];
-  const uint32_t p0 = (uint32_t)(p & 0x1fffffull), p1 = (uint32_t)((p >> 21) & 0x1fffffull), p2 = (uint32_t)((p >> 42) & 0x1fffffull);
-  if (l) {
-    const uint4* sp = reinterpret_cast<const uint4*>(pts) + 2 * (size_t)src[j];
-    const uint4 a = sp[0], b = sp[1];
-    if (l & 1) { uint4* o = reinterpret_cast<uint4*>(out0) + 2 * (size_t)p0; o[0] = a; o[1] = b; }
-    if (l & 2) { uint4* o = reinterpret_cast<uint4*>(out1) + 2 * (size_t)p1; o[0] = a; o[1] = b; }
-    if (l & 4) { uint4* o = reinterpret_cast<uint4*>(out2) + 2 * (size_t)p2; o[0] = a; o[1] = b; }
+  uint8_t l = 0;
+  unsigned long long t_ord = 0ull;
+  if (j < n) {
+    l = label[j];
+    const unsigned long long p = pos[j];
+    const uint32_t p0 = (uint32_t)(p & 0x1fffffull), p1 = (uint32_t)((p >> 21) & 0x1fffffull), p2 = (uint32_t)((p >> 42) & 0x1fffffull);
+    if (l) {
+      const uint4* sp = reinterpret_cast<const uint4*>(pts) + 2 * (size_t)src[j];
+      const uint4 a = sp[0], b = sp[1];
+      if (l & 1) { uint4* o = reinterpret_cast<uint4*>(out0) + 2 * (size_t)p0; o[0] = a; o[1] = b; }
+      if (l & 2) { uint4* o = reinterpret_cast<uint4*>(out1) + 2 * (size_t)p1; o[0] = a; o[1] = b; }
+      if (l & 4) { uint4* o = reinterpret_cast<uint4*>(out2) + 2 * (size_t)p2; o[0] = a; o[1] = b; }
+      t_ord = time_ord(__longlong_as_double((long long)(((unsigned long long)b.y << 32) | b.x)));
+    }
+    if (j == n - 1) {
+      d_counts[0] = p0 + (l & 1);
+      d_counts[1] = p1 + ((l >> 1) & 1);
+      d_counts[2] = p2 + ((l >> 2) & 1);
+    }
   }
-  if (j == n - 1) {
-    d_counts[0] = p0 + (l & 1);
-    d_counts[1] = p1 + ((l >> 1) & 1);
-    d_counts[2] = p2 + ((l >> 2) & 1);
+  if (__ballot_sync(0xffffffffu, l != 0) == 0u) return;
+  unsigned long long* tmm = reinterpret_cast<unsigned long long*>(d_counts + 8);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const bool in = (l >> k) & 1;
+    unsigned long long mn = in ? t_ord : ~0ull, mx = in ? t_ord : 0ull;
+#pragma unroll
+    for (int off = 16; off; off >>= 1) {
+      mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, off));
+      mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    }
+    if ((threadIdx.x & 31) == 0 && mn != ~0ull) { atomicMin(tmm + 2 * k, mn); atomicMax(tmm + 2 * k + 1, mx); }
   }
 }
 
@@ -415,8 +444,8 @@ void ExtractorGpu::compute(const lsb_point* d_pts, size_t n_, cudaStream_t s, La
   scan_in.reserve(n, s); scan_out.reserve(n, s);
   for (int k = 0; k < 3; ++k) kp[k].reserve(n, s);
   ring_start.reserve(KE_MAX_RINGS, s); ring_end.reserve(KE_MAX_RINGS, s);
-  d_counts.reserve(8, s); d_az.reserve(4, s);
-  h_counts.reserve(8); h_az.reserve(4);
+  d_counts.reserve(24, s); d_az.reserve(4, s);
+  h_counts.reserve(24); h_az.reserve(4);
 
   const unsigned G = div_up(n, TPB);
   // K1: stable bucket by laser_id
@@ -480,14 +509,22 @@ void ExtractorGpu::compute(const lsb_point* d_pts, size_t n_, cudaStream_t s, La
                                                  P.edge_intensity_gap_threshold, P.plane_sin_angle_threshold);
   LSB_LAUNCH_CHECK(); lc.add();
   // K5
-  k_pack_flags<<<G, TPB, 0, s>>>(label.p, N, scan_in.p); LSB_LAUNCH_CHECK(); lc.add();
+  k_pack_flags<<<G, TPB, 0, s>>>(label.p, N, scan_in.p, d_counts.p); LSB_LAUNCH_CHECK(); lc.add();
   tb = cub_tmp.cap;
   LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, scan_in.p, scan_out.p, N, s)); lc.add(2);
   k_scatter_keypoints<<<G, TPB, 0, s>>>(d_pts, src.p, label.p, scan_out.p, N, kp[0].p, kp[1].p, kp[2].p, d_counts.p);
   LSB_LAUNCH_CHECK(); lc.add();
-  LSB_CUDA(cudaMemcpyAsync(h_counts.p, d_counts.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaMemcpyAsync(h_counts.p, d_counts.p, 20 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
   LSB_CUDA(cudaStreamSynchronize(s));
-  for (int k = 0; k < 3; ++k) counts[k] = h_counts.p[k];
+  for (int k = 0; k < 3; ++k) {
+    counts[k] = h_counts.p[k];
+    for (int e = 0; e < 2; ++e) {
+      unsigned long long u;
+      std::memcpy(&u, h_counts.p + 8 + 2 * (2 * k + e), 8);
+      u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
+      std::memcpy(e ? &time_max[k] : &time_min[k], &u, 8);
+    }
+  }
   if (h_counts.p[3] > (uint32_t)KE_MAX_RINGS) throw CudaError(LSB_E_CAPACITY, "laser_id >= 1024 is not supported");
   if (h_counts.p[3] > nb_rings) nb_rings = h_counts.p[3];
 }

@@ -14,6 +14,7 @@ struct ExtractorGpu {
   size_t n = 0;                    // points of the last frame
   unsigned nb_rings = 0;           // max laser_id + 1 (never shrinks, SSKE.cxx:156-164)
   uint32_t counts[3] = {0, 0, 0};  // keypoints per type of the last frame
+  double time_min[3] = {0, 0, 0}, time_max[3] = {0, 0, 0};   // range of their `time` field (valid where counts[k] > 0)
 
   // ring-major ("scan line") order: position j <-> (ring, index in ring)
   DevBuf<uint32_t> key_a, key_b, idx_a, src;   // src[j] = input index of ring-ordered point j
@@ -23,7 +24,7 @@ struct ExtractorGpu {
   DevBuf<float> angles, depth_gap, saliency, intensity_gap, nms_vals;
   DevBuf<unsigned long long> scan_in, scan_out;
   DevBuf<lsb_point> kp[3];                     // extracted keypoints, ring-major / index-minor
-  DevBuf<uint32_t> d_counts;                   // [4]: 3 counts + nb_rings
+  DevBuf<uint32_t> d_counts;                   // 3 counts, nb_rings, [4] azimuth count, [8..19] time ranges
   DevBuf<float> az_angles, az_sorted;          // azimuthal resolution estimation
   DevBuf<float> d_az;                          // [2]: resolution, number of angles
   DevBuf<unsigned char> cub_tmp;

@@ -259,19 +259,29 @@ __global__ void k_flag_old(const lsb_point* __restrict__ pts, int n, double curr
 // ============================================================== host side ====
 static inline float ord2f_host(int i) { const int j = (i >= 0) ? i : (i ^ 0x7fffffff); float f; std::memcpy(&f, &j, 4); return f; }
 
-void cloud_bbox(const lsb_point* d_cloud, size_t n, float mn[3], float mx[3], DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
-                cudaStream_t s, LaunchCounter& lc)
+void cloud_bbox_async(const lsb_point* d_cloud, size_t n, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc)
 {
   d_bbox.reserve(8, s); h_bbox.reserve(8);
   k_bbox_init<<<1, 32, 0, s>>>((int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
   k_bbox<<<std::min(div_up(n, TPB), 592u), TPB, 0, s>>>(d_cloud, (int)n, (int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
   LSB_CUDA(cudaMemcpyAsync(h_bbox.p, d_bbox.p, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
-  LSB_CUDA(cudaStreamSynchronize(s));
+}
+
+void bbox_decode(const float* h_bbox, float mn[3], float mx[3])
+{
   for (int a = 0; a < 3; ++a) {
     int v;
-    std::memcpy(&v, h_bbox.p + a, 4); mn[a] = ord2f_host(v);
-    std::memcpy(&v, h_bbox.p + 3 + a, 4); mx[a] = ord2f_host(v);
+    std::memcpy(&v, h_bbox + a, 4); mn[a] = ord2f_host(v);
+    std::memcpy(&v, h_bbox + 3 + a, 4); mx[a] = ord2f_host(v);
   }
+}
+
+void cloud_bbox(const lsb_point* d_cloud, size_t n, float mn[3], float mx[3], DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
+                cudaStream_t s, LaunchCounter& lc)
+{
+  cloud_bbox_async(d_cloud, n, d_bbox, h_bbox, s, lc);
+  LSB_CUDA(cudaStreamSynchronize(s));
+  bbox_decode(h_bbox.p, mn, mx);
 }
 
 static GridGeom make_geom(const RollingGridGpu& m)
@@ -351,13 +361,23 @@ void RollingGridGpu::Roll(const float mn[3], const float mx[3], cudaStream_t s, 
   for (int a = 0; a < 3; ++a) Position[a] += (float)vo[a] * r;
 }
 
-void RollingGridGpu::Add(const lsb_point* d_cloud, size_t n, bool fixed, double currentTime, bool roll, cudaStream_t s, LaunchCounter& lc)
+// Add (:160-318) in three host phases so that the three maps of a frame can run on their own
+// streams with their read-backs overlapped: AddBegin (bbox of the cloud), AddSort (roll, then
+// key / sort / replay / gather), AddMerge (rank merge of the new leaves).
+void RollingGridGpu::AddBegin(const lsb_point* d_cloud, size_t n, bool roll, cudaStream_t s, LaunchCounter& lc)
 {
   if (n == 0) return;
   if (Sampling == LSB_SAMPLING_CENTROID) throw CudaError(LSB_E_INVALID, "SamplingMode::CENTROID is not implemented on the GPU map");
+  if (roll) cloud_bbox_async(d_cloud, n, d_bbox, h_bbox, s, lc);
+}
+
+void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, double currentTime, bool roll, cudaStream_t s, LaunchCounter& lc)
+{
+  if (n == 0) return;
   if (roll) {
     float mn[3], mx[3];
-    cloud_bbox(d_cloud, n, mn, mx, d_bbox, h_bbox, s, lc);
+    LSB_CUDA(cudaStreamSynchronize(s));
+    bbox_decode(h_bbox.p, mn, mx);
     Roll(mn, mx, s, lc);
   }
   const GridGeom g = make_geom(*this);
@@ -379,6 +399,11 @@ void RollingGridGpu::Add(const lsb_point* d_cloud, size_t n, bool fixed, double 
   k_gather_inserts<<<G, TPB, 0, s>>>(flags.p, scan.p, N, nk_b.p, pts_b.p, counts_b.p, ins_keys.p, ins_pts.p, ins_counts.p, d_info.p);
   LSB_LAUNCH_CHECK(); lc.add();
   LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+}
+
+void RollingGridGpu::AddMerge(size_t n, cudaStream_t s, LaunchCounter& lc)
+{
+  if (n == 0) return;
   LSB_CUDA(cudaStreamSynchronize(s));
   const bool updated = h_info.p[0] != 0;
   const size_t n_ins = h_info.p[1];
@@ -394,6 +419,13 @@ void RollingGridGpu::Add(const lsb_point* d_cloud, size_t n, bool fixed, double 
     NbPoints += (unsigned)n_ins;
   }
   if (updated) ResetTree();
+}
+
+void RollingGridGpu::Add(const lsb_point* d_cloud, size_t n, bool fixed, double currentTime, bool roll, cudaStream_t s, LaunchCounter& lc)
+{
+  AddBegin(d_cloud, n, roll, s, lc);
+  AddSort(d_cloud, n, fixed, currentTime, roll, s, lc);
+  AddMerge(n, s, lc);
 }
 
 void RollingGridGpu::ClearOldPoints(double currentTime, cudaStream_t s, LaunchCounter& lc)
@@ -438,44 +470,67 @@ void RollingGridGpu::BuildSubMapKdTree(cudaStream_t s, LaunchCounter& lc)
   build_grid(nullptr, nullptr, s, lc);
 }
 
-void RollingGridGpu::BuildSubMapKdTree(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc)
+// BuildSubMapKdTree(mn, mx, minNbPoints) (:362-442) in two host phases (SubMapSelect enqueues the
+// first selection pass and its count read-back, SubMapFinish consumes it and builds the kNN grid)
+// so that the three maps overlap their read-backs on their own streams.
+void RollingGridGpu::submap_pass(int mode, size_t offset, cudaStream_t s, LaunchCounter& lc)
+{
+  const int n = (int)n_entries;
+  k_flag_entries<<<div_up(n_entries, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, sub_lo[0], sub_lo[1], sub_lo[2],
+                                                        sub_hi[0], sub_hi[1], sub_hi[2], mode, MinFramesPerVoxel, flags.p);
+  LSB_LAUNCH_CHECK(); lc.add();
+  size_t tb = cub_tmp.cap;
+  LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, n, s)); lc.add(2);
+  k_compact<<<div_up(n_entries, TPB), TPB, 0, s>>>(flags.p, scan.p, n, nullptr, pts.p, nullptr, nullptr, submap.p + offset, nullptr, d_info.p);
+  LSB_LAUNCH_CHECK(); lc.add();
+  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+}
+
+void RollingGridGpu::SubMapSelect(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc)
 {
   const GridGeom g = make_geom(*this);
-  int lo[3], hi[3];
   const float o[3] = {g.ox, g.oy, g.oz};
   for (int a = 0; a < 3; ++a) {
-    lo[a] = std::max(pos2vox(mn[a], o[a], g.res), 0);
-    hi[a] = std::min(pos2vox(mx[a], o[a], g.res), GridSize - 1);
+    sub_lo[a] = std::max(pos2vox(mn[a], o[a], g.res), 0);
+    sub_hi[a] = std::min(pos2vox(mx[a], o[a], g.res), GridSize - 1);
   }
   n_submap = 0;
+  sub_min_nb = minNbPoints;
+  sub_filter = !(minNbPoints < 0 || MinFramesPerVoxel <= 1);
   submap.reserve(std::max<size_t>(n_entries, 1), s);
   if (n_entries) {
-    const int n = (int)n_entries;
     ensure_scratch(n_entries, s);
-    const bool filter = !(minNbPoints < 0 || MinFramesPerVoxel <= 1);
-    auto pass = [&](int mode, size_t offset) -> size_t {
-      k_flag_entries<<<div_up(n_entries, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], mode,
-                                                            MinFramesPerVoxel, flags.p);
-      LSB_LAUNCH_CHECK(); lc.add();
-      size_t tb = cub_tmp.cap;
-      LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, n, s)); lc.add(2);
-      k_compact<<<div_up(n_entries, TPB), TPB, 0, s>>>(flags.p, scan.p, n, nullptr, pts.p, nullptr, nullptr, submap.p + offset, nullptr, d_info.p);
-      LSB_LAUNCH_CHECK(); lc.add();
-      LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    submap_pass(sub_filter ? 1 : 0, 0, s, lc);
+  }
+}
+
+void RollingGridGpu::SubMapFinish(cudaStream_t s, LaunchCounter& lc)
+{
+  if (n_entries) {
+    LSB_CUDA(cudaStreamSynchronize(s));
+    n_submap = h_info.p[2];
+    if (sub_filter && (int)n_submap < sub_min_nb) {
+      submap_pass(2, n_submap, s, lc);
       LSB_CUDA(cudaStreamSynchronize(s));
-      return h_info.p[2];
-    };
-    n_submap = pass(filter ? 1 : 0, 0);
-    if (filter && (int)n_submap < minNbPoints) n_submap += pass(2, n_submap);
+      n_submap += h_info.p[2];
+    }
   }
   // every submap point lies in an outer voxel of [lo, hi]: host-known kNN grid bounds (with slack)
+  const GridGeom g = make_geom(*this);
+  const float o[3] = {g.ox, g.oy, g.oz};
   float blo[3], bhi[3];
   for (int a = 0; a < 3; ++a) {
-    blo[a] = o[a] + ((float)lo[a] - 0.5f) * g.res - 0.01f * g.res;
-    bhi[a] = o[a] + ((float)hi[a] + 0.5f) * g.res + 0.01f * g.res;
+    blo[a] = o[a] + ((float)sub_lo[a] - 0.5f) * g.res - 0.01f * g.res;
+    bhi[a] = o[a] + ((float)sub_hi[a] + 0.5f) * g.res + 0.01f * g.res;
   }
-  const bool bounded = lo[0] <= hi[0] && lo[1] <= hi[1] && lo[2] <= hi[2];
+  const bool bounded = sub_lo[0] <= sub_hi[0] && sub_lo[1] <= sub_hi[1] && sub_lo[2] <= sub_hi[2];
   build_grid(bounded ? blo : nullptr, bounded ? bhi : nullptr, s, lc);
+}
+
+void RollingGridGpu::BuildSubMapKdTree(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc)
+{
+  SubMapSelect(mn, mx, minNbPoints, s, lc);
+  SubMapFinish(s, lc);
 }
 
 void RollingGridGpu::SetGridSize(int size, cudaStream_t s, LaunchCounter& lc)

@@ -53,9 +53,15 @@ struct RollingGridGpu {
   void Roll(const float mn[3], const float mx[3], cudaStream_t s, LaunchCounter& lc);   // :117-157
   // Add (:160-318) of a DEVICE cloud
   void Add(const lsb_point* d_cloud, size_t n, bool fixed, double currentTime, bool roll, cudaStream_t s, LaunchCounter& lc);
+  // the same in three host phases (one stream per map, read-backs overlapped)
+  void AddBegin(const lsb_point* d_cloud, size_t n, bool roll, cudaStream_t s, LaunchCounter& lc);
+  void AddSort(const lsb_point* d_cloud, size_t n, bool fixed, double currentTime, bool roll, cudaStream_t s, LaunchCounter& lc);
+  void AddMerge(size_t n, cudaStream_t s, LaunchCounter& lc);
   void ClearOldPoints(double currentTime, cudaStream_t s, LaunchCounter& lc);           // :325-350
   void BuildSubMapKdTree(cudaStream_t s, LaunchCounter& lc);                             // :353-359
   void BuildSubMapKdTree(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc);   // :362-442
+  void SubMapSelect(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc);
+  void SubMapFinish(cudaStream_t s, LaunchCounter& lc);
   bool IsSubMapKdTreeValid() const { return tree_valid && n_submap > 0; }               // RollingGrid.h:132-135
   bool IsTimeThreshold() const { return DecayingThreshold > 0; }
   void ResetTree() { tree_valid = false; n_submap = 0; grid.clear(); }
@@ -64,9 +70,14 @@ struct RollingGridGpu {
   void build_grid(const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc);
   size_t compact_entries(cudaStream_t s, LaunchCounter& lc);   // keeps entries with flags[i] != 0
   void ensure_scratch(size_t n, cudaStream_t s);
+  void submap_pass(int mode, size_t offset, cudaStream_t s, LaunchCounter& lc);
+  int sub_lo[3] = {0, 0, 0}, sub_hi[3] = {-1, -1, -1}, sub_min_nb = -1;
+  bool sub_filter = false;
 };
 
-// min/max of the xyz of a device cloud (pcl::getMinMax3D); one stream sync
+// min/max of the xyz of a device cloud (pcl::getMinMax3D): enqueue + decode after a sync, or both with one sync
+void cloud_bbox_async(const lsb_point* d_cloud, size_t n, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc);
+void bbox_decode(const float* h_bbox, float mn[3], float mx[3]);
 void cloud_bbox(const lsb_point* d_cloud, size_t n, float mn[3], float mx[3], DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
                 cudaStream_t s, LaunchCounter& lc);
 

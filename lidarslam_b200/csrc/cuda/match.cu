@@ -316,11 +316,14 @@ k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchu
 }
 
 __global__ void k_lm_begin(LmState* state, LmPoint* point, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5,
-                           int max_iter, int two_d)
+                           int max_iter, int two_d, const int* __restrict__ hist, unsigned min_matches)
 {
   const double x[6] = {x0, x1, x2, x3, x4, x5};
   LmState s;
   lm_begin(s, x, max_iter, two_d);
+  unsigned matched = 0;
+  for (int t = 0; t < 3; ++t) matched += (unsigned)hist[t * LSB_MATCH_N_STATUS + LSB_MATCH_SUCCESS];
+  if (matched < min_matches) { s.done = 1; s.term = LSB_LM_SKIPPED; }
   *state = s;
   LmPoint pt;
   lm_make_point(x, pt);
@@ -336,8 +339,10 @@ void MatchWorkspace::begin_iteration(const size_t nk[3], cudaStream_t s)
   off[0] = 0;
   for (int k = 0; k < 3; ++k) off[k + 1] = off[k] + nk[k];
   total = off[3];
-  size_t maxq = std::max(nk[0], std::max(nk[1], nk[2]));
-  nn_idx.reserve(maxq * KNN_MAX_K, s); nn_d2.reserve(maxq * KNN_MAX_K, s); nn_found.reserve(maxq, s);
+  for (int k = 0; k < 3; ++k) {
+    const size_t q = std::max<size_t>(nk[k], 1);
+    nn_idx[k].reserve(q * KNN_MAX_K, s); nn_d2[k].reserve(q * KNN_MAX_K, s); nn_found[k].reserve(q, s);
+  }
   rec_stride = (total + 31) / 32 * 32;
   records.reserve(std::max<size_t>(16 * rec_stride, 16), s); status.reserve(total, s); weight.reserve(total, s);
   hist.reserve(3 * LSB_MATCH_N_STATUS, s);
@@ -376,13 +381,13 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
   // planes / blobs only need neighbours within MaxNeighborsDistance (else NEIGHBORS_TOO_FAR);
   // the line neighbourhood selection needs the exact k nearest whatever their distance
   const float cap = (type == LSB_EDGE) ? -1.f : (float)mp.max_neighbors_distance * 1.0001f + 1e-3f;
-  target.search_points(d_kp, nk, prior, k, cap, nn_idx.p, nn_d2.p, nn_found.p, /*entry_major=*/true, s, lc);
+  target.search_points(d_kp, nk, prior, k, cap, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, /*entry_major=*/true, s, lc);
   t_knn.end(s);
   const int NQ = (int)nk;
   t_fit.begin(s);
-  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, rec_stride, st, wt, h);
-  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, rec_stride, st, wt, h);
-  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx.p, nn_d2.p, nn_found.p, k, fp, rec, rec_stride, st, wt, h);
+  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h);
+  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h);
+  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h);
   LSB_LAUNCH_CHECK(); lc.add();
   t_fit.end(s);
 }
@@ -396,13 +401,16 @@ void MatchWorkspace::read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaSt
     for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) hist_out[t][q] = h_hist.p[t * LSB_MATCH_N_STATUS + q];
 }
 
-LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, double saturation, cudaStream_t s, LaunchCounter& lc)
+LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches,
+                              int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc)
 {
   const int n = (int)total;
   const int nchunks = std::max(1, (int)div_up(total, LSB_LM_CHUNK));
   part_a.reserve((size_t)nchunks * LSB_LM_NSUM, s);
   lm_state.reserve(1, s); lm_point.reserve(1, s); lm_counter.reserve(1, s); h_lm.reserve(1);
-  k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_point.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d); LSB_LAUNCH_CHECK(); lc.add();
+  k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_point.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d,
+                             hist.p, min_matches);
+  LSB_LAUNCH_CHECK(); lc.add();
   t_lm.begin(s);
   for (int e = 0; e <= max_iter; ++e) {
     k_lm_eval<<<nchunks, LM_THREADS, 0, s>>>(records.p, rec_stride, n, nchunks, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
@@ -410,9 +418,12 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   }
   t_lm.end(s);
   t_lm.launches += (unsigned)max_iter;
-  d2h_bytes += sizeof(LmState);
+  d2h_bytes += sizeof(LmState) + 3 * LSB_MATCH_N_STATUS * sizeof(int);
+  LSB_CUDA(cudaMemcpyAsync(h_hist.p, hist.p, 3 * LSB_MATCH_N_STATUS * sizeof(int), cudaMemcpyDeviceToHost, s));
   LSB_CUDA(cudaMemcpyAsync(h_lm.p, lm_state.p, sizeof(LmState), cudaMemcpyDeviceToHost, s));
   LSB_CUDA(cudaStreamSynchronize(s));
+  for (int t = 0; t < 3; ++t)
+    for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) hist_out[t][q] = h_hist.p[t * LSB_MATCH_N_STATUS + q];
   return *h_lm.p;
 }
 

@@ -11,8 +11,8 @@ namespace lsb {
 // Everything one ICP iteration needs on the device.  Records / status / weight are
 // index-aligned with the keypoints, the three types concatenated EDGE | PLANE | BLOB.
 struct MatchWorkspace {
-  DevBuf<int32_t> nn_idx, nn_found;
-  DevBuf<float> nn_d2;
+  DevBuf<int32_t> nn_idx[3], nn_found[3];   // per type: the three types are matched on their own streams
+  DevBuf<float> nn_d2[3];
   DevBuf<double> records;           // 16 planes x rec_stride (structure of arrays)
   size_t rec_stride = 0;
   DevBuf<uint8_t> status;
@@ -35,8 +35,12 @@ struct MatchWorkspace {
                   cudaStream_t s, LaunchCounter& lc);
   // reads the status histograms back (one stream sync); hist_out[3][LSB_MATCH_N_STATUS]
   void read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s);
-  // LocalOptimizer::Solve on the current records; returns the final state (one stream sync)
-  LmState solve(const double x0[6], int max_iter, int two_d, double saturation, cudaStream_t s, LaunchCounter& lc);
+  // LocalOptimizer::Solve on the current records; returns the final state and the match histograms
+  // with ONE stream sync.  The "enough matches" test of the caller (Slam.cxx:919, :1098) is taken on
+  // the device too: below min_matches the LM launches exit at once and the state comes back with
+  // term == LSB_LM_SKIPPED (x == x0).
+  LmState solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches,
+                int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc);
 };
 
 }  // namespace lsb

@@ -160,19 +160,21 @@ void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx)
   mx = ord2d(h_mm[1]);
 }
 
-void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,
-                          PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc)
+void dev_transformed_bbox_async(const lsb_point* d_pts, size_t n, const Iso3d& T, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
+                                cudaStream_t s, LaunchCounter& lc)
 {
   d_bbox.reserve(8, s); h_bbox.reserve(8);
   k_bbox_init<<<1, 32, 0, s>>>((int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
   if (n) { k_transformed_bbox<<<std::min(div_up(n, TPB), 592u), TPB, 0, s>>>(d_pts, (int)n, T, (int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add(); }
   LSB_CUDA(cudaMemcpyAsync(h_bbox.p, d_bbox.p, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+}
+
+void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,
+                          PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc)
+{
+  dev_transformed_bbox_async(d_pts, n, T, d_bbox, h_bbox, s, lc);
   LSB_CUDA(cudaStreamSynchronize(s));
-  for (int a = 0; a < 3; ++a) {
-    int v, j;
-    std::memcpy(&v, h_bbox.p + a, 4); j = (v >= 0) ? v : (v ^ 0x7fffffff); std::memcpy(&mn[a], &j, 4);
-    std::memcpy(&v, h_bbox.p + 3 + a, 4); j = (v >= 0) ? v : (v ^ 0x7fffffff); std::memcpy(&mx[a], &j, 4);
-  }
+  bbox_decode(h_bbox.p, mn, mx);
 }
 
 }  // namespace lsb

@@ -242,7 +242,12 @@ long lsb_get_ke_debug(lsb_slam* h, int device_id, int field, float* out, long ca
   });
 }
 int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s) { *s = h->Stats; return LSB_OK; }
-int lsb_set_profiling(lsb_slam* h, int on) { h->mw.t_knn.enabled = h->mw.t_fit.enabled = h->mw.t_lm.enabled = (on != 0); return LSB_OK; }
+int lsb_set_profiling(lsb_slam* h, int on)
+{
+  h->mw.t_knn.enabled = h->mw.t_fit.enabled = h->mw.t_lm.enabled = (on != 0);
+  h->serial_types = (on != 0);   // kernel durations are taken without overlap between the keypoint types
+  return LSB_OK;
+}
 float lsb_get_overlap(const lsb_slam* h) { return h->OverlapEstimation; }
 unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h) { return h->TotalMatchedKeypoints; }
 

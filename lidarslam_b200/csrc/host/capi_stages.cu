@@ -146,7 +146,7 @@ int lsb_match_and_solve(lsb_slam* h, const lsb_point* const keypoints[3], const 
     }
     double x0[6];
     iso_to_xyzrpy(T, x0);
-    const LmState st = mw.solve(x0, lm_max_iter, h->P.two_d_mode != 0, mp->saturation_distance, h->stream, h->lc);
+    const LmState st = mw.solve(x0, lm_max_iter, h->P.two_d_mode != 0, mp->saturation_distance, 1u, hist, h->stream, h->lc);
     ToRowMajor(xyzrpy_to_iso(st.x), pose_out_rowmajor);
     *lm_accepted_steps = st.num_successful;
     *lm_iterations = st.iter;

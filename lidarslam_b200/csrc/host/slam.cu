@@ -5,6 +5,7 @@
 #include <cstring>
 #include <cmath>
 #include <cfloat>
+#include <limits>
 #include <algorithm>
 
 using namespace lsb;
@@ -22,6 +23,9 @@ lsb_slam::lsb_slam(int dev) : device(dev)
     LSB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
   }
   for (auto& e : ev) LSB_CUDA(cudaEventCreate(&e));
+  for (auto& t : tstream) LSB_CUDA(cudaStreamCreateWithFlags(&t, cudaStreamNonBlocking));
+  LSB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+  for (auto& e : ev_join) LSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   lsb_default_params(&P);
   KeyPointsExtractors[0].reset(new ExtractorGpu());
   // Slam.cxx:153-157: resolution is snapped with the leaf size at call time (0.2 -> 10.0)
@@ -41,9 +45,29 @@ lsb_slam::lsb_slam(int dev) : device(dev)
 lsb_slam::~lsb_slam()
 {
   cudaSetDevice(device);
+  for (auto& t : tstream) if (t) cudaStreamSynchronize(t);
   if (stream) cudaStreamSynchronize(stream);
   for (auto& e : ev) if (e) cudaEventDestroy(e);
+  if (ev_fork) cudaEventDestroy(ev_fork);
+  for (auto& e : ev_join) if (e) cudaEventDestroy(e);
+  for (auto& t : tstream) if (t) cudaStreamDestroy(t);
   if (stream) cudaStreamDestroy(stream);
+}
+
+void lsb_slam::Fork()
+{
+  if (serial_types) return;
+  LSB_CUDA(cudaEventRecord(ev_fork, stream));
+  for (auto& t : tstream) LSB_CUDA(cudaStreamWaitEvent(t, ev_fork, 0));
+}
+
+void lsb_slam::Join()
+{
+  if (serial_types) return;
+  for (int k = 0; k < 3; ++k) {
+    LSB_CUDA(cudaEventRecord(ev_join[k], tstream[k]));
+    LSB_CUDA(cudaStreamWaitEvent(stream, ev_join[k], 0));
+  }
 }
 
 void lsb_slam::ClearMaps()
@@ -119,7 +143,10 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
     }
     f.device_id = 0;
     if (n[i]) {
-      if (on_device) {
+      if (on_device && KeyPointsExtractors.size() == 1 && BaseToLidarOffsets.empty()) {
+        // one sensor, no calibration: the device id selects nothing (Slam.cxx:764-780), no read-back
+        f.device_id = KeyPointsExtractors.begin()->first;
+      } else if (on_device) {
         lsb_point first;
         LSB_CUDA(cudaMemcpyAsync(&first, frames[i], sizeof(lsb_point), cudaMemcpyDeviceToHost, stream));
         LSB_CUDA(cudaStreamSynchronize(stream));
@@ -140,6 +167,7 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   uint32_t n_submap[3];
   for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // the map update invalidates the submaps
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
+  Join();
   LSB_CUDA(cudaEventRecord(ev[4], stream));
   LSB_CUDA(cudaEventSynchronize(ev[4]));
   LogCurrentFrameState(CurrentTime);
@@ -190,6 +218,8 @@ bool lsb_slam::CheckFrames(int n_frames, const size_t* n, const uint64_t* stamp_
 void lsb_slam::ExtractKeypoints()
 {
   for (int k = 0; k < 3; ++k) { PreviousKeypoints[k].swap(CurrentKeypoints[k]); CurrentKeypoints[k].n = 0; }   // :751
+  KpTimeMin = std::numeric_limits<double>::max();
+  KpTimeMax = std::numeric_limits<double>::lowest();
   // With several input frames the extractor buffers are reused, so keypoints are
   // appended to the aggregate right after each extraction.
   for (size_t fi = 0; fi < NbCurrentFrames; ++fi) {
@@ -214,6 +244,11 @@ void lsb_slam::ExtractKeypoints()
       const Iso3d tf = GetBaseToLidarOffset(f.device_id);
       const bool ident = iso_is_approx(tf, Iso3d::identity());
       if (!ident || timeOffset != 0.0) dev_aggregate(agg.buf.p + start, cnt, timeOffset, tf, !ident, stream, lc);
+      // time range of the aggregate: t -> t + offset is monotone, so min / max commute with it
+      const double lo = (timeOffset != 0.0) ? ke.time_min[k] + timeOffset : ke.time_min[k];
+      const double hi = (timeOffset != 0.0) ? ke.time_max[k] + timeOffset : ke.time_max[k];
+      KpTimeMin = std::min(KpTimeMin, lo);
+      KpTimeMax = std::max(KpTimeMax, hi);
     }
   }
 }
@@ -281,8 +316,9 @@ void lsb_slam::ComputeEgoMotion()
   }
   // Frame-to-frame registration (:839-964)
   if (P.ego_motion == LSB_EGO_REGISTRATION || P.ego_motion == LSB_EGO_MOTION_EXTRAPOLATION_AND_REGISTRATION) {
+    Fork();
     for (int k = 0; k < 2; ++k) {
-      if (PreviousKeypoints[k].n) EgoGrids[k].build(PreviousKeypoints[k].buf.p, PreviousKeypoints[k].n, 1.0f, nullptr, nullptr, stream, lc);
+      if (PreviousKeypoints[k].n) EgoGrids[k].build(PreviousKeypoints[k].buf.p, PreviousKeypoints[k].n, 1.0f, nullptr, nullptr, TypeStream(k), lc);
       else EgoGrids[k].clear();
     }
     TotalMatchedKeypoints = 0;
@@ -292,18 +328,21 @@ void lsb_slam::ComputeEgoMotion()
       const double iterRatio = icpIter / static_cast<double>(P.ego_motion_icp_max_iter - 1);
       mp.saturation_distance = (1 - iterRatio) * P.ego_motion_init_saturation_distance + iterRatio * P.ego_motion_final_saturation_distance;
       mw.begin_iteration(nk, stream);
+      Fork();
       for (int k = 0; k < 2; ++k) {
-        mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], EgoGrids[k], Trelative, mp, stream, lc);
+        mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], EgoGrids[k], Trelative, mp, TypeStream(k), lc);
         Stats.knn_queries += (uint32_t)nk[k];
       }
-      mw.read_histograms(EgoDebug.hist, stream);
+      Join();
+      // the "enough matches" test (:919-923) is taken on the device as well: one read-back per ICP iteration
+      double x0[6];
+      iso_to_xyzrpy(Trelative, x0);
+      const LmState st = mw.solve(x0, (int)P.ego_motion_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance,
+                                  P.min_nb_matched_keypoints, EgoDebug.hist, stream, lc);
       Stats.ego_icp_iters++;
       TotalMatchedKeypoints = 0;
       for (int k = 0; k < 2; ++k) TotalMatchedKeypoints += (unsigned)EgoDebug.hist[k][LSB_MATCH_SUCCESS];
       if (TotalMatchedKeypoints < P.min_nb_matched_keypoints) { Warnings |= LSB_W_EGO_SKIPPED; break; }   // :919-923
-      double x0[6];
-      iso_to_xyzrpy(Trelative, x0);
-      const LmState st = mw.solve(x0, (int)P.ego_motion_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance, stream, lc);
       Stats.ego_lm_iters += (uint32_t)st.iter;
       Trelative = xyzrpy_to_iso(st.x);
       if (st.num_successful + 1 == 1) break;   // summary.num_successful_steps == 1 (:950)
@@ -321,16 +360,30 @@ void lsb_slam::Localization()
   for (auto& o : LocDebug.off) o = 0;
   if (P.undistortion) { InitUndistortion(); RefineUndistortion(); }   // :986-995
 
-  // Submaps (:1003-1037)
+  // Submaps (:1003-1037): the three maps work on their own streams, in host phases so that
+  // their read-backs (bbox of the keypoints, size of the submap) overlap
+  bool pending[3] = {false, false, false};
+  Fork();
   for (int k = 0; k < 3; ++k) {
     RollingGridGpu& map = LocalMaps[k];
     if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) continue;
-    if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(stream, lc); continue; }
-    if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, stream, lc);
-    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    if (CurrentKeypoints[k].n) dev_transformed_bbox(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, mn, mx, d_bbox, h_bbox, stream, lc);
-    map.BuildSubMapKdTree(mn, mx, (int)(CurrentKeypoints[k].n / 2), stream, lc);
+    cudaStream_t ts = TypeStream(k);
+    if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(ts, lc); continue; }
+    if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, ts, lc);
+    if (CurrentKeypoints[k].n) dev_transformed_bbox_async(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, map.d_bbox, map.h_bbox, ts, lc);
+    pending[k] = true;
   }
+  for (int k = 0; k < 3; ++k) {
+    if (!pending[k]) continue;
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (CurrentKeypoints[k].n) {
+      LSB_CUDA(cudaStreamSynchronize(TypeStream(k)));
+      bbox_decode(LocalMaps[k].h_bbox.p, mn, mx);
+    }
+    LocalMaps[k].SubMapSelect(mn, mx, (int)(CurrentKeypoints[k].n / 2), TypeStream(k), lc);
+  }
+  for (int k = 0; k < 3; ++k)
+    if (pending[k]) LocalMaps[k].SubMapFinish(TypeStream(k), lc);
 
   // ICP - LM loop (:1051-1156)
   TotalMatchedKeypoints = 0;
@@ -340,11 +393,17 @@ void lsb_slam::Localization()
     const double iterRatio = icpIter / static_cast<double>(P.localization_icp_max_iter - 1);
     mp.saturation_distance = (1 - iterRatio) * P.localization_init_saturation_distance + iterRatio * P.localization_final_saturation_distance;
     mw.begin_iteration(nk, stream);
+    Fork();
     for (int k = 0; k < 3; ++k) {
-      mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], LocalMaps[k].grid, Tworld, mp, stream, lc);
+      mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], LocalMaps[k].grid, Tworld, mp, TypeStream(k), lc);
       Stats.knn_queries += (uint32_t)nk[k];
     }
-    mw.read_histograms(LocDebug.hist, stream);
+    Join();
+    // the "enough matches" test (:1098-1107) is taken on the device as well: one read-back per ICP iteration
+    double x0[6];
+    iso_to_xyzrpy(Tworld, x0);
+    const LmState st = mw.solve(x0, (int)P.localization_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance,
+                                P.min_nb_matched_keypoints, LocDebug.hist, stream, lc);
     SaveDebug(LocDebug);
     Stats.loc_icp_iters++;
     TotalMatchedKeypoints = 0;
@@ -356,9 +415,6 @@ void lsb_slam::Localization()
       Warnings |= LSB_W_LOC_SKIPPED;
       break;
     }
-    double x0[6];
-    iso_to_xyzrpy(Tworld, x0);
-    const LmState st = mw.solve(x0, (int)P.localization_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance, stream, lc);
     Stats.loc_lm_iters += (uint32_t)st.iter;
     Tworld = xyzrpy_to_iso(st.x);
     Trelative = inverse(PreviousTworld) * Tworld;
@@ -385,16 +441,27 @@ void lsb_slam::UpdateMapsUsingTworld()
   Stats.is_keyframe = 1;
   KfCounter++;
   KfLastPose = Tworld;
+  // RollingGrid::Add of the three types, each on its stream, in host phases (read-backs overlapped)
+  Fork();
   for (int k = 0; k < 3; ++k) {
     if (!P.use_keypoints[k]) continue;
-    const DCloud& w = WorldKeypoints(k);
-    LocalMaps[k].Add(w.buf.p, w.n, false, CurrentTime, true, stream, lc);
+    const DCloud& w = WorldKeypoints(k, TypeStream(k));
+    LocalMaps[k].AddBegin(w.buf.p, w.n, true, TypeStream(k), lc);
   }
+  for (int k = 0; k < 3; ++k) {
+    if (!P.use_keypoints[k]) continue;
+    const DCloud& w = CurrentWorldKeypoints[k];
+    LocalMaps[k].AddSort(w.buf.p, w.n, false, CurrentTime, true, TypeStream(k), lc);
+  }
+  for (int k = 0; k < 3; ++k)
+    if (P.use_keypoints[k]) LocalMaps[k].AddMerge(CurrentWorldKeypoints[k].n, TypeStream(k), lc);
+  Join();
 }
 
 // GetKeypoints(k, true) -> TransformPointCloud (:690-702, :1491-1509), cached per frame
-const DCloud& lsb_slam::WorldKeypoints(int k)
+const DCloud& lsb_slam::WorldKeypoints(int k, cudaStream_t s)
 {
+  cudaStream_t stream = s ? s : this->stream;
   DCloud& w = CurrentWorldKeypoints[k];
   if (!WorldKeypointsValid[k]) {
     const DCloud& c = CurrentKeypoints[k];
@@ -433,17 +500,9 @@ Iso3d lsb_slam::InterpolateScanPose(double time)
 
 void lsb_slam::InitUndistortion()
 {
-  // time range over ALL keypoint clouds (:1293-1300)
-  double first = std::numeric_limits<double>::max(), last = std::numeric_limits<double>::lowest();
-  size_t total = 0;
-  for (int k = 0; k < 3; ++k) total += CurrentKeypoints[k].n;
-  if (total) {
-    dev_time_minmax_begin(d_minmax.p, stream, lc);
-    for (int k = 0; k < 3; ++k) dev_time_minmax(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_minmax.p, stream, lc);
-    LSB_CUDA(cudaMemcpyAsync(h_minmax.p, d_minmax.p, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
-    LSB_CUDA(cudaStreamSynchronize(stream));
-    time_minmax_decode(h_minmax.p, first, last);
-  }
+  // time range over ALL keypoint clouds (:1293-1300): reduced by the extraction kernels and read
+  // back with the keypoint counts (ExtractKeypoints), no extra pass / synchronisation here
+  const double first = KpTimeMin, last = KpTimeMax;
   WithinFrameMotion.set_times(first, last);
   WithinFrameMotion.set_transforms(Iso3d::identity(), Iso3d::identity());
   if (WithinFrameMotion.t1 - WithinFrameMotion.t0 < 1e-6) { Warnings |= LSB_W_TIME_FIELD; WithinFrameMotion.set_times(0., 0.); }

@@ -24,6 +24,14 @@ struct DCloud {
 struct lsb_slam {
   int device = 0;
   cudaStream_t stream = nullptr;
+  // one stream per keypoint type: sub-map extraction, kNN + model fit and the map update of the three
+  // types are independent until the LM reduction (KeypointsMatcher / RollingGrid instances per type)
+  cudaStream_t tstream[3] = {nullptr, nullptr, nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join[3] = {nullptr, nullptr, nullptr};
+  bool serial_types = false;       // profiling: every type on `stream`, kernels timed without overlap
+  cudaStream_t TypeStream(int k) const { return serial_types ? stream : tstream[k]; }
+  void Fork();                     // type streams wait for `stream`
+  void Join();                     // `stream` waits for the type streams
   lsb::LaunchCounter lc;
   lsb_params P;
 
@@ -47,6 +55,7 @@ struct lsb_slam {
   // reference (Slam.cxx:984): one device storage.
   DCloud CurrentKeypoints[3], PreviousKeypoints[3], CurrentWorldKeypoints[3];
   bool WorldKeypointsValid[3] = {false, false, false};
+  double KpTimeMin = 0., KpTimeMax = 0.;   // `time` range of CurrentKeypoints (read back with the keypoint counts)
 
   // device copies of the input frames (the reference retains the input clouds, Slam.cxx:237)
   struct DFrame { DCloud own; const lsb_point* d = nullptr; size_t n = 0; uint64_t stamp_us = 0; uint32_t seq = 0; int device_id = 0; };
@@ -83,7 +92,7 @@ struct lsb_slam {
   lsb::Iso3d GetBaseToLidarOffset(int dev) const;
   lsb::ExtractorGpu& Extractor(int dev);
   // device clouds produced on demand
-  const DCloud& WorldKeypoints(int k);
+  const DCloud& WorldKeypoints(int k, cudaStream_t s = nullptr);
   size_t RegisteredFrame(lsb::DevBuf<lsb_point>& out);
 
  private:
@@ -107,7 +116,10 @@ void dev_undistort(lsb_point* d_pts, size_t n, const Interpolator& it, double ti
 void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
 void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
 void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx);
-// bbox of (float)(T * p) in the pcl::transformPointCloud arithmetic (Slam.cxx:1026-1029); one sync
+// bbox of (float)(T * p) in the pcl::transformPointCloud arithmetic (Slam.cxx:1026-1029): enqueue only
+// (decode h_bbox with bbox_decode after a sync), or both with one sync
+void dev_transformed_bbox_async(const lsb_point* d_pts, size_t n, const Iso3d& T, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
+                                cudaStream_t s, LaunchCounter& lc);
 void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,
                           PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc);
 }  // namespace lsb
