@@ -125,12 +125,16 @@ LSB_HD void lm_eval_record(const LmRecord& rec, const LmPoint& pt, double sat, d
   out[27] = 0.5 * rho0;
 }
 
-// Cholesky solve of the symmetric 6x6 system M y = b (M full, row-major).
-// Returns false if M is not positive definite or the result is not finite.
+// Cholesky solve of the symmetric 6x6 system M y = b (M full, row-major; only the lower
+// triangle is read).  Returns false if M is not positive definite or the result is not finite.
+// Canonical operation order (the CUDA control step runs the same operations spread over the
+// lanes of a warp, see lm_propose_warp in cuda/match.cu, and must round identically):
+//   L[i][j] = (M[i][j] - sum_{k<j, ascending} L[i][k] L[j][k]) * (1 / L[j][j])
+//   z[i]    = (b[i]    - sum_{k<i, ascending}  L[i][k] z[k])   * (1 / L[i][i])
+//   y[i]    = (z[i]    - sum_{k>i, DESCENDING} L[k][i] y[k])   * (1 / L[i][i])
 LSB_HD bool lm_chol_solve6(const double* M, const double* b, double* y)
 {
-  // fully unrolled (compile-time indices) so that everything stays in registers on the GPU
-  double L[36];
+  double L[36], inv[6];
   bool ok = true;
 #pragma unroll
   for (int i = 0; i < 36; ++i) L[i] = 0.0;
@@ -141,13 +145,14 @@ LSB_HD bool lm_chol_solve6(const double* M, const double* b, double* y)
     for (int k = 0; k < j; ++k) d = d - L[j * 6 + k] * L[j * 6 + k];
     if (!(d > 0.0)) ok = false;
     const double ljj = ::sqrt(d);
+    inv[j] = 1.0 / ljj;
     L[j * 6 + j] = ljj;
 #pragma unroll
     for (int i = j + 1; i < 6; ++i) {
       double s = M[i * 6 + j];
 #pragma unroll
       for (int k = 0; k < j; ++k) s = s - L[i * 6 + k] * L[j * 6 + k];
-      L[i * 6 + j] = s / ljj;
+      L[i * 6 + j] = s * inv[j];
     }
   }
   if (!ok) return false;
@@ -157,14 +162,14 @@ LSB_HD bool lm_chol_solve6(const double* M, const double* b, double* y)
     double s = b[i];
 #pragma unroll
     for (int k = 0; k < i; ++k) s = s - L[i * 6 + k] * z[k];
-    z[i] = s / L[i * 6 + i];
+    z[i] = s * inv[i];
   }
 #pragma unroll
   for (int i = 5; i >= 0; --i) {
     double s = z[i];
 #pragma unroll
-    for (int k = i + 1; k < 6; ++k) s = s - L[k * 6 + i] * y[k];
-    y[i] = s / L[i * 6 + i];
+    for (int k = 5; k > i; --k) s = s - L[k * 6 + i] * y[k];
+    y[i] = s * inv[i];
   }
 #pragma unroll
   for (int i = 0; i < 6; ++i)
@@ -298,28 +303,30 @@ LSB_HD double lm_grad_max(const LmState& s)
   return m;
 }
 
-// E = the 28 sums evaluated at s.x (iteration 0)
-LSB_HD void lm_first_eval(LmState& s, const double* E)
+// E = the 28 sums evaluated at s.x (iteration 0).  Returns true when a first step has to be
+// proposed (lm_propose), false when the solve is over.
+LSB_HD bool lm_first_update(LmState& s, const double* E)
 {
   for (int i = 0; i < 21; ++i) s.H[i] = E[i];
   for (int i = 0; i < 6; ++i) s.g[i] = E[21 + i];
   s.cost = E[27];
   for (int i = 0; i < 6; ++i) s.S[i] = 1.0 / (1.0 + ::sqrt(s.H[lm_hidx(i, i)]));
-  if (lm_grad_max(s) <= 1e-10) { s.done = 1; s.term = LSB_LM_CONV_GRADIENT; return; }
-  lm_propose(s);
+  if (lm_grad_max(s) <= 1e-10) { s.done = 1; s.term = LSB_LM_CONV_GRADIENT; return false; }
+  return true;
 }
 
-// E = the 28 sums evaluated at s.xc
-LSB_HD void lm_next_eval(LmState& s, const double* E)
+// E = the 28 sums evaluated at s.xc: accepts or rejects the candidate.  Returns true when the
+// next step has to be proposed, false when the solve is over.
+LSB_HD bool lm_next_update(LmState& s, const double* E)
 {
   const double cost_c = E[27];
   double xn = 0.0;
   for (int i = 0; i < 6; ++i) xn += s.x[i] * s.x[i];
   xn = ::sqrt(xn);
-  if (s.step_norm <= 1e-8 * (xn + 1e-8)) { s.done = 1; s.term = LSB_LM_CONV_PARAMETER; return; }
+  if (s.step_norm <= 1e-8 * (xn + 1e-8)) { s.done = 1; s.term = LSB_LM_CONV_PARAMETER; return false; }
   const double cost_change = s.cost - cost_c;
   const double acc = (cost_change < 0.0) ? -cost_change : cost_change;
-  if (acc <= 1e-6 * s.cost) { s.done = 1; s.term = LSB_LM_CONV_FUNCTION; return; }
+  if (acc <= 1e-6 * s.cost) { s.done = 1; s.term = LSB_LM_CONV_FUNCTION; return false; }
   const double rho = cost_change / s.model_cost_change;
   if (rho > 1e-3) {
     for (int i = 0; i < 6; ++i) { s.x[i] = s.xc[i]; s.g[i] = E[21 + i]; }
@@ -332,12 +339,15 @@ LSB_HD void lm_next_eval(LmState& s, const double* E)
     s.radius = s.radius / den;
     s.radius = (s.radius > 1e16) ? 1e16 : s.radius;
     s.decrease_factor = 2.0;
-    if (lm_grad_max(s) <= 1e-10) { s.done = 1; s.term = LSB_LM_CONV_GRADIENT; return; }
+    if (lm_grad_max(s) <= 1e-10) { s.done = 1; s.term = LSB_LM_CONV_GRADIENT; return false; }
   } else {
     s.radius = s.radius / s.decrease_factor;
     s.decrease_factor *= 2.0;
   }
-  lm_propose(s);
+  return true;
 }
+
+LSB_HD void lm_first_eval(LmState& s, const double* E) { if (lm_first_update(s, E)) lm_propose(s); }
+LSB_HD void lm_next_eval(LmState& s, const double* E) { if (lm_next_update(s, E)) lm_propose(s); }
 
 }  // namespace lsb

@@ -203,34 +203,173 @@ __global__ void k_fit_empty(int nq, double* __restrict__ records, size_t rec_str
 // and its derivatives for the next evaluation point.  A launch whose state is
 // already `done` exits at once, so the host enqueues 1 + max_iter launches back
 // to back without reading anything back.
-// The trust-region step, run by warp 0 of the last CTA and kept out of line so that its
-// registers do not weigh on the 256 evaluating threads.  Lane 0 advances the state machine;
-// the six sin/cos of the next evaluation point are computed by six lanes in parallel.
-__device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned* counter, const double* sE, int first)
+// lm_propose (common/lm_core.h) spread over the lanes of one warp: lane r < 6 owns row r of the
+// scaled normal matrix, of its Cholesky factor and of the right-hand side; pivots, columns and
+// the solution travel by shuffles.  Every floating-point operation of the sequential function is
+// performed once, on the same operands and in the same order (see the canonical order stated at
+// lm_chol_solve6), so the CPU oracle and this kernel take bit-identical steps; what changes is
+// that independent rows advance together and nothing spills (the sequential form needs three
+// 6x6 FP64 matrices per thread).  `s` lives in shared memory; all 32 lanes must call.
+__device__ __forceinline__ void lm_propose_warp(LmState& s)
 {
+  constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  double xc[6];
-  int done = 1;
-  if (lane == 0) {
-    double E[LSB_LM_NSUM];
+  const int r = lane < 6 ? lane : 5;            // lanes >= 6 shadow row 5 (their results are never read)
+  int iter = s.iter, num_invalid = s.num_invalid;
+  const int max_iter = s.max_iter;
+  const bool two_d = s.two_d != 0;
+  double radius = s.radius, dec = s.decrease_factor;
+  const bool free_r = !(two_d && (r == 2 || r == 3 || r == 4));
+  const double Sr = s.S[r];
+  double Hs[6];
 #pragma unroll
-    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = sE[q];
-    LmState s = *state;
-    if (first) lm_first_eval(s, E); else lm_next_eval(s, E);
-    *state = s;
-    *counter = 0u;
-    done = s.done;
-#pragma unroll
-    for (int q = 0; q < 6; ++q) xc[q] = s.xc[q];
+  for (int j = 0; j < 6; ++j) {
+    const double h = (r <= j) ? s.H[lm_hidx(r, j)] : s.H[lm_hidx(j, r)];
+    const bool free_j = !(two_d && (j == 2 || j == 3 || j == 4));
+    Hs[j] = (free_r && free_j) ? h * Sr * s.S[j] : 0.0;
   }
-  done = __shfl_sync(0xffffffffu, done, 0);
-  if (done) return;
+  const double gs = free_r ? s.g[r] * Sr : 0.0;
+  double hdiag = Hs[0];
 #pragma unroll
-  for (int q = 0; q < 6; ++q) xc[q] = __shfl_sync(0xffffffffu, xc[q], 0);
+  for (int c = 1; c < 6; ++c) hdiag = (r == c) ? Hs[c] : hdiag;
+  const double xr = s.x[r];
+  int done = 0, term = LSB_LM_RUNNING;
+  double mcc = 0.0, step_norm = 0.0, xcr = xr;
+  bool stepped = false;
+  while (true) {
+    if (iter >= max_iter) { done = 1; term = LSB_LM_MAX_ITER; break; }
+    if (radius < 1e-32) { done = 1; term = LSB_LM_CONV_RADIUS; break; }
+    iter += 1;
+    double mdiag = 1.0;                        // held parameter: decoupled dummy row -> delta = 0
+    if (free_r) {
+      double d = hdiag;
+      d = (d < 1e-6) ? 1e-6 : d;
+      d = (d > 1e32) ? 1e32 : d;
+      mdiag = hdiag + d / radius;
+    }
+    double Mr[6], Lr[6], inv[6];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) Mr[c] = (c == r) ? mdiag : ((c < r) ? Hs[c] : 0.0);
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const double d = __shfl_sync(FULL, Mr[k], k);
+      if (!(d > 0.0)) ok = false;
+      const double ljj = ::sqrt(d);
+      inv[k] = 1.0 / ljj;
+      const double Lik = (r == k) ? ljj : ((r > k) ? Mr[k] * inv[k] : 0.0);
+      Lr[k] = Lik;
+#pragma unroll
+      for (int j = k + 1; j < 6; ++j) {
+        const double Ljk = __shfl_sync(FULL, Lik, j);
+        if (j <= r) Mr[j] = Mr[j] - Lik * Ljk;
+      }
+    }
+    double db[6], db_r = 0.0;
+    if (ok) {
+      double sv = -gs, z_r = 0.0;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {                       // forward substitution
+        const double zk = __shfl_sync(FULL, sv * inv[k], k);
+        if (r == k) z_r = zk;
+        if (r > k) sv = sv - Lr[k] * zk;
+      }
+      double Lc[6];                                        // column r of L: Lc[k] = L[k][r], k > r
+#pragma unroll
+      for (int k = 1; k < 6; ++k) {
+        double v = 0.0;
+#pragma unroll
+        for (int c = 0; c < k; ++c) {
+          const double t = __shfl_sync(FULL, Lr[c], k);
+          if (r == c) v = t;
+        }
+        Lc[k] = v;
+      }
+      sv = z_r;
+#pragma unroll
+      for (int k = 5; k >= 0; --k) {                       // backward substitution, k descending
+        const double yk = __shfl_sync(FULL, sv * inv[k], k);
+        db[k] = yk;
+        if (r == k) db_r = yk;
+        if (r < k) sv = sv - Lc[k] * yk;
+      }
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+        if (!(db[i] - db[i] == 0.0)) ok = false;           // NaN / inf
+    }
+    mcc = 0.0;
+    if (ok) {
+      // model_cost_change = -delta^T (g + 0.5 H delta)   (scaled quantities)
+      double hd = 0.0;
+#pragma unroll
+      for (int j = 0; j < 6; ++j) hd += Hs[j] * db[j];
+      const double t = db_r * (gs + 0.5 * hd);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) mcc -= __shfl_sync(FULL, t, i);
+      ok = (mcc > 0.0);
+    }
+    if (!ok) {
+      num_invalid += 1;
+      if (num_invalid >= 5) { done = 1; term = LSB_LM_FAIL_INVALID; break; }
+      radius = radius / dec;
+      dec *= 2.0;
+      continue;
+    }
+    num_invalid = 0;
+    const double dstep = db_r * Sr;
+    xcr = xr + dstep;
+    const double e = xr - xcr;
+    const double ee = e * e;
+    double sn = 0.0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) sn += __shfl_sync(FULL, ee, i);
+    step_norm = ::sqrt(sn);
+    stepped = true;
+    break;
+  }
+  __syncwarp();
+  if (stepped && lane < 6) s.xc[lane] = xcr;
+  if (lane == 0) {
+    s.iter = iter;
+    s.num_invalid = num_invalid;
+    s.radius = radius;
+    s.decrease_factor = dec;
+    if (stepped) { s.model_cost_change = mcc; s.step_norm = step_norm; }
+    if (done) { s.done = 1; s.term = term; }
+  }
+  __syncwarp();
+}
+
+// The trust-region step, run by warp 0 of the last CTA and kept out of line so that its
+// registers do not weigh on the evaluating threads.  The state is staged in shared memory;
+// lane 0 takes the accept / reject decision (scalar), the warp proposes the next step, and the
+// six sin/cos of the next evaluation point are computed by six lanes in parallel.
+__device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned* counter, const double* sE, int first,
+                                        unsigned long long* s_state_raw)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int NW = (int)(sizeof(LmState) / 8);
+  static_assert(sizeof(LmState) % 8 == 0, "LmState is copied as 64-bit words");
+  const int lane = threadIdx.x & 31;
+  for (int w = lane; w < NW; w += 32) s_state_raw[w] = reinterpret_cast<const unsigned long long*>(state)[w];
+  __syncwarp();
+  LmState& s = *reinterpret_cast<LmState*>(s_state_raw);
+  int propose = 0;
+  if (lane == 0) propose = (first ? lm_first_update(s, sE) : lm_next_update(s, sE)) ? 1 : 0;
+  __syncwarp();
+  propose = __shfl_sync(FULL, propose, 0);
+  if (propose) lm_propose_warp(s);
+  __syncwarp();
+  for (int w = lane; w < NW; w += 32) reinterpret_cast<unsigned long long*>(state)[w] = s_state_raw[w];
+  if (lane == 0) *counter = 0u;
+  if (s.done) return;
+  double xc[6];
+#pragma unroll
+  for (int q = 0; q < 6; ++q) xc[q] = s.xc[q];
   const double tv = (lane < 6) ? lm_point_trig(xc, lane) : 0.0;
   double trig[6];
 #pragma unroll
-  for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(0xffffffffu, tv, q);
+  for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(FULL, tv, q);
   if (lane == 0) {
     LmPoint pt;
     lm_make_point_from_trig(xc, trig, pt);
@@ -251,6 +390,7 @@ k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchu
   __shared__ double s_E[LSB_LM_NSUM];
   __shared__ double s_tile[LM_TILE * LSB_LM_NSUM];
   __shared__ int s_last;
+  __shared__ __align__(16) unsigned long long s_state_raw[sizeof(LmState) / 8];
   if (state->done) return;   // uniform: written by the previous launch
   if (threadIdx.x < sizeof(LmPoint) / sizeof(double)) s_pt_raw[threadIdx.x] = reinterpret_cast<const double*>(point)[threadIdx.x];
   __syncthreads();
@@ -312,7 +452,7 @@ k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchu
   }
   if (threadIdx.x < LSB_LM_NSUM) s_E[threadIdx.x] = e;
   __syncthreads();
-  if (threadIdx.x < 32) lm_control(state, point, counter, s_E, first);
+  if (threadIdx.x < 32) lm_control(state, point, counter, s_E, first, s_state_raw);
 }
 
 __global__ void k_lm_begin(LmState* state, LmPoint* point, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5,
