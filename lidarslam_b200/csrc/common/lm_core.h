@@ -24,23 +24,42 @@ namespace lsb {
 // [0..20] upper triangle of J~^T J~ (row-major: 00 01 02 03 04 05 11 12 ...),
 // [21..26] J~^T r~, [27] cost = sum 0.5*rho.
 #define LSB_LM_NSUM 28
-// Canonical reduction order (GPU and oracle): records in chunks of 1024; inside a
-// chunk each group of 32 consecutive records is folded with offsets 16,8,4,2,1,
-// the 32 group sums are added in order, and the chunk sums are added in chunk order.
+// Canonical reduction order (GPU and oracle): a radix-32 tree.  fold32(v[0..31]) is the pairwise
+// tree  for off in 16,8,4,2,1: v[i] += v[i+off] (i < off);  missing leaves are +0.0.
+//   group sum  G_g = fold32 of the records 32g .. 32g+31
+//   chunk sum  C_c = fold32 of G_32c .. G_32c+31          (1024 records, one CTA)
+//   block sum  B_b = fold32 of C_32b .. C_32b+31
+//   E          = B_0 + B_1 + ...                          (in order)
 #define LSB_LM_CHUNK 1024
 
-// One residual record, 16 doubles (A row-major, P, X, weight).  weight < 0 marks
-// "no residual" (match failed): contributes exactly zero.
+// One residual record (13 doubles): the residual of the reference is r = A (R X + t - P)
+// (CeresCostFunctions.h:105-152); only M = A^T A enters the normal equations and the cost
+// (r.r = d^T M d, J^T J = Jd^T M Jd, J^T r = Jd^T M d with d = R X + t - P), so the record keeps
+// the 6 unique entries of M.  w < 0 marks "no residual" (match failed): contributes exactly zero.
 struct LmRecord {
-  double A[9];
+  double M[6];   // 00 01 02 11 12 22
   double P[3];
   double X[3];
   double w;
 };
 
-struct LmPoint {   // quantities that depend only on the current parameters
-  Mat3d R, dRx, dRy, dRz;
+// M = A^T A, each entry summed over the rows of A in order (shared by k_fit and the oracle)
+LSB_HD void lm_record_set(LmRecord& r, const double* A, const double* P, const double* X, double w)
+{
+  int o = 0;
+  for (int i = 0; i < 3; ++i)
+    for (int j = i; j < 3; ++j) r.M[o++] = A[0 + i] * A[0 + j] + A[3 + i] * A[3 + j] + A[6 + i] * A[6 + j];
+  for (int k = 0; k < 3; ++k) { r.P[k] = P[k]; r.X[k] = X[k]; }
+  r.w = w;
+}
+
+// Quantities that depend only on the current parameters.  R = Rz(rz) Ry(ry) Rx(rx); its
+// derivatives are cross products with the rotated point Y = R X:
+//   dR/drx X = (first column of R) x Y,   dR/dry X = (-sz, cz, 0) x Y,   dR/drz X = (0, 0, 1) x Y.
+struct LmPoint {
+  Mat3d R;
   Vec3d t;
+  double sz, cz;
 };
 
 // trig[6] = cos rx, sin rx, cos ry, sin ry, cos rz, sin rz  (entry j: angle x[3 + j/2], cos if j even)
@@ -60,18 +79,8 @@ LSB_HD void lm_make_point_from_trig(const double* x, const double* trig, LmPoint
   R(0, 0) = cy * cz; R(0, 1) = sx * sy * cz - cx * sz; R(0, 2) = cx * sy * cz + sx * sz;
   R(1, 0) = cy * sz; R(1, 1) = sx * sy * sz + cx * cz; R(1, 2) = cx * sy * sz - sx * cz;
   R(2, 0) = -sy;     R(2, 1) = sx * cy;                R(2, 2) = cx * cy;
-  Mat3d& A = p.dRx;  // d/drx
-  A(0, 0) = 0.0; A(0, 1) = cx * sy * cz + sx * sz; A(0, 2) = -sx * sy * cz + cx * sz;
-  A(1, 0) = 0.0; A(1, 1) = cx * sy * sz - sx * cz; A(1, 2) = -sx * sy * sz - cx * cz;
-  A(2, 0) = 0.0; A(2, 1) = cx * cy;                A(2, 2) = -sx * cy;
-  Mat3d& B = p.dRy;  // d/dry
-  B(0, 0) = -sy * cz; B(0, 1) = sx * cy * cz; B(0, 2) = cx * cy * cz;
-  B(1, 0) = -sy * sz; B(1, 1) = sx * cy * sz; B(1, 2) = cx * cy * sz;
-  B(2, 0) = -cy;      B(2, 1) = -sx * sy;     B(2, 2) = -cx * sy;
-  Mat3d& C = p.dRz;  // d/drz
-  C(0, 0) = -cy * sz; C(0, 1) = -sx * sy * sz - cx * cz; C(0, 2) = -cx * sy * sz + sx * cz;
-  C(1, 0) = cy * cz;  C(1, 1) = sx * sy * cz - cx * sz;  C(1, 2) = cx * sy * cz + sx * sz;
-  C(2, 0) = 0.0;      C(2, 1) = 0.0;                     C(2, 2) = 0.0;
+  p.sz = sz;
+  p.cz = cz;
 }
 
 LSB_HD void lm_make_point(const double* x, LmPoint& p)
@@ -88,13 +97,15 @@ LSB_HD void lm_eval_record(const LmRecord& rec, const LmPoint& pt, double sat, d
     for (int i = 0; i < LSB_LM_NSUM; ++i) out[i] = 0.0;
     return;
   }
-  Mat3d A;
-  for (int i = 0; i < 9; ++i) A.m[i] = rec.A[i];
+  const double m00 = rec.M[0], m01 = rec.M[1], m02 = rec.M[2], m11 = rec.M[3], m12 = rec.M[4], m22 = rec.M[5];
   const Vec3d X(rec.X[0], rec.X[1], rec.X[2]);
-  const Vec3d P(rec.P[0], rec.P[1], rec.P[2]);
-  const Vec3d Y = pt.R * X + pt.t;
-  const Vec3d r = A * (Y - P);
-  const double s = dot(r, r);
+  const Vec3d Y = pt.R * X;                                   // rotated point (no translation)
+  const double d0 = (Y.x + pt.t.x) - rec.P[0], d1 = (Y.y + pt.t.y) - rec.P[1], d2 = (Y.z + pt.t.z) - rec.P[2];
+  // u = M d,  s = d.u = |A d|^2
+  const double u0 = m00 * d0 + m01 * d1 + m02 * d2;
+  const double u1 = m01 * d0 + m11 * d1 + m12 * d2;
+  const double u2 = m02 * d0 + m12 * d1 + m22 * d2;
+  const double s = d0 * u0 + d1 * u1 + d2 * u2;
   // TukeyLoss(sat) scaled by w (Ceres >= 2.0 form, KeypointsMatcher.cxx:96-101)
   const double a2 = sat * sat;
   double rho0, rho1;
@@ -109,19 +120,31 @@ LSB_HD void lm_eval_record(const LmRecord& rec, const LmPoint& pt, double sat, d
   }
   rho0 = rec.w * rho0;
   rho1 = rec.w * rho1;
-  // Ceres corrector with rho'' <= 0: residual and Jacobian scaled by sqrt(rho')
-  const double sr = ::sqrt(rho1);
-  const Vec3d rt = sr * r;
-  // J~ columns: translation = A columns, rotation = A * (dR_k * X)
-  Vec3d J[6];
-  J[0] = sr * A.col(0); J[1] = sr * A.col(1); J[2] = sr * A.col(2);
-  J[3] = sr * (A * (pt.dRx * X));
-  J[4] = sr * (A * (pt.dRy * X));
-  J[5] = sr * (A * (pt.dRz * X));
-  int o = 0;
-  for (int i = 0; i < 6; ++i)
-    for (int j = i; j < 6; ++j) out[o++] = dot(J[i], J[j]);
-  for (int i = 0; i < 6; ++i) out[21 + i] = dot(J[i], rt);
+  // Ceres corrector with rho'' <= 0: residual and Jacobian scaled by sqrt(rho'), i.e. the normal
+  // equations scaled by rho'.  Rotation columns of Jd = d(d)/d(rx, ry, rz):
+  const double ax = pt.R.m[0], ay = pt.R.m[3], az = pt.R.m[6];            // first column of R
+  const double cx0 = ay * Y.z - az * Y.y, cx1 = az * Y.x - ax * Y.z, cx2 = ax * Y.y - ay * Y.x;
+  const double cy0 = pt.cz * Y.z, cy1 = pt.sz * Y.z, cy2 = -(pt.sz * Y.y) - pt.cz * Y.x;
+  const double cz0 = -Y.y, cz1 = Y.x;                                      // cz2 = 0
+  // v_k = M c_k
+  const double vx0 = m00 * cx0 + m01 * cx1 + m02 * cx2, vx1 = m01 * cx0 + m11 * cx1 + m12 * cx2, vx2 = m02 * cx0 + m12 * cx1 + m22 * cx2;
+  const double vy0 = m00 * cy0 + m01 * cy1 + m02 * cy2, vy1 = m01 * cy0 + m11 * cy1 + m12 * cy2, vy2 = m02 * cy0 + m12 * cy1 + m22 * cy2;
+  const double vz0 = m00 * cz0 + m01 * cz1, vz1 = m01 * cz0 + m11 * cz1, vz2 = m02 * cz0 + m12 * cz1;
+  // J~^T J~ (upper triangle, parameter order tx ty tz rx ry rz)
+  out[0] = rho1 * m00; out[1] = rho1 * m01; out[2] = rho1 * m02; out[3] = rho1 * vx0; out[4] = rho1 * vy0; out[5] = rho1 * vz0;
+  out[6] = rho1 * m11; out[7] = rho1 * m12; out[8] = rho1 * vx1; out[9] = rho1 * vy1; out[10] = rho1 * vz1;
+  out[11] = rho1 * m22; out[12] = rho1 * vx2; out[13] = rho1 * vy2; out[14] = rho1 * vz2;
+  out[15] = rho1 * (cx0 * vx0 + cx1 * vx1 + cx2 * vx2);
+  out[16] = rho1 * (cx0 * vy0 + cx1 * vy1 + cx2 * vy2);
+  out[17] = rho1 * (cx0 * vz0 + cx1 * vz1 + cx2 * vz2);
+  out[18] = rho1 * (cy0 * vy0 + cy1 * vy1 + cy2 * vy2);
+  out[19] = rho1 * (cy0 * vz0 + cy1 * vz1 + cy2 * vz2);
+  out[20] = rho1 * (cz0 * vz0 + cz1 * vz1);
+  // J~^T r~
+  out[21] = rho1 * u0; out[22] = rho1 * u1; out[23] = rho1 * u2;
+  out[24] = rho1 * (cx0 * u0 + cx1 * u1 + cx2 * u2);
+  out[25] = rho1 * (cy0 * u0 + cy1 * u1 + cy2 * u2);
+  out[26] = rho1 * (cz0 * u0 + cz1 * u1);
   out[27] = 0.5 * rho0;
 }
 

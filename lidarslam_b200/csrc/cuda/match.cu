@@ -38,15 +38,20 @@ __device__ __forceinline__ int cloud_ring(const lsb_point* __restrict__ cloud, i
 
 __device__ __forceinline__ bool dev_isfinite(double v) { return (v - v) == 0.0; }
 
-// Residual records live in a structure-of-arrays layout (16 planes of doubles, plane f of
-// record i at rec[f * stride + i]) so that the per-thread accesses of the fit and LM kernels coalesce.
-constexpr int REC_W = 15;   // plane of the weight (w < 0: no residual)
+// Residual records live in a structure-of-arrays layout (13 planes of doubles, plane f of
+// record i at rec[f * stride + i]: M 0..5, P 6..8, X 9..11, w 12) so that the per-thread accesses
+// of the fit and LM kernels coalesce.
+constexpr int REC_PLANES = 13;
+constexpr int REC_W = 12;   // plane of the weight (w < 0: no residual)
 __device__ __forceinline__ void write_record(double* __restrict__ rec, size_t stride, const Mat3d& A, const Vec3d& mean, const Vec3d& X, double w)
 {
+  LmRecord r;
+  const double P[3] = {mean.x, mean.y, mean.z}, Xa[3] = {X.x, X.y, X.z};
+  lm_record_set(r, A.m, P, Xa, w);
 #pragma unroll
-  for (int t = 0; t < 9; ++t) rec[t * stride] = A.m[t];
-  rec[9 * stride] = mean.x; rec[10 * stride] = mean.y; rec[11 * stride] = mean.z;
-  rec[12 * stride] = X.x; rec[13 * stride] = X.y; rec[14 * stride] = X.z;
+  for (int t = 0; t < 6; ++t) rec[t * stride] = r.M[t];
+#pragma unroll
+  for (int t = 0; t < 3; ++t) { rec[(6 + t) * stride] = r.P[t]; rec[(9 + t) * stride] = r.X[t]; }
   rec[REC_W * stride] = w;
 }
 __device__ __forceinline__ LmRecord load_record(const double* __restrict__ rec, size_t stride)
@@ -55,9 +60,9 @@ __device__ __forceinline__ LmRecord load_record(const double* __restrict__ rec, 
   r.w = rec[REC_W * stride];
   if (r.w >= 0.0) {
 #pragma unroll
-    for (int t = 0; t < 9; ++t) r.A[t] = rec[t * stride];
+    for (int t = 0; t < 6; ++t) r.M[t] = rec[t * stride];
 #pragma unroll
-    for (int t = 0; t < 3; ++t) { r.P[t] = rec[(9 + t) * stride]; r.X[t] = rec[(12 + t) * stride]; }
+    for (int t = 0; t < 3; ++t) { r.P[t] = rec[(6 + t) * stride]; r.X[t] = rec[(9 + t) * stride]; }
   }
   return r;
 }
@@ -195,14 +200,6 @@ __global__ void k_fit_empty(int nq, double* __restrict__ records, size_t rec_str
 }
 
 // ---------------------------------------------------------------- K10/K11 ----
-// One launch = one cost/Jacobian evaluation of the whole problem + one step of
-// the trust-region state machine (common/lm_core.h).  Each CTA reduces one
-// canonical chunk of 256 records (warp shuffles, offsets 16..1, the 8 warp sums
-// added in order); the last CTA to finish adds the chunk sums in chunk order
-// (one thread per quantity), advances the LM state and precomputes the rotation
-// and its derivatives for the next evaluation point.  A launch whose state is
-// already `done` exits at once, so the host enqueues 1 + max_iter launches back
-// to back without reading anything back.
 // lm_propose (common/lm_core.h) spread over the lanes of one warp: lane r < 6 owns row r of the
 // scaled normal matrix, of its Cholesky factor and of the right-hand side; pivots, columns and
 // the solution travel by shuffles.  Every floating-point operation of the sequential function is
@@ -341,7 +338,8 @@ __device__ __forceinline__ void lm_propose_warp(LmState& s)
 }
 
 // The trust-region step, run by warp 0 of the last CTA and kept out of line so that its
-// registers do not weigh on the evaluating threads.  The state is staged in shared memory;
+// registers do not weigh on the evaluating threads.  The state was staged in shared memory by the
+// kernel prologue (s_state_raw: it only changes here, at the end of a launch);
 // lane 0 takes the accept / reject decision (scalar), the warp proposes the next step, and the
 // six sin/cos of the next evaluation point are computed by six lanes in parallel.
 __device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned* counter, const double* sE, int first,
@@ -351,8 +349,6 @@ __device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned
   constexpr int NW = (int)(sizeof(LmState) / 8);
   static_assert(sizeof(LmState) % 8 == 0, "LmState is copied as 64-bit words");
   const int lane = threadIdx.x & 31;
-  for (int w = lane; w < NW; w += 32) s_state_raw[w] = reinterpret_cast<const unsigned long long*>(state)[w];
-  __syncwarp();
   LmState& s = *reinterpret_cast<LmState*>(s_state_raw);
   int propose = 0;
   if (lane == 0) propose = (first ? lm_first_update(s, sE) : lm_next_update(s, sE)) ? 1 : 0;
@@ -377,27 +373,83 @@ __device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned
   }
 }
 
-constexpr int LM_TILE = 160;      // chunk partials staged per pass of the final sum (35 KB)
-constexpr int LM_THREADS = 512;   // 16 warps; each warp folds LSB_LM_CHUNK / 32 / 16 = 2 groups of 32 records
+constexpr int LM_THREADS = 512;   // 16 warps; each warp evaluates 2 groups of 32 records of the CTA's chunk
+constexpr int LM_WARPS = LM_THREADS / 32;
 constexpr int LM_GROUPS = LSB_LM_CHUNK / 32;
+static_assert(LM_GROUPS == 32, "a chunk is a fold32 of 32 groups");
 
+// fold32 (lm_core.h) of 28 per-lane values at once: instead of 28 butterflies (140 shuffles and
+// adds) the lanes split the quantities as they fold (14 + 7 + 4 + 2 + 1 = 28 shuffles and adds).
+// After step `off` the lanes whose bit `off` is clear hold the first half of the quantities, the
+// others the second half; each partial sum is v[i] + v[i + off] exactly as in the butterfly.
+// On return lane L holds the complete fold32 of quantity q(L) (q < 0: padding).
+__device__ __forceinline__ double warp_fold28(const double (&v)[LSB_LM_NSUM], int lane, int& q)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  double a1[14], a2[7], a3[4], a4[2];
+  const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2, b1 = lane & 1;
+#pragma unroll
+  for (int i = 0; i < 14; ++i) {
+    const double keep = b16 ? v[i + 14] : v[i], send = b16 ? v[i] : v[i + 14];
+    a1[i] = keep + __shfl_xor_sync(FULL, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 7; ++i) {
+    const double keep = b8 ? a1[i + 7] : a1[i], send = b8 ? a1[i] : a1[i + 7];
+    a2[i] = keep + __shfl_xor_sync(FULL, send, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const double hi = (i + 4 < 7) ? a2[(i + 4 < 7) ? i + 4 : 0] : 0.0;
+    const double keep = b4 ? hi : a2[i], send = b4 ? a2[i] : hi;
+    a3[i] = keep + __shfl_xor_sync(FULL, send, 4);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const double keep = b2 ? a3[i + 2] : a3[i], send = b2 ? a3[i] : a3[i + 2];
+    a4[i] = keep + __shfl_xor_sync(FULL, send, 2);
+  }
+  const double keep = b1 ? a4[1] : a4[0], send = b1 ? a4[0] : a4[1];
+  const double r = keep + __shfl_xor_sync(FULL, send, 1);
+  const int l7 = lane & 7;
+  q = (l7 < 7) ? (b16 ? 14 : 0) + (b8 ? 7 : 0) + l7 : -1;
+  return r;
+}
+
+__device__ __forceinline__ double warp_fold32(double v)
+{
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+  return v;   // complete in lane 0
+}
+
+// One launch = one cost/Jacobian evaluation of the whole problem + one step of the trust-region
+// state machine (common/lm_core.h), in the canonical radix-32 reduction order: a warp folds the
+// 28 sums of a group of 32 records, the CTA folds the 32 groups of its chunk, and the last CTA to
+// finish folds the chunk sums in blocks of 32 (one warp per quantity, one L2 round trip), adds the
+// block sums in order, advances the LM state and prepares the rotation for the next evaluation
+// point.  A launch whose state is already `done` exits at once, so the host enqueues
+// 1 + max_iter launches back to back without reading anything back.
+// part: [LSB_LM_NSUM][pstride] chunk sums, pstride = 32 * number of blocks.
 __global__ void __launch_bounds__(LM_THREADS, 1)
-k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, double sat, LmState* __restrict__ state,
+k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, int pstride, double sat, LmState* __restrict__ state,
           LmPoint* __restrict__ point, double* __restrict__ part, unsigned* __restrict__ counter, int first)
 {
-  __shared__ __align__(16) double s_pt_raw[sizeof(LmPoint) / sizeof(double)];
-  __shared__ double s_group[LM_GROUPS][LSB_LM_NSUM];
+  constexpr int NW = (int)(sizeof(LmState) / 8), NP = (int)(sizeof(LmPoint) / 8);
+  __shared__ __align__(16) unsigned long long s_pt_raw[NP];
+  __shared__ __align__(16) unsigned long long s_state_raw[NW];
+  __shared__ double s_group[LSB_LM_NSUM][LM_GROUPS];
   __shared__ double s_E[LSB_LM_NSUM];
-  __shared__ double s_tile[LM_TILE * LSB_LM_NSUM];
   __shared__ int s_last;
-  __shared__ __align__(16) unsigned long long s_state_raw[sizeof(LmState) / 8];
-  if (state->done) return;   // uniform: written by the previous launch
-  if (threadIdx.x < sizeof(LmPoint) / sizeof(double)) s_pt_raw[threadIdx.x] = reinterpret_cast<const double*>(point)[threadIdx.x];
+  static_assert(NW <= 64 && NP <= 64, "prologue copies with threads 0..63 / 64..127");
+  if (threadIdx.x < NW) s_state_raw[threadIdx.x] = reinterpret_cast<const unsigned long long*>(state)[threadIdx.x];
+  else if (threadIdx.x >= 64 && threadIdx.x < 64 + NP) s_pt_raw[threadIdx.x - 64] = reinterpret_cast<const unsigned long long*>(point)[threadIdx.x - 64];
   __syncthreads();
+  if (reinterpret_cast<const LmState*>(s_state_raw)->done) return;   // uniform: written by the previous launch
   const LmPoint& s_pt = *reinterpret_cast<const LmPoint*>(s_pt_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll 1
-  for (int g = warp; g < LM_GROUPS; g += LM_THREADS / 32) {
+  for (int g = warp; g < LM_GROUPS; g += LM_WARPS) {
     const int i = blockIdx.x * LSB_LM_CHUNK + g * 32 + lane;
     double out[LSB_LM_NSUM];
     if (i < n) lm_eval_record(load_record(records + i, rec_stride), s_pt, sat, out);
@@ -405,21 +457,15 @@ k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchu
 #pragma unroll
       for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
     }
-#pragma unroll
-    for (int q = 0; q < LSB_LM_NSUM; ++q) {
-      double v = out[q];
-#pragma unroll
-      for (int off = 16; off >= 1; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-      if (lane == 0) s_group[g][q] = v;
-    }
+    int q;
+    const double r = warp_fold28(out, lane, q);
+    if (q >= 0) s_group[q][g] = r;
   }
   __syncthreads();
-  if (threadIdx.x < LSB_LM_NSUM) {
-    double c = s_group[0][threadIdx.x];
-#pragma unroll 8
-    for (int g = 1; g < LM_GROUPS; ++g) c = c + s_group[g][threadIdx.x];
-    part[(size_t)blockIdx.x * LSB_LM_NSUM + threadIdx.x] = c;
-    __threadfence();
+#pragma unroll
+  for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
+    const double c = warp_fold32(s_group[q][lane]);
+    if (lane == 0) { part[(size_t)q * pstride + blockIdx.x] = c; __threadfence(); }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -429,28 +475,18 @@ k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchu
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // chunk sums added in chunk order: tiles of the partials are staged in shared memory by
-  // the whole CTA (independent loads first, one L2 round trip), then one thread per quantity adds them
-  double e = 0.0;
-  for (int c0 = 0; c0 < nchunks; c0 += LM_TILE) {
-    const int nt = min(LM_TILE, nchunks - c0) * LSB_LM_NSUM;
-    const double* src = part + (size_t)c0 * LSB_LM_NSUM;
-    for (int t0 = 0; t0 < nt; t0 += LM_THREADS * 4) {
-      double v[4];
+  const int nblocks = pstride >> 5;
 #pragma unroll
-      for (int u = 0; u < 4; ++u) { const int t = t0 + u * LM_THREADS + threadIdx.x; v[u] = (t < nt) ? __ldcg(src + t) : 0.0; }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) { const int t = t0 + u * LM_THREADS + threadIdx.x; if (t < nt) s_tile[t] = v[u]; }
+  for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
+    const double* src = part + (size_t)q * pstride;
+    double e = 0.0;
+    for (int b = 0; b < nblocks; ++b) {
+      const int c = b * 32 + lane;
+      const double v = warp_fold32((c < nchunks) ? __ldcg(src + c) : 0.0);
+      e = (b == 0) ? v : e + v;
     }
-    __syncthreads();
-    if (threadIdx.x < LSB_LM_NSUM) {
-      int c = 0;
-      if (c0 == 0) { e = s_tile[threadIdx.x]; c = 1; }
-      for (; c * LSB_LM_NSUM < nt; ++c) e = e + s_tile[c * LSB_LM_NSUM + threadIdx.x];
-    }
-    __syncthreads();
+    if (lane == 0) s_E[q] = e;
   }
-  if (threadIdx.x < LSB_LM_NSUM) s_E[threadIdx.x] = e;
   __syncthreads();
   if (threadIdx.x < 32) lm_control(state, point, counter, s_E, first, s_state_raw);
 }
@@ -484,7 +520,7 @@ void MatchWorkspace::begin_iteration(const size_t nk[3], cudaStream_t s)
     nn_idx[k].reserve(q * KNN_MAX_K, s); nn_d2[k].reserve(q * KNN_MAX_K, s); nn_found[k].reserve(q, s);
   }
   rec_stride = (total + 31) / 32 * 32;
-  records.reserve(std::max<size_t>(16 * rec_stride, 16), s); status.reserve(total, s); weight.reserve(total, s);
+  records.reserve(std::max<size_t>(REC_PLANES * rec_stride, REC_PLANES), s); status.reserve(total, s); weight.reserve(total, s);
   hist.reserve(3 * LSB_MATCH_N_STATUS, s);
   h_hist.reserve(3 * LSB_MATCH_N_STATUS);
   LSB_CUDA(cudaMemsetAsync(hist.p, 0, 3 * LSB_MATCH_N_STATUS * sizeof(int), s));
@@ -546,14 +582,15 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
 {
   const int n = (int)total;
   const int nchunks = std::max(1, (int)div_up(total, LSB_LM_CHUNK));
-  part_a.reserve((size_t)nchunks * LSB_LM_NSUM, s);
+  const int pstride = (nchunks + 31) / 32 * 32;
+  part_a.reserve((size_t)pstride * LSB_LM_NSUM, s);
   lm_state.reserve(1, s); lm_point.reserve(1, s); lm_counter.reserve(1, s); h_lm.reserve(1);
   k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_point.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d,
                              hist.p, min_matches);
   LSB_LAUNCH_CHECK(); lc.add();
   t_lm.begin(s);
   for (int e = 0; e <= max_iter; ++e) {
-    k_lm_eval<<<nchunks, LM_THREADS, 0, s>>>(records.p, rec_stride, n, nchunks, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
+    k_lm_eval<<<nchunks, LM_THREADS, 0, s>>>(records.p, rec_stride, n, nchunks, pstride, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
     LSB_LAUNCH_CHECK(); lc.add();
   }
   t_lm.end(s);

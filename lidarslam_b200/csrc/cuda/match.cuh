@@ -13,14 +13,14 @@ namespace lsb {
 struct MatchWorkspace {
   DevBuf<int32_t> nn_idx[3], nn_found[3];   // per type: the three types are matched on their own streams
   DevBuf<float> nn_d2[3];
-  DevBuf<double> records;           // 16 planes x rec_stride (structure of arrays)
+  DevBuf<double> records;           // 13 planes x rec_stride (structure of arrays)
   size_t rec_stride = 0;
   DevBuf<uint8_t> status;
   DevBuf<double> weight;
   DevBuf<int> hist;                 // [3][LSB_MATCH_N_STATUS]
   DevBuf<double> part_a;            // LM chunk partial sums
   DevBuf<LmState> lm_state;         // [1]
-  DevBuf<LmPoint> lm_point;         // [1] rotation + derivatives at the next evaluation point
+  DevBuf<LmPoint> lm_point;         // [1] rotation at the next evaluation point
   DevBuf<unsigned> lm_counter;      // [1]
   PinnedBuf<int> h_hist;
   PinnedBuf<LmState> h_lm;

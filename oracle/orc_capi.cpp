@@ -227,4 +227,41 @@ ORC_API void orc_eigen33(const double* m9, double* evals3, double* evecs9, long 
   }
 }
 
+// The 28 terms of lm_eval_record for n records (A row-major 9, P 3, X 3, w) at pose x[6]
+// (tests/test_oracle_math.py checks them against a numpy restatement of the reference residual
+// r = sqrt(w rho') A (R X + t - P) with a finite-difference Jacobian).
+ORC_API void orc_lm_terms(const double* A9, const double* P3, const double* X3, const double* w, long n, const double* x6, double sat,
+                          double* out28)
+{
+  lsb::LmPoint pt;
+  lsb::lm_make_point(x6, pt);
+  for (long i = 0; i < n; ++i) {
+    lsb::LmRecord r;
+    lsb::lm_record_set(r, A9 + 9 * i, P3 + 3 * i, X3 + 3 * i, w[i]);
+    lsb::lm_eval_record(r, pt, sat, out28 + 28 * i);
+  }
+}
+// LocalOptimizer::Solve on raw residual records; returns the number of LM iterations.
+ORC_API int orc_lm_solve(const double* A9, const double* P3, const double* X3, const double* w, long n, const double* x0, double sat,
+                         int max_iter, int two_d, int threads, double* x_out, double* cost_out, int* accepted_out, int* term_out)
+{
+  Optimizer opt;
+  opt.TwoDMode = two_d != 0;
+  opt.LMMaxIter = (unsigned)max_iter;
+  opt.NbThreads = threads > 0 ? threads : 1;
+  opt.Sat = sat;
+  for (int i = 0; i < 6; ++i) opt.PoseArray[i] = x0[i];
+  for (long i = 0; i < n; ++i) {
+    lsb::LmRecord r;
+    lsb::lm_record_set(r, A9 + 9 * i, P3 + 3 * i, X3 + 3 * i, w[i]);
+    opt.Records.push_back(r);
+  }
+  opt.Solve();
+  for (int i = 0; i < 6; ++i) x_out[i] = opt.State.x[i];
+  *cost_out = opt.State.cost;
+  *accepted_out = opt.State.num_successful;
+  *term_out = opt.State.term;
+  return opt.State.iter;
+}
+
 }  // extern "C"

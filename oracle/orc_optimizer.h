@@ -26,43 +26,53 @@ struct Optimizer {
     for (size_t i = 0; i < m.Residuals.size(); ++i) {
       lsb::LmRecord r;
       const MatchRecord& s = m.Residuals[i];
-      for (int k = 0; k < 9; ++k) r.A[k] = s.A[k];
-      for (int k = 0; k < 3; ++k) { r.P[k] = s.P[k]; r.X[k] = s.X[k]; }
-      r.w = (m.Rejections[i] == LSB_MATCH_SUCCESS) ? s.weight : -1.0;
+      lsb::lm_record_set(r, s.A, s.P, s.X, (m.Rejections[i] == LSB_MATCH_SUCCESS) ? s.weight : -1.0);
       Records.push_back(r);
     }
   }
 
-  // 28 sums at x in the canonical order of lm_core.h
+  // fold32 of lm_core.h: v[0] receives the pairwise tree sum of v[0..31]
+  static void Fold32(double v[32][LSB_LM_NSUM])
+  {
+    for (int off = 16; off >= 1; off >>= 1)
+      for (int l = 0; l < off; ++l)
+        for (int q = 0; q < LSB_LM_NSUM; ++q) v[l][q] += v[l + off][q];
+  }
+
+  // 28 sums at x in the canonical order of lm_core.h (radix-32 tree: records -> groups ->
+  // chunks -> blocks, block sums added in order)
   void Evaluate(const double* x, double* E)
   {
     ++NumEvaluations;
     lsb::LmPoint pt;
     lsb::lm_make_point(x, pt);
     const size_t n = Records.size();
-    const size_t nChunks = (n + LSB_LM_CHUNK - 1) / LSB_LM_CHUNK;
-    std::vector<double> part(std::max<size_t>(nChunks, 1) * LSB_LM_NSUM, 0.0);
+    const size_t nChunks = std::max<size_t>((n + LSB_LM_CHUNK - 1) / LSB_LM_CHUNK, 1);
+    const size_t nBlocks = (nChunks + 31) / 32;
+    std::vector<double> part(nBlocks * 32 * LSB_LM_NSUM, 0.0);   // missing chunks stay +0.0
 #pragma omp parallel for num_threads(NbThreads) schedule(static)
     for (long c = 0; c < (long)nChunks; ++c) {
-      double chunk[LSB_LM_NSUM];
-      for (int q = 0; q < LSB_LM_NSUM; ++q) chunk[q] = 0.0;
-      for (int w = 0; w < LSB_LM_CHUNK / 32; ++w) {
+      double group[32][LSB_LM_NSUM];
+      for (int g = 0; g < 32; ++g) {
         double lane[32][LSB_LM_NSUM];
         for (int l = 0; l < 32; ++l) {
-          const size_t i = (size_t)c * LSB_LM_CHUNK + w * 32 + l;
+          const size_t i = (size_t)c * LSB_LM_CHUNK + g * 32 + l;
           if (i < n) lsb::lm_eval_record(Records[i], pt, Sat, lane[l]);
           else for (int q = 0; q < LSB_LM_NSUM; ++q) lane[l][q] = 0.0;
         }
-        for (int off = 16; off >= 1; off >>= 1)
-          for (int l = 0; l < off; ++l)
-            for (int q = 0; q < LSB_LM_NSUM; ++q) lane[l][q] += lane[l + off][q];
-        for (int q = 0; q < LSB_LM_NSUM; ++q) chunk[q] = (w == 0) ? lane[0][q] : chunk[q] + lane[0][q];
+        Fold32(lane);
+        for (int q = 0; q < LSB_LM_NSUM; ++q) group[g][q] = lane[0][q];
       }
-      for (int q = 0; q < LSB_LM_NSUM; ++q) part[c * LSB_LM_NSUM + q] = chunk[q];
+      Fold32(group);
+      for (int q = 0; q < LSB_LM_NSUM; ++q) part[c * LSB_LM_NSUM + q] = group[0][q];
     }
-    for (size_t c = 1; c < nChunks; ++c)   // chunk sums in chunk order
-      for (int q = 0; q < LSB_LM_NSUM; ++q) part[q] = part[q] + part[c * LSB_LM_NSUM + q];
-    for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = part[q];
+    for (size_t b = 0; b < nBlocks; ++b) {
+      double chunk[32][LSB_LM_NSUM];
+      for (int l = 0; l < 32; ++l)
+        for (int q = 0; q < LSB_LM_NSUM; ++q) chunk[l][q] = part[(b * 32 + l) * LSB_LM_NSUM + q];
+      Fold32(chunk);
+      for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = (b == 0) ? chunk[0][q] : E[q] + chunk[0][q];
+    }
   }
 
   // LocalOptimizer::Solve (:74-102). Returns Ceres' num_successful_steps

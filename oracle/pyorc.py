@@ -65,3 +65,29 @@ def eigen33(mats, as_float=False):
     vec = np.zeros((len(m), 9))
     load().orc_eigen33(capi._ptr(m), capi._ptr(ev), capi._ptr(vec), C.c_long(len(m)), C.c_int(1 if as_float else 0))
     return ev, vec.reshape(-1, 3, 3)
+
+
+def lm_terms(A, P, X, w, x, sat):
+    """28 normal-equation terms per record (common/lm_core.h::lm_eval_record)."""
+    A = np.ascontiguousarray(A, dtype=np.float64).reshape(-1, 9)
+    P = np.ascontiguousarray(P, dtype=np.float64).reshape(-1, 3)
+    X = np.ascontiguousarray(X, dtype=np.float64).reshape(-1, 3)
+    w = np.ascontiguousarray(w, dtype=np.float64)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    out = np.zeros((len(A), 28))
+    load().orc_lm_terms(capi._ptr(A), capi._ptr(P), capi._ptr(X), capi._ptr(w), C.c_long(len(A)), capi._ptr(x), C.c_double(sat), capi._ptr(out))
+    return out
+
+
+def lm_solve(A, P, X, w, x0, sat, max_iter=15, two_d=False, threads=1):
+    """The oracle's LocalOptimizer::Solve on raw residual records."""
+    A = np.ascontiguousarray(A, dtype=np.float64).reshape(-1, 9)
+    P = np.ascontiguousarray(P, dtype=np.float64).reshape(-1, 3)
+    X = np.ascontiguousarray(X, dtype=np.float64).reshape(-1, 3)
+    w = np.ascontiguousarray(w, dtype=np.float64)
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    x = np.zeros(6)
+    cost, acc, term = C.c_double(), C.c_int(), C.c_int()
+    it = load().orc_lm_solve(capi._ptr(A), capi._ptr(P), capi._ptr(X), capi._ptr(w), C.c_long(len(A)), capi._ptr(x0), C.c_double(sat),
+                             C.c_int(max_iter), C.c_int(1 if two_d else 0), C.c_int(threads), capi._ptr(x), C.byref(cost), C.byref(acc), C.byref(term))
+    return dict(x=x, cost=cost.value, iterations=it, accepted=acc.value, term=term.value)

@@ -121,3 +121,118 @@ def test_rolling_grid_against_dict_model(oracle_lib, synth):
     exp["label"] = 0
     assert len(got) == len(exp)
     assert got.tobytes() == exp.tobytes()
+
+
+# ---------------------------------------------------------------- LM (common/lm_core.h)
+def _euler_zyx(rx, ry, rz):
+    cx, sx, cy, sy, cz, sz = np.cos(rx), np.sin(rx), np.cos(ry), np.sin(ry), np.cos(rz), np.sin(rz)
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    return Rz @ Ry @ Rx
+
+
+def _lm_problem(rng, n, x_true, noise=0.0):
+    """Records of the reference's three residual kinds (KeypointsMatcher.cxx:270-480): A = I - n n^T (line),
+    n n^T (plane), a full SPD root (blob); X is the keypoint, P the model point."""
+    R, t = _euler_zyx(*x_true[3:]), x_true[:3]
+    nrm = rng.normal(size=(n, 3))
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    kind = rng.integers(0, 3, n)
+    A = np.zeros((n, 3, 3))
+    for i in range(n):
+        nn = np.outer(nrm[i], nrm[i])
+        if kind[i] == 0:
+            A[i] = np.eye(3) - nn
+        elif kind[i] == 1:
+            A[i] = nn
+        else:
+            B = rng.normal(size=(3, 3))
+            A[i] = B @ B.T / 3 + 0.2 * np.eye(3)
+    P = rng.uniform(-30, 30, (n, 3))
+    X = (P + noise * rng.normal(size=(n, 3)) - t) @ R      # R^T (P - t), row form
+    w = rng.uniform(0.3, 1.0, n)
+    return A, P, X, w
+
+
+def _tukey(s, a2):
+    v = np.clip(1 - s / a2, 0, None)
+    return np.where(s <= a2, a2 / 3 * (1 - v ** 3), a2 / 3), np.where(s <= a2, v ** 2, 0.0)
+
+
+def test_lm_terms_against_numpy(oracle_lib):
+    """J^T J, J^T r and the cost of lm_eval_record == the reference residual r = A (R X + t - P) under
+    ScaledLoss(TukeyLoss) with the Ceres corrector, Jacobian by central differences."""
+    rng = np.random.default_rng(3)
+    x = np.array([0.4, -0.2, 0.1, 0.03, -0.05, 0.7])
+    A, P, X, w = _lm_problem(rng, 200, x + [0.05, 0.02, -0.04, 0.01, -0.01, 0.02], noise=0.02)
+    w[::11] = -1.0                                          # failed matches contribute zero
+    sat = 0.3
+    got = oracle_lib.lm_terms(A, P, X, w, x, sat)
+
+    def resid(xx):
+        return np.einsum("nij,nj->ni", A, X @ _euler_zyx(*xx[3:]).T + xx[:3] - P)
+
+    r = resid(x)
+    J = np.zeros((len(A), 3, 6))
+    for k in range(6):
+        h = np.zeros(6)
+        h[k] = 1e-6
+        J[:, :, k] = (resid(x + h) - resid(x - h)) / 2e-6
+    rho0, rho1 = _tukey((r * r).sum(1), sat * sat)
+    ok = w >= 0
+    scale = np.where(ok, w * rho1, 0.0)
+    H = np.einsum("n,nki,nkj->nij", scale, J, J)
+    g = np.einsum("n,nki,nk->ni", scale, J, r)
+    iu = np.triu_indices(6)
+    assert np.allclose(got[:, :21], H[:, iu[0], iu[1]], rtol=1e-6, atol=1e-9)
+    assert np.allclose(got[:, 21:27], g, rtol=1e-6, atol=1e-9)
+    assert np.allclose(got[:, 27], np.where(ok, 0.5 * w * rho0, 0.0), rtol=1e-12, atol=0)
+    assert (got[~ok] == 0).all()
+
+
+def test_lm_reduction_tree_and_thread_invariance(oracle_lib):
+    """The cost after the first evaluation is the radix-32 tree sum of lm_core.h, bit for bit, and does not
+    depend on the number of threads."""
+    rng = np.random.default_rng(4)
+    x = np.array([0.1, 0.0, -0.1, 0.0, 0.01, -0.02])
+    n = 70001                                               # 69 chunks -> 3 blocks, ragged tail
+    A, P, X, w = _lm_problem(rng, n, x, noise=0.05)
+    terms = oracle_lib.lm_terms(A, P, X, w, x, 1.0)[:, 27]
+
+    def fold32(v):                                          # v: (..., 32)
+        for off in (16, 8, 4, 2, 1):
+            v = v[..., :off] + v[..., off:2 * off]
+        return v[..., 0]
+
+    pad = np.zeros(3 * 32 * 1024)
+    pad[:n] = terms
+    blocks = fold32(fold32(fold32(pad.reshape(3, 32, 32, 32))))
+    expect = (blocks[0] + blocks[1]) + blocks[2]
+    r1 = oracle_lib.lm_solve(A, P, X, w, x, 1.0, max_iter=0, threads=1)
+    r8 = oracle_lib.lm_solve(A, P, X, w, x, 1.0, max_iter=0, threads=8)
+    assert r1["cost"] == expect == r8["cost"]
+    s1 = oracle_lib.lm_solve(A, P, X, w, x + 0.01, 1.0, max_iter=15, threads=1)
+    s8 = oracle_lib.lm_solve(A, P, X, w, x + 0.01, 1.0, max_iter=15, threads=8)
+    assert np.array_equal(s1["x"], s8["x"]) and s1["iterations"] == s8["iterations"]
+
+
+def test_lm_solve_against_scipy(oracle_lib):
+    """Trust-region LM of lm_core.h reaches the least-squares solution scipy finds (near-quadratic loss)."""
+    from scipy.optimize import least_squares
+    rng = np.random.default_rng(5)
+    x_true = np.array([0.3, -0.4, 0.2, 0.02, -0.03, 0.05])
+    A, P, X, w = _lm_problem(rng, 3000, x_true, noise=0.01)
+
+    def resid(xx):
+        d = X @ _euler_zyx(*xx[3:]).T + xx[:3] - P
+        return (np.sqrt(w)[:, None] * np.einsum("nij,nj->ni", A, d)).ravel()
+
+    ref = least_squares(resid, np.zeros(6), method="lm", xtol=1e-14, ftol=1e-14, gtol=1e-14)
+    got = oracle_lib.lm_solve(A, P, X, w, np.zeros(6), 1e3, max_iter=50)
+    assert got["term"] in (1, 2, 3)                          # converged (gradient / parameter / function tolerance)
+    assert np.abs(got["x"] - ref.x).max() < 2e-6
+    assert np.abs(got["x"] - x_true).max() < 5e-3
+    # held parameters (2-D mode): z, rx, ry stay put (LocalOptimizer.cxx:89-90)
+    g2 = oracle_lib.lm_solve(A, P, X, w, np.zeros(6), 1e3, max_iter=50, two_d=True)
+    assert (g2["x"][[2, 3, 4]] == 0).all() and np.abs(g2["x"][[0, 1, 5]] - x_true[[0, 1, 5]]).max() < 0.05

@@ -31,7 +31,7 @@ int main(int argc, char** argv)
   const int n = argc > 1 ? atoi(argv[1]) : 118000;
   const size_t stride = (size_t)(n + 31) / 32 * 32;
   const int nchunks = (n + LSB_LM_CHUNK - 1) / LSB_LM_CHUNK;
-  std::vector<double> rec(16 * stride, 0.0);
+  std::vector<double> rec(13 * stride, 0.0);
   srand(7);
   auto rnd = [] { return rand() / (double)RAND_MAX - 0.5; };
   for (int i = 0; i < n; ++i) {
@@ -40,20 +40,22 @@ int main(int argc, char** argv)
     nx /= nn; ny /= nn; nz /= nn;
     const double A[9] = {nx * nx, nx * ny, nx * nz, nx * ny, ny * ny, ny * nz, nx * nz, ny * nz, nz * nz};
     const double P[3] = {40 * rnd(), 40 * rnd(), 6 * rnd()};
-    for (int q = 0; q < 9; ++q) rec[q * stride + i] = A[q];
-    for (int q = 0; q < 3; ++q) rec[(9 + q) * stride + i] = P[q];
-    for (int q = 0; q < 3; ++q) rec[(12 + q) * stride + i] = P[q] + 0.05 * rnd();
-    rec[15 * stride + i] = (i % 17 == 0) ? -1.0 : 0.8;
+    LmRecord r;
+    const double X[3] = {P[0] + 0.05 * rnd(), P[1] + 0.05 * rnd(), P[2] + 0.05 * rnd()};
+    lm_record_set(r, A, P, X, (i % 17 == 0) ? -1.0 : 0.8);
+    for (int q = 0; q < 6; ++q) rec[q * stride + i] = r.M[q];
+    for (int q = 0; q < 3; ++q) { rec[(6 + q) * stride + i] = r.P[q]; rec[(9 + q) * stride + i] = r.X[q]; }
+    rec[12 * stride + i] = r.w;
   }
   double* d_rec; double* d_part; LmState* d_state; LmPoint* d_point; unsigned* d_counter; int* d_hist;
-  cudaMalloc(&d_rec, rec.size() * 8); cudaMalloc(&d_part, (size_t)nchunks * LSB_LM_NSUM * 8);
+  cudaMalloc(&d_rec, rec.size() * 8); const int pstride = (nchunks + 31) / 32 * 32; cudaMalloc(&d_part, (size_t)pstride * LSB_LM_NSUM * 8);
   cudaMalloc(&d_state, sizeof(LmState)); cudaMalloc(&d_point, sizeof(LmPoint)); cudaMalloc(&d_counter, 8);
   cudaMalloc(&d_hist, 3 * LSB_MATCH_N_STATUS * 4);
   std::vector<int> hist(3 * LSB_MATCH_N_STATUS, 1000);
   cudaMemcpy(d_hist, hist.data(), hist.size() * 4, cudaMemcpyHostToDevice);
   cudaMemcpy(d_rec, rec.data(), rec.size() * 8, cudaMemcpyHostToDevice);
   auto begin = [&] { k_lm_begin<<<1, 1>>>(d_state, d_point, d_counter, 0.01, 0.02, 0.03, 0.001, 0.002, 0.003, 15, 0, d_hist, 100u); };
-  auto eval = [&](int first) { k_lm_eval<<<nchunks, LM_THREADS>>>(d_rec, stride, n, nchunks, 1.0, d_state, d_point, d_part, d_counter, first); };
+  auto eval = [&](int first) { k_lm_eval<<<nchunks, LM_THREADS>>>(d_rec, stride, n, nchunks, pstride, 1.0, d_state, d_point, d_part, d_counter, first); };
   printf("n = %d records, %d chunks of %d, %d threads per CTA\n", n, nchunks, LSB_LM_CHUNK, LM_THREADS);
   const float t_empty = time_launches(200, [&] { k_empty<<<nchunks, LM_THREADS>>>(0); });
   const float t_begin = time_launches(200, [&] { begin(); });
