@@ -94,38 +94,59 @@ __global__ void k_cell_start(const uint32_t* __restrict__ key_sorted, int m, int
 }
 
 // ------------------------------------------------------------------ search ---
+// A candidate is one 64-bit key: (bits of d2) << 32 | cloud index.  d2 >= +0, so the unsigned
+// order of the keys is the canonical order of the results: ascending d2, ties by smaller index.
+typedef unsigned long long Key;
+constexpr Key KEY_NONE = ((Key)0x7f800000u << 32) | 0x7fffffffu;     // (+inf, INT_MAX)
+__device__ __forceinline__ Key make_key(float d2, int id) { return ((Key)__float_as_uint(d2) << 32) | (unsigned)id; }
+__device__ __forceinline__ float key_d2(Key k) { return __uint_as_float((unsigned)(k >> 32)); }
+__device__ __forceinline__ int key_id(Key k) { return (int)(unsigned)k; }
+
 template <int KMAX>
 struct TopK {
-  float d[KMAX];
-  int id[KMAX];
+  Key key[KMAX];     // ascending
   __device__ __forceinline__ void init()
   {
 #pragma unroll
-    for (int t = 0; t < KMAX; ++t) { d[t] = INFINITY; id[t] = INT_MAX; }
+    for (int t = 0; t < KMAX; ++t) key[t] = KEY_NONE;
   }
-  __device__ __forceinline__ void offer(float dd, int ii)
+  __device__ __forceinline__ float kth() const { return key_d2(key[KMAX - 1]); }
+  __device__ __forceinline__ void offer(Key x)
   {
-    if (dd < d[KMAX - 1] || (dd == d[KMAX - 1] && ii < id[KMAX - 1])) {
-      d[KMAX - 1] = dd; id[KMAX - 1] = ii;
+    if (x < key[KMAX - 1]) {
 #pragma unroll
-      for (int t = KMAX - 1; t > 0; --t) {
-        const bool sw = d[t] < d[t - 1] || (d[t] == d[t - 1] && id[t] < id[t - 1]);
-        const float td = d[t]; const int ti = id[t];
-        d[t] = sw ? d[t - 1] : td; id[t] = sw ? id[t - 1] : ti;
-        d[t - 1] = sw ? td : d[t - 1]; id[t - 1] = sw ? ti : id[t - 1];
+      for (int t = 0; t < KMAX; ++t) {          // bubble: x carries the displaced larger key upward
+        const bool lt = key[t] < x;
+        const Key lo = lt ? key[t] : x;
+        x = lt ? x : key[t];
+        key[t] = lo;
       }
     }
   }
+  __device__ __forceinline__ void pop()
+  {
+#pragma unroll
+    for (int u = 0; u + 1 < KMAX; ++u) key[u] = key[u + 1];
+    key[KMAX - 1] = KEY_NONE;
+  }
 };
 
+// scans sorted[b, e): two candidates per trip, both loads issued before the first insertion
 template <int KMAX>
 __device__ __forceinline__ void scan_range(TopK<KMAX>& tk, const float4* __restrict__ sorted, uint32_t b, uint32_t e, float qx, float qy, float qz)
 {
-  for (uint32_t p = b; p < e; ++p) {
-    const float4 s = __ldg(sorted + p);
-    const float dx = qx - s.x, dy = qy - s.y, dz = qz - s.z;
-    const float d = (dx * dx + dy * dy) + dz * dz;
-    tk.offer(d, __float_as_int(s.w));
+  uint32_t p = b;
+  for (; p + 1 < e; p += 2) {
+    const float4 s0 = __ldg(sorted + p), s1 = __ldg(sorted + p + 1);
+    const float ax = qx - s0.x, ay = qy - s0.y, az = qz - s0.z;
+    const float bx = qx - s1.x, by = qy - s1.y, bz = qz - s1.z;
+    tk.offer(make_key((ax * ax + ay * ay) + az * az, __float_as_int(s0.w)));
+    tk.offer(make_key((bx * bx + by * by) + bz * bz, __float_as_int(s1.w)));
+  }
+  if (p < e) {
+    const float4 s0 = __ldg(sorted + p);
+    const float ax = qx - s0.x, ay = qy - s0.y, az = qz - s0.z;
+    tk.offer(make_key((ax * ax + ay * ay) + az * az, __float_as_int(s0.w)));
   }
 }
 
@@ -187,105 +208,121 @@ __device__ __forceinline__ float axis_gap(int d, float off, float cell)
 
 // visiting order of the 27 cells of the 3x3x3 cube: the query's cell, the 6 face
 // neighbours, the 12 edge neighbours, the 8 corners (packed (dz+1)*9 + (dy+1)*3 + (dx+1))
-__constant__ unsigned char c_cube_order[27] = {13, 12, 14, 10, 16, 4, 22, 9, 11, 15, 17, 3, 5, 21, 23, 1, 7, 19, 25, 0, 2, 6, 8, 18, 20, 24, 26};
+__constant__ unsigned char c_cube_order[28] = {13, 12, 14, 10, 16, 4, 22, 9, 11, 15, 17, 3, 5, 21, 23, 1, 7, 19, 25, 0, 2, 6, 8, 18, 20, 24, 26, 255};
 
-// Phase 1: one thread per query scans the 3x3x3 cube around its cell, nearest cells first;
-// a cell whose lower distance bound is not below the current k-th distance is skipped.
-// Queries it cannot settle go to the warp-per-query kernel below.
+// Phase 1: FOUR lanes per query (a thread per query leaves the GPU three quarters empty at
+// 10^5 queries and serialises ~30 dependent cell visits per thread).  The 27 cells of the
+// 3x3x3 cube around the query's cell are dealt nearest-first to the four lanes (lane s takes
+// positions s, s+4, ... of c_cube_order); a cell whose lower distance bound is not below the
+// smallest k-th distance held by the four lanes is skipped.  The four sorted lists are then
+// merged (k rounds of a 2-step min).  The merged list is always written: for a query that the
+// cube does not settle it is a tentative answer whose k-th distance bounds the true one, which
+// is what the warp kernel below starts from.
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
       const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, size_t qs, size_t ts, int32_t* __restrict__ idx_out,
       float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nq) return;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int sub = t & 3;
+  const bool live = (t >> 2) < nq;
+  const int i = live ? (t >> 2) : nq - 1;      // idle quads of the last warp shadow the last query (shuffles need all lanes)
   const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
   TopK<KMAX> tk;
   tk.init();
-  bool done = !q.finite;          // NaN query: nothing found, as an exact search would
-  if (q.finite && q.rfirst <= 1) {
-    // cell boundaries of the 9 rows: cs[row][j] = first point of cell cx-1+j (j = 0..3)
-    uint32_t cs[9][4];
+  const bool scan = q.finite && q.rfirst <= 1;   // NaN query: nothing found, as an exact search would
+  const float gx[3] = {axis_gap(-1, q.ox, gp.cell), 0.f, axis_gap(1, q.ox, gp.cell)};
+  const float gy[3] = {axis_gap(-1, q.oy, gp.cell), 0.f, axis_gap(1, q.oy, gp.cell)};
+  const float gz[3] = {axis_gap(-1, q.oz, gp.cell), 0.f, axis_gap(1, q.oz, gp.cell)};
+  // the lane's 7 cells: index ranges first (independent loads), then the scans
+  uint32_t cb[7], ce[7];
+  float lb[7];
 #pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      const int z = q.cz + t / 3 - 1, y = q.cy + t % 3 - 1;
-      const bool in = z >= 0 && z < gp.nz && y >= 0 && y < gp.ny;
-      const int base = (z * gp.ny + y) * gp.nx;
+  for (int j = 0; j < 7; ++j) {
+    const int c = c_cube_order[sub + 4 * j];
+    const int jz = c / 9, jy = (c / 3) % 3, jx = c % 3;
+    const int z = q.cz + jz - 1, y = q.cy + jy - 1, x = q.cx + jx - 1;
+    const bool in = scan && c != 255 && z >= 0 && z < gp.nz && y >= 0 && y < gp.ny && x >= 0 && x < gp.nx;
+    const int cell_id = in ? (z * gp.ny + y) * gp.nx + x : 0;
+    cb[j] = in ? __ldg(cell_start + cell_id) : 0u;
+    ce[j] = in ? __ldg(cell_start + cell_id + 1) : 0u;
+    lb[j] = in ? (gx[jx] * gx[jx] + gy[jy] * gy[jy]) + gz[jz] * gz[jz] : INFINITY;
+  }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int x = min(max(q.cx - 1 + j, 0), gp.nx);   // clamped: out-of-grid cells become empty ranges
-        cs[t][j] = in ? __ldg(cell_start + base + x) : 0u;
-      }
-    }
-    const float gx[3] = {axis_gap(-1, q.ox, gp.cell), 0.f, axis_gap(1, q.ox, gp.cell)};
-    const float gy[3] = {axis_gap(-1, q.oy, gp.cell), 0.f, axis_gap(1, q.oy, gp.cell)};
-    const float gz[3] = {axis_gap(-1, q.oz, gp.cell), 0.f, axis_gap(1, q.oz, gp.cell)};
-#pragma unroll 1
-    for (int o = 0; o < 27; ++o) {
-      const int c = c_cube_order[o];
-      const int jz = c / 9, jy = (c / 3) % 3, jx = c % 3;
-      const float lb = (gx[jx] * gx[jx] + gy[jy] * gy[jy]) + gz[jz] * gz[jz];
-      if (!(lb < tk.d[KMAX - 1])) continue;
-      const int row = jz * 3 + jy;
-      scan_range(tk, sorted, cs[row][jx], cs[row][jx + 1], q.qx, q.qy, q.qz);
-    }
-    done = (q.rcover <= 1) || resolved_at(tk.d[KMAX - 1], 1, gp.cell, q.minoff);
+  for (int j = 0; j < 7; ++j) {
+    float thr = tk.kth();
+    thr = fminf(thr, __shfl_xor_sync(FULL, thr, 1));
+    thr = fminf(thr, __shfl_xor_sync(FULL, thr, 2));
+    if (lb[j] < thr) scan_range(tk, sorted, cb[j], ce[j], q.qx, q.qy, q.qz);
+    __syncwarp();
   }
-  if (!done) {
-    unres_list[atomicAdd(unres_count, 1u)] = i;
-    return;
-  }
+  // merge: round r yields the r-th smallest key of the four lists
   int nf = 0;
-#pragma unroll
-  for (int t = 0; t < KMAX; ++t) {
-    if (t < k) {
-      const bool ok = tk.d[t] < INFINITY;
-      idx_out[(size_t)i * qs + t * ts] = ok ? tk.id[t] : -1;
-      d2_out[(size_t)i * qs + t * ts] = ok ? tk.d[t] : INFINITY;
-      nf += ok ? 1 : 0;
+  float kd = INFINITY;
+#pragma unroll 1
+  for (int r = 0; r < KMAX; ++r) {
+    if (r >= k) break;
+    Key m = tk.key[0];
+    { const Key o = __shfl_xor_sync(FULL, m, 1); m = (o < m) ? o : m; }
+    { const Key o = __shfl_xor_sync(FULL, m, 2); m = (o < m) ? o : m; }
+    if (tk.key[0] == m && m != KEY_NONE) tk.pop();
+    const bool ok = key_d2(m) < INFINITY;
+    if (live && sub == 0) {
+      idx_out[(size_t)i * qs + r * ts] = ok ? key_id(m) : -1;
+      d2_out[(size_t)i * qs + r * ts] = ok ? key_d2(m) : INFINITY;
     }
+    nf += ok ? 1 : 0;
+    kd = key_d2(m);
   }
+  if (!live || sub != 0) return;
   if (nfound_out) nfound_out[i] = nf;
+  const bool done = !q.finite || (scan && ((q.rcover <= 1) || resolved_at(kd, 1, gp.cell, q.minoff)));
+  if (!done) unres_list[atomicAdd(unres_count, 1u)] = i;
 }
 
-// merges the 32 per-lane sorted lists: round t yields the t-th smallest (d2, id) of the
-// warp.  Writes the first k; returns the number found and the KMAX-th distance.
+// merges the 32 per-lane sorted lists: round t yields the t-th smallest key of the warp
+// (two warp-wide integer min reductions per round).  Writes the first k; returns the number
+// found and the k-th distance.
 template <int KMAX>
 __device__ __forceinline__ int warp_merge_write(TopK<KMAX>& tk, int k, int lane, int32_t* __restrict__ idx_row, float* __restrict__ d2_row,
-                                                size_t ts, float& kmax_d2)
+                                                size_t ts, float& kth_d2)
 {
+  constexpr unsigned FULL = 0xffffffffu;
   int nf = 0;
-  kmax_d2 = INFINITY;
+  kth_d2 = INFINITY;
 #pragma unroll 1
-  for (int t = 0; t < KMAX; ++t) {
-    float bd = tk.d[0];
-    int bi = tk.id[0];
-#pragma unroll
-    for (int off = 16; off; off >>= 1) {
-      const float od = __shfl_xor_sync(0xffffffffu, bd, off);
-      const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
-      if (od < bd || (od == bd && oi < bi)) { bd = od; bi = oi; }
-    }
-    const bool ok = bd < INFINITY;
-    if (ok && tk.id[0] == bi && tk.d[0] == bd) {   // the winning lane pops its head
-#pragma unroll
-      for (int u = 0; u + 1 < KMAX; ++u) { tk.d[u] = tk.d[u + 1]; tk.id[u] = tk.id[u + 1]; }
-      tk.d[KMAX - 1] = INFINITY; tk.id[KMAX - 1] = INT_MAX;
-    }
-    if (t < k) {
-      if (lane == 0) { idx_row[t * ts] = ok ? bi : -1; d2_row[t * ts] = ok ? bd : INFINITY; }
-      nf += ok ? 1 : 0;
-    }
-    if (t == KMAX - 1) kmax_d2 = bd;
+  for (int t = 0; t < k; ++t) {
+    const unsigned hi = (unsigned)(tk.key[0] >> 32), lo = (unsigned)tk.key[0];
+    const unsigned mhi = __reduce_min_sync(FULL, hi);
+    const unsigned mlo = __reduce_min_sync(FULL, (hi == mhi) ? lo : 0xffffffffu);
+    const Key m = ((Key)mhi << 32) | mlo;
+    if (tk.key[0] == m && m != KEY_NONE) tk.pop();     // the winning lane pops its head
+    const bool ok = key_d2(m) < INFINITY;
+    if (lane == 0) { idx_row[t * ts] = ok ? key_id(m) : -1; d2_row[t * ts] = ok ? key_d2(m) : INFINITY; }
+    nf += ok ? 1 : 0;
+    kth_d2 = key_d2(m);
   }
   return nf;
 }
 
-// Phase 2: one warp per unsettled query.  The lanes share the rows of the cube of radius
-// rcap (each row one contiguous range), keep per-lane top-K lists and merge them.  If even
-// that cube does not settle the query: capped mode reports "k-th neighbour beyond the cap",
-// exact mode falls back to a brute-force pass over all m points (rare: isolated queries).
+// cells of [lo, hi] along one axis, clamped to the grid (monotone in the same floorf((v - o) / cell)
+// that binned the points, so every point with a coordinate in [lo, hi] lies in the returned cells)
+__device__ __forceinline__ void axis_cells(float lo, float hi, float o, float cell, int n, int& c0, int& c1)
+{
+  c0 = (int)fminf(fmaxf(floorf((lo - o) / cell), 0.f), (float)(n - 1));
+  c1 = (int)fminf(fmaxf(floorf((hi - o) / cell), 0.f), (float)(n - 1));
+}
+
+// Phase 2: one warp per query that the 3x3x3 cube did not settle.  If phase 1 found k points,
+// its k-th distance T bounds the true one: the warp scans the box of the sphere of radius
+// sqrt(T) (capped mode: at most the cap) and is done - exact.  Otherwise (fewer than k points in
+// the cube) capped mode scans the box of the cap sphere and reports "k-th neighbour beyond the
+// cap" if that is what it finds; exact mode scans the cube of radius rcap and, if even that does
+// not settle the query, falls back to a brute-force pass over all m points (isolated queries).
+// The lanes share the rows of the box (each row one contiguous index range), keep per-lane
+// top-K lists and merge them.
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
@@ -304,27 +341,41 @@ k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Is
     const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
     TopK<KMAX> tk;
     tk.init();
-    const int R = max(rcap, 1);
-    if (q.rfirst <= R) {
-      const int z0 = max(0, q.cz - R), z1 = min(gp.nz - 1, q.cz + R);
-      const int y0 = max(0, q.cy - R), y1 = min(gp.ny - 1, q.cy + R);
-      const int x0 = max(0, q.cx - R), x1 = min(gp.nx - 1, q.cx + R);
-      const int nyr = y1 - y0 + 1, nrows = (z1 - z0 + 1) * nyr;
-      if (x0 <= x1 && nyr > 0) {
-        for (int t = lane; t < nrows; t += 32) {
-          const int z = z0 + t / nyr, y = y0 + t % nyr;
-          // rows that cannot hold anything nearer than this lane's k-th candidate (or than the cap) are skipped
-          const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
-          const float lb = gy * gy + gz * gz;
-          if (!(lb < tk.d[KMAX - 1]) || lb > cap2) continue;
-          const int base = (z * gp.ny + y) * gp.nx;
-          scan_range(tk, sorted, __ldg(cell_start + base + x0), __ldg(cell_start + base + x1 + 1), q.qx, q.qy, q.qz);
-        }
+    // threshold: every point that can belong to the answer has d2 <= T
+    const float tentative = d2_out[(size_t)i * qs + (size_t)(k - 1) * ts];
+    float T = tentative;
+    if (capped) T = fminf(T, cap2);
+    const bool sphere = T < INFINITY;
+    int x0, x1, y0, y1, z0, z1;
+    if (sphere) {
+      const float r = sqrtf(T);
+      const float rr = r + (1.0e-3f + 1.0e-4f * (r + gp.cell));
+      axis_cells(q.qx - rr, q.qx + rr, gp.ox, gp.cell, gp.nx, x0, x1);
+      axis_cells(q.qy - rr, q.qy + rr, gp.oy, gp.cell, gp.ny, y0, y1);
+      axis_cells(q.qz - rr, q.qz + rr, gp.oz, gp.cell, gp.nz, z0, z1);
+    } else {
+      const int R = max(rcap, 1);
+      z0 = max(0, q.cz - R); z1 = min(gp.nz - 1, q.cz + R);
+      y0 = max(0, q.cy - R); y1 = min(gp.ny - 1, q.cy + R);
+      x0 = max(0, q.cx - R); x1 = min(gp.nx - 1, q.cx + R);
+    }
+    const int nyr = y1 - y0 + 1, nrows = (z1 - z0 + 1) * nyr;
+    if (q.finite && x0 <= x1 && nyr > 0) {
+      for (int t = lane; t < nrows; t += 32) {
+        const int z = z0 + t / nyr, y = y0 + t % nyr;
+        // rows that cannot hold anything nearer than this lane's k-th candidate (or than T) are skipped
+        const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
+        const float lb = gy * gy + gz * gz;
+        if (!(lb < tk.kth()) || lb > T) continue;
+        const int base = (z * gp.ny + y) * gp.nx;
+        scan_range(tk, sorted, __ldg(cell_start + base + x0), __ldg(cell_start + base + x1 + 1), q.qx, q.qy, q.qz);
       }
     }
     float kd;
     int nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * qs, d2_out + (size_t)i * qs, ts, kd);
-    const bool settled = (q.rcover <= R) || resolved_at(kd, R, gp.cell, q.minoff);
+    bool settled;
+    if (sphere) settled = (T == tentative) || (kd <= cap2);          // all points with d2 <= T were visited
+    else settled = (q.rcover <= max(rcap, 1)) || resolved_at(kd, max(rcap, 1), gp.cell, q.minoff);
     if (!settled) {
       if (capped) {
         // every point within the cap distance has been visited and the k-th neighbour is
@@ -335,7 +386,7 @@ k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Is
         for (int p = lane; p < m; p += 32) {
           const float4 s = __ldg(sorted + p);
           const float dx = q.qx - s.x, dy = q.qy - s.y, dz = q.qz - s.z;
-          tk.offer((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w));
+          tk.offer(make_key((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w)));
         }
         nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * qs, d2_out + (size_t)i * qs, ts, kd);
       }
@@ -349,7 +400,7 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
                 float* d2, int32_t* nf, bool entry_major, cudaStream_t s, LaunchCounter& lc)
 {
   const size_t qs = entry_major ? 1 : (size_t)k, ts = entry_major ? nq : 1;
-  const unsigned G = div_up(nq, 128);
+  const unsigned G = div_up(nq * 4, 128);   // four lanes per query
   const int NQ = (int)nq, M = (int)g.m;
   const int capped = cap_dist >= 0.f ? 1 : 0;
   // radius of the warp kernel's cube: capped => everything within cap_dist is inside it

@@ -3,6 +3,8 @@
 // every cloud operation is a kernel on the handle's stream.
 #include "slam.cuh"
 #include <cstring>
+#include <cstdlib>
+#include <cstdio>
 #include <cmath>
 #include <cfloat>
 #include <limits>
@@ -27,6 +29,7 @@ lsb_slam::lsb_slam(int dev) : device(dev)
   LSB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   for (auto& e : ev_join) LSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   lsb_default_params(&P);
+  if (const char* e = std::getenv("LSB_TRACE")) trace.on = (e[0] == '1');
   KeyPointsExtractors[0].reset(new ExtractorGpu());
   // Slam.cxx:153-157: resolution is snapped with the leaf size at call time (0.2 -> 10.0)
   for (auto& m : LocalMaps) m.SetVoxelResolution(10., stream, lc);
@@ -38,6 +41,11 @@ lsb_slam::lsb_slam(int dev) : device(dev)
   LocalMaps[LSB_EDGE].knn_cell_factor = 5.0f;
   LocalMaps[LSB_PLANE].knn_cell_factor = 2.5f;
   LocalMaps[LSB_BLOB].knn_cell_factor = 2.5f;
+  if (const char* e = std::getenv("LSB_KNN_CELL_FACTORS")) {   // tuning hook: "edge,plane,blob"
+    float f[3];
+    if (std::sscanf(e, "%f,%f,%f", &f[0], &f[1], &f[2]) == 3)
+      for (int k = 0; k < 3; ++k) if (f[k] > 0.f) LocalMaps[k].knn_cell_factor = f[k];
+  }
   d_minmax.reserve(2, stream); h_minmax.reserve(2);
   Reset(true);
 }
@@ -52,6 +60,27 @@ lsb_slam::~lsb_slam()
   for (auto& e : ev_join) if (e) cudaEventDestroy(e);
   for (auto& t : tstream) if (t) cudaStreamDestroy(t);
   if (stream) cudaStreamDestroy(stream);
+}
+
+void lsb_slam::Trace::mark(const char* name, cudaStream_t s)
+{
+  if (!on) return;
+  if (used == evs.size()) { cudaEvent_t e; LSB_CUDA(cudaEventCreate(&e)); evs.push_back(e); names.push_back(name); }
+  names[used] = name;
+  LSB_CUDA(cudaEventRecord(evs[used++], s));
+}
+
+void lsb_slam::Trace::dump()
+{
+  if (!on || used < 2) { used = 0; return; }
+  std::fprintf(stderr, "[lsb trace]");
+  for (size_t i = 1; i < used; ++i) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, evs[i - 1], evs[i]);
+    std::fprintf(stderr, " %s=%.0fus", names[i], ms * 1e3f);
+  }
+  std::fprintf(stderr, "\n");
+  used = 0;
 }
 
 void lsb_slam::Fork()
@@ -127,6 +156,7 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   if (!CheckFrames(n_frames, n, stamp_us, seq)) return LSB_W_FRAME_IGNORED;
   const unsigned launches0 = lc.n;
   LSB_CUDA(cudaEventRecord(ev[0], stream));
+  trace.mark("start", stream);
   // host -> device copy of the input frames (skipped for device-resident input)
   while (FramePool.size() < (size_t)n_frames) FramePool.emplace_back(new DFrame());
   NbCurrentFrames = (size_t)n_frames;
@@ -158,7 +188,9 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   CurrentTime = StampToSec(CurrentStamp);
   for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
 
+  trace.mark("h2d", stream);
   ExtractKeypoints();
+  trace.mark("extract", stream);
   LSB_CUDA(cudaEventRecord(ev[1], stream));
   ComputeEgoMotion();
   LSB_CUDA(cudaEventRecord(ev[2], stream));
@@ -168,8 +200,10 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // the map update invalidates the submaps
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
   Join();
+  trace.mark("map_update", stream);
   LSB_CUDA(cudaEventRecord(ev[4], stream));
   LSB_CUDA(cudaEventSynchronize(ev[4]));
+  trace.dump();
   LogCurrentFrameState(CurrentTime);
   for (int k = 0; k < 3; ++k) {
     Stats.n_keypoints[k] = (uint32_t)CurrentKeypoints[k].n;
@@ -359,6 +393,7 @@ void lsb_slam::Localization()
   std::memset(LocDebug.hist, 0, sizeof(LocDebug.hist));
   for (auto& o : LocDebug.off) o = 0;
   if (P.undistortion) { InitUndistortion(); RefineUndistortion(); }   // :986-995
+  trace.mark("undistort", stream);
 
   // Submaps (:1003-1037): the three maps work on their own streams, in host phases so that
   // their read-backs (bbox of the keypoints, size of the submap) overlap
@@ -384,6 +419,7 @@ void lsb_slam::Localization()
   }
   for (int k = 0; k < 3; ++k)
     if (pending[k]) LocalMaps[k].SubMapFinish(TypeStream(k), lc);
+  if (trace.on) { Join(); trace.mark("submap+grid", stream); }
 
   // ICP - LM loop (:1051-1156)
   TotalMatchedKeypoints = 0;
@@ -399,11 +435,13 @@ void lsb_slam::Localization()
       Stats.knn_queries += (uint32_t)nk[k];
     }
     Join();
+    trace.mark("match", stream);
     // the "enough matches" test (:1098-1107) is taken on the device as well: one read-back per ICP iteration
     double x0[6];
     iso_to_xyzrpy(Tworld, x0);
     const LmState st = mw.solve(x0, (int)P.localization_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance,
                                 P.min_nb_matched_keypoints, LocDebug.hist, stream, lc);
+    trace.mark("lm", stream);
     SaveDebug(LocDebug);
     Stats.loc_icp_iters++;
     TotalMatchedKeypoints = 0;

@@ -82,6 +82,15 @@ struct lsb_slam {
   lsb::DevBuf<float> tmp_f;
   lsb::DevBuf<uint8_t> tmp_u8;
   cudaEvent_t ev[6] = {};
+  // LSB_TRACE=1: named spans of the frame on `stream` (CUDA events), printed to stderr per frame
+  struct Trace {
+    bool on = false;
+    std::vector<cudaEvent_t> evs;
+    std::vector<const char*> names;
+    size_t used = 0;
+    void mark(const char* name, cudaStream_t s);
+    void dump();
+  } trace;
 
   explicit lsb_slam(int dev);
   ~lsb_slam();
