@@ -16,6 +16,7 @@
 #include <climits>
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 namespace lsb {
 
@@ -282,6 +283,115 @@ k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d p
   if (!done) unres_list[atomicAdd(unres_count, 1u)] = i;
 }
 
+// Phase 1 for large query sets: ONE thread per query, every trip taken by the 32 lanes together.
+// With a scan loop per cell a warp pays, cell after cell, for the longest cell among its lanes,
+// and for a ~60-instruction sorted insertion on nearly every trip (some lane always inserts).
+// Here each lane runs ONE candidate stream over the non-empty rows of the 3x3x3 cube (a row =
+// three x-adjacent cells = one contiguous index range; own row first, a row skipped when its
+// lower bound is not below the lane's k-th distance); a trip is branch-free (advance-row step,
+// load, distance, compare) and STREAM_TRIPS candidates are loaded together; each is then offered
+// in turn, the sorted insertion being executed only when some lane of the warp needs it (the
+// other lanes bubble KEY_NONE through, unchanged).  Row ranges and bounds live in shared memory
+// (per-lane dynamic index).
+constexpr int STREAM_TRIPS = 4;
+__constant__ unsigned char c_row_order[9] = {4, 1, 7, 3, 5, 0, 2, 6, 8};   // (dz+1)*3 + (dy+1), nearest first
+
+template <int KMAX, bool FROM_POINTS>
+__global__ void __launch_bounds__(128)
+k_knn_stream(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
+             const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, size_t qs, size_t ts,
+             int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list,
+             unsigned* __restrict__ unres_count)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  __shared__ uint32_t s_rb[9][128], s_re[9][128];
+  __shared__ float s_rl[9][128];
+  const int tid = threadIdx.x;
+  const int i0 = blockIdx.x * blockDim.x + tid;
+  const bool live = i0 < nq;
+  const int i = live ? i0 : nq - 1;
+  const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
+  const bool scan = live && q.finite && q.rfirst <= 1;
+  const float gy[3] = {axis_gap(-1, q.oy, gp.cell), 0.f, axis_gap(1, q.oy, gp.cell)};
+  const float gz[3] = {axis_gap(-1, q.oz, gp.cell), 0.f, axis_gap(1, q.oz, gp.cell)};
+  // the lane's non-empty rows, in visiting order
+  uint32_t rb[9], re[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    const int r = c_row_order[t];
+    const int z = q.cz + r / 3 - 1, y = q.cy + r % 3 - 1;
+    const bool in = scan && z >= 0 && z < gp.nz && y >= 0 && y < gp.ny;
+    const int base = (z * gp.ny + y) * gp.nx;
+    const int xa = min(max(q.cx - 1, 0), gp.nx), xb = min(max(q.cx + 2, 0), gp.nx);   // clamped: out-of-grid cells are empty
+    rb[t] = in ? __ldg(cell_start + base + xa) : 0u;
+    re[t] = in ? __ldg(cell_start + base + xb) : 0u;
+  }
+  int nrow = 0;
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    const int r = c_row_order[t];
+    if (rb[t] < re[t]) {
+      s_rb[nrow][tid] = rb[t];
+      s_re[nrow][tid] = re[t];
+      s_rl[nrow][tid] = gy[r % 3] * gy[r % 3] + gz[r / 3] * gz[r / 3];
+      ++nrow;
+    }
+  }
+  TopK<KMAX> tk;
+  tk.init();
+  int o = 0;
+  uint32_t p = 0, e = 0;
+  while (true) {
+    // one advance-row step (skips a row whose lower bound cannot beat the lane's k-th)
+    const bool adv = p >= e && o < nrow;
+    const int oo = adv ? o : 0;
+    const bool take = adv && s_rl[oo][tid] < tk.kth();
+    p = take ? s_rb[oo][tid] : p;
+    e = take ? s_re[oo][tid] : e;
+    o += adv ? 1 : 0;
+    // STREAM_TRIPS candidates loaded together (one memory round trip); each is offered in turn, and
+    // a sorted insertion is executed only if some lane of the warp needs it
+    float4 sv[STREAM_TRIPS];
+#pragma unroll
+    for (int j = 0; j < STREAM_TRIPS; ++j) sv[j] = __ldg(sorted + ((p + j < e) ? p + j : 0u));
+    Key kj[STREAM_TRIPS];
+#pragma unroll
+    for (int j = 0; j < STREAM_TRIPS; ++j) {
+      const float ax = q.qx - sv[j].x, ay = q.qy - sv[j].y, az = q.qz - sv[j].z;
+      kj[j] = (p + j < e) ? make_key((ax * ax + ay * ay) + az * az, __float_as_int(sv[j].w)) : KEY_NONE;
+    }
+    p = min(p + (uint32_t)STREAM_TRIPS, max(p, e));
+#pragma unroll
+    for (int j = 0; j < STREAM_TRIPS; ++j) {
+      Key x = (kj[j] < tk.key[KMAX - 1]) ? kj[j] : KEY_NONE;
+      if (__any_sync(FULL, x != KEY_NONE)) {
+#pragma unroll
+        for (int t = 0; t < KMAX; ++t) {
+          const bool lt = tk.key[t] < x;
+          const Key lo = lt ? tk.key[t] : x;
+          x = lt ? x : tk.key[t];
+          tk.key[t] = lo;
+        }
+      }
+    }
+    if (!__any_sync(FULL, p < e || o < nrow)) break;
+  }
+  if (!live) return;
+  int nf = 0;
+#pragma unroll
+  for (int t = 0; t < KMAX; ++t) {
+    if (t < k) {
+      const bool ok = key_d2(tk.key[t]) < INFINITY;
+      idx_out[(size_t)i * qs + t * ts] = ok ? key_id(tk.key[t]) : -1;
+      d2_out[(size_t)i * qs + t * ts] = ok ? key_d2(tk.key[t]) : INFINITY;
+      nf += ok ? 1 : 0;
+    }
+  }
+  if (nfound_out) nfound_out[i] = nf;
+  const bool done = !q.finite || (scan && ((q.rcover <= 1) || resolved_at(tk.kth(), 1, gp.cell, q.minoff)));
+  if (!done) unres_list[atomicAdd(unres_count, 1u)] = i;
+}
+
 // merges the 32 per-lane sorted lists: round t yields the t-th smallest key of the warp
 // (two warp-wide integer min reductions per round).  Writes the first k; returns the number
 // found and the k-th distance.
@@ -410,10 +520,19 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   const float cap2 = capped ? cap_dist * cap_dist : INFINITY;   // rows farther than the cap cannot matter
   g.unres_list.reserve(nq, s); g.unres_count.reserve(2, s);
   LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 2 * sizeof(unsigned), s));
+  // few queries: four lanes per query (fills the SMs, short per-lane chains); many queries: one
+  // thread per query with warp-synchronous insertions (fewest instructions)
+  static const long quad_max = [] { const char* e = std::getenv("LSB_KNN_QUAD_MAX"); return e ? std::atol(e) : 148L * 64; }();   // tuning hook
+  const bool quad = (long)nq <= quad_max;
+  const unsigned G1 = div_up(nq, 128);
 #define LSB_KNN_CASE(KM)                                                                                                                   \
   do {                                                                                                                                     \
-    k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, qs, ts, idx, d2, nf, g.unres_list.p,    \
-                                             g.unres_count.p);                                                                             \
+    if (quad)                                                                                                                              \
+      k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, qs, ts, idx, d2, nf, g.unres_list.p,  \
+                                               g.unres_count.p);                                                                           \
+    else                                                                                                                                   \
+      k_knn_stream<KM, FROM_POINTS><<<G1, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, qs, ts, idx, d2, nf,          \
+                                                       g.unres_list.p, g.unres_count.p);                                                   \
     LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
     k_knn_warp<KM, FROM_POINTS><<<148 * 4, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, cap2, qs, ts, idx, d2, nf, \
                                                         g.unres_list.p, g.unres_count.p);                                                  \
