@@ -23,6 +23,19 @@ lsb_slam::lsb_slam(int dev) : device(dev)
     LSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
     unsigned long long keep = ~0ull;
     LSB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    // pre-warm: one large block taken from the driver and handed back to the pool, so that the
+    // growth of the maps during a sequence is served by the pool (a driver allocation in the
+    // middle of a frame costs milliseconds).  LSB_POOL_PREWARM_MB overrides the size (0 = none).
+    static bool warmed = false;
+    if (!warmed) {
+      warmed = true;
+      size_t mb = 2048;
+      if (const char* e = std::getenv("LSB_POOL_PREWARM_MB")) mb = (size_t)std::atol(e);
+      void* blk = nullptr;
+      if (mb && cudaMallocAsync(&blk, mb << 20, stream) == cudaSuccess) cudaFreeAsync(blk, stream);
+      else cudaGetLastError();
+      LSB_CUDA(cudaStreamSynchronize(stream));
+    }
   }
   for (auto& e : ev) LSB_CUDA(cudaEventCreate(&e));
   for (auto& t : tstream) LSB_CUDA(cudaStreamCreateWithFlags(&t, cudaStreamNonBlocking));
