@@ -256,6 +256,14 @@ def main():
         except Exception:
             pass
         peak = peaks.get("hbm_gbs", 6650.0)
+        traffic = None
+        try:
+            import glob
+            tf = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_knn_traffic.json")))
+            if tf and a.sensor == "os128":
+                traffic = json.load(open(tf[-1]))["bytes_per_search"]     # from the committed ncu --set full capture
+        except Exception:
+            pass
         per_launch_bytes = knn_bytes / max(knn_launches, 1)
         per_launch_s = knn_ms * 1e-3 / max(knn_launches, 1)
         achieved = per_launch_bytes / per_launch_s / 1e9 if per_launch_s > 0 else 0.0
@@ -274,7 +282,7 @@ def main():
                 "gpu_launches": int(n_launches),
                 "clocks": sampler.result(),
                 "roofline": {"kernel": "k_knn (exact grid kNN)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak if peak else None, "traffic": None,
+                             "frac": achieved / peak if peak else None, "traffic": traffic,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                              "bytes_per_launch": per_launch_bytes, "us_per_launch": per_launch_s * 1e6, "launches": knn_launches},
                 "phase_ms_per_frame": {"extract": phase[0] / K, "ego_motion": phase[1] / K, "localization": phase[2] / K,
