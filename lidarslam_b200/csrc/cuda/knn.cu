@@ -1,15 +1,15 @@
-// Exact kNN on a uniform grid — see knn.cuh.  Hand-written search kernel; CUB is
-// used only for the radix sort that orders the target points by cell.
+// Exact kNN on a uniform grid — see knn.cuh and DESIGN.md §3 K8.  Hand-written search kernels;
+// CUB is used only for the radix sort that orders the target points by cell.
 //
-// Search (one thread per query): the cube of cells of Chebyshev radius r around
-// the query's cell is scanned shell by shell.  Cells of one (z, y) row are
-// contiguous in the cell-major point array, so a row of a shell is ONE index range
-// (two cell_start loads), which makes empty space cheap.  After the cube of radius
-// r is complete every unvisited point is farther than
+// Cells of one (z, y) row are contiguous in the cell-major point array, so a row of cells is ONE
+// index range (two cell_start loads), which makes empty space cheap.  After the cube of Chebyshev
+// radius r around the query's cell is complete every unvisited point is farther than
 //   bound(r) = r * cell + min over axes of the query's distance to its cell faces,
-// so the search stops as soon as the k-th best distance is strictly below
-// bound(r) (minus a rounding margin) or the cube covers the whole grid: exact,
-// with ties at equal d2 resolved by the smaller cloud index.
+// so a query is settled as soon as its k-th best distance is strictly below bound(r) (minus a
+// rounding margin) or the cube covers the whole grid: exact, with ties at equal d2 resolved by
+// the smaller cloud index.  Cube pass (r = 1): k_knn (four lanes per query) or k_knn_stream (one
+// thread per query, warp-synchronous insertions); unsettled queries: k_knn_warp (box of the
+// sphere of the tentative k-th distance).
 #include "knn.cuh"
 #include <cub/cub.cuh>
 #include <cfloat>
