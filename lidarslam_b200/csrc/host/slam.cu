@@ -3,6 +3,7 @@
 // every cloud operation is a kernel on the handle's stream.
 #include "slam.cuh"
 #include <cstring>
+#include <chrono>
 #include <cstdlib>
 #include <cstdio>
 #include <cmath>
@@ -11,6 +12,10 @@
 #include <algorithm>
 
 using namespace lsb;
+
+// Enqueue order of the per-type work: the type with the most keypoints first, so that the longest
+// chain of a fork/join section starts first (the results do not depend on the order).
+static const int kTypeOrder[3] = {LSB_BLOB, LSB_PLANE, LSB_EDGE};
 
 static inline double StampToSec(uint64_t us) { return us * 1e-6; }   // Utils::PclStampToSec
 
@@ -78,8 +83,9 @@ lsb_slam::~lsb_slam()
 void lsb_slam::Trace::mark(const char* name, cudaStream_t s)
 {
   if (!on) return;
-  if (used == evs.size()) { cudaEvent_t e; LSB_CUDA(cudaEventCreate(&e)); evs.push_back(e); names.push_back(name); }
+  if (used == evs.size()) { cudaEvent_t e; LSB_CUDA(cudaEventCreate(&e)); evs.push_back(e); names.push_back(name); host_us.push_back(0.); }
   names[used] = name;
+  host_us[used] = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
   LSB_CUDA(cudaEventRecord(evs[used++], s));
 }
 
@@ -90,7 +96,7 @@ void lsb_slam::Trace::dump()
   for (size_t i = 1; i < used; ++i) {
     float ms = 0.f;
     cudaEventElapsedTime(&ms, evs[i - 1], evs[i]);
-    std::fprintf(stderr, " %s=%.0fus", names[i], ms * 1e3f);
+    std::fprintf(stderr, " %s=%.0f(h%.0f)", names[i], ms * 1e3f, host_us[i] - host_us[i - 1]);
   }
   std::fprintf(stderr, "\n");
   used = 0;
@@ -412,7 +418,7 @@ void lsb_slam::Localization()
   // their read-backs (bbox of the keypoints, size of the submap) overlap
   bool pending[3] = {false, false, false};
   Fork();
-  for (int k = 0; k < 3; ++k) {
+  for (int k : kTypeOrder) {
     RollingGridGpu& map = LocalMaps[k];
     if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) continue;
     cudaStream_t ts = TypeStream(k);
@@ -421,7 +427,7 @@ void lsb_slam::Localization()
     if (CurrentKeypoints[k].n) dev_transformed_bbox_async(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, map.d_bbox, map.h_bbox, ts, lc);
     pending[k] = true;
   }
-  for (int k = 0; k < 3; ++k) {
+  for (int k : kTypeOrder) {
     if (!pending[k]) continue;
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     if (CurrentKeypoints[k].n) {
@@ -430,7 +436,7 @@ void lsb_slam::Localization()
     }
     LocalMaps[k].SubMapSelect(mn, mx, (int)(CurrentKeypoints[k].n / 2), TypeStream(k), lc);
   }
-  for (int k = 0; k < 3; ++k)
+  for (int k : kTypeOrder)
     if (pending[k]) LocalMaps[k].SubMapFinish(TypeStream(k), lc);
   if (trace.on) { Join(); trace.mark("submap+grid", stream); }
 
@@ -443,7 +449,7 @@ void lsb_slam::Localization()
     mp.saturation_distance = (1 - iterRatio) * P.localization_init_saturation_distance + iterRatio * P.localization_final_saturation_distance;
     mw.begin_iteration(nk, stream);
     Fork();
-    for (int k = 0; k < 3; ++k) {
+    for (int k : kTypeOrder) {
       mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], LocalMaps[k].grid, Tworld, mp, TypeStream(k), lc);
       Stats.knn_queries += (uint32_t)nk[k];
     }
@@ -494,17 +500,19 @@ void lsb_slam::UpdateMapsUsingTworld()
   KfLastPose = Tworld;
   // RollingGrid::Add of the three types, each on its stream, in host phases (read-backs overlapped)
   Fork();
-  for (int k = 0; k < 3; ++k) {
+  for (int k : kTypeOrder) {
     if (!P.use_keypoints[k]) continue;
     const DCloud& w = WorldKeypoints(k, TypeStream(k));
     LocalMaps[k].AddBegin(w.buf.p, w.n, true, TypeStream(k), lc);
   }
-  for (int k = 0; k < 3; ++k) {
+  if (trace.on) { Join(); trace.mark("map.bbox", stream); Fork(); }
+  for (int k : kTypeOrder) {
     if (!P.use_keypoints[k]) continue;
     const DCloud& w = CurrentWorldKeypoints[k];
     LocalMaps[k].AddSort(w.buf.p, w.n, false, CurrentTime, true, TypeStream(k), lc);
   }
-  for (int k = 0; k < 3; ++k)
+  if (trace.on) { Join(); trace.mark("map.sort", stream); Fork(); }
+  for (int k : kTypeOrder)
     if (P.use_keypoints[k]) LocalMaps[k].AddMerge(CurrentWorldKeypoints[k].n, TypeStream(k), lc);
   Join();
 }

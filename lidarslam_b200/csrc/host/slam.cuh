@@ -87,6 +87,7 @@ struct lsb_slam {
     bool on = false;
     std::vector<cudaEvent_t> evs;
     std::vector<const char*> names;
+    std::vector<double> host_us;      // host clock at the mark (enqueue time line)
     size_t used = 0;
     void mark(const char* name, cudaStream_t s);
     void dump();
