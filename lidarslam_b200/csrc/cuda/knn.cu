@@ -425,22 +425,51 @@ __device__ __forceinline__ void axis_cells(float lo, float hi, float o, float ce
   c1 = (int)fminf(fmaxf(floorf((hi - o) / cell), 0.f), (float)(n - 1));
 }
 
-// Phase 2: one warp per query that the 3x3x3 cube did not settle.  If phase 1 found k points,
-// its k-th distance T bounds the true one: the warp scans the box of the sphere of radius
-// sqrt(T) (capped mode: at most the cap) and is done - exact.  Otherwise (fewer than k points in
-// the cube) capped mode scans the box of the cap sphere and reports "k-th neighbour beyond the
-// cap" if that is what it finds; exact mode scans the cube of radius rcap and, if even that does
-// not settle the query, falls back to a brute-force pass over all m points (isolated queries).
-// The lanes share the rows of the box (each row one contiguous index range), keep per-lane
-// top-K lists and merge them.
+// The lanes of a warp share the rows of a box of cells (each row one contiguous index range) and
+// keep per-lane top-K lists.  Rows that cannot hold anything nearer than the lane's k-th candidate,
+// or than T, are skipped.
+template <int KMAX>
+__device__ __forceinline__ void warp_scan_box(TopK<KMAX>& tk, const QueryCell& q, const KnnGridParams& gp, const float4* __restrict__ sorted,
+                                              const uint32_t* __restrict__ cell_start, int x0, int x1, int y0, int y1, int z0, int z1, float T,
+                                              int lane)
+{
+  tk.init();
+  const int nyr = y1 - y0 + 1, nrows = (z1 - z0 + 1) * nyr;
+  if (!q.finite || x0 > x1 || nyr <= 0) return;
+  for (int t = lane; t < nrows; t += 32) {
+    const int z = z0 + t / nyr, y = y0 + t % nyr;
+    const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
+    const float lb = gy * gy + gz * gz;
+    if (!(lb < tk.kth()) || lb > T) continue;
+    const int base = (z * gp.ny + y) * gp.nx;
+    scan_range(tk, sorted, __ldg(cell_start + base + x0), __ldg(cell_start + base + x1 + 1), q.qx, q.qy, q.qz);
+  }
+}
+
+// Phase 2: one warp per query that the 3x3x3 cube did not settle.
+// (a) With a threshold T such that every point of the answer has d2 <= T (the k-th distance of
+//     phase 1's tentative list; capped mode: at most the cap) no top-k list is needed while
+//     scanning: the lanes share the rows of the box of the sphere of radius sqrt(T) (a row = one
+//     contiguous index range), every point with d2 <= T is appended to a per-warp buffer in
+//     shared memory (a few dozen keys: about k of them when T is the tentative k-th distance), and
+//     the k smallest are then placed by rank (each lane counts the keys smaller than its own):
+//     sorted output without any sorted insertion.  Exact by construction; in capped mode fewer
+//     than k keys within the cap means "k-th neighbour beyond the cap", all the caller needs.
+//     A buffer overflow (dense box under a loose cap) falls back to per-lane lists.
+// (b) Exact mode without a threshold (fewer than k points in the cube): cube of radius rcap with
+//     per-lane lists; a query that even this does not settle goes to the brute-force kernel.
+constexpr int WARP_BUF = 128;
+
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
 k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
            const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped, float cap2,
            size_t qs, size_t ts, int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
-           const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
+           const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count, int32_t* __restrict__ bf_list, unsigned bf_cap)
 {
-  const int lane = threadIdx.x & 31;
+  __shared__ Key s_keys[4][WARP_BUF];
+  __shared__ int s_cnt[4];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const unsigned count = unres_count[0];
   while (true) {
     unsigned slot = 0;
@@ -449,59 +478,162 @@ k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Is
     if (slot >= count) break;
     const int i = unres_list[slot];
     const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
-    TopK<KMAX> tk;
-    tk.init();
-    // threshold: every point that can belong to the answer has d2 <= T
-    const float tentative = d2_out[(size_t)i * qs + (size_t)(k - 1) * ts];
+    int32_t* idx_row = idx_out + (size_t)i * qs;
+    float* d2_row = d2_out + (size_t)i * qs;
+    const float tentative = d2_row[(size_t)(k - 1) * ts];
     float T = tentative;
     if (capped) T = fminf(T, cap2);
-    const bool sphere = T < INFINITY;
-    int x0, x1, y0, y1, z0, z1;
-    if (sphere) {
-      const float r = sqrtf(T);
-      const float rr = r + (1.0e-3f + 1.0e-4f * (r + gp.cell));
-      axis_cells(q.qx - rr, q.qx + rr, gp.ox, gp.cell, gp.nx, x0, x1);
-      axis_cells(q.qy - rr, q.qy + rr, gp.oy, gp.cell, gp.ny, y0, y1);
-      axis_cells(q.qz - rr, q.qz + rr, gp.oz, gp.cell, gp.nz, z0, z1);
+    int x0, x1, y0, y1, z0, z1, nf = 0;
+    TopK<KMAX> tk;
+    float kd;
+    if (T < INFINITY) {
+      // without a tentative k-th distance T is the cap, a loose bound: try the sphere of two cells first
+      const float T2 = 4.f * gp.cell * gp.cell;
+      const bool loose = !(tentative < INFINITY) && T2 < T;
+      bool placed = false;
+      for (int stage = loose ? 0 : 1; stage < 2 && !placed; ++stage) {
+        const float Ts = (stage == 0) ? T2 : T;
+        const float r = sqrtf(Ts);
+        const float rr = r + (1.0e-3f + 1.0e-4f * (r + gp.cell));
+        axis_cells(q.qx - rr, q.qx + rr, gp.ox, gp.cell, gp.nx, x0, x1);
+        axis_cells(q.qy - rr, q.qy + rr, gp.oy, gp.cell, gp.ny, y0, y1);
+        axis_cells(q.qz - rr, q.qz + rr, gp.oz, gp.cell, gp.nz, z0, z1);
+        const int nyr = y1 - y0 + 1, nrows = (z1 - z0 + 1) * nyr;
+        if (lane == 0) s_cnt[w] = 0;
+        __syncwarp();
+        for (int t = lane; t < nrows; t += 32) {
+          const int z = z0 + t / nyr, y = y0 + t % nyr;
+          const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
+          if (gy * gy + gz * gz > Ts) continue;       // nothing of this row can be within Ts
+          const int base = (z * gp.ny + y) * gp.nx;
+          const uint32_t b = __ldg(cell_start + base + x0), e = __ldg(cell_start + base + x1 + 1);
+          for (uint32_t p = b; p < e; p += 2) {
+            const bool two = p + 1 < e;
+            const float4 s0 = __ldg(sorted + p), s1 = __ldg(sorted + (two ? p + 1 : p));
+            const float ax = q.qx - s0.x, ay = q.qy - s0.y, az = q.qz - s0.z;
+            const float bx = q.qx - s1.x, by = q.qy - s1.y, bz = q.qz - s1.z;
+            const float da = (ax * ax + ay * ay) + az * az, db = (bx * bx + by * by) + bz * bz;
+            if (da <= Ts) { const int o = atomicAdd(&s_cnt[w], 1); if (o < WARP_BUF) s_keys[w][o] = make_key(da, __float_as_int(s0.w)); }
+            if (two && db <= Ts) { const int o = atomicAdd(&s_cnt[w], 1); if (o < WARP_BUF) s_keys[w][o] = make_key(db, __float_as_int(s1.w)); }
+          }
+        }
+        __syncwarp();
+        const int C = s_cnt[w];
+        if (stage == 0 && C < k) continue;            // fewer than k points within two cells: the cap decides
+        if (C > WARP_BUF) {
+          if (stage == 0) continue;
+          break;                                      // dense box under a loose cap: per-lane lists below
+        }
+        for (int j = lane; j < C; j += 32) {
+          const Key mine = s_keys[w][j];
+          int rank = 0;
+          for (int u = 0; u < C; ++u) rank += (s_keys[w][u] < mine) ? 1 : 0;
+          if (rank < k) { idx_row[(size_t)rank * ts] = key_id(mine); d2_row[(size_t)rank * ts] = key_d2(mine); }
+        }
+        for (int r2 = C + lane; r2 < k; r2 += 32) { idx_row[(size_t)r2 * ts] = -1; d2_row[(size_t)r2 * ts] = INFINITY; }
+        nf = min(C, k);
+        // fewer than k points within the cap: the k-th neighbour is farther than the cap
+        if (C < k && m >= k) nf = k;
+        placed = true;
+        __syncwarp();
+      }
+      if (!placed) {
+        warp_scan_box<KMAX>(tk, q, gp, sorted, cell_start, x0, x1, y0, y1, z0, z1, T, lane);
+        nf = warp_merge_write<KMAX>(tk, k, lane, idx_row, d2_row, ts, kd);
+        if (!(T == tentative || kd <= cap2) && m >= k) nf = k;
+      }
     } else {
       const int R = max(rcap, 1);
       z0 = max(0, q.cz - R); z1 = min(gp.nz - 1, q.cz + R);
       y0 = max(0, q.cy - R); y1 = min(gp.ny - 1, q.cy + R);
       x0 = max(0, q.cx - R); x1 = min(gp.nx - 1, q.cx + R);
-    }
-    const int nyr = y1 - y0 + 1, nrows = (z1 - z0 + 1) * nyr;
-    if (q.finite && x0 <= x1 && nyr > 0) {
-      for (int t = lane; t < nrows; t += 32) {
-        const int z = z0 + t / nyr, y = y0 + t % nyr;
-        // rows that cannot hold anything nearer than this lane's k-th candidate (or than T) are skipped
-        const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
-        const float lb = gy * gy + gz * gz;
-        if (!(lb < tk.kth()) || lb > T) continue;
-        const int base = (z * gp.ny + y) * gp.nx;
-        scan_range(tk, sorted, __ldg(cell_start + base + x0), __ldg(cell_start + base + x1 + 1), q.qx, q.qy, q.qz);
-      }
-    }
-    float kd;
-    int nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * qs, d2_out + (size_t)i * qs, ts, kd);
-    bool settled;
-    if (sphere) settled = (T == tentative) || (kd <= cap2);          // all points with d2 <= T were visited
-    else settled = (q.rcover <= max(rcap, 1)) || resolved_at(kd, max(rcap, 1), gp.cell, q.minoff);
-    if (!settled) {
-      if (capped) {
-        // every point within the cap distance has been visited and the k-th neighbour is
-        // farther than the cap: the caller only needs "k found, too far"
-        if (m >= k) nf = k;
-      } else {
-        tk.init();
-        for (int p = lane; p < m; p += 32) {
-          const float4 s = __ldg(sorted + p);
-          const float dx = q.qx - s.x, dy = q.qy - s.y, dz = q.qz - s.z;
-          tk.offer(make_key((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w)));
+      warp_scan_box<KMAX>(tk, q, gp, sorted, cell_start, x0, x1, y0, y1, z0, z1, INFINITY, lane);
+      nf = warp_merge_write<KMAX>(tk, k, lane, idx_row, d2_row, ts, kd);
+      const bool settled = (q.rcover <= R) || resolved_at(kd, R, gp.cell, q.minoff);
+      if (!settled) {            // isolated query: brute force, shared by many warps (k_knn_brute)
+        unsigned o = 0;
+        if (lane == 0) o = atomicAdd(unres_count + 2, 1u);
+        o = __shfl_sync(0xffffffffu, o, 0);
+        if (o < bf_cap) {
+          if (lane == 0) bf_list[o] = i;
+          continue;
         }
-        nf = warp_merge_write<KMAX>(tk, k, lane, idx_out + (size_t)i * qs, d2_out + (size_t)i * qs, ts, kd);
+        tk.init();               // list full: this warp scans the whole cloud itself
+        for (int p = lane; p < m; p += 32) {
+          const float4 sp = __ldg(sorted + p);
+          const float dx = q.qx - sp.x, dy = q.qy - sp.y, dz = q.qz - sp.z;
+          tk.offer(make_key((dx * dx + dy * dy) + dz * dz, __float_as_int(sp.w)));
+        }
+        nf = warp_merge_write<KMAX>(tk, k, lane, idx_row, d2_row, ts, kd);
       }
     }
     if (lane == 0 && nfound_out) nfound_out[i] = nf;
+  }
+}
+
+// Brute force for the isolated queries of an exact search: a work item is (query, segment of the
+// cloud); the warp keeps per-lane lists over its segment, merges them, and writes a sorted partial
+// list; the warp that completes a query's last segment merges the BF_SEGS partial lists.
+constexpr int BF_SEGS = 16;
+
+template <int KMAX, bool FROM_POINTS>
+__global__ void __launch_bounds__(128)
+k_knn_brute(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
+            const float4* __restrict__ sorted, int m, int k, size_t qs, size_t ts, int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
+            int32_t* __restrict__ nfound_out, const int32_t* __restrict__ bf_list, unsigned* __restrict__ unres_count,
+            Key* __restrict__ partial, unsigned* __restrict__ tickets, unsigned bf_cap)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned nbf = min(unres_count[2], bf_cap);
+  const unsigned nitems = nbf * BF_SEGS;
+  const int seg_len = (m + BF_SEGS - 1) / BF_SEGS;
+  while (true) {
+    unsigned item = 0;
+    if (lane == 0) item = atomicAdd(unres_count + 3, 1u);
+    item = __shfl_sync(FULL, item, 0);
+    if (item >= nitems) break;
+    const unsigned qslot = item / BF_SEGS, seg = item % BF_SEGS;
+    const int i = bf_list[qslot];
+    const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
+    TopK<KMAX> tk;
+    tk.init();
+    const int p0 = (int)seg * seg_len, p1 = min(m, p0 + seg_len);
+    for (int p = p0 + lane; p < p1; p += 32) {
+      const float4 s = __ldg(sorted + p);
+      const float dx = q.qx - s.x, dy = q.qy - s.y, dz = q.qz - s.z;
+      tk.offer(make_key((dx * dx + dy * dy) + dz * dz, __float_as_int(s.w)));
+    }
+    Key* out = partial + ((size_t)qslot * BF_SEGS + seg) * k;
+    for (int t = 0; t < k; ++t) {          // warp merge of the per-lane lists -> sorted partial list
+      const unsigned hi = (unsigned)(tk.key[0] >> 32), lo = (unsigned)tk.key[0];
+      const unsigned mhi = __reduce_min_sync(FULL, hi);
+      const unsigned mlo = __reduce_min_sync(FULL, (hi == mhi) ? lo : 0xffffffffu);
+      const Key mk = ((Key)mhi << 32) | mlo;
+      if (tk.key[0] == mk && mk != KEY_NONE) tk.pop();
+      if (lane == 0) out[t] = mk;
+    }
+    __threadfence();
+    unsigned done = 0;
+    if (lane == 0) done = atomicAdd(tickets + qslot, 1u);
+    done = __shfl_sync(FULL, done, 0);
+    if (done != BF_SEGS - 1) continue;
+    __threadfence();
+    // last segment of this query: merge the BF_SEGS sorted lists (lane s < BF_SEGS walks list s)
+    const Key* lists = partial + (size_t)qslot * BF_SEGS * k;
+    int pos = 0, nf = 0;
+    for (int t = 0; t < k; ++t) {
+      const Key head = (lane < BF_SEGS && pos < k) ? __ldcg(lists + (size_t)lane * k + pos) : KEY_NONE;
+      const unsigned hi = (unsigned)(head >> 32), lo = (unsigned)head;
+      const unsigned mhi = __reduce_min_sync(FULL, hi);
+      const unsigned mlo = __reduce_min_sync(FULL, (hi == mhi) ? lo : 0xffffffffu);
+      const Key mk = ((Key)mhi << 32) | mlo;
+      if (head == mk && mk != KEY_NONE) ++pos;
+      const bool ok = key_d2(mk) < INFINITY;
+      if (lane == 0) { idx_out[(size_t)i * qs + t * ts] = ok ? key_id(mk) : -1; d2_out[(size_t)i * qs + t * ts] = ok ? key_d2(mk) : INFINITY; }
+      nf += ok ? 1 : 0;
+    }
+    if (lane == 0) { if (nfound_out) nfound_out[i] = nf; tickets[qslot] = 0u; }
   }
 }
 
@@ -518,8 +650,15 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   const float reach = capped ? cap_dist : 5.0f;
   const int rcap = std::max(2, (int)std::ceil(reach / g.gp.cell) + 1);
   const float cap2 = capped ? cap_dist * cap_dist : INFINITY;   // rows farther than the cap cannot matter
-  g.unres_list.reserve(nq, s); g.unres_count.reserve(2, s);
-  LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 2 * sizeof(unsigned), s));
+  // unres_count: [0] unsettled queries, [1] cursor, [2] brute-force queries, [3] cursor
+  g.unres_list.reserve(nq, s); g.unres_count.reserve(4, s);
+  LSB_CUDA(cudaMemsetAsync(g.unres_count.p, 0, 4 * sizeof(unsigned), s));
+  const unsigned bf_cap = (unsigned)std::min<size_t>(nq, 16384);   // more isolated queries than that scan the cloud on their own
+  if (!capped) {
+    g.bf_list.reserve(bf_cap, s);
+    g.bf_partial.reserve((size_t)bf_cap * BF_SEGS * (size_t)k, s);
+    if (g.bf_tickets.cap < bf_cap) { g.bf_tickets.reserve(bf_cap, s); LSB_CUDA(cudaMemsetAsync(g.bf_tickets.p, 0, g.bf_tickets.cap * sizeof(unsigned), s)); }
+  }
   // few queries: four lanes per query (fills the SMs, short per-lane chains); many queries: one
   // thread per query with warp-synchronous insertions (fewest instructions)
   static const long quad_max = [] { const char* e = std::getenv("LSB_KNN_QUAD_MAX"); return e ? std::atol(e) : 148L * 64; }();   // tuning hook
@@ -534,9 +673,14 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
       k_knn_stream<KM, FROM_POINTS><<<G1, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, qs, ts, idx, d2, nf,          \
                                                        g.unres_list.p, g.unres_count.p);                                                   \
     LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
-    k_knn_warp<KM, FROM_POINTS><<<148 * 4, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, cap2, qs, ts, idx, d2, nf, \
-                                                        g.unres_list.p, g.unres_count.p);                                                  \
+    k_knn_warp<KM, FROM_POINTS><<<148 * 8, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, g.cell_start.p, M, k, rcap, capped, cap2, qs, ts, idx, d2, nf, \
+                                                        g.unres_list.p, g.unres_count.p, g.bf_list.p, bf_cap);                             \
     LSB_LAUNCH_CHECK(); lc.add();                                                                                                          \
+    if (!capped) {                                                                                                                         \
+      k_knn_brute<KM, FROM_POINTS><<<148 * 8, 128, 0, s>>>(q, kp, prior, g.gp, g.sorted.p, M, k, qs, ts, idx, d2, nf, g.bf_list.p,          \
+                                                           g.unres_count.p, reinterpret_cast<Key*>(g.bf_partial.p), g.bf_tickets.p, bf_cap); \
+      LSB_LAUNCH_CHECK(); lc.add();                                                                                                        \
+    }                                                                                                                                      \
   } while (0)
   if (k <= 1) LSB_KNN_CASE(1);
   else if (k <= 5) LSB_KNN_CASE(5);

@@ -27,7 +27,10 @@ struct KnnGrid {
   DevBuf<uint32_t> cell_start;    // [ncells + 1] prefix offsets into sorted
   DevBuf<unsigned char> cub_tmp;
   mutable DevBuf<int32_t> unres_list;    // queries handed to the brute-force kernel
-  mutable DevBuf<unsigned> unres_count;  // [2]: count, cursor
+  mutable DevBuf<unsigned> unres_count;  // [4]: unsettled count, cursor, brute-force count, cursor
+  mutable DevBuf<int32_t> bf_list;       // exact search: isolated queries for the brute-force kernel
+  mutable DevBuf<unsigned long long> bf_partial;   // their per-segment partial lists
+  mutable DevBuf<unsigned> bf_tickets;   // per-query segment counter (self-resetting)
   DevBuf<float> d_bbox;           // [6]
   PinnedBuf<float> h_bbox;
 
