@@ -442,6 +442,9 @@ k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchu
   __shared__ double s_E[LSB_LM_NSUM];
   __shared__ int s_last;
   static_assert(NW <= 64 && NP <= 64, "prologue copies with threads 0..63 / 64..127");
+  // programmatic dependent launch: this grid may have been scheduled while the previous
+  // evaluation was still in its (single-CTA) control step; wait for it before reading the state
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   if (threadIdx.x < NW) s_state_raw[threadIdx.x] = reinterpret_cast<const unsigned long long*>(state)[threadIdx.x];
   else if (threadIdx.x >= 64 && threadIdx.x < 64 + NP) s_pt_raw[threadIdx.x - 64] = reinterpret_cast<const unsigned long long*>(point)[threadIdx.x - 64];
   __syncthreads();
@@ -468,6 +471,8 @@ k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchu
     if (lane == 0) { part[(size_t)q * pstride + blockIdx.x] = c; __threadfence(); }
   }
   __syncthreads();
+  // the next evaluation may be scheduled from here on (it waits for this grid to complete)
+  asm volatile("griddepcontrol.launch_dependents;");
   if (threadIdx.x == 0) {
     const unsigned t = atomicAdd(counter, 1u);
     s_last = (t == (unsigned)(nchunks - 1));
@@ -589,9 +594,22 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
                              hist.p, min_matches);
   LSB_LAUNCH_CHECK(); lc.add();
   t_lm.begin(s);
+  // every evaluation is launched with programmatic stream serialization: its CTAs are scheduled
+  // while the previous evaluation finishes its control step (launch latency hidden)
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)nchunks);
+  cfg.blockDim = dim3(LM_THREADS);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
   for (int e = 0; e <= max_iter; ++e) {
-    k_lm_eval<<<nchunks, LM_THREADS, 0, s>>>(records.p, rec_stride, n, nchunks, pstride, saturation, lm_state.p, lm_point.p, part_a.p, lm_counter.p, e == 0 ? 1 : 0);
-    LSB_LAUNCH_CHECK(); lc.add();
+    LSB_CUDA(cudaLaunchKernelEx(&cfg, k_lm_eval, (const double*)records.p, rec_stride, n, nchunks, pstride, saturation, lm_state.p, lm_point.p,
+                                part_a.p, lm_counter.p, e == 0 ? 1 : 0));
+    lc.add();
   }
   t_lm.end(s);
   t_lm.launches += (unsigned)max_iter;
