@@ -266,6 +266,11 @@ class CApi:
         self._check(self._f("get_frame_stats")(self.h, C.byref(s)))
         return s
 
+    def GetOverlapEstimation(self):
+        f = self._f("get_overlap")
+        f.restype = C.c_float
+        return float(f(self.h))
+
     def GetTotalMatchedKeypoints(self):
         f = self._f("get_total_matched_keypoints")
         f.restype = C.c_uint

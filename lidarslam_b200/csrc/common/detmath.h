@@ -14,6 +14,7 @@
 // (almost always) correctly rounded like glibc's sinf/cosf/atan2f.
 #pragma once
 #include <math.h>
+#include <string.h>
 
 #if defined(__CUDACC__)
 #define LSB_HD __host__ __device__ __forceinline__
@@ -151,6 +152,46 @@ LSB_HD double acos(double x)
 }
 
 // float variants: evaluate in double, round once
+// exp(x): Cody-Waite reduction x = n ln2 + r, |r| <= ln2/2, Taylor polynomial of degree 13 in
+// Horner form (remainder < 1e-17 relative), scaling by 2^n through the exponent bits.  Used by the
+// overlap estimator (std::exp in ConfidenceEstimators.cxx:55); inputs there are <= 0.
+LSB_HD double exp(double x)
+{
+  if (!(x == x)) return x;
+  if (x > 709.0) return INFINITY;
+  if (x < -745.0) return 0.0;
+  const double ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10, inv_ln2 = 1.44269504088896338700e+00;
+  const double fn = floor(x * inv_ln2 + 0.5);
+  const double r = (x - fn * ln2_hi) - fn * ln2_lo;
+  double p = 1.0 / 6227020800.0;
+  p = p * r + 1.0 / 479001600.0;
+  p = p * r + 1.0 / 39916800.0;
+  p = p * r + 1.0 / 3628800.0;
+  p = p * r + 1.0 / 362880.0;
+  p = p * r + 1.0 / 40320.0;
+  p = p * r + 1.0 / 5040.0;
+  p = p * r + 1.0 / 720.0;
+  p = p * r + 1.0 / 120.0;
+  p = p * r + 1.0 / 24.0;
+  p = p * r + 1.0 / 6.0;
+  p = p * r + 0.5;
+  p = p * r + 1.0;
+  p = p * r + 1.0;
+  // 2^n in two exact factors so that results in the subnormal range round once
+  int n = (int)fn;
+  double scale = 1.0;
+  if (n < -1000) { scale = 1.4916681462400413e-154; n += 512; }   // 2^-512
+#ifdef __CUDA_ARCH__
+  const double two_n = __longlong_as_double((long long)(n + 1023) << 52);
+#else
+  const long long bits = (long long)(n + 1023) << 52;
+  double two_n;
+  memcpy(&two_n, &bits, 8);
+#endif
+  return (p * two_n) * scale;
+}
+LSB_HD float expf(float x) { return (float)exp((double)x); }
+
 LSB_HD float sinf(float x) { return (float)sin((double)x); }
 LSB_HD float cosf(float x) { return (float)cos((double)x); }
 LSB_HD float atan2f(float y, float x) { return (float)atan2((double)y, (double)x); }

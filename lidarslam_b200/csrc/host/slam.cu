@@ -2,6 +2,7 @@
 // LidarSlam::Slam (reference slam_lib/src/Slam.cxx, line ranges per function);
 // every cloud operation is a kernel on the handle's stream.
 #include "slam.cuh"
+#include "../common/lcp_core.h"
 #include <cstring>
 #include <chrono>
 #include <cstdlib>
@@ -215,6 +216,9 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   LSB_CUDA(cudaEventRecord(ev[2], stream));
   Localization();
   LSB_CUDA(cudaEventRecord(ev[3], stream));
+  // confidence estimators (:272-279)
+  if (P.overlap_sampling_ratio > 0.f) EstimateOverlap();
+  else OverlapEstimation = -1.f;                                                // SetOverlapSamplingRatio (:1365-1366)
   uint32_t n_submap[3];
   for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // the map update invalidates the submaps
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
@@ -222,6 +226,7 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   trace.mark("map_update", stream);
   LSB_CUDA(cudaEventRecord(ev[4], stream));
   LSB_CUDA(cudaEventSynchronize(ev[4]));
+  if (lcp_pending) { OverlapEstimation = h_lcp.p[0]; lcp_pending = false; }
   trace.dump();
   LogCurrentFrameState(CurrentTime);
   for (int k = 0; k < 3; ++k) {
@@ -580,6 +585,40 @@ void lsb_slam::RefineUndistortion()
   interp.set_transforms(newBegin * inverse(prevBegin), newEnd * inverse(prevEnd));
   for (int k = 0; k < 3; ++k) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, interp, 0.0, stream, lc);
   for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
+}
+
+//-----------------------------------------------------------------------------
+// Slam::EstimateOverlap (:1370-1388): LCP estimator of ConfidenceEstimators.cxx:27-65 on the device.
+// A sampled point's nearest sub-map point is searched in every map in use (k = 1, capped at the
+// distance beyond which the probability is exactly 0.f), on the maps' own streams.
+void lsb_slam::EstimateOverlap()
+{
+  const size_t total = RegisteredFrame(tmp_cloud);
+  const float ratio = std::min(std::max(P.overlap_sampling_ratio, 0.f), 1.f);
+  const int nb = (int)((float)total * ratio);
+  bool use[3];
+  int nuse = 0;
+  for (int k = 0; k < 3; ++k) { use[k] = P.use_keypoints[k] && LocalMaps[k].IsSubMapKdTreeValid(); nuse += use[k] ? 1 : 0; }
+  if (nb == 0 || nuse == 0) { OverlapEstimation = -1.f; return; }
+  lcp_q.reserve(3 * (size_t)nb, stream);
+  d_lcp.reserve(1, stream); h_lcp.reserve(1);
+  dev_lcp_gather(tmp_cloud.p, nb, ratio, lcp_q.p, stream, lc);
+  for (int k = 0; k < 3; ++k) if (use[k]) { lcp_d2[k].reserve((size_t)nb, stream); lcp_idx[k].reserve((size_t)nb, stream); }
+  Fork();
+  const float* d2[3] = {nullptr, nullptr, nullptr};
+  float thr[3] = {1.f, 1.f, 1.f};
+  for (int k : kTypeOrder) {
+    if (!use[k]) continue;
+    thr[k] = lcp_sq_threshold(LocalMaps[k].LeafSize);
+    const float cap = std::sqrt(lcp_sq_cutoff(thr[k])) * 1.0001f + 1e-3f;
+    LocalMaps[k].grid.search(lcp_q.p, (size_t)nb, 1, cap, lcp_idx[k].p, lcp_d2[k].p, nullptr, /*entry_major=*/true, TypeStream(k), lc);
+    d2[k] = lcp_d2[k].p;
+    Stats.knn_queries += (uint32_t)nb;
+  }
+  Join();
+  dev_lcp_reduce(d2, thr, nb, lcp_chunks, d_lcp.p, stream, lc);
+  LSB_CUDA(cudaMemcpyAsync(h_lcp.p, d_lcp.p, sizeof(float), cudaMemcpyDeviceToHost, stream));
+  lcp_pending = true;
 }
 
 //-----------------------------------------------------------------------------

@@ -116,6 +116,12 @@ struct lsb_slam {
   void InitUndistortion();                               // :1288-1319
   void RefineUndistortion();                             // :1322-1352
   void SaveDebug(StageDebug& d);
+  void EstimateOverlap();                                // :1370-1388 + ConfidenceEstimators.cxx:27-65
+  // overlap estimator scratch
+  lsb::DevBuf<float> lcp_q, lcp_d2[3], lcp_chunks, d_lcp;
+  lsb::DevBuf<int32_t> lcp_idx[3];
+  lsb::PinnedBuf<float> h_lcp;
+  bool lcp_pending = false;        // a value is on its way to h_lcp (read after the frame's final sync)
 };
 
 namespace lsb {
@@ -128,6 +134,9 @@ void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm,
 void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx);
 // bbox of (float)(T * p) in the pcl::transformPointCloud arithmetic (Slam.cxx:1026-1029): enqueue only
 // (decode h_bbox with bbox_decode after a sync), or both with one sync
+// LCP overlap estimator (cuda/lcp.cu)
+void dev_lcp_gather(const lsb_point* d_cloud, int nb, float ratio, float* d_q_xyz, cudaStream_t s, LaunchCounter& lc);
+void dev_lcp_reduce(const float* const d2[3], const float thr[3], int nb, DevBuf<float>& chunk_sum, float* d_out, cudaStream_t s, LaunchCounter& lc);
 void dev_transformed_bbox_async(const lsb_point* d_pts, size_t n, const Iso3d& T, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
                                 cudaStream_t s, LaunchCounter& lc);
 void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,

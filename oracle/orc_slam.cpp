@@ -1,6 +1,7 @@
 // CPU ORACLE (test infrastructure) — LidarSlam::Slam pipeline driver restatement.
 // Reference: slam_lib/src/Slam.cxx (line ranges per function).
 #include "orc_slam.h"
+#include "../lidarslam_b200/csrc/common/lcp_core.h"
 #include <chrono>
 #include <cstring>
 
@@ -74,7 +75,8 @@ int Slam::AddFrames(const std::vector<Frame>& frames)
   a = tick(); Stats.ms_ego = ms(b, a);
   Localization();
   b = tick(); Stats.ms_localization = ms(a, b);
-  if (P.overlap_sampling_ratio > 0) EstimateOverlap();
+  if (P.overlap_sampling_ratio > 0) EstimateOverlap();       // :272-276
+  else OverlapEstimation = -1.f;                             // SetOverlapSamplingRatio (:1365-1366)
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
   a = tick(); Stats.ms_map_update = ms(b, a);
   LogCurrentFrameState(CurrentTime);
@@ -399,10 +401,59 @@ Cloud Slam::GetRegisteredFrame()
   return agg;
 }
 
+// Slam::EstimateOverlap (:1370-1388) + Confidence::LCPEstimator (ConfidenceEstimators.cxx:27-65)
 void Slam::EstimateOverlap()
 {
-  // "next" row: LCP estimator not restated yet.
-  OverlapEstimation = -1.f;
+  const Cloud agg = GetRegisteredFrame();
+  std::vector<int> maps;
+  for (int k = 0; k < 3; ++k)
+    if (P.use_keypoints[k] && LocalMaps[k].IsSubMapKdTreeValid()) maps.push_back(k);
+  const float ratio = P.overlap_sampling_ratio;
+  const int nbPoints = (int)(agg.size() * ratio);
+  if (nbPoints == 0 || maps.empty()) { OverlapEstimation = -1.f; return; }
+  std::vector<float> proba((size_t)nbPoints, 0.f);
+#pragma omp parallel for num_threads(P.nb_threads > 0 ? P.nb_threads : 1) schedule(static)
+  for (int n = 0; n < nbPoints; ++n) {
+    const Point& pt = agg[lsb::lcp_sample_index(n, ratio)];
+    const float q[3] = {pt.x, pt.y, pt.z};
+    float best = 0.f;
+    for (int k : maps) {
+      int idx;
+      float d2;
+      if (LocalMaps[k].Tree.Knn(q, 1, &idx, &d2)) {
+        const float pr = lsb::lcp_probability(d2, lsb::lcp_sq_threshold(LocalMaps[k].LeafSize));
+        if (pr > best) best = pr;
+      }
+    }
+    proba[n] = best;
+  }
+  // canonical radix-32 tree sum (common/lcp_core.h)
+  auto fold32 = [](float* v) { for (int off = 16; off >= 1; off >>= 1) for (int l = 0; l < off; ++l) v[l] += v[l + off]; };
+  const size_t nChunks = ((size_t)nbPoints + LSB_LCP_CHUNK - 1) / LSB_LCP_CHUNK;
+  const size_t nBlocks = (nChunks + 31) / 32;
+  std::vector<float> chunk(nBlocks * 32, 0.f);
+  for (size_t c = 0; c < nChunks; ++c) {
+    float group[32];
+    for (int g = 0; g < 32; ++g) {
+      float lane[32];
+      for (int l = 0; l < 32; ++l) {
+        const size_t i = c * LSB_LCP_CHUNK + (size_t)g * 32 + l;
+        lane[l] = (i < (size_t)nbPoints) ? proba[i] : 0.f;
+      }
+      fold32(lane);
+      group[g] = lane[0];
+    }
+    fold32(group);
+    chunk[c] = group[0];
+  }
+  float lcp = 0.f;
+  for (size_t b = 0; b < nBlocks; ++b) {
+    float v[32];
+    for (int l = 0; l < 32; ++l) v[l] = chunk[b * 32 + l];
+    fold32(v);
+    lcp = (b == 0) ? v[0] : lcp + v[0];
+  }
+  OverlapEstimation = lcp / nbPoints;
 }
 
 }  // namespace orc

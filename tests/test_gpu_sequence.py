@@ -42,6 +42,9 @@ def _run(gpu, oracle_lib, synth, sensors, n_frames, configure, check_maps_every=
         dr = _rot_angle(Tg[:3, :3].T @ To[:3, :3])
         worst_t, worst_r = max(worst_t, dt), max(worst_r, dr)
         assert dt <= 1e-6 and dr <= 1e-6, "frame %d: pose differs by %g m / %g rad" % (i, dt, dr)
+        # LCP overlap estimator (ConfidenceEstimators.cxx:27-65): same samples, distances, exp and sum tree
+        assert np.float32(g.GetOverlapEstimation()).tobytes() == np.float32(o.GetOverlapEstimation()).tobytes(), \
+            "frame %d: overlap %r vs %r" % (i, g.GetOverlapEstimation(), o.GetOverlapEstimation())
         sg, so = g.GetFrameStats(), o.GetFrameStats()
         assert list(sg.n_matches) == list(so.n_matches) and sg.is_keyframe == so.is_keyframe
         assert sg.loc_lm_iters == so.loc_lm_iters and sg.ego_lm_iters == so.ego_lm_iters
@@ -70,6 +73,24 @@ def test_tiny_blobs_and_ego_registration(gpu, oracle_lib, synth):
         sb, _ = o.GetMatchDebug(0, k)
         assert np.array_equal(sa, sb)
     assert g.GetRegisteredFrame().tobytes() == o.GetRegisteredFrame().tobytes()
+
+
+def test_overlap_estimator(gpu, oracle_lib, synth):
+    """OverlapSamplingRatio = 0.33 (the shipped YAML), blobs on, two undistortion modes."""
+    for und in (2, 0):
+        def cfg(s):
+            p = s.GetParams()
+            p.use_keypoints[2] = 1
+            p.overlap_sampling_ratio = 0.33
+            p.undistortion = und
+            s.SetParams(p)
+        g, o = _run(gpu, oracle_lib, synth, [synth.sensor("vlp16")], 6, cfg)
+        assert 0.2 < g.GetOverlapEstimation() <= 1.0
+    # disabled: -1
+    g2 = gpu()
+    pts, _, stamp = synth.Sequence().frame(synth.sensor("tiny"), 0)
+    g2.AddFrame(pts, stamp, 1)
+    assert g2.GetOverlapEstimation() == -1.0
 
 
 def test_os128_blobs_undistortion(gpu, oracle_lib, synth):

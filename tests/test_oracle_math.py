@@ -236,3 +236,14 @@ def test_lm_solve_against_scipy(oracle_lib):
     # held parameters (2-D mode): z, rx, ry stay put (LocalOptimizer.cxx:89-90)
     g2 = oracle_lib.lm_solve(A, P, X, w, np.zeros(6), 1e3, max_iter=50, two_d=True)
     assert (g2["x"][[2, 3, 4]] == 0).all() and np.abs(g2["x"][[0, 1, 5]] - x_true[[0, 1, 5]]).max() < 0.05
+
+
+def test_detmath_exp(oracle_lib):
+    """dm::exp (overlap estimator): <= 1 ulp in double, and the float variant equals the correctly rounded exp."""
+    rng = np.random.default_rng(1)
+    x = np.concatenate([np.linspace(-700, 5, 50001), -rng.uniform(0, 120, 50000)])
+    assert _ulp_err(oracle_lib.detmath(5, x), np.exp(x)).max() <= 2
+    xs = np.linspace(-112, 0, 50001).astype(np.float32)
+    got = oracle_lib.detmath(6, xs.astype(np.float64)).astype(np.float32)
+    assert np.array_equal(got, np.exp(xs.astype(np.float64)).astype(np.float32))
+    assert oracle_lib.detmath(5, np.array([0.0]))[0] == 1.0 and oracle_lib.detmath(5, np.array([-800.0]))[0] == 0.0

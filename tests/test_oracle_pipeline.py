@@ -76,3 +76,35 @@ def test_soft_failures(oracle_lib, synth):
     assert len(o.GetKeypoints(2)) == 0                    # blobs dropped unless UseBlobs (Slam.cxx:790-800)
     o.Reset()
     assert len(o.GetMap(0)) == 0 and len(o.GetMap(1)) == 0
+
+
+def test_overlap_estimator_against_numpy(oracle_lib, synth):
+    """LCP estimator (ConfidenceEstimators.cxx:27-65) of the oracle == a numpy/cKDTree restatement."""
+    from scipy.spatial import cKDTree
+    o = oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
+    p = o.GetParams()
+    p.overlap_sampling_ratio = 0.33
+    p.use_keypoints[2] = 1
+    o.SetParams(p)
+    seq, sens = synth.Sequence(), synth.sensor("vlp16")
+    for i in range(3):
+        pts, _, stamp = seq.frame(sens, i)
+        o.AddFrame(pts, stamp, i + 1)
+        ov = o.GetOverlapEstimation()
+        if i == 0:
+            assert ov == -1.0                    # no sub-map yet
+            continue
+        reg = o.GetRegisteredFrame()
+        n = int(np.float32(len(reg)) * np.float32(0.33))
+        idx = (np.arange(n, dtype=np.float32) / np.float32(0.33)).astype(np.int64)
+        q = np.stack([reg["x"], reg["y"], reg["z"]], 1)[idx].astype(np.float64)
+        best = np.zeros(n, np.float32)
+        for k, leaf in ((0, 0.3), (1, 0.6), (2, 0.3)):
+            sub = o.GetTargetSubMap(k)
+            if len(sub) == 0:
+                continue
+            d, _ = cKDTree(np.stack([sub["x"], sub["y"], sub["z"]], 1).astype(np.float64)).query(q)
+            thr = np.float32((leaf / 3.0) ** 2)
+            best = np.maximum(best, np.exp(-(d.astype(np.float32) ** 2) / (2 * thr)).astype(np.float32))
+        assert abs(ov - best.mean(dtype=np.float64)) < 2e-6
+        assert 0.3 < ov < 1.0
