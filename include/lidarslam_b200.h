@@ -36,6 +36,8 @@ extern "C" {
 #define LSB_W_EXTRAPOLATION 8      /* Slam.cxx:829-830 / 1278-1282 */
 #define LSB_W_TIME_FIELD 16        /* Slam.cxx:1307-1318 */
 #define LSB_W_FRAMES_DROPPED 32    /* Slam.cxx:734-740 */
+#define LSB_W_TIME_WINDOW 64       /* Slam.cxx:1421-1432 velocity estimated on another window than required */
+#define LSB_W_MOTION_LIMITS 128    /* Slam.cxx:1482-1483 pose does not comply with the motion limits */
 
 /* ---- data contracts -------------------------------------------------------- */
 
@@ -130,6 +132,10 @@ typedef struct lsb_params {
   double max_extrapolation_ratio;      /* 3 */
   uint32_t min_nb_matched_keypoints;   /* 20 */
   float overlap_sampling_ratio;        /* 0 (disabled) */
+  /* Slam::CheckMotionLimits (Slam.cxx:1391-1484, Slam.h:685-694) */
+  float time_window_duration;          /* 0 (disabled), seconds */
+  float velocity_limits[2];            /* FLT_MAX: linear m/s, angular deg/s */
+  float acceleration_limits[2];        /* FLT_MAX: linear m/s2, angular deg/s2 */
 } lsb_params;
 
 /* LocalOptimizer::RegistrationError (LocalOptimizer.h:34-49) */
@@ -233,6 +239,7 @@ LSB_API int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s);
  * durations are those of the kernels alone (slower frames: not for throughput runs). */
 LSB_API int lsb_set_profiling(lsb_slam* h, int on);
 LSB_API float lsb_get_overlap(const lsb_slam* h);                                              /* Slam::GetOverlapEstimation */
+LSB_API int lsb_get_comply_motion_limits(const lsb_slam* h);                                   /* Slam::GetComplyMotionLimits (Slam.h:394) */
 LSB_API unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h);                       /* Slam.h TotalMatchedKeypoints */
 
 /* ---- state control ---------------------------------------------------------- */

@@ -58,7 +58,8 @@ class Params(C.Structure):
                 ("localization_init_saturation_distance", C.c_double), ("localization_final_saturation_distance", C.c_double),
                 ("kf_distance_threshold", C.c_double), ("kf_angle_threshold", C.c_double),
                 ("map_update", C.c_int32), ("max_extrapolation_ratio", C.c_double),
-                ("min_nb_matched_keypoints", C.c_uint32), ("overlap_sampling_ratio", C.c_float)]
+                ("min_nb_matched_keypoints", C.c_uint32), ("overlap_sampling_ratio", C.c_float),
+                ("time_window_duration", C.c_float), ("velocity_limits", C.c_float * 2), ("acceleration_limits", C.c_float * 2)]
 
 
 class RegistrationError(C.Structure):
@@ -270,6 +271,9 @@ class CApi:
         f = self._f("get_overlap")
         f.restype = C.c_float
         return float(f(self.h))
+
+    def GetComplyMotionLimits(self):
+        return bool(self._f("get_comply_motion_limits")(self.h))
 
     def GetTotalMatchedKeypoints(self):
         f = self._f("get_total_matched_keypoints")

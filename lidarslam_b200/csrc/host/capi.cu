@@ -249,6 +249,7 @@ int lsb_set_profiling(lsb_slam* h, int on)
   return LSB_OK;
 }
 float lsb_get_overlap(const lsb_slam* h) { return h->OverlapEstimation; }
+int lsb_get_comply_motion_limits(const lsb_slam* h) { return h->MotionLimits.Comply ? 1 : 0; }
 unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h) { return h->TotalMatchedKeypoints; }
 
 int lsb_set_world_transform_from_guess(lsb_slam* h, const double T[16]) { h->SetWorldTransformFromGuess(FromRowMajor(T)); return LSB_OK; }

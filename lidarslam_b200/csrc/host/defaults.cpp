@@ -2,6 +2,7 @@
 // the oracle (they are interface constants, not algorithms).
 //   lsb_default_params     <- slam_lib/include/LidarSlam/Slam.h:403-694
 //   lsb_default_ke_params  <- slam_lib/include/LidarSlam/SpinningSensorKeypointExtractor.h:126-167
+#include <cfloat>
 #include <cstring>
 #include "../../../include/lidarslam_b200.h"
 
@@ -46,6 +47,9 @@ void lsb_default_params(lsb_params* p)
   p->max_extrapolation_ratio = 3.;
   p->min_nb_matched_keypoints = 20;
   p->overlap_sampling_ratio = 0.f;
+  p->time_window_duration = 0.f;                                   // Slam.h:694
+  p->velocity_limits[0] = p->velocity_limits[1] = FLT_MAX;         // Slam.h:685
+  p->acceleration_limits[0] = p->acceleration_limits[1] = FLT_MAX; // Slam.h:687
 }
 
 void lsb_default_ke_params(lsb_ke_params* p)

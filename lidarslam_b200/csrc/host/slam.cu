@@ -219,6 +219,12 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   // confidence estimators (:272-279)
   if (P.overlap_sampling_ratio > 0.f) EstimateOverlap();
   else OverlapEstimation = -1.f;                                                // SetOverlapSamplingRatio (:1365-1366)
+  if (P.time_window_duration > 0.f) {
+    const int w = check_motion_limits(LogTrajectory, Tworld, CurrentTime, P.time_window_duration, P.velocity_limits, P.acceleration_limits,
+                                      NbrFrameProcessed, MotionLimits);
+    if (w & 1) Warnings |= LSB_W_TIME_WINDOW;
+    if (w & 2) Warnings |= LSB_W_MOTION_LIMITS;
+  }
   uint32_t n_submap[3];
   for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // the map update invalidates the submaps
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();

@@ -14,6 +14,7 @@
 #include "../cuda/map.cuh"
 #include "../common/linalg.h"
 #include "../common/lm_covariance.h"
+#include "../common/motion_limits.h"
 
 struct DCloud {
   lsb::DevBuf<lsb_point> buf;
@@ -70,6 +71,7 @@ struct lsb_slam {
   lsb_registration_error LocalizationUncertainty;
   unsigned TotalMatchedKeypoints = 0;
   float OverlapEstimation = -1.f;
+  lsb::MotionLimitsState MotionLimits;                                     // Slam.h:660-663
   lsb_frame_stats Stats;
   int Warnings = 0;
 

@@ -99,6 +99,7 @@ ORC_API long orc_get_ke_debug(Slam* h, int dev, int field, float* out, long cap)
 ORC_API int orc_get_frame_stats(const Slam* h, lsb_frame_stats* s) { *s = h->Stats; return 0; }
 ORC_API unsigned orc_get_total_matched_keypoints(const Slam* h) { return h->TotalMatchedKeypoints; }
 ORC_API float orc_get_overlap(const Slam* h) { return h->OverlapEstimation; }
+ORC_API int orc_get_comply_motion_limits(const Slam* h) { return h->MotionLimits.Comply ? 1 : 0; }
 ORC_API int orc_set_world_transform_from_guess(Slam* h, const double* T) { h->SetWorldTransformFromGuess(FromRowMajor(T)); return 0; }
 ORC_API int orc_clear_maps(Slam* h) { h->ClearMaps(); return 0; }
 ORC_API int orc_map_load_points(Slam* h, int type, const lsb_point* pts, long n, int fixed)

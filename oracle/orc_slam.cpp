@@ -77,6 +77,12 @@ int Slam::AddFrames(const std::vector<Frame>& frames)
   b = tick(); Stats.ms_localization = ms(a, b);
   if (P.overlap_sampling_ratio > 0) EstimateOverlap();       // :272-276
   else OverlapEstimation = -1.f;                             // SetOverlapSamplingRatio (:1365-1366)
+  if (P.time_window_duration > 0.f) {                        // :277-278
+    const int w = lsb::check_motion_limits(LogTrajectory, Tworld, CurrentTime, P.time_window_duration, P.velocity_limits, P.acceleration_limits,
+                                           NbrFrameProcessed, MotionLimits);
+    if (w & 1) Warnings |= LSB_W_TIME_WINDOW;
+    if (w & 2) Warnings |= LSB_W_MOTION_LIMITS;
+  }
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
   a = tick(); Stats.ms_map_update = ms(b, a);
   LogCurrentFrameState(CurrentTime);

@@ -1,6 +1,7 @@
 // CPU ORACLE (test infrastructure) — LidarSlam::Slam pipeline driver restatement
 // (reference slam_lib/src/Slam.cxx, defaults slam_lib/include/LidarSlam/Slam.h:403-694).
 #pragma once
+#include "../lidarslam_b200/csrc/common/motion_limits.h"
 #include "orc_extractor.h"
 #include "orc_matcher.h"
 #include "orc_optimizer.h"
@@ -40,6 +41,7 @@ struct Slam {
   lsb_registration_error LocalizationUncertainty;
   unsigned TotalMatchedKeypoints = 0;
   float OverlapEstimation = -1.f;
+  lsb::MotionLimitsState MotionLimits;
   lsb_frame_stats Stats;
   int Warnings = 0;
 

@@ -45,6 +45,7 @@ def _run(gpu, oracle_lib, synth, sensors, n_frames, configure, check_maps_every=
         # LCP overlap estimator (ConfidenceEstimators.cxx:27-65): same samples, distances, exp and sum tree
         assert np.float32(g.GetOverlapEstimation()).tobytes() == np.float32(o.GetOverlapEstimation()).tobytes(), \
             "frame %d: overlap %r vs %r" % (i, g.GetOverlapEstimation(), o.GetOverlapEstimation())
+        assert g.GetComplyMotionLimits() == o.GetComplyMotionLimits()
         sg, so = g.GetFrameStats(), o.GetFrameStats()
         assert list(sg.n_matches) == list(so.n_matches) and sg.is_keyframe == so.is_keyframe
         assert sg.loc_lm_iters == so.loc_lm_iters and sg.ego_lm_iters == so.ego_lm_iters
@@ -83,9 +84,15 @@ def test_overlap_estimator(gpu, oracle_lib, synth):
             p.use_keypoints[2] = 1
             p.overlap_sampling_ratio = 0.33
             p.undistortion = und
+            # CheckMotionLimits (Slam.cxx:1391-1484): the trajectory accelerates past 1 m/s within a few frames, limit 0.5 m/s
+            p.time_window_duration = 0.25
+            p.logging_timeout = 5.0
+            p.velocity_limits[0], p.velocity_limits[1] = 0.5, 90.0
+            p.acceleration_limits[0], p.acceleration_limits[1] = 200.0, 2000.0
             s.SetParams(p)
         g, o = _run(gpu, oracle_lib, synth, [synth.sensor("vlp16")], 6, cfg)
         assert 0.2 < g.GetOverlapEstimation() <= 1.0
+        assert g.GetComplyMotionLimits() is False
     # disabled: -1
     g2 = gpu()
     pts, _, stamp = synth.Sequence().frame(synth.sensor("tiny"), 0)
