@@ -61,7 +61,7 @@ def build(verbose=False, force=False):
         objs = list(ex.map(lambda s: _compile(s, hd, verbose), SOURCES))
     newest = max(os.path.getmtime(o) for o in objs)
     if force or not os.path.exists(OUT) or os.path.getmtime(OUT) < newest:
-        cmd = [NVCC, "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC"]
+        cmd = [NVCC, "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC", "-lpthread"]
         if verbose:
             print(" ".join(cmd), flush=True)
         subprocess.check_call(cmd)

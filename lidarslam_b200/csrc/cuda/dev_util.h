@@ -2,6 +2,7 @@
 // handling, growable device buffers, launch helpers.  No torch types: the
 // library owns its device memory and one CUDA stream per lsb_slam handle.
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstddef>
@@ -112,9 +113,9 @@ struct KernelTimer {
 };
 
 // Launch counter of one handle (lsb_frame_stats.kernel_launches).
-struct LaunchCounter {
-  unsigned n = 0;
-  void add(unsigned k = 1) { n += k; }
+struct LaunchCounter {   // bumped from the host lanes (host/lanes.h) as well
+  std::atomic<unsigned> n{0};
+  void add(unsigned k = 1) { n.fetch_add(k, std::memory_order_relaxed); }
 };
 
 }  // namespace lsb

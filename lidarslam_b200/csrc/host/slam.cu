@@ -49,6 +49,7 @@ lsb_slam::lsb_slam(int dev) : device(dev)
   for (auto& e : ev_join) LSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   lsb_default_params(&P);
   if (const char* e = std::getenv("LSB_TRACE")) trace.on = (e[0] == '1');
+  if (const char* e = std::getenv("LSB_HOST_LANES")) use_lanes = (e[0] != '0');
   KeyPointsExtractors[0].reset(new ExtractorGpu());
   // Slam.cxx:153-157: resolution is snapped with the leaf size at call time (0.2 -> 10.0)
   for (auto& m : LocalMaps) m.SetVoxelResolution(10., stream, lc);
@@ -71,6 +72,7 @@ lsb_slam::lsb_slam(int dev) : device(dev)
 
 lsb_slam::~lsb_slam()
 {
+  lanes.reset();   // joins the helper threads
   cudaSetDevice(device);
   for (auto& t : tstream) if (t) cudaStreamSynchronize(t);
   if (stream) cudaStreamSynchronize(stream);
@@ -108,6 +110,18 @@ void lsb_slam::Fork()
   if (serial_types) return;
   LSB_CUDA(cudaEventRecord(ev_fork, stream));
   for (auto& t : tstream) LSB_CUDA(cudaStreamWaitEvent(t, ev_fork, 0));
+}
+
+void lsb_slam::ForEachType(const std::function<void(int)>& fn)
+{
+  Fork();
+  if (serial_types || !use_lanes) {
+    for (int k : kTypeOrder) fn(k);
+  } else {
+    if (!lanes) lanes.reset(new TypeLanes(device));
+    lanes->run(kTypeOrder, fn);
+  }
+  Join();
 }
 
 void lsb_slam::Join()
@@ -425,31 +439,24 @@ void lsb_slam::Localization()
   if (P.undistortion) { InitUndistortion(); RefineUndistortion(); }   // :986-995
   trace.mark("undistort", stream);
 
-  // Submaps (:1003-1037): the three maps work on their own streams, in host phases so that
-  // their read-backs (bbox of the keypoints, size of the submap) overlap
-  bool pending[3] = {false, false, false};
-  Fork();
-  for (int k : kTypeOrder) {
+  // Submaps (:1003-1037): the three maps work on their own streams and host lanes; each lane waits
+  // for its own read-backs (bbox of the keypoints, size of the submap)
+  ForEachType([&](int k) {
     RollingGridGpu& map = LocalMaps[k];
-    if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) continue;
+    if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) return;
     cudaStream_t ts = TypeStream(k);
-    if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(ts, lc); continue; }
+    if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(ts, lc); return; }
     if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, ts, lc);
-    if (CurrentKeypoints[k].n) dev_transformed_bbox_async(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, map.d_bbox, map.h_bbox, ts, lc);
-    pending[k] = true;
-  }
-  for (int k : kTypeOrder) {
-    if (!pending[k]) continue;
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     if (CurrentKeypoints[k].n) {
-      LSB_CUDA(cudaStreamSynchronize(TypeStream(k)));
-      bbox_decode(LocalMaps[k].h_bbox.p, mn, mx);
+      dev_transformed_bbox_async(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, map.d_bbox, map.h_bbox, ts, lc);
+      LSB_CUDA(cudaStreamSynchronize(ts));
+      bbox_decode(map.h_bbox.p, mn, mx);
     }
-    LocalMaps[k].SubMapSelect(mn, mx, (int)(CurrentKeypoints[k].n / 2), TypeStream(k), lc);
-  }
-  for (int k : kTypeOrder)
-    if (pending[k]) LocalMaps[k].SubMapFinish(TypeStream(k), lc);
-  if (trace.on) { Join(); trace.mark("submap+grid", stream); }
+    map.SubMapSelect(mn, mx, (int)(CurrentKeypoints[k].n / 2), ts, lc);
+    map.SubMapFinish(ts, lc);
+  });
+  trace.mark("submap+grid", stream);
 
   // ICP - LM loop (:1051-1156)
   TotalMatchedKeypoints = 0;
@@ -509,23 +516,13 @@ void lsb_slam::UpdateMapsUsingTworld()
   Stats.is_keyframe = 1;
   KfCounter++;
   KfLastPose = Tworld;
-  // RollingGrid::Add of the three types, each on its stream, in host phases (read-backs overlapped)
-  Fork();
-  for (int k : kTypeOrder) {
-    if (!P.use_keypoints[k]) continue;
-    const DCloud& w = WorldKeypoints(k, TypeStream(k));
-    LocalMaps[k].AddBegin(w.buf.p, w.n, true, TypeStream(k), lc);
-  }
-  if (trace.on) { Join(); trace.mark("map.bbox", stream); Fork(); }
-  for (int k : kTypeOrder) {
-    if (!P.use_keypoints[k]) continue;
-    const DCloud& w = CurrentWorldKeypoints[k];
-    LocalMaps[k].AddSort(w.buf.p, w.n, false, CurrentTime, true, TypeStream(k), lc);
-  }
-  if (trace.on) { Join(); trace.mark("map.sort", stream); Fork(); }
-  for (int k : kTypeOrder)
-    if (P.use_keypoints[k]) LocalMaps[k].AddMerge(CurrentWorldKeypoints[k].n, TypeStream(k), lc);
-  Join();
+  // RollingGrid::Add of the three types, each on its stream and host lane
+  ForEachType([&](int k) {
+    if (!P.use_keypoints[k]) return;
+    cudaStream_t ts = TypeStream(k);
+    const DCloud& w = WorldKeypoints(k, ts);
+    LocalMaps[k].Add(w.buf.p, w.n, false, CurrentTime, true, ts, lc);
+  });
 }
 
 // GetKeypoints(k, true) -> TransformPointCloud (:690-702, :1491-1509), cached per frame

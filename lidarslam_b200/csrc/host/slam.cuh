@@ -15,6 +15,7 @@
 #include "../common/linalg.h"
 #include "../common/lm_covariance.h"
 #include "../common/motion_limits.h"
+#include "lanes.h"
 
 struct DCloud {
   lsb::DevBuf<lsb_point> buf;
@@ -33,6 +34,10 @@ struct lsb_slam {
   cudaStream_t TypeStream(int k) const { return serial_types ? stream : tstream[k]; }
   void Fork();                     // type streams wait for `stream`
   void Join();                     // `stream` waits for the type streams
+  // Fork, fn(k) for the three types (each on its own host lane unless serial_types / LSB_HOST_LANES=0), Join
+  std::unique_ptr<lsb::TypeLanes> lanes;
+  bool use_lanes = true;
+  void ForEachType(const std::function<void(int)>& fn);
   lsb::LaunchCounter lc;
   lsb_params P;
 

@@ -4,6 +4,8 @@
 // restatement of Ceres, shared with the GPU on purpose); this file provides the
 // sequential CPU evaluation in the canonical reduction order.
 #pragma once
+#include <cstdio>
+#include <cstdlib>
 #include "orc_matcher.h"
 #include "../lidarslam_b200/csrc/common/lm_core.h"
 #include "../lidarslam_b200/csrc/common/lm_covariance.h"
@@ -83,10 +85,13 @@ struct Optimizer {
     lsb::lm_begin(State, PoseArray, (int)LMMaxIter, TwoDMode ? 1 : 0);
     Evaluate(State.x, E);
     lsb::lm_first_eval(State, E);
+    const bool trace = std::getenv("ORC_LM_TRACE") != nullptr;   // debugging aid: one line per evaluation on stderr
     while (!State.done) {
       Evaluate(State.xc, E);
+      if (trace) std::fprintf(stderr, "[orc lm] iter %d cost %.12g -> %.12g radius %.3g step %.3g\n", State.iter, State.cost, E[27], State.radius, State.step_norm);
       lsb::lm_next_eval(State, E);
     }
+    if (trace) std::fprintf(stderr, "[orc lm] done: iter %d accepted %d term %d n %zu\n", State.iter, State.num_successful, State.term, Records.size());
     for (int i = 0; i < 6; ++i) PoseArray[i] = State.x[i];
     return State.num_successful + 1;
   }
