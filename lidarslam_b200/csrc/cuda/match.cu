@@ -337,17 +337,15 @@ __device__ __forceinline__ void lm_propose_warp(LmState& s)
   __syncwarp();
 }
 
-// The trust-region step, run by warp 0 of the last CTA and kept out of line so that its
-// registers do not weigh on the evaluating threads.  The state was staged in shared memory by the
-// kernel prologue (s_state_raw: it only changes here, at the end of a launch);
-// lane 0 takes the accept / reject decision (scalar), the warp proposes the next step, and the
-// six sin/cos of the next evaluation point are computed by six lanes in parallel.
-__device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned* counter, const double* sE, int first,
-                                        unsigned long long* s_state_raw)
+// The trust-region step, run by warp 0 of every CTA on the CTA's own copy of the state (shared
+// memory) and kept out of line so that its registers do not weigh on the evaluating threads.
+// Every CTA holds the same state and the same 28 sums, and every operation below is
+// deterministic, so the copies stay bit-identical without any exchange.  Lane 0 takes the accept /
+// reject decision (scalar), the warp proposes the next step, and the six sin/cos of the next
+// evaluation point are computed by six lanes in parallel.
+__device__ __noinline__ void lm_control(unsigned long long* s_state_raw, unsigned long long* s_pt_raw, const double* sE, int first)
 {
   constexpr unsigned FULL = 0xffffffffu;
-  constexpr int NW = (int)(sizeof(LmState) / 8);
-  static_assert(sizeof(LmState) % 8 == 0, "LmState is copied as 64-bit words");
   const int lane = threadIdx.x & 31;
   LmState& s = *reinterpret_cast<LmState*>(s_state_raw);
   int propose = 0;
@@ -356,8 +354,6 @@ __device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned
   propose = __shfl_sync(FULL, propose, 0);
   if (propose) lm_propose_warp(s);
   __syncwarp();
-  for (int w = lane; w < NW; w += 32) reinterpret_cast<unsigned long long*>(state)[w] = s_state_raw[w];
-  if (lane == 0) *counter = 0u;
   if (s.done) return;
   double xc[6];
 #pragma unroll
@@ -366,11 +362,7 @@ __device__ __noinline__ void lm_control(LmState* state, LmPoint* point, unsigned
   double trig[6];
 #pragma unroll
   for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(FULL, tv, q);
-  if (lane == 0) {
-    LmPoint pt;
-    lm_make_point_from_trig(xc, trig, pt);
-    *point = pt;
-  }
+  if (lane == 0) lm_make_point_from_trig(xc, trig, *reinterpret_cast<LmPoint*>(s_pt_raw));
 }
 
 constexpr int LM_THREADS = 512;   // 16 warps; each warp evaluates 2 groups of 32 records of the CTA's chunk
@@ -423,93 +415,149 @@ __device__ __forceinline__ double warp_fold32(double v)
   return v;   // complete in lane 0
 }
 
-// One launch = one cost/Jacobian evaluation of the whole problem + one step of the trust-region
-// state machine (common/lm_core.h), in the canonical radix-32 reduction order: a warp folds the
-// 28 sums of a group of 32 records, the CTA folds the 32 groups of its chunk, and the last CTA to
-// finish folds the chunk sums in blocks of 32 (one warp per quantity, one L2 round trip), adds the
-// block sums in order, advances the LM state and prepares the rotation for the next evaluation
-// point.  A launch whose state is already `done` exits at once, so the host enqueues
-// 1 + max_iter launches back to back without reading anything back.
-// part: [LSB_LM_NSUM][pstride] chunk sums, pstride = 32 * number of blocks.
+// Arrive-and-wait over the whole (cooperatively launched, hence co-resident) grid.  `bar` only
+// grows during a solve: the e-th barrier completes when it reaches (e + 1) * gridDim.x.
+__device__ __forceinline__ void lm_grid_barrier(unsigned* bar, unsigned target)
+{
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar, 1u);
+    unsigned v;
+    do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory"); } while (v < target);
+  }
+  __syncthreads();
+}
+
+struct LmStart { double x[6]; };
+
+// tools/probes/lm_eval_probe.cu defines LSB_LM_PROBE to time the phases of one evaluation (CTA 0)
+#ifdef LSB_LM_PROBE
+__device__ unsigned long long g_lm_probe[64 * 5];
+#define LM_PROBE_STAMP(e, k) do { if (blockIdx.x == 0 && threadIdx.x == 0 && (e) < 64) { unsigned long long t_; \
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_lm_probe[(e) * 5 + (k)] = t_; } } while (0)
+#else
+#define LM_PROBE_STAMP(e, k) do { } while (0)
+#endif
+
+// LocalOptimizer::Solve as ONE persistent kernel: the whole trust-region loop (common/lm_core.h)
+// with a grid barrier per cost/Jacobian evaluation instead of a launch.  CTA b owns the chunks
+// b, b + gridDim.x, ... of 1024 records; the first one is staged in shared memory once (13 planes,
+// 104 KB) and re-read from there at every evaluation.  One evaluation, in the canonical radix-32
+// reduction order: a warp folds the 28 sums of a group of 32 records, the CTA folds the 32 groups
+// of a chunk and publishes the chunk sums; after the barrier EVERY CTA folds the chunk sums in
+// blocks of 32 (one warp per quantity), adds the block sums in order and advances its own copy of
+// the LM state (lm_control), so no second barrier and no state round trip through memory is needed.
+// part: [2][LSB_LM_NSUM][pstride] chunk sums (double-buffered by evaluation parity: a CTA may start
+// the next evaluation while a slower one still reads the previous sums), pstride = 32 * blocks.
+// bar: [2] = arrival counter, exit counter; both are zero again when the grid has exited.
 __global__ void __launch_bounds__(LM_THREADS, 1)
-k_lm_eval(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, int pstride, double sat, LmState* __restrict__ state,
-          LmPoint* __restrict__ point, double* __restrict__ part, unsigned* __restrict__ counter, int first)
+k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, int pstride, double sat, LmStart start, int max_iter,
+           int two_d, const int* __restrict__ hist, unsigned min_matches, LmState* __restrict__ state_out, double* __restrict__ part,
+           unsigned* __restrict__ bar)
 {
   constexpr int NW = (int)(sizeof(LmState) / 8), NP = (int)(sizeof(LmPoint) / 8);
+  static_assert(sizeof(LmState) % 8 == 0 && sizeof(LmPoint) % 8 == 0, "copied as 64-bit words");
+  extern __shared__ __align__(16) double s_rec[];                 // [REC_PLANES][LSB_LM_CHUNK]: the CTA's first chunk
   __shared__ __align__(16) unsigned long long s_pt_raw[NP];
   __shared__ __align__(16) unsigned long long s_state_raw[NW];
   __shared__ double s_group[LSB_LM_NSUM][LM_GROUPS];
   __shared__ double s_E[LSB_LM_NSUM];
-  __shared__ int s_last;
-  static_assert(NW <= 64 && NP <= 64, "prologue copies with threads 0..63 / 64..127");
-  // programmatic dependent launch: this grid may have been scheduled while the previous
-  // evaluation was still in its (single-CTA) control step; wait for it before reading the state
-  asm volatile("griddepcontrol.wait;" ::: "memory");
-  if (threadIdx.x < NW) s_state_raw[threadIdx.x] = reinterpret_cast<const unsigned long long*>(state)[threadIdx.x];
-  else if (threadIdx.x >= 64 && threadIdx.x < 64 + NP) s_pt_raw[threadIdx.x - 64] = reinterpret_cast<const unsigned long long*>(point)[threadIdx.x - 64];
-  __syncthreads();
-  if (reinterpret_cast<const LmState*>(s_state_raw)->done) return;   // uniform: written by the previous launch
+  LmState& s_state = *reinterpret_cast<LmState*>(s_state_raw);
   const LmPoint& s_pt = *reinterpret_cast<const LmPoint*>(s_pt_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll 1
-  for (int g = warp; g < LM_GROUPS; g += LM_WARPS) {
-    const int i = blockIdx.x * LSB_LM_CHUNK + g * 32 + lane;
-    double out[LSB_LM_NSUM];
-    if (i < n) lm_eval_record(load_record(records + i, rec_stride), s_pt, sat, out);
-    else {
-#pragma unroll
-      for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
-    }
-    int q;
-    const double r = warp_fold28(out, lane, q);
-    if (q >= 0) s_group[q][g] = r;
-  }
-  __syncthreads();
-#pragma unroll
-  for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
-    const double c = warp_fold32(s_group[q][lane]);
-    if (lane == 0) { part[(size_t)q * pstride + blockIdx.x] = c; __threadfence(); }
-  }
-  __syncthreads();
-  // the next evaluation may be scheduled from here on (it waits for this grid to complete)
-  asm volatile("griddepcontrol.launch_dependents;");
-  if (threadIdx.x == 0) {
-    const unsigned t = atomicAdd(counter, 1u);
-    s_last = (t == (unsigned)(nchunks - 1));
-  }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  const int nblocks = pstride >> 5;
-#pragma unroll
-  for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
-    const double* src = part + (size_t)q * pstride;
-    double e = 0.0;
-    for (int b = 0; b < nblocks; ++b) {
-      const int c = b * 32 + lane;
-      const double v = warp_fold32((c < nchunks) ? __ldcg(src + c) : 0.0);
-      e = (b == 0) ? v : e + v;
-    }
-    if (lane == 0) s_E[q] = e;
-  }
-  __syncthreads();
-  if (threadIdx.x < 32) lm_control(state, point, counter, s_E, first, s_state_raw);
-}
 
-__global__ void k_lm_begin(LmState* state, LmPoint* point, unsigned* counter, double x0, double x1, double x2, double x3, double x4, double x5,
-                           int max_iter, int two_d, const int* __restrict__ hist, unsigned min_matches)
-{
-  const double x[6] = {x0, x1, x2, x3, x4, x5};
-  LmState s;
-  lm_begin(s, x, max_iter, two_d);
-  unsigned matched = 0;
-  for (int t = 0; t < 3; ++t) matched += (unsigned)hist[t * LSB_MATCH_N_STATUS + LSB_MATCH_SUCCESS];
-  if (matched < min_matches) { s.done = 1; s.term = LSB_LM_SKIPPED; }
-  *state = s;
-  LmPoint pt;
-  lm_make_point(x, pt);
-  *point = pt;
-  *counter = 0u;
+  // prologue: initial state (lm_begin + the "enough matches" gate of the caller) and first chunk
+  if (warp == 0) {
+    if (lane == 0) {
+      lm_begin(s_state, start.x, max_iter, two_d);
+      unsigned matched = 0;
+      for (int t = 0; t < 3; ++t) matched += (unsigned)hist[t * LSB_MATCH_N_STATUS + LSB_MATCH_SUCCESS];
+      if (matched < min_matches) { s_state.done = 1; s_state.term = LSB_LM_SKIPPED; }
+    }
+    const double tv = (lane < 6) ? lm_point_trig(start.x, lane) : 0.0;
+    double trig[6];
+#pragma unroll
+    for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(0xffffffffu, tv, q);
+    if (lane == 0) lm_make_point_from_trig(start.x, trig, *reinterpret_cast<LmPoint*>(s_pt_raw));
+  }
+  {
+    const int base = blockIdx.x * LSB_LM_CHUNK;
+    for (int j = threadIdx.x; j < REC_PLANES * LSB_LM_CHUNK; j += LM_THREADS) {
+      const int q = j / LSB_LM_CHUNK, r = j % LSB_LM_CHUNK;
+      const int i = base + r;
+      s_rec[j] = (i < n) ? records[(size_t)q * rec_stride + i] : ((q == REC_W) ? -1.0 : 0.0);
+    }
+  }
+  __syncthreads();
+
+  const int nblocks = pstride >> 5;
+  for (int e = 0; !s_state.done; ++e) {           // uniform over the grid: every CTA holds the same state
+    double* my_part = part + (size_t)(e & 1) * LSB_LM_NSUM * pstride;
+    LM_PROBE_STAMP(e, 0);
+    for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+      const bool cached = (c == (int)blockIdx.x);
+#pragma unroll 1
+      for (int g = warp; g < LM_GROUPS; g += LM_WARPS) {
+        double out[LSB_LM_NSUM];
+        if (cached) {
+          lm_eval_record(load_record(s_rec + g * 32 + lane, LSB_LM_CHUNK), s_pt, sat, out);
+        } else {
+          const int i = c * LSB_LM_CHUNK + g * 32 + lane;
+          if (i < n) lm_eval_record(load_record(records + i, rec_stride), s_pt, sat, out);
+          else {
+#pragma unroll
+            for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
+          }
+        }
+        int q;
+        const double r = warp_fold28(out, lane, q);
+        if (q >= 0) s_group[q][g] = r;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
+        const double v = warp_fold32(s_group[q][lane]);
+        if (lane == 0) my_part[(size_t)q * pstride + c] = v;
+      }
+      __syncthreads();
+    }
+    LM_PROBE_STAMP(e, 1);
+    lm_grid_barrier(bar, (unsigned)(e + 1) * gridDim.x);
+    LM_PROBE_STAMP(e, 2);
+#pragma unroll
+    for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
+      const double* src = my_part + (size_t)q * pstride;
+      double acc = 0.0;
+      for (int b0 = 0; b0 < nblocks; b0 += 4) {
+        double v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int c = (b0 + u) * 32 + lane;
+          v[u] = (b0 + u < nblocks && c < nchunks) ? __ldcg(src + c) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (b0 + u < nblocks) {
+            const double f = warp_fold32(v[u]);
+            acc = (b0 + u == 0) ? f : acc + f;
+          }
+        }
+      }
+      if (lane == 0) s_E[q] = acc;
+    }
+    __syncthreads();
+    LM_PROBE_STAMP(e, 3);
+    if (warp == 0) lm_control(s_state_raw, s_pt_raw, s_E, e == 0);
+    __syncthreads();
+    LM_PROBE_STAMP(e, 4);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < NW) reinterpret_cast<unsigned long long*>(state_out)[threadIdx.x] = s_state_raw[threadIdx.x];
+  // the last CTA to leave re-arms the barrier for the next solve (every CTA is past its last wait)
+  if (threadIdx.x == 0) {
+    const unsigned t = atomicAdd(bar + 1, 1u);
+    if (t == gridDim.x - 1) { bar[0] = 0u; bar[1] = 0u; __threadfence(); }
+  }
 }
 
 }  // namespace
@@ -588,31 +636,40 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   const int n = (int)total;
   const int nchunks = std::max(1, (int)div_up(total, LSB_LM_CHUNK));
   const int pstride = (nchunks + 31) / 32 * 32;
-  part_a.reserve((size_t)pstride * LSB_LM_NSUM, s);
-  lm_state.reserve(1, s); lm_point.reserve(1, s); lm_counter.reserve(1, s); h_lm.reserve(1);
-  k_lm_begin<<<1, 1, 0, s>>>(lm_state.p, lm_point.p, lm_counter.p, x0[0], x0[1], x0[2], x0[3], x0[4], x0[5], max_iter, two_d,
-                             hist.p, min_matches);
-  LSB_LAUNCH_CHECK(); lc.add();
+  constexpr size_t kSmem = (size_t)REC_PLANES * LSB_LM_CHUNK * sizeof(double);
+  if (lm_grid_limit == 0) {      // co-resident CTAs of the persistent kernel on this device
+    int dev = 0, sms = 0, per_sm = 0;
+    LSB_CUDA(cudaGetDevice(&dev));
+    LSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    LSB_CUDA(cudaFuncSetAttribute(k_lm_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    LSB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_lm_solve, LM_THREADS, kSmem));
+    if (per_sm < 1) throw CudaError(LSB_E_CUDA, "k_lm_solve does not fit on a multiprocessor");
+    lm_grid_limit = sms * per_sm;
+  }
+  part_a.reserve((size_t)2 * pstride * LSB_LM_NSUM, s);
+  lm_state.reserve(1, s); h_lm.reserve(1);
+  if (!lm_counter.p) {           // [arrivals, exits] of the grid barrier: zero between solves
+    lm_counter.reserve(2, s);
+    LSB_CUDA(cudaMemsetAsync(lm_counter.p, 0, 2 * sizeof(unsigned), s));
+  }
+  LmStart start;
+  for (int i = 0; i < 6; ++i) start.x[i] = x0[i];
   t_lm.begin(s);
-  // every evaluation is launched with programmatic stream serialization: its CTAs are scheduled
-  // while the previous evaluation finishes its control step (launch latency hidden)
+  // one cooperative launch = the whole LM loop (co-residency of the grid is what the barrier needs)
   cudaLaunchAttribute attr;
-  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr.val.programmaticStreamSerializationAllowed = 1;
+  attr.id = cudaLaunchAttributeCooperative;
+  attr.val.cooperative = 1;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)nchunks);
+  cfg.gridDim = dim3((unsigned)std::min(nchunks, lm_grid_limit));
   cfg.blockDim = dim3(LM_THREADS);
-  cfg.dynamicSmemBytes = 0;
+  cfg.dynamicSmemBytes = kSmem;
   cfg.stream = s;
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
-  for (int e = 0; e <= max_iter; ++e) {
-    LSB_CUDA(cudaLaunchKernelEx(&cfg, k_lm_eval, (const double*)records.p, rec_stride, n, nchunks, pstride, saturation, lm_state.p, lm_point.p,
-                                part_a.p, lm_counter.p, e == 0 ? 1 : 0));
-    lc.add();
-  }
+  LSB_CUDA(cudaLaunchKernelEx(&cfg, k_lm_solve, (const double*)records.p, rec_stride, n, nchunks, pstride, saturation, start, max_iter, two_d,
+                              (const int*)hist.p, min_matches, lm_state.p, part_a.p, lm_counter.p));
+  lc.add();
   t_lm.end(s);
-  t_lm.launches += (unsigned)max_iter;
   d2h_bytes += sizeof(LmState) + 3 * LSB_MATCH_N_STATUS * sizeof(int);
   LSB_CUDA(cudaMemcpyAsync(h_hist.p, hist.p, 3 * LSB_MATCH_N_STATUS * sizeof(int), cudaMemcpyDeviceToHost, s));
   LSB_CUDA(cudaMemcpyAsync(h_lm.p, lm_state.p, sizeof(LmState), cudaMemcpyDeviceToHost, s));

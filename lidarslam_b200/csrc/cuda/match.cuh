@@ -18,10 +18,10 @@ struct MatchWorkspace {
   DevBuf<uint8_t> status;
   DevBuf<double> weight;
   DevBuf<int> hist;                 // [3][LSB_MATCH_N_STATUS]
-  DevBuf<double> part_a;            // LM chunk partial sums
-  DevBuf<LmState> lm_state;         // [1]
-  DevBuf<LmPoint> lm_point;         // [1] rotation at the next evaluation point
-  DevBuf<unsigned> lm_counter;      // [1]
+  DevBuf<double> part_a;            // LM chunk partial sums, double-buffered
+  DevBuf<LmState> lm_state;         // [1] final state of the last solve
+  DevBuf<unsigned> lm_counter;      // [2] grid barrier of the persistent LM kernel
+  int lm_grid_limit = 0;            // co-resident CTAs of that kernel on this device
   PinnedBuf<int> h_hist;
   PinnedBuf<LmState> h_lm;
   KernelTimer t_knn, t_fit, t_lm;   // lsb_set_profiling
@@ -36,9 +36,9 @@ struct MatchWorkspace {
   // reads the status histograms back (one stream sync); hist_out[3][LSB_MATCH_N_STATUS]
   void read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s);
   // LocalOptimizer::Solve on the current records; returns the final state and the match histograms
-  // with ONE stream sync.  The "enough matches" test of the caller (Slam.cxx:919, :1098) is taken on
-  // the device too: below min_matches the LM launches exit at once and the state comes back with
-  // term == LSB_LM_SKIPPED (x == x0).
+  // with ONE launch and ONE stream sync.  The "enough matches" test of the caller (Slam.cxx:919,
+  // :1098) is taken on the device too: below min_matches the kernel exits at once and the state
+  // comes back with term == LSB_LM_SKIPPED (x == x0).
   LmState solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches,
                 int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc);
 };

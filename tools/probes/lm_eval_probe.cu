@@ -1,19 +1,19 @@
-// Probe (not product): where one k_lm_eval launch spends its time, on synthetic records of the
-// OS-128 problem size.  Uses the product kernel unmodified:
-//   full      = evaluation + last-CTA tail (chunk-order sum + trust-region control)
-//   main only = the ticket counter is preset so that no CTA is "last" (no tail)
-//   empty     = a kernel of the same grid that does nothing (launch floor)
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -fmad=false -o lm_eval_probe lm_eval_probe.cu
+// Probe (not product): cost of the persistent LM kernel (k_lm_solve, used unmodified) per
+// cost/Jacobian evaluation, on synthetic records of the OS-128 problem size: the kernel is timed
+// with max_iter = 0, 1, 2, ... (the synthetic problem converges after a few steps, the slope over
+// the first ones is the cost of one evaluation + barrier + control step).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -fmad=false -I../../include -o lm_eval_probe lm_eval_probe.cu ../../lidarslam_b200/csrc/cuda/knn.cu
+#define LSB_LM_PROBE 1
 #include "../../lidarslam_b200/csrc/cuda/match.cu"
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
 #include <cmath>
+#include <algorithm>
 #include <functional>
 using namespace lsb;
 
 __global__ void k_empty(int) {}
-__global__ void k_set(unsigned* c, unsigned v) { *c = v; }
 
 static float time_launches(int reps, const std::function<void()>& f)
 {
@@ -47,28 +47,46 @@ int main(int argc, char** argv)
     for (int q = 0; q < 3; ++q) { rec[(6 + q) * stride + i] = r.P[q]; rec[(9 + q) * stride + i] = r.X[q]; }
     rec[12 * stride + i] = r.w;
   }
-  double* d_rec; double* d_part; LmState* d_state; LmPoint* d_point; unsigned* d_counter; int* d_hist;
-  cudaMalloc(&d_rec, rec.size() * 8); const int pstride = (nchunks + 31) / 32 * 32; cudaMalloc(&d_part, (size_t)pstride * LSB_LM_NSUM * 8);
-  cudaMalloc(&d_state, sizeof(LmState)); cudaMalloc(&d_point, sizeof(LmPoint)); cudaMalloc(&d_counter, 8);
+  double* d_rec; double* d_part; LmState* d_state; unsigned* d_bar; int* d_hist;
+  const int pstride = (nchunks + 31) / 32 * 32;
+  cudaMalloc(&d_rec, rec.size() * 8); cudaMalloc(&d_part, (size_t)2 * pstride * LSB_LM_NSUM * 8);
+  cudaMalloc(&d_state, sizeof(LmState)); cudaMalloc(&d_bar, 8); cudaMemset(d_bar, 0, 8);
   cudaMalloc(&d_hist, 3 * LSB_MATCH_N_STATUS * 4);
   std::vector<int> hist(3 * LSB_MATCH_N_STATUS, 1000);
   cudaMemcpy(d_hist, hist.data(), hist.size() * 4, cudaMemcpyHostToDevice);
   cudaMemcpy(d_rec, rec.data(), rec.size() * 8, cudaMemcpyHostToDevice);
-  auto begin = [&] { k_lm_begin<<<1, 1>>>(d_state, d_point, d_counter, 0.01, 0.02, 0.03, 0.001, 0.002, 0.003, 15, 0, d_hist, 100u); };
-  auto eval = [&](int first) { k_lm_eval<<<nchunks, LM_THREADS>>>(d_rec, stride, n, nchunks, pstride, 1.0, d_state, d_point, d_part, d_counter, first); };
-  printf("n = %d records, %d chunks of %d, %d threads per CTA\n", n, nchunks, LSB_LM_CHUNK, LM_THREADS);
-  const float t_empty = time_launches(200, [&] { k_empty<<<nchunks, LM_THREADS>>>(0); });
-  const float t_begin = time_launches(200, [&] { begin(); });
-  const float t_full = time_launches(200, [&] { begin(); eval(1); });
-  const float t_main = time_launches(200, [&] { begin(); k_set<<<1, 1>>>(d_counter, 1u << 30); eval(1); });
-  const float t_set = time_launches(200, [&] { begin(); k_set<<<1, 1>>>(d_counter, 1u << 30); });
-  printf("empty launch             %7.2f us\n", t_empty);
-  printf("k_lm_begin               %7.2f us\n", t_begin);
-  printf("begin + eval (full)      %7.2f us  -> eval  %7.2f us\n", t_full, t_full - t_begin);
-  printf("begin + set + eval(main) %7.2f us  -> main  %7.2f us  (tail %7.2f us)\n", t_main, t_main - t_set, (t_full - t_begin) - (t_main - t_set));
-  // product-like sequence: 1 + 15 launches back to back (they may finish early when the LM converges)
-  const float t_seq = time_launches(50, [&] { begin(); for (int e = 0; e <= 15; ++e) eval(e == 0); });
-  LmState st; cudaMemcpy(&st, d_state, sizeof(st), cudaMemcpyDeviceToHost);
-  printf("begin + 16 evals         %7.2f us  (LM iter %d, term %d, cost %.6g)  %s\n", t_seq, st.iter, st.term, st.cost, cudaGetErrorString(cudaGetLastError()));
+  constexpr size_t kSmem = (size_t)REC_PLANES * LSB_LM_CHUNK * sizeof(double);
+  cudaFuncSetAttribute(k_lm_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
+  int per_sm = 0, sms = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_lm_solve, LM_THREADS, kSmem);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+  const int grid = std::min(nchunks, per_sm * sms);
+  LmStart start = {{0.01, 0.02, 0.03, 0.001, 0.002, 0.003}};
+  auto solve = [&](int max_iter) {
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeCooperative;
+    attr.val.cooperative = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(LM_THREADS); cfg.dynamicSmemBytes = kSmem; cfg.attrs = &attr; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, k_lm_solve, (const double*)d_rec, stride, n, nchunks, pstride, 1.0, start, max_iter, 0, (const int*)d_hist, 100u,
+                       d_state, d_part, d_bar);
+  };
+  printf("n = %d records, %d chunks of %d, grid %d x %d threads (%d CTA/SM)\n", n, nchunks, LSB_LM_CHUNK, grid, LM_THREADS, per_sm);
+  printf("empty launch   %7.2f us\n", time_launches(200, [&] { k_empty<<<grid, LM_THREADS>>>(0); }));
+  float prev = 0.f;
+  for (int mi : {0, 1, 2, 3, 15}) {
+    const float t = time_launches(200, [&] { solve(mi); });
+    LmState st; cudaMemcpy(&st, d_state, sizeof(st), cudaMemcpyDeviceToHost);
+    printf("max_iter %2d    %7.2f us  (+%6.2f)  LM iter %d, term %d, cost %.6g  %s\n", mi, t, t - prev, st.iter, st.term, st.cost,
+           cudaGetErrorString(cudaGetLastError()));
+    prev = t;
+  }
+  // phases of each evaluation on CTA 0 (globaltimer, ns)
+  solve(3); cudaDeviceSynchronize();
+  unsigned long long st[64 * 5];
+  cudaMemcpyFromSymbol(st, g_lm_probe, sizeof(st));
+  for (int e = 0; e < 4; ++e)
+    printf("eval %d: evaluate+chunk fold %5.2f us | barrier %5.2f | final fold %5.2f | control %5.2f\n", e, (st[e * 5 + 1] - st[e * 5]) * 1e-3,
+           (st[e * 5 + 2] - st[e * 5 + 1]) * 1e-3, (st[e * 5 + 3] - st[e * 5 + 2]) * 1e-3, (st[e * 5 + 4] - st[e * 5 + 3]) * 1e-3);
   return 0;
 }
