@@ -337,6 +337,20 @@ __device__ __forceinline__ void lm_propose_warp(LmState& s)
   __syncwarp();
 }
 
+// rotation at the evaluation point x (LmPoint): the six sin/cos on six lanes, assembled by lane 0
+__device__ __noinline__ void lm_point_warp(const double* x, unsigned long long* s_pt_raw)
+{
+  const int lane = threadIdx.x & 31;
+  double xl[6];
+#pragma unroll
+  for (int q = 0; q < 6; ++q) xl[q] = x[q];
+  const double tv = (lane < 6) ? lm_point_trig(xl, lane) : 0.0;
+  double trig[6];
+#pragma unroll
+  for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(0xffffffffu, tv, q);
+  if (lane == 0) lm_make_point_from_trig(xl, trig, *reinterpret_cast<LmPoint*>(s_pt_raw));
+}
+
 // The trust-region step, run by warp 0 of every CTA on the CTA's own copy of the state (shared
 // memory) and kept out of line so that its registers do not weigh on the evaluating threads.
 // Every CTA holds the same state and the same 28 sums, and every operation below is
@@ -355,14 +369,7 @@ __device__ __noinline__ void lm_control(unsigned long long* s_state_raw, unsigne
   if (propose) lm_propose_warp(s);
   __syncwarp();
   if (s.done) return;
-  double xc[6];
-#pragma unroll
-  for (int q = 0; q < 6; ++q) xc[q] = s.xc[q];
-  const double tv = (lane < 6) ? lm_point_trig(xc, lane) : 0.0;
-  double trig[6];
-#pragma unroll
-  for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(FULL, tv, q);
-  if (lane == 0) lm_make_point_from_trig(xc, trig, *reinterpret_cast<LmPoint*>(s_pt_raw));
+  lm_point_warp(s.xc, s_pt_raw);
 }
 
 constexpr int LM_THREADS = 512;   // 16 warps; each warp evaluates 2 groups of 32 records of the CTA's chunk
@@ -475,11 +482,8 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
       for (int t = 0; t < 3; ++t) matched += (unsigned)hist[t * LSB_MATCH_N_STATUS + LSB_MATCH_SUCCESS];
       if (matched < min_matches) { s_state.done = 1; s_state.term = LSB_LM_SKIPPED; }
     }
-    const double tv = (lane < 6) ? lm_point_trig(start.x, lane) : 0.0;
-    double trig[6];
-#pragma unroll
-    for (int q = 0; q < 6; ++q) trig[q] = __shfl_sync(0xffffffffu, tv, q);
-    if (lane == 0) lm_make_point_from_trig(start.x, trig, *reinterpret_cast<LmPoint*>(s_pt_raw));
+    __syncwarp();
+    lm_point_warp(s_state.x, s_pt_raw);
   }
   {
     const int base = blockIdx.x * LSB_LM_CHUNK;
@@ -496,19 +500,19 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
     double* my_part = part + (size_t)(e & 1) * LSB_LM_NSUM * pstride;
     LM_PROBE_STAMP(e, 0);
     for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
+      // one code path for both sources (generic loads): the chunk staged in shared memory, or global
       const bool cached = (c == (int)blockIdx.x);
+      const double* src = cached ? s_rec : records + (size_t)c * LSB_LM_CHUNK;
+      const size_t stride = cached ? (size_t)LSB_LM_CHUNK : rec_stride;
+      const int left = cached ? LSB_LM_CHUNK : n - c * LSB_LM_CHUNK;     // records of this chunk that exist
 #pragma unroll 1
       for (int g = warp; g < LM_GROUPS; g += LM_WARPS) {
         double out[LSB_LM_NSUM];
-        if (cached) {
-          lm_eval_record(load_record(s_rec + g * 32 + lane, LSB_LM_CHUNK), s_pt, sat, out);
-        } else {
-          const int i = c * LSB_LM_CHUNK + g * 32 + lane;
-          if (i < n) lm_eval_record(load_record(records + i, rec_stride), s_pt, sat, out);
-          else {
+        const int j = g * 32 + lane;
+        if (j < left) lm_eval_record(load_record(src + j, stride), s_pt, sat, out);
+        else {
 #pragma unroll
-            for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
-          }
+          for (int q = 0; q < LSB_LM_NSUM; ++q) out[q] = 0.0;
         }
         int q;
         const double r = warp_fold28(out, lane, q);
