@@ -38,6 +38,7 @@ extern "C" {
 #define LSB_W_FRAMES_DROPPED 32    /* Slam.cxx:734-740 */
 #define LSB_W_TIME_WINDOW 64       /* Slam.cxx:1421-1432 velocity estimated on another window than required */
 #define LSB_W_MOTION_LIMITS 128    /* Slam.cxx:1482-1483 pose does not comply with the motion limits */
+#define LSB_W_SENSOR_TIME 256      /* SensorConstraints.cxx:19,75,121 no wheel-odometer / IMU measure around the frame stamp */
 
 /* ---- data contracts -------------------------------------------------------- */
 
@@ -246,6 +247,34 @@ LSB_API unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h);        
 LSB_API int lsb_set_world_transform_from_guess(lsb_slam* h, const double T_rowmajor[16]);      /* Slam.cxx:490-501 */
 LSB_API int lsb_clear_maps(lsb_slam* h);                                                        /* Slam.cxx:1639-1643 */
 LSB_API int lsb_map_load_points(lsb_slam* h, int type, const lsb_point* pts, long n, int fixed); /* body of Slam::LoadMapsFromPCD Slam.cxx:520-543 */
+
+/* ---- external sensor constraints of the localization solve ------------------ */
+typedef struct lsb_wheel_odom_measurement { double time, distance; } lsb_wheel_odom_measurement;            /* SensorConstraints.h:13-17 */
+typedef struct lsb_gravity_measurement { double time; double acceleration[3]; } lsb_gravity_measurement;    /* SensorConstraints.h:19-23 */
+LSB_API int lsb_add_wheel_odom_measurement(lsb_slam* h, const lsb_wheel_odom_measurement* m);   /* Slam::AddWheelOdomMeasurement Slam.cxx:1589-1592 */
+LSB_API int lsb_add_gravity_measurement(lsb_slam* h, const lsb_gravity_measurement* m);         /* Slam::AddGravityMeasurement Slam.cxx:1584-1587 */
+LSB_API int lsb_clear_sensor_measurements(lsb_slam* h);                                          /* Slam.cxx:1594-1598 */
+LSB_API int lsb_set_wheel_odom_weight(lsb_slam* h, double weight);                               /* Slam.h:331 */
+LSB_API double lsb_get_wheel_odom_weight(const lsb_slam* h);                                     /* Slam.h:332 */
+LSB_API int lsb_set_gravity_weight(lsb_slam* h, double weight);                                  /* Slam.h:334 */
+LSB_API double lsb_get_gravity_weight(const lsb_slam* h);                                        /* Slam.h:335 */
+LSB_API int lsb_set_sensor_time_offset(lsb_slam* h, double seconds);                             /* Slam.cxx:223-227 */
+LSB_API double lsb_get_sensor_time_offset(const lsb_slam* h);                                    /* Slam.h:339 */
+LSB_API int lsb_get_gravity_reference(const lsb_slam* h, double g[3]);                           /* ImuManager::GetGravityRef SensorConstraints.h:103 */
+
+/* ---- map persistence: PCD wire format (pcl::io::savePCDFile* / loadPCDFile restated, no PCL) ---- */
+enum { LSB_PCD_ASCII = 0, LSB_PCD_BINARY = 1, LSB_PCD_BINARY_COMPRESSED = 2 };                    /* PointCloudStorage.h:60-65 PCDFormat */
+/* Slam::SaveMapsToPCD (Slam.cxx:504-517): writes <prefix>{edges,planes,blobs}.pcd for the keypoint types in use;
+ * an empty map writes nothing.  LSB_E_INVALID if a file cannot be written. */
+LSB_API int lsb_save_maps_to_pcd(lsb_slam* h, const char* file_prefix, int pcd_format, int filtered);
+/* Slam::LoadMapsFromPCD (Slam.cxx:520-543): a missing / unreadable file is skipped; points are fixed when map_update is
+ * NONE or ADD_KPTS_TO_FIXED_MAP; their time is the wall clock.  Returns a bit mask of the types loaded (1 << type). */
+LSB_API int lsb_load_maps_from_pcd(lsb_slam* h, const char* file_prefix, int reset_maps);
+/* savePointCloudToPCD (PointCloudStorage.h:85-115): 0 ok, -1 I/O error, -3 empty cloud, -4 unknown format. */
+LSB_API int lsb_pcd_write(const char* path, const lsb_point* pts, size_t n, int pcd_format);
+/* pcl::io::loadPCDFile<LidarPoint> (Slam.cxx:531): returns the number of points in the file (-1: unreadable) and copies
+ * at most `cap` of them; call with cap = 0 to size the buffer.  Needs no device. */
+LSB_API long lsb_pcd_read(const char* path, lsb_point* out, long cap);
 
 /* ---- kernel-level entry points (parity tests and benchmarks) -----------------
  * Each runs ONE stage of the path on caller-supplied host data through the same

@@ -18,6 +18,7 @@ POINT_DTYPE = np.dtype(
 assert POINT_DTYPE.itemsize == 32
 
 EDGE, PLANE, BLOB = 0, 1, 2
+PCD_ASCII, PCD_BINARY, PCD_BINARY_COMPRESSED = 0, 1, 2   # reference PointCloudStorage.h:60-65
 KEYPOINT_TYPES = (EDGE, PLANE, BLOB)
 MATCH_STATUS_NAMES = ("SUCCESS", "BAD_MODEL_PARAMETRIZATION", "NOT_ENOUGH_NEIGHBORS", "NEIGHBORS_TOO_FAR",
                       "BAD_PCA_STRUCTURE", "INVALID_NUMERICAL", "MSE_TOO_LARGE", "UNKNOWN")
@@ -237,6 +238,44 @@ class CApi:
     def GetMap(self, k, clean=False):
         return self._cloud("get_map", C.c_int(k), C.c_int(1 if clean else 0))
 
+    # ---- external sensor constraints (reference Slam.h:331-344) ------------
+    def AddWheelOdomMeasurement(self, time, distance):
+        m = (C.c_double * 2)(time, distance)
+        self._check(self._f("add_wheel_odom_measurement")(self.h, m))
+
+    def AddGravityMeasurement(self, time, acceleration):
+        m = (C.c_double * 4)(time, *[float(v) for v in acceleration])
+        self._check(self._f("add_gravity_measurement")(self.h, m))
+
+    def ClearSensorMeasurements(self):
+        self._check(self._f("clear_sensor_measurements")(self.h))
+
+    def SetWheelOdomWeight(self, w):
+        self._check(self._f("set_wheel_odom_weight")(self.h, C.c_double(w)))
+
+    def SetGravityWeight(self, w):
+        self._check(self._f("set_gravity_weight")(self.h, C.c_double(w)))
+
+    def SetSensorTimeOffset(self, t):
+        self._check(self._f("set_sensor_time_offset")(self.h, C.c_double(t)))
+
+    def GetGravityReference(self):
+        g = np.zeros(3)
+        self._check(self._f("get_gravity_reference")(self.h, _ptr(g)))
+        return g
+
+    def SaveMapsToPCD(self, file_prefix, pcd_format=PCD_BINARY_COMPRESSED, filtered=True):
+        """Slam::SaveMapsToPCD (reference Slam.cxx:504-517)."""
+        f = self._f("save_maps_to_pcd")
+        f.restype = C.c_int
+        return self._check(f(self.h, os.fsencode(file_prefix), C.c_int(pcd_format), C.c_int(1 if filtered else 0)))
+
+    def LoadMapsFromPCD(self, file_prefix, reset_maps=True):
+        """Slam::LoadMapsFromPCD (reference Slam.cxx:520-543); returns the bit mask of the keypoint types loaded."""
+        f = self._f("load_maps_from_pcd")
+        f.restype = C.c_int
+        return self._check(f(self.h, os.fsencode(file_prefix), C.c_int(1 if reset_maps else 0)))
+
     def GetTargetSubMap(self, k):
         return self._cloud("get_submap", C.c_int(k))
 
@@ -317,6 +356,11 @@ class CApi:
         return dict(rc=rc, status=status, weight=weight, pose=pose.reshape(4, 4), accepted=acc.value,
                     iterations=its.value, cost=cost.value, err=err)
 
+    def MapLoadPoints(self, k, pts, fixed=False):
+        """Body of Slam::LoadMapsFromPCD for one keypoint type (reference Slam.cxx:536-537) on host points."""
+        pts = as_points(pts)
+        self._check(self._f("map_load_points")(self.h, C.c_int(k), _ptr(pts), C.c_long(len(pts)), C.c_int(1 if fixed else 0)))
+
     def MapAdd(self, k, pts, fixed=False, current_time=0.0):
         pts = as_points(pts)
         self._check(self._f("map_add")(self.h, C.c_int(k), _ptr(pts), C.c_size_t(len(pts)), C.c_int(1 if fixed else 0),
@@ -358,3 +402,27 @@ def default_ke_params(lib=None):
     p = KeParams()
     (lib or load_library()).lsb_default_ke_params(C.byref(p))
     return p
+
+
+def pcd_write(path, pts, pcd_format=PCD_BINARY_COMPRESSED, lib=None):
+    """savePointCloudToPCD (reference PointCloudStorage.h:85-115): 0 ok, -1 I/O error, -3 empty cloud, -4 unknown format."""
+    pts = as_points(pts)
+    f = (lib or load_library()).lsb_pcd_write
+    f.restype = C.c_int
+    return f(os.fsencode(path), _ptr(pts), C.c_size_t(len(pts)), C.c_int(pcd_format))
+
+
+def pcd_read(path, lib=None):
+    """pcl::io::loadPCDFile<LidarPoint> (reference Slam.cxx:531); raises on an unreadable file."""
+    lib = lib or load_library()
+    f = lib.lsb_pcd_read
+    f.restype = C.c_long
+    n = f(os.fsencode(path), None, C.c_long(0))
+    if n < 0:
+        e = lib.lsb_last_error
+        e.restype = C.c_char_p
+        raise RuntimeError("lsb_pcd_read failed: %s" % (e() or b"").decode())
+    out = np.zeros(int(n), dtype=POINT_DTYPE)
+    if n:
+        f(os.fsencode(path), _ptr(out), C.c_long(n))
+    return out

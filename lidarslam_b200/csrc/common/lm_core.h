@@ -370,6 +370,60 @@ LSB_HD bool lm_next_update(LmState& s, const double* E)
   return true;
 }
 
+// Extra residual blocks of the localization solve (Slam.cxx:1123-1131), at most one of each:
+//  * wheel odometer (CeresCostFunctions.h:267-296): r = |t - prev| - dist (|.| := 0 with zero derivative when
+//    |t - prev|^2 < 1e-6), loss ScaledLoss(NULL, weight) (SensorConstraints.cxx:51): rho(s) = weight * s;
+//  * IMU gravity (CeresCostFunctions.h:311-341): r = R(rx, ry, rz) g_cur - g_ref, same loss.
+// With rho' = weight and rho'' = 0 Ceres scales residual and Jacobian by sqrt(weight): the normal equations
+// and the cost gain weight * (J^T J, J^T r, 0.5 r.r).  The terms are ADDED to the 28 reduced sums E of the
+// keypoint records, after the reduction tree, wheel first (the order the reference adds the blocks).
+struct LmSensorTerms {
+  int use_wheel, use_gravity;
+  double wheel_prev[3], wheel_dist, wheel_weight;
+  double g_ref[3], g_cur[3], gravity_weight;
+};
+
+LSB_HD void lm_sensor_terms_clear(LmSensorTerms& c)
+{
+  c.use_wheel = c.use_gravity = 0;
+  c.wheel_dist = c.wheel_weight = c.gravity_weight = 0.0;
+  for (int i = 0; i < 3; ++i) c.wheel_prev[i] = c.g_ref[i] = c.g_cur[i] = 0.0;
+}
+
+LSB_HD void lm_add_sensor_terms(const LmSensorTerms& c, const LmPoint& pt, double* E)
+{
+  if (c.use_wheel) {
+    const double d0 = pt.t.x - c.wheel_prev[0], d1 = pt.t.y - c.wheel_prev[1], d2 = pt.t.z - c.wheel_prev[2];
+    const double sq = d0 * d0 + d1 * d1 + d2 * d2;
+    double nrm = 0.0, j[3] = {0.0, 0.0, 0.0};
+    if (!(sq < 1e-6)) {
+      nrm = ::sqrt(sq);
+      j[0] = d0 / nrm; j[1] = d1 / nrm; j[2] = d2 / nrm;
+    }
+    const double r = nrm - c.wheel_dist, w = c.wheel_weight;
+    for (int a = 0; a < 3; ++a) {
+      for (int b = a; b < 3; ++b) E[lm_hidx(a, b)] += w * (j[a] * j[b]);
+      E[21 + a] += w * (j[a] * r);
+    }
+    E[27] += 0.5 * (w * (r * r));
+  }
+  if (c.use_gravity) {
+    const Vec3d Y = pt.R * Vec3d(c.g_cur[0], c.g_cur[1], c.g_cur[2]);
+    const double r0 = Y.x - c.g_ref[0], r1 = Y.y - c.g_ref[1], r2 = Y.z - c.g_ref[2];
+    const double ax = pt.R.m[0], ay = pt.R.m[3], az = pt.R.m[6];
+    // columns d(R g)/d(rx, ry, rz): the cross products of lm_eval_record
+    const double J[3][3] = {{ay * Y.z - az * Y.y, az * Y.x - ax * Y.z, ax * Y.y - ay * Y.x},
+                            {pt.cz * Y.z, pt.sz * Y.z, -(pt.sz * Y.y) - pt.cz * Y.x},
+                            {-Y.y, Y.x, 0.0}};
+    const double w = c.gravity_weight;
+    for (int a = 0; a < 3; ++a) {
+      for (int b = a; b < 3; ++b) E[lm_hidx(3 + a, 3 + b)] += w * (J[a][0] * J[b][0] + J[a][1] * J[b][1] + J[a][2] * J[b][2]);
+      E[24 + a] += w * (J[a][0] * r0 + J[a][1] * r1 + J[a][2] * r2);
+    }
+    E[27] += 0.5 * (w * (r0 * r0 + r1 * r1 + r2 * r2));
+  }
+}
+
 LSB_HD void lm_first_eval(LmState& s, const double* E) { if (lm_first_update(s, E)) lm_propose(s); }
 LSB_HD void lm_next_eval(LmState& s, const double* E) { if (lm_next_update(s, E)) lm_propose(s); }
 

@@ -461,7 +461,7 @@ __device__ unsigned long long g_lm_probe[64 * 5];
 __global__ void __launch_bounds__(LM_THREADS, 1)
 k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, int pstride, double sat, LmStart start, int max_iter,
            int two_d, const int* __restrict__ hist, unsigned min_matches, LmState* __restrict__ state_out, double* __restrict__ part,
-           unsigned* __restrict__ bar)
+           unsigned* __restrict__ bar, const LmSensorTerms terms)
 {
   constexpr int NW = (int)(sizeof(LmState) / 8), NP = (int)(sizeof(LmPoint) / 8);
   static_assert(sizeof(LmState) % 8 == 0 && sizeof(LmPoint) % 8 == 0, "copied as 64-bit words");
@@ -552,7 +552,12 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
     }
     __syncthreads();
     LM_PROBE_STAMP(e, 3);
-    if (warp == 0) lm_control(s_state_raw, s_pt_raw, s_E, e == 0);
+    if (warp == 0) {
+      // wheel-odometer / IMU gravity blocks (Slam.cxx:1123-1131): added to the reduced sums at the evaluation point
+      if ((terms.use_wheel | terms.use_gravity) && lane == 0) lm_add_sensor_terms(terms, s_pt, s_E);
+      __syncwarp();
+      lm_control(s_state_raw, s_pt_raw, s_E, e == 0);
+    }
     __syncthreads();
     LM_PROBE_STAMP(e, 4);
   }
@@ -635,9 +640,11 @@ void MatchWorkspace::read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaSt
 }
 
 LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches,
-                              int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc)
+                              int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc, const LmSensorTerms* sensor_terms)
 {
   const int n = (int)total;
+  LmSensorTerms terms;
+  if (sensor_terms) terms = *sensor_terms; else lm_sensor_terms_clear(terms);
   const int nchunks = std::max(1, (int)div_up(total, LSB_LM_CHUNK));
   const int pstride = (nchunks + 31) / 32 * 32;
   constexpr size_t kSmem = (size_t)REC_PLANES * LSB_LM_CHUNK * sizeof(double);
@@ -671,7 +678,7 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
   LSB_CUDA(cudaLaunchKernelEx(&cfg, k_lm_solve, (const double*)records.p, rec_stride, n, nchunks, pstride, saturation, start, max_iter, two_d,
-                              (const int*)hist.p, min_matches, lm_state.p, part_a.p, lm_counter.p));
+                              (const int*)hist.p, min_matches, lm_state.p, part_a.p, lm_counter.p, terms));
   lc.add();
   t_lm.end(s);
   d2h_bytes += sizeof(LmState) + 3 * LSB_MATCH_N_STATUS * sizeof(int);

@@ -40,7 +40,7 @@ struct MatchWorkspace {
   // :1098) is taken on the device too: below min_matches the kernel exits at once and the state
   // comes back with term == LSB_LM_SKIPPED (x == x0).
   LmState solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches,
-                int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc);
+                int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc, const LmSensorTerms* sensor_terms = nullptr);
 };
 
 }  // namespace lsb

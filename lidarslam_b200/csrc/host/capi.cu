@@ -2,7 +2,9 @@
 // layer over lsb_slam.  Every entry point catches exceptions and returns an
 // LSB_E_* code with a thread-local message; there is no CPU fallback.
 #include "slam.cuh"
+#include "pcd_io.h"
 #include <cstring>
+#include <ctime>
 #include <string>
 
 using namespace lsb;
@@ -254,5 +256,99 @@ unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h) { return h->Tota
 
 int lsb_set_world_transform_from_guess(lsb_slam* h, const double T[16]) { h->SetWorldTransformFromGuess(FromRowMajor(T)); return LSB_OK; }
 int lsb_clear_maps(lsb_slam* h) { return guarded([&] { h->ClearMaps(); return LSB_OK; }); }
+
+/* ---- external sensor constraints ------------------------------------ */
+int lsb_add_wheel_odom_measurement(lsb_slam* h, const lsb_wheel_odom_measurement* m)
+{
+  if (!m) return LSB_E_INVALID;
+  WheelOdomMeasurement w;
+  w.Time = m->time; w.Distance = m->distance;
+  h->WheelOdomManager.AddMeasurement(w);
+  return LSB_OK;
+}
+int lsb_add_gravity_measurement(lsb_slam* h, const lsb_gravity_measurement* m)
+{
+  if (!m) return LSB_E_INVALID;
+  GravityMeasurement g;
+  g.Time = m->time;
+  for (int i = 0; i < 3; ++i) g.Acceleration[i] = m->acceleration[i];
+  h->ImuManager.AddMeasurement(g);
+  return LSB_OK;
+}
+int lsb_clear_sensor_measurements(lsb_slam* h) { h->WheelOdomManager.Reset(); h->ImuManager.Reset(); return LSB_OK; }
+int lsb_set_wheel_odom_weight(lsb_slam* h, double w) { h->WheelOdomManager.Weight = w; return LSB_OK; }
+double lsb_get_wheel_odom_weight(const lsb_slam* h) { return h->WheelOdomManager.Weight; }
+int lsb_set_gravity_weight(lsb_slam* h, double w) { h->ImuManager.Weight = w; return LSB_OK; }
+double lsb_get_gravity_weight(const lsb_slam* h) { return h->ImuManager.Weight; }
+int lsb_set_sensor_time_offset(lsb_slam* h, double t) { h->WheelOdomManager.TimeOffset = t; h->ImuManager.TimeOffset = t; return LSB_OK; }
+double lsb_get_sensor_time_offset(const lsb_slam* h) { return h->ImuManager.TimeOffset; }
+int lsb_get_gravity_reference(const lsb_slam* h, double g[3]) { for (int i = 0; i < 3; ++i) g[i] = h->ImuManager.GravityRef[i]; return LSB_OK; }
+
+/* ---- map persistence: PCD wire format ----------------------------- */
+static const char* const kMapFileNames[3] = {"edges.pcd", "planes.pcd", "blobs.pcd"};   // Plural(KeypointTypeNames[k]) + ".pcd" (Enums.h:39, Utilities.cxx:95-98)
+
+int lsb_pcd_write(const char* path, const lsb_point* pts, size_t n, int pcd_format)
+{
+  if (!path || (n && !pts)) return LSB_E_INVALID;
+  const int rc = pcd::Write(path, pts, n, pcd_format);
+  if (rc == -1) g_last_error = std::string("cannot write ") + path;
+  return rc;
+}
+long lsb_pcd_read(const char* path, lsb_point* out, long cap)
+{
+  if (!path) return LSB_E_INVALID;
+  std::vector<lsb_point> pts;
+  std::string why;
+  if (pcd::Read(path, pts, &why) != 0) { g_last_error = why; return -1; }
+  if (out && cap > 0 && !pts.empty()) std::memcpy(out, pts.data(), std::min<size_t>(pts.size(), (size_t)cap) * sizeof(lsb_point));
+  return (long)pts.size();
+}
+int lsb_save_maps_to_pcd(lsb_slam* h, const char* file_prefix, int pcd_format, int filtered)
+{
+  if (!file_prefix || pcd_format < 0 || pcd_format > 2) return LSB_E_INVALID;
+  return guarded([&] {
+    LSB_CUDA(cudaSetDevice(h->device));
+    int worst = LSB_OK;
+    std::vector<lsb_point> host;
+    for (int k = 0; k < 3; ++k) {
+      if (!h->P.use_keypoints[k]) continue;                       // Slam.cxx:511
+      RollingGridGpu& m = h->LocalMaps[k];
+      const lsb_point* d = m.pts.p;
+      size_t n = m.n_entries;
+      if (filtered) {                                             // GetMap(k, clean) Slam.cxx:670-677
+        h->tmp_cloud.reserve(std::max<size_t>(m.n_entries, 1), h->stream);
+        n = m.Get(true, h->tmp_cloud.p, h->stream, h->lc);
+        d = h->tmp_cloud.p;
+      }
+      host.resize(n);
+      CopyOut(h, d, n, host.data(), (long)n);
+      const int rc = pcd::Write(std::string(file_prefix) + kMapFileNames[k], host.data(), n, pcd_format);
+      if (rc == -1) { g_last_error = std::string("cannot write ") + file_prefix + kMapFileNames[k]; worst = LSB_E_INVALID; }
+      // rc == -3 (empty map): nothing written, as savePointCloudToPCD (PointCloudStorage.h:91-92)
+    }
+    return worst;
+  });
+}
+int lsb_load_maps_from_pcd(lsb_slam* h, const char* file_prefix, int reset_maps)
+{
+  if (!file_prefix) return LSB_E_INVALID;
+  return guarded([&] {
+    LSB_CUDA(cudaSetDevice(h->device));
+    if (reset_maps) h->ClearMaps();                               // Slam.cxx:526-527
+    int loaded = 0;
+    std::vector<lsb_point> host;
+    for (int k = 0; k < 3; ++k) {
+      std::string why;
+      if (pcd::Read(std::string(file_prefix) + kMapFileNames[k], host, &why) != 0) continue;   // Slam.cxx:531 a missing file is skipped
+      const bool fixed = h->P.map_update == LSB_MAP_NONE || h->P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP;   // Slam.cxx:536
+      h->tmp_cloud.reserve(std::max<size_t>(host.size(), 1), h->stream);
+      if (!host.empty()) LSB_CUDA(cudaMemcpyAsync(h->tmp_cloud.p, host.data(), host.size() * sizeof(lsb_point), cudaMemcpyHostToDevice, h->stream));
+      h->LocalMaps[k].Add(h->tmp_cloud.p, host.size(), fixed, (double)std::time(nullptr), true, h->stream, h->lc);   // Slam.cxx:537
+      LSB_CUDA(cudaStreamSynchronize(h->stream));
+      loaded |= 1 << k;
+    }
+    return loaded;
+  });
+}
 
 }  // extern "C"

@@ -228,6 +228,7 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   LSB_CUDA(cudaEventRecord(ev[1], stream));
   ComputeEgoMotion();
   LSB_CUDA(cudaEventRecord(ev[2], stream));
+  if (WheelOdomManager.CanBeUsed() || ImuManager.CanBeUsed()) ComputeSensorConstraints();   // :256-261
   Localization();
   LSB_CUDA(cudaEventRecord(ev[3], stream));
   // confidence estimators (:272-279)
@@ -476,8 +477,10 @@ void lsb_slam::Localization()
     // the "enough matches" test (:1098-1107) is taken on the device as well: one read-back per ICP iteration
     double x0[6];
     iso_to_xyzrpy(Tworld, x0);
+    // wheel-odometer / gravity blocks, if the managers built one for this frame (:1123-1131)
+    const LmSensorTerms sensorTerms = MakeSensorTerms(WheelOdomManager, ImuManager);
     const LmState st = mw.solve(x0, (int)P.localization_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance,
-                                P.min_nb_matched_keypoints, LocDebug.hist, stream, lc);
+                                P.min_nb_matched_keypoints, LocDebug.hist, stream, lc, &sensorTerms);
     trace.mark("lm", stream);
     SaveDebug(LocDebug);
     Stats.loc_icp_iters++;
@@ -499,6 +502,15 @@ void lsb_slam::Localization()
       break;
     }
   }
+}
+
+//-----------------------------------------------------------------------------
+void lsb_slam::ComputeSensorConstraints()
+{
+  bool warn = false;
+  WheelOdomManager.ComputeWheelAbsoluteConstraint(CurrentTime, &warn);
+  ImuManager.ComputeGravityConstraint(CurrentTime, &warn);
+  if (warn) Warnings |= LSB_W_SENSOR_TIME;
 }
 
 //-----------------------------------------------------------------------------

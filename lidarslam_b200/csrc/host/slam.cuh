@@ -15,6 +15,7 @@
 #include "../common/linalg.h"
 #include "../common/lm_covariance.h"
 #include "../common/motion_limits.h"
+#include "../common/sensor_constraints.h"
 #include "lanes.h"
 
 struct DCloud {
@@ -77,6 +78,8 @@ struct lsb_slam {
   unsigned TotalMatchedKeypoints = 0;
   float OverlapEstimation = -1.f;
   lsb::MotionLimitsState MotionLimits;                                     // Slam.h:660-663
+  lsb::WheelOdometryManager WheelOdomManager;                              // Slam.h:572
+  lsb::ImuManager ImuManager;                                              // Slam.h:578
   lsb_frame_stats Stats;
   int Warnings = 0;
 
@@ -116,6 +119,7 @@ struct lsb_slam {
   bool CheckFrames(int n_frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq);   // Slam.cxx:709-743
   void ExtractKeypoints();                               // :746-810
   void ComputeEgoMotion();                               // :813-972
+  void ComputeSensorConstraints();                       // :346-352
   void Localization();                                   // :975-1175
   void UpdateMapsUsingTworld();                          // :1178-1222
   void LogCurrentFrameState(double time);                // :1225-1264

@@ -99,6 +99,27 @@ ORC_API long orc_get_ke_debug(Slam* h, int dev, int field, float* out, long cap)
 ORC_API int orc_get_frame_stats(const Slam* h, lsb_frame_stats* s) { *s = h->Stats; return 0; }
 ORC_API unsigned orc_get_total_matched_keypoints(const Slam* h) { return h->TotalMatchedKeypoints; }
 ORC_API float orc_get_overlap(const Slam* h) { return h->OverlapEstimation; }
+// external sensor constraints (Slam.cxx:1584-1598, Slam.h:331-339)
+ORC_API int orc_add_wheel_odom_measurement(Slam* h, const lsb_wheel_odom_measurement* m)
+{
+  lsb::WheelOdomMeasurement w;
+  w.Time = m->time; w.Distance = m->distance;
+  h->WheelOdomManager.AddMeasurement(w);
+  return 0;
+}
+ORC_API int orc_add_gravity_measurement(Slam* h, const lsb_gravity_measurement* m)
+{
+  lsb::GravityMeasurement g;
+  g.Time = m->time;
+  for (int i = 0; i < 3; ++i) g.Acceleration[i] = m->acceleration[i];
+  h->ImuManager.AddMeasurement(g);
+  return 0;
+}
+ORC_API int orc_clear_sensor_measurements(Slam* h) { h->WheelOdomManager.Reset(); h->ImuManager.Reset(); return 0; }
+ORC_API int orc_set_wheel_odom_weight(Slam* h, double w) { h->WheelOdomManager.Weight = w; return 0; }
+ORC_API int orc_set_gravity_weight(Slam* h, double w) { h->ImuManager.Weight = w; return 0; }
+ORC_API int orc_set_sensor_time_offset(Slam* h, double t) { h->WheelOdomManager.TimeOffset = t; h->ImuManager.TimeOffset = t; return 0; }
+ORC_API int orc_get_gravity_reference(const Slam* h, double* g) { for (int i = 0; i < 3; ++i) g[i] = h->ImuManager.GravityRef[i]; return 0; }
 ORC_API int orc_get_comply_motion_limits(const Slam* h) { return h->MotionLimits.Comply ? 1 : 0; }
 ORC_API int orc_set_world_transform_from_guess(Slam* h, const double* T) { h->SetWorldTransformFromGuess(FromRowMajor(T)); return 0; }
 ORC_API int orc_clear_maps(Slam* h) { h->ClearMaps(); return 0; }
@@ -246,10 +267,21 @@ ORC_API void orc_lm_terms(const double* A9, const double* P3, const double* X3, 
   }
 }
 // LocalOptimizer::Solve on raw residual records; returns the number of LM iterations.
-ORC_API int orc_lm_solve(const double* A9, const double* P3, const double* X3, const double* w, long n, const double* x0, double sat,
-                         int max_iter, int two_d, int threads, double* x_out, double* cost_out, int* accepted_out, int* term_out)
+// sensor14 (nullable): wheel {use, prev xyz, distance, weight}, gravity {use, ref xyz, current xyz, weight}
+ORC_API int orc_lm_solve_sensors(const double* A9, const double* P3, const double* X3, const double* w, long n, const double* x0, double sat,
+                                 int max_iter, int two_d, int threads, const double* sensor14, double* x_out, double* cost_out,
+                                 int* accepted_out, int* term_out)
 {
   Optimizer opt;
+  if (sensor14) {
+    lsb::LmSensorTerms& c = opt.SensorTerms;
+    c.use_wheel = sensor14[0] != 0.;
+    for (int i = 0; i < 3; ++i) c.wheel_prev[i] = sensor14[1 + i];
+    c.wheel_dist = sensor14[4]; c.wheel_weight = sensor14[5];
+    c.use_gravity = sensor14[6] != 0.;
+    for (int i = 0; i < 3; ++i) { c.g_ref[i] = sensor14[7 + i]; c.g_cur[i] = sensor14[10 + i]; }
+    c.gravity_weight = sensor14[13];
+  }
   opt.TwoDMode = two_d != 0;
   opt.LMMaxIter = (unsigned)max_iter;
   opt.NbThreads = threads > 0 ? threads : 1;
@@ -266,6 +298,11 @@ ORC_API int orc_lm_solve(const double* A9, const double* P3, const double* X3, c
   *accepted_out = opt.State.num_successful;
   *term_out = opt.State.term;
   return opt.State.iter;
+}
+ORC_API int orc_lm_solve(const double* A9, const double* P3, const double* X3, const double* w, long n, const double* x0, double sat,
+                         int max_iter, int two_d, int threads, double* x_out, double* cost_out, int* accepted_out, int* term_out)
+{
+  return orc_lm_solve_sensors(A9, P3, X3, w, n, x0, sat, max_iter, two_d, threads, nullptr, x_out, cost_out, accepted_out, term_out);
 }
 
 }  // extern "C"

@@ -21,6 +21,8 @@ struct Optimizer {
   std::vector<lsb::LmRecord> Records;   // index-aligned with the matcher output, w < 0 = no residual
   lsb::LmState State;
   int NumEvaluations = 0;
+  lsb::LmSensorTerms SensorTerms;        // wheel-odometer / IMU gravity blocks (Slam.cxx:1123-1131), none by default
+  Optimizer() { lsb::lm_sensor_terms_clear(SensorTerms); }
 
   void SetPosePrior(const Iso3d& T) { lsb::iso_to_xyzrpy(T, PoseArray); }   // LocalOptimizer.cxx:44-48
   void AddResiduals(const MatchingResults& m)                                // Slam.cxx:1120-1121
@@ -75,6 +77,7 @@ struct Optimizer {
       Fold32(chunk);
       for (int q = 0; q < LSB_LM_NSUM; ++q) E[q] = (b == 0) ? chunk[0][q] : E[q] + chunk[0][q];
     }
+    if (SensorTerms.use_wheel || SensorTerms.use_gravity) lsb::lm_add_sensor_terms(SensorTerms, pt, E);
   }
 
   // LocalOptimizer::Solve (:74-102). Returns Ceres' num_successful_steps

@@ -73,6 +73,12 @@ int Slam::AddFrames(const std::vector<Frame>& frames)
   auto b = tick(); Stats.ms_extract = ms(a, b);
   ComputeEgoMotion();
   a = tick(); Stats.ms_ego = ms(b, a);
+  if (WheelOdomManager.CanBeUsed() || ImuManager.CanBeUsed()) {   // Slam.cxx:256-261, 346-352
+    bool warn = false;
+    WheelOdomManager.ComputeWheelAbsoluteConstraint(CurrentTime, &warn);
+    ImuManager.ComputeGravityConstraint(CurrentTime, &warn);
+    if (warn) Warnings |= LSB_W_SENSOR_TIME;
+  }
   Localization();
   b = tick(); Stats.ms_localization = ms(a, b);
   if (P.overlap_sampling_ratio > 0) EstimateOverlap();       // :272-276
@@ -286,6 +292,7 @@ void Slam::Localization()
     opt.NbThreads = P.nb_threads;
     opt.Sat = mp.saturation_distance;
     for (int k = 0; k < 3; ++k) opt.AddResiduals(LocalizationMatchingResults[k]);
+    opt.SensorTerms = lsb::MakeSensorTerms(WheelOdomManager, ImuManager);   // Slam.cxx:1123-1131
     const int nSuccessful = opt.Solve();
     Stats.loc_lm_iters += (uint32_t)opt.State.iter;
     Tworld = opt.GetOptimizedPose();

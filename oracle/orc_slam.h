@@ -2,6 +2,7 @@
 // (reference slam_lib/src/Slam.cxx, defaults slam_lib/include/LidarSlam/Slam.h:403-694).
 #pragma once
 #include "../lidarslam_b200/csrc/common/motion_limits.h"
+#include "../lidarslam_b200/csrc/common/sensor_constraints.h"
 #include "orc_extractor.h"
 #include "orc_matcher.h"
 #include "orc_optimizer.h"
@@ -42,6 +43,8 @@ struct Slam {
   unsigned TotalMatchedKeypoints = 0;
   float OverlapEstimation = -1.f;
   lsb::MotionLimitsState MotionLimits;
+  lsb::WheelOdometryManager WheelOdomManager;   // Slam.h:572
+  lsb::ImuManager ImuManager;                   // Slam.h:578
   lsb_frame_stats Stats;
   int Warnings = 0;
 

@@ -79,8 +79,15 @@ def lm_terms(A, P, X, w, x, sat):
     return out
 
 
-def lm_solve(A, P, X, w, x0, sat, max_iter=15, two_d=False, threads=1):
-    """The oracle's LocalOptimizer::Solve on raw residual records."""
+def lm_solve(A, P, X, w, x0, sat, max_iter=15, two_d=False, threads=1, wheel=None, gravity=None):
+    """The oracle's LocalOptimizer::Solve on raw residual records.
+    wheel = (previous position xyz, distance, weight), gravity = (reference dir, current dir, weight): the extra
+    residual blocks of Slam.cxx:1123-1131."""
+    sensor = np.zeros(14)
+    if wheel is not None:
+        sensor[0], sensor[1:4], sensor[4], sensor[5] = 1, wheel[0], wheel[1], wheel[2]
+    if gravity is not None:
+        sensor[6], sensor[7:10], sensor[10:13], sensor[13] = 1, gravity[0], gravity[1], gravity[2]
     A = np.ascontiguousarray(A, dtype=np.float64).reshape(-1, 9)
     P = np.ascontiguousarray(P, dtype=np.float64).reshape(-1, 3)
     X = np.ascontiguousarray(X, dtype=np.float64).reshape(-1, 3)
@@ -88,6 +95,7 @@ def lm_solve(A, P, X, w, x0, sat, max_iter=15, two_d=False, threads=1):
     x0 = np.ascontiguousarray(x0, dtype=np.float64)
     x = np.zeros(6)
     cost, acc, term = C.c_double(), C.c_int(), C.c_int()
-    it = load().orc_lm_solve(capi._ptr(A), capi._ptr(P), capi._ptr(X), capi._ptr(w), C.c_long(len(A)), capi._ptr(x0), C.c_double(sat),
-                             C.c_int(max_iter), C.c_int(1 if two_d else 0), C.c_int(threads), capi._ptr(x), C.byref(cost), C.byref(acc), C.byref(term))
+    it = load().orc_lm_solve_sensors(capi._ptr(A), capi._ptr(P), capi._ptr(X), capi._ptr(w), C.c_long(len(A)), capi._ptr(x0),
+                                     C.c_double(sat), C.c_int(max_iter), C.c_int(1 if two_d else 0), C.c_int(threads), capi._ptr(sensor),
+                                     capi._ptr(x), C.byref(cost), C.byref(acc), C.byref(term))
     return dict(x=x, cost=cost.value, iterations=it, accepted=acc.value, term=term.value)

@@ -124,3 +124,106 @@ def test_dual_sensor_rig(gpu, oracle_lib, synth):
     main = synth.sensor("vlp16", device_id=0)
     sec = synth.sensor("tiny", device_id=1, mount_xyz=(0.6, 0, -0.35), mount_rpy=(0, np.deg2rad(20), np.pi / 2))
     _run(gpu, oracle_lib, synth, [main, sec], 6, cfg)
+
+
+def test_map_persistence_pcd(gpu, oracle_lib, synth, tmp_path):
+    """SURVEY 8f-2 (Slam::SaveMapsToPCD / LoadMapsFromPCD, Slam.cxx:504-543): maps survive the three PCD formats, and a
+    localization-only run (MappingMode::NONE) on the reloaded maps follows the oracle fed with the same files."""
+    from oracle import pcd_py
+
+    def cfg(s):
+        p = s.GetParams()
+        p.use_keypoints[2] = 1
+        s.SetParams(p)
+    sens = synth.sensor("vlp16")
+    g, _ = _run(gpu, oracle_lib, synth, [sens], 6, cfg)
+    maps = [g.GetMap(k, True) for k in capi.KEYPOINT_TYPES]
+    assert all(len(m) for m in maps)
+    for fmt, name in ((capi.PCD_BINARY, "bin_"), (capi.PCD_BINARY_COMPRESSED, "lzf_"), (capi.PCD_ASCII, "txt_")):
+        prefix = str(tmp_path / name)
+        assert g.SaveMapsToPCD(prefix, fmt, filtered=True) == 0
+        for k, kind in enumerate(("edges", "planes", "blobs")):
+            got = pcd_py.read(prefix + kind + ".pcd", capi.POINT_DTYPE)        # files decode with the independent reader
+            if fmt != capi.PCD_ASCII:
+                assert got.tobytes() == maps[k].tobytes()
+            else:
+                assert len(got) == len(maps[k]) and np.abs(got["x"] - maps[k]["x"]).max() < 1e-4
+        g2 = gpu()
+        cfg(g2)
+        assert g2.LoadMapsFromPCD(prefix, True) == 7
+        if fmt != capi.PCD_ASCII:
+            for k in capi.KEYPOINT_TYPES:
+                a = g2.GetMap(k)
+                assert a["time"].min() > 1.6e9                                 # Slam.cxx:537 wall clock
+                a["time"] = maps[k]["time"]
+                assert a.tobytes() == maps[k].tobytes()
+    # a type that is not in use is not saved; a missing file is skipped on load
+    p = g.GetParams()
+    p.use_keypoints[2] = 0
+    g.SetParams(p)
+    prefix = str(tmp_path / "two_")
+    assert g.SaveMapsToPCD(prefix, capi.PCD_BINARY, filtered=False) == 0
+    assert not (tmp_path / "two_blobs.pcd").exists()
+    g3 = gpu()
+    assert g3.LoadMapsFromPCD(prefix, True) == 3 and len(g3.GetMap(2)) == 0
+
+    # localization only on the reloaded maps
+    prefix = str(tmp_path / "bin_")
+    T5, _ = g.GetWorldTransform()
+    gl, ol = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
+    for s in (gl, ol):
+        p = s.GetParams()
+        p.use_keypoints[2] = 1
+        p.map_update = 0                                                       # MappingMode::NONE
+        s.SetParams(p)
+    assert gl.LoadMapsFromPCD(prefix, True) == 7
+    for k, kind in enumerate(("edges", "planes", "blobs")):
+        ol.MapLoadPoints(k, pcd_py.read(prefix + kind + ".pcd", capi.POINT_DTYPE), fixed=True)
+    for s in (gl, ol):
+        s.SetWorldTransformFromGuess(T5)
+    seq = synth.Sequence(scene_seed=1234)
+    n_map = [len(gl.GetMap(k)) for k in capi.KEYPOINT_TYPES]
+    for i in range(6, 10):
+        pts, gt, stamp = seq.frame(sens, i)
+        assert gl.AddFrame(pts, stamp, i + 1) == ol.AddFrame(pts, stamp, i + 1)
+        Tg, _ = gl.GetWorldTransform()
+        To, _ = ol.GetWorldTransform()
+        assert np.abs(Tg - To).max() <= 1e-6, i
+        for k in capi.KEYPOINT_TYPES:
+            assert gl.GetKeypoints(k).tobytes() == ol.GetKeypoints(k).tobytes()
+    assert [len(gl.GetMap(k)) for k in capi.KEYPOINT_TYPES] == n_map           # the map did not change
+    for k in capi.KEYPOINT_TYPES:
+        assert (gl.GetMap(k)["label"] == 1).all()                              # loaded as fixed points (Slam.cxx:536)
+
+
+def test_sensor_constraints(gpu, oracle_lib, synth):
+    """wheel-odometer + IMU gravity residual blocks inside the device LM loop (lm_add_sensor_terms in
+    k_lm_solve) == the oracle, frame by frame; also with a time offset and in 2-D mode."""
+    import _sensors
+    sens = synth.sensor("vlp16")
+    for two_d, offset in ((0, 0.0), (1, 0.02)):
+        def cfg(s):
+            p = s.GetParams()
+            p.two_d_mode = two_d
+            s.SetParams(p)
+            s.SetWheelOdomWeight(1e3)
+            s.SetGravityWeight(5e2)
+            s.SetSensorTimeOffset(offset)
+            _sensors.feed([s], synth.Sequence(scene_seed=1234), sens, 7, noise=1e-3)
+        g, o = _run(gpu, oracle_lib, synth, [sens], 8, cfg)       # frame 7 lies outside the measurements: LSB_W_SENSOR_TIME on both
+        assert np.array_equal(g.GetGravityReference(), o.GetGravityReference()) and abs(np.linalg.norm(g.GetGravityReference()) - 1) < 1e-12
+        assert np.array_equal(g.GetTransformCovariance(), o.GetTransformCovariance())
+    # the blocks change the solution (against a run without sensors)
+    free = gpu()
+    seq = synth.Sequence(scene_seed=1234)
+    for i in range(4):
+        pts, _, stamp = seq.frame(sens, i)
+        free.AddFrame(pts, stamp, i + 1)
+    g2 = gpu()
+    g2.SetWheelOdomWeight(1e3)
+    _sensors.feed([g2], synth.Sequence(scene_seed=1234), sens, 7)
+    seq = synth.Sequence(scene_seed=1234)
+    for i in range(4):
+        pts, _, stamp = seq.frame(sens, i)
+        g2.AddFrame(pts, stamp, i + 1)
+    assert np.abs(g2.GetWorldTransform()[0] - free.GetWorldTransform()[0]).max() > 1e-8

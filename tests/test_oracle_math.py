@@ -247,3 +247,45 @@ def test_detmath_exp(oracle_lib):
     got = oracle_lib.detmath(6, xs.astype(np.float64)).astype(np.float32)
     assert np.array_equal(got, np.exp(xs.astype(np.float64)).astype(np.float32))
     assert oracle_lib.detmath(5, np.array([0.0]))[0] == 1.0 and oracle_lib.detmath(5, np.array([-800.0]))[0] == 0.0
+
+
+def test_lm_sensor_terms_against_scipy(oracle_lib):
+    """the wheel-odometer block r = |t - prev| - dist (CeresCostFunctions.h:267-296) and the IMU gravity
+    block r = R g_cur - g_ref (:311-341), both under ScaledLoss(NULL, weight), move the solution exactly as stacking
+    sqrt(weight) * r under the keypoint residuals does in scipy."""
+    from scipy.optimize import least_squares
+    rng = np.random.default_rng(8)
+    x_true = np.array([0.3, -0.4, 0.2, 0.02, -0.03, 0.05])
+    A, P, X, w = _lm_problem(rng, 400, x_true, noise=0.02)
+    prev, dist, ww = np.array([-1.0, 0.5, 0.1]), 1.9, 50.0
+    g_cur = np.array([0.05, -0.02, -1.0])
+    g_cur /= np.linalg.norm(g_cur)
+    g_ref, wg = np.array([0.0, 0.0, -1.0]), 200.0
+
+    def resid(xx, use_w, use_g):
+        R = _euler_zyx(*xx[3:])
+        d = X @ R.T + xx[:3] - P
+        r = [(np.sqrt(w)[:, None] * np.einsum("nij,nj->ni", A, d)).ravel()]
+        if use_w:
+            r.append([np.sqrt(ww) * (np.linalg.norm(xx[:3] - prev) - dist)])
+        if use_g:
+            r.append(np.sqrt(wg) * (R @ g_cur - g_ref))
+        return np.concatenate(r)
+
+    base = oracle_lib.lm_solve(A, P, X, w, np.zeros(6), 1e3, max_iter=50)["x"]
+    for use_w, use_g in ((True, False), (False, True), (True, True)):
+        ref = least_squares(resid, np.zeros(6), args=(use_w, use_g), method="lm", xtol=1e-14, ftol=1e-14, gtol=1e-14)
+        got = oracle_lib.lm_solve(A, P, X, w, np.zeros(6), 1e3, max_iter=50, wheel=(prev, dist, ww) if use_w else None,
+                                  gravity=(g_ref, g_cur, wg) if use_g else None)
+        assert got["term"] in (1, 2, 3)
+        assert np.abs(got["x"] - ref.x).max() < 1e-5, (use_w, use_g, got["x"] - ref.x)   # function tolerance 1e-6 stops in a flat valley
+        assert np.abs(got["x"] - base).max() > 1e-4            # the constraint did pull the solution
+        # cost of the extra blocks alone, at a fixed point (max_iter = 0: one evaluation, no step)
+        c1 = oracle_lib.lm_solve(A, P, X, w, x_true, 1e3, max_iter=0, wheel=(prev, dist, ww) if use_w else None,
+                                 gravity=(g_ref, g_cur, wg) if use_g else None)["cost"]
+        c0 = oracle_lib.lm_solve(A, P, X, w, x_true, 1e3, max_iter=0)["cost"]
+        extra = 0.5 * (resid(x_true, use_w, use_g)[3 * len(A):] ** 2).sum()
+        assert abs((c1 - c0) - extra) < 1e-12 * extra
+    # degenerate odometer block: |t - prev|^2 < 1e-6 counts as zero motion with zero derivative
+    got = oracle_lib.lm_solve(A[:0], P[:0], X[:0], w[:0], np.array([1e-4, 0, 0, 0, 0, 0.]), 1.0, max_iter=5, wheel=(np.zeros(3), 0.5, 1.0))
+    assert np.array_equal(got["x"], [1e-4, 0, 0, 0, 0, 0]) and got["cost"] == 0.5 * 0.25

@@ -108,3 +108,41 @@ def test_overlap_estimator_against_numpy(oracle_lib, synth):
             best = np.maximum(best, np.exp(-(d.astype(np.float32) ** 2) / (2 * thr)).astype(np.float32))
         assert abs(ov - best.mean(dtype=np.float64)) < 2e-6
         assert 0.3 < ov < 1.0
+
+
+def test_sensor_constraints(oracle_lib, synth):
+    """SURVEY 8f-3 (SensorConstraints.cxx, Slam.cxx:256-261, 346-352, 1123-1131): wheel-odometer and IMU gravity blocks
+    in the localization solve; time mismatch warning; gravity reference = mean of the fullest direction bin."""
+    import _sensors
+    sens = synth.sensor("vlp16")
+    n = 8
+    free, cons = (oracle_lib.Oracle(nb_threads=oracle_lib.max_threads()) for _ in range(2))
+    cons.SetWheelOdomWeight(1e4)
+    cons.SetGravityWeight(1e4)
+    wheel, grav = _sensors.feed([cons], synth.Sequence(), sens, n, noise=1e-3)
+    seq = synth.Sequence()
+    T0 = None
+    for i in range(n):
+        pts, Tgt, stamp = seq.frame(sens, i)
+        rf, rc = free.AddFrame(pts, stamp, i + 1), cons.AddFrame(pts, stamp, i + 1)
+        assert rf == rc, (i, rf, rc)
+        T0 = Tgt if i == 0 else T0
+        Tf, _ = free.GetWorldTransform()
+        Tc, _ = cons.GetWorldTransform()
+        gt = _rel(T0, Tgt)
+        if i >= 2:
+            # the heavily weighted odometer block pins |t| to the measured chord (1 mm noise), the free run only to ICP accuracy
+            assert abs(np.linalg.norm(Tc[:3, 3]) - (wheel[i + 1][1] - wheel[1][1])) < 5e-3
+            assert np.abs(Tc - Tf).max() > 1e-7               # the blocks did enter the solve
+            assert np.linalg.norm(Tc[:3, 3] - gt[:3, 3]) < 0.10
+    g = cons.GetGravityReference()
+    dirs = np.array([a / np.linalg.norm(a) for _, a in grav])
+    assert abs(np.linalg.norm(g) - 1) < 1e-12 and np.abs(g - dirs.mean(0) / np.linalg.norm(dirs.mean(0))).max() < 2e-2
+    assert (free.GetGravityReference() == 0).all()
+    # stamps outside the measurements: warning, no constraint, the frame is processed as without sensors
+    pts, _, stamp = seq.frame(sens, n)
+    assert cons.AddFrame(pts, stamp, n + 1) & 256             # LSB_W_SENSOR_TIME
+    # ClearSensorMeasurements: managers empty again
+    cons.ClearSensorMeasurements()
+    pts, _, stamp = seq.frame(sens, n + 1)
+    assert cons.AddFrame(pts, stamp, n + 2) == 0
