@@ -262,6 +262,31 @@ LSB_API int lsb_set_sensor_time_offset(lsb_slam* h, double seconds);            
 LSB_API double lsb_get_sensor_time_offset(const lsb_slam* h);                                    /* Slam.h:339 */
 LSB_API int lsb_get_gravity_reference(const lsb_slam* h, double g[3]);                           /* ImuManager::GetGravityRef SensorConstraints.h:103 */
 
+/* ---- input adaptors on the device: raw driver clouds -> LidarPoint frames -------- */
+/* velodyne_pcl::PointXYZIRT (VelodyneToLidarNode.h:37), 32 B */
+typedef struct lsb_velodyne_point { float x, y, z, _pad0; float intensity; uint16_t ring; uint16_t _pad1; float time; float _pad2; } lsb_velodyne_point;
+/* pcl::PointXYZI (RobosenseToLidarNode.h:40), 32 B */
+typedef struct lsb_xyzi_point { float x, y, z, _pad0; float intensity; float _pad1[3]; } lsb_xyzi_point;
+/* node parameters (VelodyneToLidarNode.h:63-75, RobosenseToLidarNode.h:62-77) */
+typedef struct lsb_conversion_params {
+  const int32_t* laser_id_mapping;   /* NULL / 0: identity (Robosense with 16 rings: the RS16 table) */
+  int32_t n_laser_id_mapping;
+  int32_t device_id;                 /* 0 */
+  double rpm;                        /* 600 */
+  int32_t timestamp_first_packet;    /* 0: header.stamp is the last packet */
+} lsb_conversion_params;
+/* VelodyneToLidarNode::Callback (VelodyneToLidarNode.cxx:50-111): laser-id remap, device id, and - when the time field is
+ * not set (last - first <= 1e-8) - point times from the azimuth advancement (Utilities.h:58-108).  The converted frame
+ * stays on the device for lsb_add_converted_frame; `out` (host, may be NULL) receives at most `cap` points.
+ * Returns the number of points, LSB_W_FRAME_IGNORED-like 0 for an empty cloud. */
+LSB_API long lsb_convert_velodyne(lsb_slam* h, const lsb_velodyne_point* pts, size_t n, const lsb_conversion_params* p, lsb_point* out, long cap);
+/* RobosenseToLidarNode::Callback (RobosenseToLidarNode.cxx:58-137): organised cloud (width x height, ring-major); drops
+ * non-finite points and dual returns identical to the previous kept point; laser id from the row; time from the column. */
+LSB_API long lsb_convert_robosense(lsb_slam* h, const lsb_xyzi_point* pts, uint32_t width, uint32_t height, const lsb_conversion_params* p,
+                                   lsb_point* out, long cap);
+/* Slam::AddFrame on the frame left on the device by the last lsb_convert_* call (no host round trip). */
+LSB_API int lsb_add_converted_frame(lsb_slam* h, uint64_t stamp_us, uint32_t seq);
+
 /* ---- map persistence: PCD wire format (pcl::io::savePCDFile* / loadPCDFile restated, no PCL) ---- */
 enum { LSB_PCD_ASCII = 0, LSB_PCD_BINARY = 1, LSB_PCD_BINARY_COMPRESSED = 2 };                    /* PointCloudStorage.h:60-65 PCDFormat */
 /* Slam::SaveMapsToPCD (Slam.cxx:504-517): writes <prefix>{edges,planes,blobs}.pcd for the keypoint types in use;

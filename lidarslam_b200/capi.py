@@ -17,6 +17,12 @@ POINT_DTYPE = np.dtype(
      ("laser_id", "<u2"), ("device_id", "u1"), ("label", "u1")], align=True)
 assert POINT_DTYPE.itemsize == 32
 
+# raw driver clouds of the input adaptors (reference ros_wrapping/lidar_conversions)
+VELODYNE_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("_pad0", "<f4"), ("intensity", "<f4"), ("ring", "<u2"),
+                           ("_pad1", "<u2"), ("time", "<f4"), ("_pad2", "<f4")])      # velodyne_pcl::PointXYZIRT
+XYZI_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("_pad0", "<f4"), ("intensity", "<f4"), ("_pad1", "<f4", (3,))])  # pcl::PointXYZI
+assert VELODYNE_DTYPE.itemsize == 32 and XYZI_DTYPE.itemsize == 32
+
 EDGE, PLANE, BLOB = 0, 1, 2
 PCD_ASCII, PCD_BINARY, PCD_BINARY_COMPRESSED = 0, 1, 2   # reference PointCloudStorage.h:60-65
 KEYPOINT_TYPES = (EDGE, PLANE, BLOB)
@@ -61,6 +67,11 @@ class Params(C.Structure):
                 ("map_update", C.c_int32), ("max_extrapolation_ratio", C.c_double),
                 ("min_nb_matched_keypoints", C.c_uint32), ("overlap_sampling_ratio", C.c_float),
                 ("time_window_duration", C.c_float), ("velocity_limits", C.c_float * 2), ("acceleration_limits", C.c_float * 2)]
+
+
+class ConversionParams(C.Structure):
+    _fields_ = [("laser_id_mapping", C.c_void_p), ("n_laser_id_mapping", C.c_int32), ("device_id", C.c_int32), ("rpm", C.c_double),
+                ("timestamp_first_packet", C.c_int32)]
 
 
 class RegistrationError(C.Structure):
@@ -237,6 +248,35 @@ class CApi:
 
     def GetMap(self, k, clean=False):
         return self._cloud("get_map", C.c_int(k), C.c_int(1 if clean else 0))
+
+    # ---- input adaptors (reference ros_wrapping/lidar_conversions) ----------
+    def _conversion(self, name, pts, extra, laser_id_mapping, device_id, rpm, timestamp_first_packet):
+        m = np.ascontiguousarray(laser_id_mapping, dtype=np.int32) if laser_id_mapping is not None else None
+        cp = ConversionParams(_ptr(m) if m is not None else None, len(m) if m is not None else 0, device_id, rpm, 1 if timestamp_first_packet else 0)
+        f = self._f(name)
+        f.restype = C.c_long
+        n = f(self.h, _ptr(pts), *extra, C.byref(cp), None, C.c_long(0))
+        if n < 0:
+            self._check(int(n))
+        out = np.zeros(int(n), dtype=POINT_DTYPE)
+        if n:
+            f(self.h, _ptr(pts), *extra, C.byref(cp), _ptr(out), C.c_long(n))
+        return out
+
+    def ConvertVelodyne(self, pts, laser_id_mapping=None, device_id=0, rpm=600.0, timestamp_first_packet=False):
+        """VelodyneToLidarNode::Callback; the converted frame also stays inside the handle for AddConvertedFrame."""
+        pts = np.ascontiguousarray(pts)
+        assert pts.dtype == VELODYNE_DTYPE
+        return self._conversion("convert_velodyne", pts, (C.c_size_t(len(pts)),), laser_id_mapping, device_id, rpm, timestamp_first_packet)
+
+    def ConvertRobosense(self, pts, width, height, laser_id_mapping=None, device_id=0, rpm=600.0):
+        """RobosenseToLidarNode::Callback on an organised width x height cloud (ring-major)."""
+        pts = np.ascontiguousarray(pts)
+        assert pts.dtype == XYZI_DTYPE and len(pts) == width * height
+        return self._conversion("convert_robosense", pts, (C.c_uint32(width), C.c_uint32(height)), laser_id_mapping, device_id, rpm, False)
+
+    def AddConvertedFrame(self, stamp_us, seq=0):
+        return self._check(self._f("add_converted_frame")(self.h, C.c_uint64(stamp_us), C.c_uint32(seq)))
 
     # ---- external sensor constraints (reference Slam.h:331-344) ------------
     def AddWheelOdomMeasurement(self, time, distance):

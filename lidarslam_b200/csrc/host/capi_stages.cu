@@ -55,6 +55,56 @@ int lsb_map_load_points(lsb_slam* h, int type, const lsb_point* pts, long n, int
   });
 }
 
+static lsb_conversion_params ConversionDefaults(const lsb_conversion_params* p)
+{
+  lsb_conversion_params d;
+  d.laser_id_mapping = nullptr; d.n_laser_id_mapping = 0; d.device_id = 0; d.rpm = 600.; d.timestamp_first_packet = 0;   // VelodyneToLidarNode.h:69-75
+  return p ? *p : d;
+}
+static long ConvertedOut(lsb_slam* h, lsb_point* out, long cap)
+{
+  const size_t n = h->conv.n_out;
+  if (out && n && cap > 0) LSB_CUDA(cudaMemcpyAsync(out, h->conv.out.p, std::min<size_t>(n, (size_t)cap) * sizeof(lsb_point), cudaMemcpyDeviceToHost, h->stream));
+  LSB_CUDA(cudaStreamSynchronize(h->stream));
+  return (long)n;
+}
+long lsb_convert_velodyne(lsb_slam* h, const lsb_velodyne_point* pts, size_t n, const lsb_conversion_params* p, lsb_point* out, long cap)
+{
+  if (n && !pts) return LSB_E_INVALID;
+  const lsb_conversion_params cp = ConversionDefaults(p);
+  if (!(cp.rpm > 0.)) return LSB_E_INVALID;
+  long r = 0;
+  const int rc = guarded([&] {
+    LSB_CUDA(cudaSetDevice(h->device));
+    h->conv.velodyne(pts, n, cp, h->stream, h->lc);
+    r = ConvertedOut(h, out, cap);
+    return LSB_OK;
+  });
+  return rc < 0 ? rc : r;
+}
+long lsb_convert_robosense(lsb_slam* h, const lsb_xyzi_point* pts, uint32_t width, uint32_t height, const lsb_conversion_params* p, lsb_point* out, long cap)
+{
+  if ((size_t)width * height && !pts) return LSB_E_INVALID;
+  const lsb_conversion_params cp = ConversionDefaults(p);
+  if (!(cp.rpm > 0.)) return LSB_E_INVALID;
+  long r = 0;
+  const int rc = guarded([&] {
+    LSB_CUDA(cudaSetDevice(h->device));
+    h->conv.robosense(pts, width, height, cp, h->stream, h->lc);
+    r = ConvertedOut(h, out, cap);
+    return LSB_OK;
+  });
+  return rc < 0 ? rc : r;
+}
+int lsb_add_converted_frame(lsb_slam* h, uint64_t stamp_us, uint32_t seq)
+{
+  return guarded([&] {
+    const lsb_point* frame = h->conv.out.p;
+    const size_t n = h->conv.n_out;
+    return h->AddFrames(1, &frame, &n, &stamp_us, &seq, true);
+  });
+}
+
 int lsb_extract_keypoints(lsb_slam* h, const lsb_point* pts, size_t n, uint8_t* label_out, uint32_t counts[3])
 {
   return guarded([&] {

@@ -12,6 +12,7 @@
 #include "../cuda/knn.cuh"
 #include "../cuda/match.cuh"
 #include "../cuda/map.cuh"
+#include "../cuda/convert.cuh"
 #include "../common/linalg.h"
 #include "../common/lm_covariance.h"
 #include "../common/motion_limits.h"
@@ -84,6 +85,7 @@ struct lsb_slam {
   int Warnings = 0;
 
   // scratch
+  lsb::ConvertWorkspace conv;                                              // driver-cloud adaptors
   lsb::DevBuf<lsb_point> tmp_cloud;
   lsb::DevBuf<unsigned long long> d_minmax;
   lsb::PinnedBuf<unsigned long long> h_minmax;

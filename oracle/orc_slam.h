@@ -45,6 +45,7 @@ struct Slam {
   lsb::MotionLimitsState MotionLimits;
   lsb::WheelOdometryManager WheelOdomManager;   // Slam.h:572
   lsb::ImuManager ImuManager;                   // Slam.h:578
+  std::vector<lsb_point> Converted;             // last frame produced by orc_convert_* (lidar_conversions nodes)
   lsb_frame_stats Stats;
   int Warnings = 0;
 
