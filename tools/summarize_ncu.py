@@ -1,5 +1,5 @@
 """Prints the metrics DESIGN.md / profiles/ quote from an `ncu --set full` report:
-   python tools/summarize_ncu.py gpurun_out/prof.ncu-rep > profiles/r01_ncu_full_summary.txt"""
+   python tools/summarize_ncu.py gpurun_out/prof.ncu-rep|raw.csv [instances per (kernel, grid)] > profiles/r01_ncu_full_summary.txt"""
 import csv
 import io
 import subprocess
@@ -22,7 +22,10 @@ WANT = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
 
 
 def main(path, per_kernel=1):
-    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if path.endswith(".csv"):      # already exported on the GPU box: ncu -i rep --page raw --csv > file.csv
+        raw = open(path).read()
+    else:
+        raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
     name_i = hdr.index("Kernel Name")
