@@ -12,6 +12,7 @@
 // sphere of the tentative k-th distance).
 #include "knn.cuh"
 #include <cub/cub.cuh>
+#include <thrust/iterator/reverse_iterator.h>
 #include <cfloat>
 #include <climits>
 #include <algorithm>
@@ -81,18 +82,19 @@ __global__ void k_cell_gather(const lsb_point* __restrict__ pts, int m, const ui
   sorted[i] = make_float4(p.x, p.y, p.z, __int_as_float((int)o));
 }
 
-// cell_start[c] = number of points whose cell key is < c  (c in [0, ncells])
-__global__ void k_cell_start(const uint32_t* __restrict__ key_sorted, int m, int ncells, uint32_t* __restrict__ cell_start)
+// cell_start[c] = number of points whose cell key is < c  (c in [0, ncells]) = the position of the first
+// point of the first non-empty cell >= c.  Two steps instead of a binary search per cell (85 % of the
+// 2.5 M cells of an OS-128 sub-map are empty): every first point of a run of equal keys marks its cell,
+// then a suffix-min scan fills the empty cells with the start of the next non-empty one.
+__global__ void k_cell_mark(const uint32_t* __restrict__ key_sorted, int m, int ncells, uint32_t* __restrict__ mark)
 {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c > ncells) return;
-  int lo = 0, hi = m;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (key_sorted[mid] < (uint32_t)c) lo = mid + 1; else hi = mid;
-  }
-  cell_start[c] = (uint32_t)lo;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) mark[ncells] = (uint32_t)m;
+  if (i >= m) return;
+  const uint32_t k = key_sorted[i];
+  if (i == 0 || key_sorted[i - 1] != k) mark[k] = (uint32_t)i;
 }
+struct MinU32 { __host__ __device__ __forceinline__ uint32_t operator()(uint32_t a, uint32_t b) const { return a < b ? a : b; } };
 
 // ------------------------------------------------------------------ search ---
 // A candidate is one 64-bit key: (bits of d2) << 32 | cloud index.  d2 >= +0, so the unsigned
@@ -750,7 +752,19 @@ void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float
   size_t tb = cub_tmp.cap;
   LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, key_a.p, key_b.p, idx_a.p, idx_b.p, M, 0, bits, s)); lc.add(3);
   k_cell_gather<<<G, TPB, 0, s>>>(d_cloud, M, idx_b.p, sorted.p); LSB_LAUNCH_CHECK(); lc.add();
-  k_cell_start<<<div_up((size_t)ncells + 1, TPB), TPB, 0, s>>>(key_b.p, M, ncells, cell_start.p); LSB_LAUNCH_CHECK(); lc.add();
+  {
+    const int nc1 = ncells + 1;
+    cell_mark.reserve((size_t)nc1, s);
+    LSB_CUDA(cudaMemsetAsync(cell_mark.p, 0xff, (size_t)nc1 * sizeof(uint32_t), s));
+    k_cell_mark<<<G, TPB, 0, s>>>(key_b.p, M, ncells, cell_mark.p); LSB_LAUNCH_CHECK(); lc.add();
+    auto in = thrust::make_reverse_iterator(cell_mark.p + nc1);
+    auto out = thrust::make_reverse_iterator(cell_start.p + nc1);
+    size_t tb2 = 0;
+    cub::DeviceScan::InclusiveScan(nullptr, tb2, in, out, MinU32(), nc1, s);
+    cub_tmp.reserve(tb2 + 256, s);
+    tb2 = cub_tmp.cap;
+    LSB_CUDA(cub::DeviceScan::InclusiveScan(cub_tmp.p, tb2, in, out, MinU32(), nc1, s)); lc.add(2);
+  }
 }
 
 void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t* d_idx, float* d_d2, int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc) const

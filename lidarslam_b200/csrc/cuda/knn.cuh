@@ -25,6 +25,7 @@ struct KnnGrid {
   DevBuf<uint32_t> key_a, key_b, idx_a, idx_b;
   DevBuf<float4> sorted;          // cell-major points: (x, y, z, bits of the cloud index)
   DevBuf<uint32_t> cell_start;    // [ncells + 1] prefix offsets into sorted
+  DevBuf<uint32_t> cell_mark;     // [ncells + 1] first point of each non-empty cell, UINT_MAX elsewhere (input of the suffix-min scan)
   DevBuf<unsigned char> cub_tmp;
   mutable DevBuf<int32_t> unres_list;    // queries handed to the brute-force kernel
   mutable DevBuf<unsigned> unres_count;  // [4]: unsettled count, cursor, brute-force count, cursor

@@ -389,7 +389,11 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   const unsigned G = div_up(n, TPB);
   k_point_keys<<<G, TPB, 0, s>>>(d_cloud, N, g, nk_a.p, ni_a.p); LSB_LAUNCH_CHECK(); lc.add();
   size_t tb = cub_tmp.cap;
-  LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, nk_a.p, nk_b.p, ni_a.p, ni_b.p, N, 0, 64, s)); lc.add(9);
+  // significant bits only: the outer index is < G^3 and INVALID_KEY (all ones) still sorts last as long as 2^bits > G^3
+  int outer_bits = 1;
+  while ((1ll << outer_bits) <= (long long)g.G * g.G * g.G) ++outer_bits;
+  const int end_bit = std::min(64, 32 + outer_bits);
+  LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, nk_a.p, nk_b.p, ni_a.p, ni_b.p, N, 0, end_bit, s)); lc.add(2 + (end_bit + 7) / 8);
   LSB_CUDA(cudaMemsetAsync(d_info.p, 0, 8 * sizeof(uint32_t), s));
   k_apply_segments<<<G, TPB, 0, s>>>(nk_b.p, ni_b.p, N, d_cloud, keys.p, pts.p, counts.p, (int)n_entries, g, Sampling, fixed ? 1u : 0u,
                                      currentTime, flags.p, pts_b.p, counts_b.p, d_info.p);
