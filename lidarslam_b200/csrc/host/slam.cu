@@ -112,10 +112,32 @@ void lsb_slam::Fork()
   for (auto& t : tstream) LSB_CUDA(cudaStreamWaitEvent(t, ev_fork, 0));
 }
 
+// Host lanes cost two extra busy host threads per handle in flight.  They pay while every handle has three cores to
+// itself; beyond that (many sequences on one GPU, or many ranks on one host: torchrun exports LOCAL_WORLD_SIZE) the
+// spinning helpers steal the cores the other handles' callers need (8 sequences on 16 cores: 298 frames/s with lanes,
+// 856 without), so the types are then enqueued from the caller's thread.
+static std::atomic<int> g_handles_in_flight{0};
+static int HostThreadBudget()
+{
+  static const int budget = [] {
+    int hw = (int)std::thread::hardware_concurrency();
+    if (hw <= 0) hw = 4;
+    int procs = 1;
+    if (const char* e = std::getenv("LOCAL_WORLD_SIZE")) procs = std::max(1, std::atoi(e));
+    return std::max(1, hw / procs);
+  }();
+  return budget;
+}
+struct InFlightGuard {
+  InFlightGuard() { g_handles_in_flight.fetch_add(1, std::memory_order_relaxed); }
+  ~InFlightGuard() { g_handles_in_flight.fetch_sub(1, std::memory_order_relaxed); }
+};
+
 void lsb_slam::ForEachType(const std::function<void(int)>& fn)
 {
   Fork();
-  if (serial_types || !use_lanes) {
+  const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
+  if (serial_types || !use_lanes || crowded) {
     for (int k : kTypeOrder) fn(k);
   } else {
     if (!lanes) lanes.reset(new TypeLanes(device));
@@ -186,6 +208,7 @@ ExtractorGpu& lsb_slam::Extractor(int dev)
 int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq, bool on_device)
 {
   LSB_CUDA(cudaSetDevice(device));
+  InFlightGuard inflight;
   Warnings = 0;
   if (!CheckFrames(n_frames, n, stamp_us, seq)) return LSB_W_FRAME_IGNORED;
   const unsigned launches0 = lc.n;
