@@ -217,6 +217,16 @@ class CApi:
         self._check(self._f("get_world_transform")(self.h, _ptr(T), C.byref(t)))
         return T.reshape(4, 4), t.value
 
+    def GetTrajectory(self):
+        """Slam::GetTrajectory: (count, poses [n, 4, 4], times [n]) of the logged states."""
+        f = self._f("get_trajectory")
+        f.restype = C.c_long
+        n = int(f(self.h, None, None, C.c_long(0)))
+        T, t = np.zeros((n, 16)), np.zeros(n)
+        if n:
+            f(self.h, _ptr(T), _ptr(t), C.c_long(n))
+        return n, T.reshape(n, 4, 4), t
+
     def GetRelativeTransform(self):
         T = np.zeros(16)
         self._check(self._f("get_relative_transform")(self.h, _ptr(T)))

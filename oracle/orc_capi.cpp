@@ -69,6 +69,15 @@ ORC_API int orc_get_world_transform(const Slam* h, double* T, double* time)
   if (time) *time = h->LogTrajectory.back().time;
   return 0;
 }
+ORC_API long orc_get_trajectory(const Slam* h, double* Ts, double* times, long cap)   // Slam::GetTrajectory
+{
+  const long n = (long)h->LogTrajectory.size();
+  for (long i = 0; i < n && i < cap; ++i) {
+    if (Ts) ToRowMajor(h->LogTrajectory[i].T, Ts + 16 * i);
+    if (times) times[i] = h->LogTrajectory[i].time;
+  }
+  return n;
+}
 ORC_API int orc_get_relative_transform(const Slam* h, double* T) { ToRowMajor(h->Trelative, T); return 0; }
 ORC_API int orc_get_registration_error(const Slam* h, lsb_registration_error* e) { *e = h->LocalizationUncertainty; return 0; }
 ORC_API int orc_get_covariance(const Slam* h, double* c) { std::memcpy(c, h->LocalizationUncertainty.covariance, 36 * sizeof(double)); return 0; }

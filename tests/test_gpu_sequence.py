@@ -272,3 +272,25 @@ def test_vls128_pandar64_rig_dense_maps(gpu, oracle_lib, synth):
     g, o = _run(gpu, oracle_lib, synth, [main, sec], 4, cfg, check_maps_every=3)
     st = g.GetFrameStats()
     assert st.n_points == 128 * 1800 + 64 * 1800 and st.is_keyframe == 1
+
+
+def test_os128_long_sequence_drift(gpu, oracle_lib, synth):
+    """North star: per-frame pose within 1e-6 m / 1e-6 rad after each ICP solve and trajectory drift within 1 mm over the
+    sequence, on the headline configuration (OS-128, blobs, refined undistortion, overlap estimator on) over 40 frames."""
+    def cfg(s):
+        p = s.GetParams()
+        p.use_keypoints[2] = 1
+        p.overlap_sampling_ratio = 0.33
+        p.logging_timeout = 1e3                                # keep every state in the trajectory log (Slam.h LoggingTimeout)
+        s.SetParams(p)
+    g, o = _run(gpu, oracle_lib, synth, [synth.sensor("os128")], 40, cfg, check_maps_every=13)
+    n, Tg, tg = g.GetTrajectory()
+    m, To, to = o.GetTrajectory()
+    assert n == m == 40 and np.array_equal(tg, to)
+    assert np.abs(Tg - To).max() <= 1e-6                      # whole logged trajectory, not only the last pose
+    seq = synth.Sequence(scene_seed=1234)
+    sens = synth.sensor("os128")
+    G0 = seq.frame(sens, 0)[1]
+    G39 = seq.frame(sens, 39)[1]
+    rel = np.linalg.inv(G0) @ G39
+    assert np.linalg.norm(Tg[-1][:3, 3] - rel[:3, 3]) < 0.15   # and it tracks the ground truth (31 m travelled)
