@@ -360,7 +360,12 @@ __global__ void k_scatter_keypoints(const lsb_point* __restrict__ pts, const uin
       mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, off));
       mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, off));
     }
-    if ((threadIdx.x & 31) == 0 && mn != ~0ull) { atomicMin(tmm + 2 * k, mn); atomicMax(tmm + 2 * k + 1, mx); }
+    // the bounds only tighten: a (possibly stale) read that already beats this warp's value makes the atomic pointless,
+    // and a stale read can only be looser than the truth, so no needed update is ever skipped
+    if ((threadIdx.x & 31) == 0 && mn != ~0ull) {
+      if (mn < __ldcg(tmm + 2 * k)) atomicMin(tmm + 2 * k, mn);
+      if (mx > __ldcg(tmm + 2 * k + 1)) atomicMax(tmm + 2 * k + 1, mx);
+    }
   }
 }
 
