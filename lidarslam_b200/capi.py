@@ -182,6 +182,12 @@ class CApi:
     def SetVoxelGridResolution(self, res):
         self._check(self._f("set_voxel_grid_resolution")(self.h, C.c_double(res)))
 
+    def SetVoxelGridDecayingThreshold(self, seconds):
+        self._check(self._f("set_voxel_grid_decaying_threshold")(self.h, C.c_double(seconds)))
+
+    def SetVoxelGridMinFramesPerVoxel(self, n):
+        self._check(self._f("set_voxel_grid_min_frames_per_voxel")(self.h, C.c_uint(n)))
+
     def SetVoxelGridSamplingMode(self, k, mode):
         self._check(self._f("set_voxel_grid_sampling_mode")(self.h, C.c_int(k), C.c_int(mode)))
 

@@ -64,7 +64,8 @@ struct RollingGridGpu {
   void SubMapFinish(cudaStream_t s, LaunchCounter& lc);
   bool IsSubMapKdTreeValid() const { return tree_valid && n_submap > 0; }               // RollingGrid.h:132-135
   bool IsTimeThreshold() const { return DecayingThreshold > 0; }
-  void ResetTree() { tree_valid = false; n_submap = 0; grid.clear(); }
+  // KdTree.Reset() (RollingGrid.cxx:55, :317): the search structure goes, the SubMap cloud stays readable (RollingGrid.h:160, :198)
+  void ResetTree() { tree_valid = false; grid.clear(); }
 
  private:
   void build_grid(const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc);

@@ -264,7 +264,7 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
     if (w & 2) Warnings |= LSB_W_MOTION_LIMITS;
   }
   uint32_t n_submap[3];
-  for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // the map update invalidates the submaps
+  for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // sizes of the sub-maps this frame was matched against
   if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
   Join();
   trace.mark("map_update", stream);

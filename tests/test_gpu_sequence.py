@@ -294,3 +294,24 @@ def test_os128_long_sequence_drift(gpu, oracle_lib, synth):
     G39 = seq.frame(sens, 39)[1]
     rel = np.linalg.inv(G0) @ G39
     assert np.linalg.norm(Tg[-1][:3, 3] - rel[:3, 3]) < 0.15   # and it tracks the ground truth (31 m travelled)
+
+
+def test_map_options_decay_min_frames_sampling(gpu, oracle_lib, synth):
+    """RollingGrid options on a running sequence (RollingGrid.cxx:325-350 ClearOldPoints, :393-435 moving-object filter of the
+    sub-map, :230-298 sampling modes): decaying threshold, MinFramesPerVoxel and one sampling mode per keypoint type."""
+    def cfg(s):
+        p = s.GetParams()
+        p.use_keypoints[2] = 1
+        s.SetParams(p)
+        s.SetVoxelGridDecayingThreshold(0.35)              # seconds: points not seen for 3 frames leave the maps
+        s.SetVoxelGridMinFramesPerVoxel(2)
+        for k, mode in ((0, 0), (1, 3), (2, 1)):           # FIRST, CENTER_POINT, LAST
+            s.SetVoxelGridSamplingMode(k, mode)
+    g, o = _run(gpu, oracle_lib, synth, [synth.sensor("vlp16")], 10, cfg, check_maps_every=1)
+    for k in capi.KEYPOINT_TYPES:
+        assert g.GetMap(k, True).tobytes() == o.GetMap(k, True).tobytes()          # GetMap(clean): count > MinFramesPerVoxel
+        assert g.GetTargetSubMap(k).tobytes() == o.GetTargetSubMap(k).tobytes()
+        assert 0 < len(g.GetMap(k, True)) < len(g.GetMap(k))
+    old = g.GetMap(1)["time"]
+    assert old.max() - old.min() <= 0.35 + 1e-9           # nothing older than the threshold survived
+

@@ -122,6 +122,48 @@ def test_map_add_bit_exact(gpu, oracle_lib, synth, mode):
             assert a.tobytes() == b.tobytes(), "map %d differs after add %d" % (k, i)
 
 
+def test_map_roll_drops_voxels(gpu, oracle_lib):
+    """A 8^3 grid of 5 m voxels (40 m across): clouds that fit the grid make it roll to their bounding box and drop the voxels
+    that leave it (RollingGrid.cxx:117-157); points outside the grid are skipped (:190-196); re-binning on SetVoxelGridSize /
+    SetVoxelGridResolution (:59-88)."""
+    rng = np.random.default_rng(21)
+
+    def cloud(centre, half, n):
+        p = np.zeros(n, dtype=capi.POINT_DTYPE)
+        xyz = (rng.uniform(-half, half, (n, 3)) + np.asarray(centre)).astype(np.float32)
+        p["x"], p["y"], p["z"], p["w"] = xyz[:, 0], xyz[:, 1], xyz[:, 2], 1.0
+        p["intensity"] = rng.uniform(0, 255, n).astype(np.float32)
+        return p
+
+    g, o = gpu(), oracle_lib.Oracle()
+    for s in (g, o):
+        s.SetVoxelGridSize(8)
+        s.SetVoxelGridResolution(5.0)
+    sizes = []
+    steps = [((0, 0, 0), 14.0), ((22, 3, -2), 14.0), ((47, -20, 4), 12.0), ((47, -20, 4), 30.0), ((-5, 0, 0), 6.0)]
+    for i, (centre, half) in enumerate(steps):
+        c = cloud(centre, half, 6000)
+        g.MapAdd(1, c, False, 0.1 * i)
+        o.MapAdd(1, c, False, 0.1 * i)
+        a, b = g.GetMap(1), o.GetMap(1)
+        assert a.tobytes() == b.tobytes(), "map differs after add %d" % i
+        sizes.append(len(a))
+        for ax in ("x", "y", "z"):
+            assert a[ax].max() - a[ax].min() <= 45.0 + 1e-3          # never wider than the grid (+ one voxel of slack)
+    assert sizes[0] > 3000 and sizes[1] < sizes[0] + 6000           # the second add rolled the grid and dropped part of the first cloud
+    assert (g.GetMap(1)["x"] < 20).any()                             # the last cloud pulled the grid back
+    # re-binning: a larger grid keeps everything, a coarser resolution re-snaps the voxels
+    for s in (g, o):
+        s.SetVoxelGridSize(20)
+        s.SetVoxelGridResolution(10.0)
+    assert g.GetMap(1).tobytes() == o.GetMap(1).tobytes()
+    c = cloud((60, 0, 0), 40.0, 8000)
+    g.MapAdd(1, c, True, 1.0)
+    o.MapAdd(1, c, True, 1.0)
+    a = g.GetMap(1)
+    assert a.tobytes() == o.GetMap(1).tobytes() and (a["label"] == 1).any()
+
+
 def test_match_and_solve(gpu, oracle_lib, synth):
     g, o = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
     seq = synth.Sequence()
