@@ -315,3 +315,59 @@ def test_map_options_decay_min_frames_sampling(gpu, oracle_lib, synth):
     old = g.GetMap(1)["time"]
     assert old.max() - old.min() <= 0.35 + 1e-9           # nothing older than the threshold survived
 
+
+
+def test_soft_failures_and_state_control(gpu, oracle_lib, synth):
+    """The reference's soft-fail paths through the C ABI, GPU against oracle: duplicate stamp and empty frame ignored
+    (Slam.cxx:720-731), dropped-frame warning (:734-740), localization skipped on empty maps (:1098-1107), a frame with too
+    few points for any keypoint, Reset / ClearMaps / SetWorldTransformFromGuess, 2-D mode."""
+    g, o = gpu(), oracle_lib.Oracle(nb_threads=4)
+    seq, sens = synth.Sequence(scene_seed=1234), synth.sensor("tiny")
+    both = (g, o)
+
+    def same(i=""):
+        Tg, To = g.GetWorldTransform(), o.GetWorldTransform()
+        assert np.abs(Tg[0] - To[0]).max() <= 1e-6 and Tg[1] == To[1], i
+        for k in capi.KEYPOINT_TYPES:
+            assert g.GetKeypoints(k).tobytes() == o.GetKeypoints(k).tobytes(), i
+            assert g.GetMap(k).tobytes() == o.GetMap(k).tobytes(), i
+
+    pts, _, stamp = seq.frame(sens, 0)
+    assert [s.AddFrame(pts, stamp, 1) for s in both] == [2, 2]                      # LSB_W_LOC_SKIPPED: empty maps
+    assert [s.AddFrame(pts, stamp, 2) for s in both] == [1, 1]                      # duplicate stamp
+    assert [s.AddFrame(pts[:0], stamp + 100000, 3) for s in both] == [1, 1]         # empty frame
+    same("after ignored frames")
+    pts1, _, stamp1 = seq.frame(sens, 1)
+    r = [s.AddFrame(pts1, stamp1, 9) for s in both]
+    assert r[0] == r[1] and r[0] & 32                                               # LSB_W_FRAMES_DROPPED
+    same("frame 1")
+    # a sliver of a frame: two columns of 16 rings, too short for any keypoint (< 2W + 1 points per ring)
+    sl, _, stamp2 = seq.frame(sens, 2)
+    r = [s.AddFrame(sl[:32], stamp2, 10) for s in both]
+    assert r[0] == r[1] and r[0] & 2
+    same("sliver")
+    # state control
+    T = np.eye(4)
+    T[:3, 3] = [1.0, -2.0, 0.5]
+    for s in both:
+        s.SetWorldTransformFromGuess(T)
+    pts3, _, stamp3 = seq.frame(sens, 3)
+    assert g.AddFrame(pts3, stamp3, 11) == o.AddFrame(pts3, stamp3, 11)
+    same("after guess")
+    for s in both:
+        s.ClearMaps()
+    assert all(len(g.GetMap(k)) == 0 for k in capi.KEYPOINT_TYPES)
+    pts4, _, stamp4 = seq.frame(sens, 4)
+    assert g.AddFrame(pts4, stamp4, 12) == o.AddFrame(pts4, stamp4, 12)
+    same("after ClearMaps")
+    for s in both:
+        s.Reset(True)
+        p = s.GetParams()
+        p.two_d_mode = 1
+        s.SetParams(p)
+    for i in range(5, 9):
+        pts, _, stamp = seq.frame(sens, i)
+        assert g.AddFrame(pts, stamp, i) == o.AddFrame(pts, stamp, i)
+        same("2-D mode frame %d" % i)
+    Tg, _ = g.GetWorldTransform()
+    assert Tg[2, 3] == 0.0 and abs(Tg[2, 2] - 1.0) < 1e-15                          # z, roll and pitch held (LocalOptimizer.cxx:89-90)
