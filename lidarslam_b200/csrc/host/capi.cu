@@ -290,7 +290,8 @@ static const char* const kMapFileNames[3] = {"edges.pcd", "planes.pcd", "blobs.p
 int lsb_pcd_write(const char* path, const lsb_point* pts, size_t n, int pcd_format)
 {
   if (!path || (n && !pts)) return LSB_E_INVALID;
-  const int rc = pcd::Write(path, pts, n, pcd_format);
+  int rc = -1;
+  try { rc = pcd::Write(path, pts, n, pcd_format); } catch (const std::exception& e) { g_last_error = e.what(); return -1; }
   if (rc == -1) g_last_error = std::string("cannot write ") + path;
   return rc;
 }
@@ -299,7 +300,9 @@ long lsb_pcd_read(const char* path, lsb_point* out, long cap)
   if (!path) return LSB_E_INVALID;
   std::vector<lsb_point> pts;
   std::string why;
-  if (pcd::Read(path, pts, &why) != 0) { g_last_error = why; return -1; }
+  try {
+    if (pcd::Read(path, pts, &why) != 0) { g_last_error = why; return -1; }
+  } catch (const std::exception& e) { g_last_error = e.what(); return -1; }
   if (out && cap > 0 && !pts.empty()) std::memcpy(out, pts.data(), std::min<size_t>(pts.size(), (size_t)cap) * sizeof(lsb_point));
   return (long)pts.size();
 }

@@ -267,8 +267,13 @@ int Read(const std::string& path, std::vector<lsb_point>& out, std::string* err)
       if (f.name == kFields[k].name && f.count == 1 && f.size == kFields[k].size && f.type == kFields[k].type) f.target = k;
     stride += (size_t)f.size * f.count;
   }
-  out.assign(npoints, DefaultPoint());
   if (npoints == 0) return 0;
+  // a header cannot promise more points than the payload can hold (checked before anything is allocated)
+  const size_t payload = buf.size() - pos;
+  if (stride == 0 || npoints > payload) return Fail(err, "POINTS exceeds what the file can hold");
+  if (data == "binary" && npoints > payload / stride) return Fail(err, "binary payload shorter than POINTS x point size");
+  if (data == "binary_compressed" && npoints > (size_t)0xffffffffu / stride) return Fail(err, "raw size differs from POINTS x point size");
+  out.assign(npoints, DefaultPoint());
 
   if (data == "ascii") {
     size_t i = 0;

@@ -148,6 +148,12 @@ def test_error_codes(built, tmp_path):
     open(path, "wb").write(raw[:-5])
     with pytest.raises(RuntimeError, match="shorter"):
         capi.pcd_read(path)
+    # a header that promises far more points than the file holds is refused before anything is allocated
+    head = raw[:raw.index(b"DATA")].replace(b"POINTS 4", b"POINTS 4000000000000").replace(b"WIDTH 4", b"WIDTH 4000000000000")
+    for kind in (b"binary", b"ascii", b"binary_compressed"):
+        open(path, "wb").write(head + b"DATA " + kind + b"\n" + raw[-4 * 28:])
+        with pytest.raises(RuntimeError):
+            capi.pcd_read(path)
     assert capi.pcd_write(path, p, capi.PCD_BINARY_COMPRESSED) == 0
     raw = bytearray(open(path, "rb").read())
     raw[-1] ^= 0xFF
