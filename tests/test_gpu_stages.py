@@ -89,6 +89,50 @@ def test_knn_bit_exact_large_query_set(gpu, oracle_lib, synth, k):
     assert np.array_equal(dg.view(np.uint32), do.view(np.uint32))
 
 
+@pytest.mark.parametrize("case", ["lattice", "collinear", "identical", "clusters", "huge_extent", "tiny"])
+def test_knn_degenerate_clouds(gpu, oracle_lib, case):
+    """Exact kNN with (d2, index) ordering on clouds that stress ties, empty cells and the fall-back passes; results against the
+    oracle's kd-tree and an O(NQ x M) numpy scan with the same float arithmetic ((dx*dx + dy*dy) + dz*dz in f32)."""
+    rng = np.random.default_rng(5)
+    if case == "lattice":          # integer lattice: dozens of exact ties per query, decided by the smaller index
+        g3 = np.stack(np.meshgrid(np.arange(12), np.arange(12), np.arange(6), indexing="ij"), -1).reshape(-1, 3).astype(np.float32) * 0.5
+        xyz = g3[rng.permutation(len(g3))]
+        q = np.concatenate([xyz[:200], xyz[:200] + np.float32(0.25)])
+    elif case == "collinear":
+        t = rng.uniform(-30, 30, 3000).astype(np.float32)
+        xyz = np.stack([t, 0.5 * t, np.zeros_like(t)], 1)
+        q = np.stack([rng.uniform(-35, 35, 500), rng.uniform(-20, 20, 500), rng.uniform(-3, 3, 500)], 1).astype(np.float32)
+    elif case == "identical":      # every target point at the same place
+        xyz = np.tile(np.float32([3.0, -2.0, 1.0]), (500, 1))
+        q = rng.normal(0, 5, (100, 3)).astype(np.float32)
+    elif case == "clusters":       # dense blobs far apart: most cells empty, isolated queries between them
+        c = rng.uniform(-80, 80, (12, 3)).astype(np.float32)
+        xyz = (c[rng.integers(0, 12, 8000)] + rng.normal(0, 0.2, (8000, 3))).astype(np.float32)
+        q = np.concatenate([xyz[:1500] + rng.normal(0, 0.05, (1500, 3)).astype(np.float32), rng.uniform(-100, 100, (500, 3)).astype(np.float32)])
+    elif case == "huge_extent":    # the cell size has to grow to respect the cell budget
+        xyz = rng.uniform(-3000, 3000, (5000, 3)).astype(np.float32)
+        q = rng.uniform(-3500, 3500, (800, 3)).astype(np.float32)
+    else:                          # fewer points than k, one point, queries on top of the points
+        xyz = rng.normal(0, 1, (7, 3)).astype(np.float32)
+        q = np.concatenate([xyz, rng.normal(0, 10, (20, 3)).astype(np.float32)])
+    cloud = np.zeros(len(xyz), dtype=capi.POINT_DTYPE)
+    cloud["x"], cloud["y"], cloud["z"], cloud["w"] = xyz[:, 0], xyz[:, 1], xyz[:, 2], 1.0
+    q = np.ascontiguousarray(q, dtype=np.float32)
+    g, o = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
+    for k in (1, 5, 10, 32):
+        ig, dg = g.KnnSearch(cloud, q, k)
+        io, do = o.KnnSearch(cloud, q, k)
+        assert np.array_equal(ig, io), (case, k)
+        assert np.array_equal(dg.view(np.uint32), do.view(np.uint32)), (case, k)
+        # independent scan: distances in float32 with the reference's summation order, ties to the smaller index
+        d = q[:, None, :] - xyz[None, :, :]
+        d2 = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
+        kk = min(k, len(xyz))
+        order = np.lexsort((np.broadcast_to(np.arange(len(xyz)), d2.shape), d2), axis=1)[:, :kk]
+        assert np.array_equal(ig[:, :kk], order.astype(np.int32)), (case, k)
+        assert np.array_equal(dg[:, :kk], np.take_along_axis(d2, order, 1)), (case, k)
+
+
 def test_undistort_bit_exact(gpu, oracle_lib, synth):
     pts, _, _ = _frame(synth, "tiny")
     H0 = np.eye(4)
