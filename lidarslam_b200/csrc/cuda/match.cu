@@ -4,6 +4,8 @@
 // (common/pca.h), model checks and the residual record (A, P, X, w)
 // (KeypointsMatcher.cxx:106-346).  Plain IEEE arithmetic, no FMA contraction.
 #include "match.cuh"
+#include <cstring>
+#include <atomic>
 #include "../common/pca.h"
 #include <cfloat>
 #include <cmath>
@@ -461,7 +463,7 @@ __device__ unsigned long long g_lm_probe[64 * 5];
 __global__ void __launch_bounds__(LM_THREADS, 1)
 k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, int pstride, double sat, LmStart start, int max_iter,
            int two_d, const int* __restrict__ hist, unsigned min_matches, LmState* __restrict__ state_out, double* __restrict__ part,
-           unsigned* __restrict__ bar, const LmSensorTerms terms)
+           unsigned* __restrict__ bar, const LmSensorTerms terms, MatchWorkspace::LmHostBlock* host_out, unsigned host_seq)
 {
   constexpr int NW = (int)(sizeof(LmState) / 8), NP = (int)(sizeof(LmPoint) / 8);
   static_assert(sizeof(LmState) % 8 == 0 && sizeof(LmPoint) % 8 == 0, "copied as 64-bit words");
@@ -561,7 +563,16 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
     __syncthreads();
     LM_PROBE_STAMP(e, 4);
   }
-  if (blockIdx.x == 0 && threadIdx.x < NW) reinterpret_cast<unsigned long long*>(state_out)[threadIdx.x] = s_state_raw[threadIdx.x];
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < NW) reinterpret_cast<unsigned long long*>(state_out)[threadIdx.x] = s_state_raw[threadIdx.x];
+    if (host_out) {     // every CTA holds the final state: CTA 0 hands it (and the histograms) to the host, then raises the flag
+      if (threadIdx.x < NW) reinterpret_cast<volatile unsigned long long*>(&host_out->state)[threadIdx.x] = s_state_raw[threadIdx.x];
+      if (threadIdx.x < 3 * LSB_MATCH_N_STATUS) reinterpret_cast<volatile int*>(host_out->hist)[threadIdx.x] = hist[threadIdx.x];
+      __threadfence_system();
+      __syncthreads();
+      if (threadIdx.x == 0) { *reinterpret_cast<volatile unsigned*>(&host_out->seq) = host_seq; __threadfence_system(); }
+    }
+  }
   // the last CTA to leave re-arms the barrier for the next solve (every CTA is past its last wait)
   if (threadIdx.x == 0) {
     const unsigned t = atomicAdd(bar + 1, 1u);
@@ -659,6 +670,8 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   }
   part_a.reserve((size_t)2 * pstride * LSB_LM_NSUM, s);
   lm_state.reserve(1, s); h_lm.reserve(1);
+  if (!h_block.p) { h_block.reserve(1); h_block.p->seq = 0; }
+  const unsigned seq = ++solve_seq ? solve_seq : ++solve_seq;   // never 0 (the initial value of the flag)
   if (!lm_counter.p) {           // [arrivals, exits] of the grid barrier: zero between solves
     lm_counter.reserve(2, s);
     LSB_CUDA(cudaMemsetAsync(lm_counter.p, 0, 2 * sizeof(unsigned), s));
@@ -678,16 +691,27 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
   LSB_CUDA(cudaLaunchKernelEx(&cfg, k_lm_solve, (const double*)records.p, rec_stride, n, nchunks, pstride, saturation, start, max_iter, two_d,
-                              (const int*)hist.p, min_matches, lm_state.p, part_a.p, lm_counter.p, terms));
+                              (const int*)hist.p, min_matches, lm_state.p, part_a.p, lm_counter.p, terms, h_block.p, seq));
   lc.add();
   t_lm.end(s);
   d2h_bytes += sizeof(LmState) + 3 * LSB_MATCH_N_STATUS * sizeof(int);
-  LSB_CUDA(cudaMemcpyAsync(h_hist.p, hist.p, 3 * LSB_MATCH_N_STATUS * sizeof(int), cudaMemcpyDeviceToHost, s));
-  LSB_CUDA(cudaMemcpyAsync(h_lm.p, lm_state.p, sizeof(LmState), cudaMemcpyDeviceToHost, s));
-  LSB_CUDA(cudaStreamSynchronize(s));
+  // wait for the kernel's own hand-off (no copy, no stream synchronisation); the stream is queried now and then so that a
+  // failed launch surfaces as an error instead of an endless wait
+  volatile unsigned* flag = &h_block.p->seq;
+  for (unsigned spins = 1; *flag != seq; ++spins) {
+    if ((spins & 4095u) == 0) {
+      const cudaError_t q = cudaStreamQuery(s);
+      if (q == cudaSuccess) { if (*flag != seq) throw CudaError(LSB_E_CUDA, "k_lm_solve finished without handing its result over"); break; }
+      if (q != cudaErrorNotReady) cuda_check(q, "k_lm_solve", __FILE__, __LINE__);
+    }
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  const LmHostBlock& blk = *h_block.p;
   for (int t = 0; t < 3; ++t)
-    for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) hist_out[t][q] = h_hist.p[t * LSB_MATCH_N_STATUS + q];
-  return *h_lm.p;
+    for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) hist_out[t][q] = blk.hist[t * LSB_MATCH_N_STATUS + q];
+  LmState st;
+  std::memcpy(&st, (const void*)&blk.state, sizeof(LmState));
+  return st;
 }
 
 }  // namespace lsb

@@ -24,6 +24,11 @@ struct MatchWorkspace {
   int lm_grid_limit = 0;            // co-resident CTAs of that kernel on this device
   PinnedBuf<int> h_hist;
   PinnedBuf<LmState> h_lm;
+  // result block of a solve in pinned (device-visible) host memory: k_lm_solve stores the final state and the match
+  // histograms there itself and raises `seq` last; the host polls `seq` instead of copying and synchronising
+  struct LmHostBlock { LmState state; int hist[3 * LSB_MATCH_N_STATUS]; unsigned seq; };
+  PinnedBuf<LmHostBlock> h_block;
+  unsigned solve_seq = 0;
   KernelTimer t_knn, t_fit, t_lm;   // lsb_set_profiling
   size_t d2h_bytes = 0;
   size_t total = 0;                 // records of the current iteration

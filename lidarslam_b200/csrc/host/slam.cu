@@ -492,9 +492,12 @@ void lsb_slam::Localization()
     mw.begin_iteration(nk, stream);
     Fork();
     for (int k : kTypeOrder) {
+      // the undistortion refinement of the previous iteration (:1146-1147): three independent clouds, one per type stream
+      if (HasPendingRefinement) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, PendingRefinement, 0.0, TypeStream(k), lc);
       mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], LocalMaps[k].grid, Tworld, mp, TypeStream(k), lc);
       Stats.knn_queries += (uint32_t)nk[k];
     }
+    HasPendingRefinement = false;
     Join();
     trace.mark("match", stream);
     // the "enough matches" test (:1098-1107) is taken on the device as well: one read-back per ICP iteration
@@ -519,8 +522,9 @@ void lsb_slam::Localization()
     Stats.loc_lm_iters += (uint32_t)st.iter;
     Tworld = xyzrpy_to_iso(st.x);
     Trelative = inverse(PreviousTworld) * Tworld;
-    if (P.undistortion == LSB_UNDISTORTION_REFINED) RefineUndistortion();
-    if (st.num_successful + 1 == 1 || icpIter == P.localization_icp_max_iter - 1) {   // :1151-1155
+    const bool lastIter = st.num_successful + 1 == 1 || icpIter == P.localization_icp_max_iter - 1;
+    if (P.undistortion == LSB_UNDISTORTION_REFINED) RefineUndistortion(/*defer=*/!lastIter);
+    if (lastIter) {   // :1151-1155
       registration_error_from_normal_matrix(st.H, P.two_d_mode != 0, &LocalizationUncertainty);
       break;
     }
@@ -611,7 +615,7 @@ void lsb_slam::InitUndistortion()
   else if (WithinFrameMotion.t1 - WithinFrameMotion.t0 > 10.) Warnings |= LSB_W_TIME_FIELD;
 }
 
-void lsb_slam::RefineUndistortion()
+void lsb_slam::RefineUndistortion(bool defer)
 {
   const Iso3d prevBegin = WithinFrameMotion.H0(), prevEnd = WithinFrameMotion.H1();
   const Iso3d wBegin = InterpolateScanPose(WithinFrameMotion.t0);
@@ -621,8 +625,13 @@ void lsb_slam::RefineUndistortion()
   WithinFrameMotion.set_transforms(newBegin, newEnd);
   Interpolator interp = WithinFrameMotion;
   interp.set_transforms(newBegin * inverse(prevBegin), newEnd * inverse(prevEnd));
-  for (int k = 0; k < 3; ++k) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, interp, 0.0, stream, lc);
   for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
+  if (defer) {          // applied per type, on the type's own stream, at the head of the next matching pass
+    PendingRefinement = interp;
+    HasPendingRefinement = true;
+    return;
+  }
+  for (int k = 0; k < 3; ++k) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, interp, 0.0, stream, lc);
 }
 
 //-----------------------------------------------------------------------------

@@ -127,7 +127,9 @@ struct lsb_slam {
   void LogCurrentFrameState(double time);                // :1225-1264
   lsb::Iso3d InterpolateScanPose(double time);           // :1271-1285
   void InitUndistortion();                               // :1288-1319
-  void RefineUndistortion();                             // :1322-1352
+  void RefineUndistortion(bool defer = false);           // :1322-1352
+  lsb::Interpolator PendingRefinement;                   // refinement enqueued with the next matching pass (per type stream)
+  bool HasPendingRefinement = false;
   void SaveDebug(StageDebug& d);
   void EstimateOverlap();                                // :1370-1388 + ConfidenceEstimators.cxx:27-65
   // overlap estimator scratch

@@ -71,7 +71,7 @@ int main(int argc, char** argv)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(LM_THREADS); cfg.dynamicSmemBytes = kSmem; cfg.attrs = &attr; cfg.numAttrs = 1;
     cudaLaunchKernelEx(&cfg, k_lm_solve, (const double*)d_rec, stride, n, nchunks, pstride, 1.0, start, max_iter, 0, (const int*)d_hist, 100u,
-                       d_state, d_part, d_bar, terms);
+                       d_state, d_part, d_bar, terms, (MatchWorkspace::LmHostBlock*)nullptr, 0u);
   };
   printf("n = %d records, %d chunks of %d, grid %d x %d threads (%d CTA/SM)\n", n, nchunks, LSB_LM_CHUNK, grid, LM_THREADS, per_sm);
   printf("empty launch   %7.2f us\n", time_launches(200, [&] { k_empty<<<grid, LM_THREADS>>>(0); }));
