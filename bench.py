@@ -196,9 +196,11 @@ def main():
         print(json.dumps(line), flush=True)
         return 0
 
+    import gc
     import torch
     import torch.distributed as dist
     from lidarslam_b200.slam import Slam, pinned_points, pinned_free
+    gc.disable()        # no collector pauses inside the wall-clock (e2e) steps
 
     if world > 1:
         torch.cuda.set_device(local)
