@@ -134,6 +134,19 @@ def run_cpu(frames, warmup, steps, threads=None):
     return times, threads
 
 
+def _pool_stats():
+    """Reserved / used bytes of the device's default stream-ordered pool (diagnostic, LSB_TRACE=1 only)."""
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    pool, out, v = ctypes.c_void_p(), {}, ctypes.c_uint64()
+    if rt.cudaDeviceGetDefaultMemPool(ctypes.byref(pool), 0):
+        return "unavailable"
+    for name, attr in (("reserved", 5), ("reserved_high", 6), ("used", 7), ("used_high", 8)):
+        rt.cudaMemPoolGetAttribute(pool, attr, ctypes.byref(v))
+        out[name] = v.value >> 20
+    return out
+
+
 def run_multi_sequence(n_seq, sensor, warm, steps, device, first):
     """several handles per GPU (one host thread + streams each) fill the SMs a single latency-bound
     trajectory leaves idle.  Wall clock around `steps` frames of every sequence, frames resident in HBM, no L2 flush
@@ -297,6 +310,10 @@ def main():
         d2h += se.d2h_bytes + 128
         h2d += se.h2d_bytes
     barrier()
+    if max(e2e_steps) > 2 * statistics.median(e2e_steps):
+        print("[bench rank %d] e2e outlier steps (ms): %s" % (rank, " ".join("%.2f" % (1e3 * t) for t in e2e_steps)), file=sys.stderr, flush=True)
+    if os.environ.get("LSB_TRACE") == "1":
+        print("[bench rank %d] device memory pool (MiB): %s" % (rank, _pool_stats()), file=sys.stderr, flush=True)
     Tg, _ = g.GetWorldTransform()
     same_pose = bool(np.abs(Tg - T).max() < 1e-9 and np.abs(Tg - Tp).max() < 1e-9)
     pinned_free(pin_ptr)

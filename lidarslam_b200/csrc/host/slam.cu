@@ -29,16 +29,19 @@ lsb_slam::lsb_slam(int dev) : device(dev)
     LSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
     unsigned long long keep = ~0ull;
     LSB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
-    // pre-warm: one large block taken from the driver and handed back to the pool, so that the
-    // growth of the maps during a sequence is served by the pool (a driver allocation in the
-    // middle of a frame costs milliseconds).  LSB_POOL_PREWARM_MB overrides the size (0 = none).
-    static bool warmed = false;
-    if (!warmed) {
-      warmed = true;
-      size_t mb = 2048;
-      if (const char* e = std::getenv("LSB_POOL_PREWARM_MB")) mb = (size_t)std::atol(e);
+    // head-room: every new handle makes sure the pool holds LSB_POOL_PREWARM_MB (default 4096) of
+    // unused memory, by taking one block from the driver and handing it back to the pool.  The maps,
+    // grids and sort scratch of a sequence then grow out of the pool: a driver allocation in the
+    // middle of a frame was measured at 5 - 125 ms on B200 (profiles/r01_e2e_stalls.txt), against
+    // 2.3 ms for the whole frame.  0 = no reservation.
+    size_t mb = 4096;
+    if (const char* e = std::getenv("LSB_POOL_PREWARM_MB")) mb = (size_t)std::atol(e);
+    unsigned long long reserved = 0, used = 0;
+    LSB_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved));
+    LSB_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used));
+    if (mb && reserved - used < ((unsigned long long)mb << 20)) {
       void* blk = nullptr;
-      if (mb && cudaMallocAsync(&blk, mb << 20, stream) == cudaSuccess) cudaFreeAsync(blk, stream);
+      if (cudaMallocAsync(&blk, mb << 20, stream) == cudaSuccess) cudaFreeAsync(blk, stream);
       else cudaGetLastError();
       LSB_CUDA(cudaStreamSynchronize(stream));
     }
@@ -460,15 +463,17 @@ void lsb_slam::Localization()
   Tworld = PreviousTworld * Trelative;
   std::memset(LocDebug.hist, 0, sizeof(LocDebug.hist));
   for (auto& o : LocDebug.off) o = 0;
-  if (P.undistortion) { InitUndistortion(); RefineUndistortion(); }   // :986-995
+  // :986-995; the three clouds are undistorted on their own streams at the head of the submap lanes below
+  if (P.undistortion) { InitUndistortion(); RefineUndistortion(/*defer=*/true); }
   trace.mark("undistort", stream);
 
   // Submaps (:1003-1037): the three maps work on their own streams and host lanes; each lane waits
   // for its own read-backs (bbox of the keypoints, size of the submap)
   ForEachType([&](int k) {
     RollingGridGpu& map = LocalMaps[k];
-    if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) return;
     cudaStream_t ts = TypeStream(k);
+    if (HasPendingRefinement) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, PendingRefinement, 0.0, ts, lc);
+    if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) return;
     if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(ts, lc); return; }
     if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, ts, lc);
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
@@ -480,6 +485,7 @@ void lsb_slam::Localization()
     map.SubMapSelect(mn, mx, (int)(CurrentKeypoints[k].n / 2), ts, lc);
     map.SubMapFinish(ts, lc);
   });
+  HasPendingRefinement = false;
   trace.mark("submap+grid", stream);
 
   // ICP - LM loop (:1051-1156)
