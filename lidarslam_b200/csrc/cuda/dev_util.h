@@ -41,7 +41,16 @@ struct DevBuf {
   DevBuf() = default;
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
-  ~DevBuf() { if (p) cudaFree(p); }
+  // A block of the stream-ordered allocator goes back to its pool only through cudaFreeAsync: after cudaFree the
+  // pool keeps counting it as used (measured, tools/probes/pool_free_probe.cu: 161 MiB lost per destroyed OS-128
+  // handle).  The owner may have destroyed its streams already, so the free is ordered on the legacy stream,
+  // behind a device-wide synchronisation (what cudaFree did implicitly).
+  ~DevBuf()
+  {
+    if (!p) return;
+    cudaDeviceSynchronize();
+    if (cudaFreeAsync(p, cudaStreamLegacy) != cudaSuccess) { cudaGetLastError(); cudaFree(p); }
+  }
   void reserve(size_t n, cudaStream_t s = 0, bool keep = false, size_t keep_n = 0)
   {
     if (n <= cap) return;

@@ -41,9 +41,17 @@ lsb_slam::lsb_slam(int dev) : device(dev)
     LSB_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used));
     if (mb && reserved - used < ((unsigned long long)mb << 20)) {
       void* blk = nullptr;
-      if (cudaMallocAsync(&blk, mb << 20, stream) == cudaSuccess) cudaFreeAsync(blk, stream);
+      const cudaError_t rc = cudaMallocAsync(&blk, mb << 20, stream);
+      if (rc == cudaSuccess) cudaFreeAsync(blk, stream);
       else cudaGetLastError();
       LSB_CUDA(cudaStreamSynchronize(stream));
+      if (const char* e = std::getenv("LSB_TRACE")) if (e[0] == '1') {
+        unsigned long long r2 = 0, u2 = 0;
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &r2);
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &u2);
+        std::fprintf(stderr, "[lsb pool] reserved %llu used %llu MiB -> top-up %zu MiB rc=%d -> reserved %llu used %llu MiB\n",
+                     reserved >> 20, used >> 20, mb, (int)rc, r2 >> 20, u2 >> 20);
+      }
     }
   }
   for (auto& e : ev) LSB_CUDA(cudaEventCreate(&e));

@@ -231,3 +231,44 @@ def test_match_and_solve(gpu, oracle_lib, synth):
         assert np.array_equal(rg["pose"], ro["pose"])
         assert rg["cost"] == ro["cost"]
         assert np.allclose(np.array(rg["err"].covariance), np.array(ro["err"].covariance), rtol=1e-6, atol=1e-12)
+
+
+def _pool_mib():
+    """(reserved, used) MiB of device 0's default stream-ordered memory pool, asked from the CUDA runtime directly."""
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    pool, v, out = ctypes.c_void_p(), ctypes.c_uint64(), []
+    assert rt.cudaDeviceGetDefaultMemPool(ctypes.byref(pool), 0) == 0
+    for attr in (5, 7):   # cudaMemPoolAttrReservedMemCurrent, cudaMemPoolAttrUsedMemCurrent
+        assert rt.cudaMemPoolGetAttribute(pool, attr, ctypes.byref(v)) == 0
+        out.append(v.value >> 20)
+    return out
+
+
+def test_every_handle_tops_up_the_memory_pool(gpu, synth):
+    """Buffer growth in the middle of a frame must be served by the pool, never by the driver (5 - 125 ms a time,
+    profiles/r01_e2e_stalls.txt): every new handle leaves at least LSB_POOL_PREWARM_MB (4096) unused in the pool,
+    also when earlier handles of the process are alive and hold memory."""
+    import os
+    want = int(os.environ.get("LSB_POOL_PREWARM_MB", "4096"))
+    if want == 0:
+        pytest.skip("pool reservation switched off")
+    import torch
+    torch.zeros(1, device="cuda")                    # libcudart of the torch wheel needs a context to answer
+    import gc
+    gc.collect()                                     # handles of earlier tests give their memory back now, not in between
+    handles = []
+    for i in range(3):
+        _, used_before = _pool_mib()
+        h = gpu(device=0)
+        handles.append(h)
+        reserved, used = _pool_mib()                 # the handle's own first buffers already come out of the head-room
+        assert reserved - used_before >= want - 1, (i, reserved, used_before, used)
+        seq = synth.Sequence(scene_seed=77 + i)
+        for j in range(3):                           # the handle takes memory out of the pool
+            pts, _, stamp = seq.frame(synth.sensor("hdl64"), j)
+            h.AddFrame(pts, stamp, j + 1)
+    r2, u2 = _pool_mib()
+    assert u2 > 0 and r2 >= u2
+    for h in handles:
+        h.close()
