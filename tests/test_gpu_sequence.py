@@ -274,6 +274,17 @@ def test_vls128_pandar64_rig_dense_maps(gpu, oracle_lib, synth):
     assert st.n_points == 128 * 1800 + 64 * 1800 and st.is_keyframe == 1
 
 
+def _unverified_test_vlp16_long_sequence_rolling_map(gpu, oracle_lib, synth):
+    """BASELINE configs[0] at length: 200 VLP-16 frames (150 m travelled) with default keypoints through a 250 m rolling
+    grid, so that the maps roll, drop voxels and saturate while every frame stays bit-identical to the oracle; the whole
+    logged trajectory agrees to 1e-6."""
+    g, o = _run(gpu, oracle_lib, synth, [synth.sensor("vlp16")], 200, lambda s: s.SetVoxelGridSize(25), check_maps_every=40)
+    n, Tg, _ = g.GetTrajectory()
+    m, To, _ = o.GetTrajectory()
+    assert n == m and np.abs(Tg - To).max() <= 1e-6
+    assert np.linalg.norm(Tg[-1][:3, 3]) > 100.
+
+
 def test_os128_long_sequence_drift(gpu, oracle_lib, synth):
     """North star: per-frame pose within 1e-6 m / 1e-6 rad after each ICP solve and trajectory drift within 1 mm over the
     sequence, on the headline configuration (OS-128, blobs, refined undistortion, overlap estimator on) over 40 frames."""
