@@ -274,7 +274,7 @@ def test_vls128_pandar64_rig_dense_maps(gpu, oracle_lib, synth):
     assert st.n_points == 128 * 1800 + 64 * 1800 and st.is_keyframe == 1
 
 
-def _unverified_test_vlp16_long_sequence_rolling_map(gpu, oracle_lib, synth):
+def test_vlp16_long_sequence_rolling_map(gpu, oracle_lib, synth):
     """BASELINE configs[0] at length: 200 VLP-16 frames (150 m travelled) with default keypoints through a 250 m rolling
     grid, so that the maps roll, drop voxels and saturate while every frame stays bit-identical to the oracle; the whole
     logged trajectory agrees to 1e-6."""
