@@ -188,6 +188,7 @@ public:
     if (rc & LSB_W_SENSOR_TIME) LSB_PRINT_WARNING("No external sensor measure corresponds to the current frame acquisition (times don't match)");  // SensorConstraints.cxx:19
     if (rc & LSB_W_MOTION_LIMITS) LSB_PRINT_WARNING("The pose does not comply with the motion limits.");                                         // :1482-1483
     if (!(rc & LSB_W_FRAME_IGNORED)) { this->CurrentFrames = frames; ++this->NbrFrameProcessed; }                                               // :237, :342
+    this->PullExtractors();
   }
 
   Transform GetWorldTransform() const                                        // Slam.cxx:550-553
@@ -415,11 +416,32 @@ private:
   SamplingMode VoxelGridSamplingMode[3] = {SamplingMode::MAX_INTENSITY, SamplingMode::MAX_INTENSITY, SamplingMode::MAX_INTENSITY};
 
   void PushParams() { lsb_set_params(this->Gpu, &this->P); }
-  // the wrappers set parameters directly on the extractor objects they installed (LidarSlamNode.cxx:778-817): forward before each frame
+  // The wrappers set parameters directly on the extractor objects they installed (LidarSlamNode.cxx:778-817), so the blocks
+  // are compared with what the library last saw before each frame and forwarded only when a setter changed something.
+  std::map<std::uint8_t, lsb_ke_params> PushedExtractors;
   void PushExtractors()
   {
-    for (const auto& kv : this->KeyPointsExtractors)
-      if (kv.second) lsb_set_extractor_params(this->Gpu, kv.first, &kv.second->P);
+    for (const auto& kv : this->KeyPointsExtractors) {
+      if (!kv.second) continue;
+      auto it = this->PushedExtractors.find(kv.first);
+      if (it != this->PushedExtractors.end() && std::memcmp(&it->second, &kv.second->P, sizeof(lsb_ke_params)) == 0) continue;
+      lsb_set_extractor_params(this->Gpu, kv.first, &kv.second->P);
+      this->PushedExtractors[kv.first] = kv.second->P;
+    }
+  }
+  // The azimuthal resolution estimated from the first frame lives in the extractor object in the reference
+  // (SpinningSensorKeypointExtractor.cxx:169) and is kept from then on: mirror it so that GetAzimuthalResolution() reports
+  // it and a later parameter push carries it instead of resetting it.
+  void PullExtractors()
+  {
+    for (const auto& kv : this->KeyPointsExtractors) {
+      lsb_ke_params lib;
+      if (!kv.second || lsb_get_extractor_params(this->Gpu, kv.first, &lib) != LSB_OK) continue;
+      auto it = this->PushedExtractors.find(kv.first);
+      if (it == this->PushedExtractors.end()) continue;
+      if (std::memcmp(&it->second, &kv.second->P, sizeof(lsb_ke_params)) == 0) kv.second->P.azimuthal_resolution = lib.azimuthal_resolution;
+      it->second.azimuthal_resolution = lib.azimuthal_resolution;
+    }
   }
   template <typename F>
   PointCloud::Ptr Cloud(F&& get, const std::string& frameId) const

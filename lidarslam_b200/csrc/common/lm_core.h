@@ -278,8 +278,7 @@ LSB_HD void lm_propose(LmState& s)
     if (!ok) {
       s.num_invalid += 1;
       if (s.num_invalid >= 5) { s.done = 1; s.term = LSB_LM_FAIL_INVALID; return; }
-      s.radius = s.radius / s.decrease_factor;
-      s.decrease_factor *= 2.0;
+      s.radius = s.radius * 0.5;          // LevenbergMarquardtStrategy::StepIsInvalid: halve, decrease_factor untouched
       continue;
     }
     s.num_invalid = 0;

@@ -102,14 +102,61 @@ __device__ __forceinline__ void raw_set_time_label(PointRaw& r, double t, unsign
   r.b.w = (r.b.w & 0x00ffffffu) | (label << 24);
 }
 
+// SamplingMode::CENTROID (:266-297) couples the leaves of one Add call: after EVERY point that reaches the end of
+// the loop body (in bounds and not skipped by the fixed-point test; "effective" below) the reference re-averages
+// every leaf that has received a centroid update so far in this call with that leaf's running mean.  What a leaf
+// needs from the rest of the cloud is therefore only HOW MANY effective points arrive between its own ones.
+// Whether a point is effective depends on its own leaf alone (the leaf existed with label 1, or `fixed` set the
+// label on an earlier point of the call), so: this kernel flags the effective points (one thread per segment head,
+// flags written in arrival order), an exclusive scan turns the flags into arrival positions, and k_apply_segments
+// replays each leaf's recurrence over those positions.
+__global__ void k_centroid_effective(const unsigned long long* __restrict__ skey, const uint32_t* __restrict__ sidx, int n,
+                                     const unsigned long long* __restrict__ map_keys, const lsb_point* __restrict__ map_pts, int n_map,
+                                     unsigned fixed, uint32_t* __restrict__ eff)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned long long k = skey[i];
+  if (k == INVALID_KEY) return;            // out of bounds: eff stays 0
+  if (i > 0 && skey[i - 1] == k) return;   // not a segment head
+  const int pos = lower_bound_key(map_keys, n_map, k);
+  bool exists = pos < n_map && map_keys[pos] == k;
+  unsigned label = exists ? (reinterpret_cast<const uint4*>(map_pts)[2 * (size_t)pos + 1].w >> 24) : 0u;
+  for (int j = i; j < n && skey[j] == k; ++j) {
+    uint32_t e = 1u;
+    if (!exists) exists = true;
+    else if (label == 1u) e = 0u;
+    if (e) label = fixed;
+    eff[sidx[j]] = e;
+  }
+}
+
+// `steps` re-averaging passes of RollingGrid.cxx:282-297 on one leaf: x <- (x * c + m) / (c + 1) per coordinate,
+// in float.  The map is a contraction towards m: once a pass leaves the three coordinates unchanged every later
+// pass does too, so the loop stops there (same values as running all the passes).
+__device__ __forceinline__ void centroid_passes(PointRaw& cur, float mx, float my, float mz, uint32_t count, uint32_t steps)
+{
+  const float c = (float)count, c1 = (float)(count + 1u);
+  float x = __uint_as_float(cur.a.x), y = __uint_as_float(cur.a.y), z = __uint_as_float(cur.a.z);
+  for (uint32_t t = 0; t < steps; ++t) {
+    const float nx = (x * c + mx) / c1, ny = (y * c + my) / c1, nz = (z * c + mz) / c1;
+    const bool same = __float_as_uint(nx) == __float_as_uint(x) && __float_as_uint(ny) == __float_as_uint(y) && __float_as_uint(nz) == __float_as_uint(z);
+    x = nx; y = ny; z = nz;
+    if (same) break;
+  }
+  cur.a.x = __float_as_uint(x); cur.a.y = __float_as_uint(y); cur.a.z = __float_as_uint(z);
+}
+
 // One thread per segment head of the sorted incoming keys: replays the sequential
 // insertion rule of RollingGrid::Add for that leaf (:203-311).
 // info[0] |= updated, flags[i] = 1 for heads that create a NEW leaf.
+// CENTROID only: tpos = arrival position of every point among the effective ones (exclusive scan of eff).
 __global__ void k_apply_segments(const unsigned long long* __restrict__ skey, const uint32_t* __restrict__ sidx, int n,
                                  const lsb_point* __restrict__ cloud, unsigned long long* __restrict__ map_keys,
                                  lsb_point* __restrict__ map_pts, uint32_t* __restrict__ map_counts, int n_map, GridGeom g, int sampling,
                                  unsigned fixed, double currentTime, uint32_t* __restrict__ flags, lsb_point* __restrict__ seg_pts,
-                                 uint32_t* __restrict__ seg_counts, uint32_t* __restrict__ info)
+                                 uint32_t* __restrict__ seg_counts, uint32_t* __restrict__ info, const uint32_t* __restrict__ eff,
+                                 const uint32_t* __restrict__ tpos)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -124,12 +171,28 @@ __global__ void k_apply_segments(const unsigned long long* __restrict__ skey, co
   uint32_t count = 0;
   if (exists) { cur = load_raw(map_pts + pos); count = map_counts[pos]; }
   bool updated = false, seen = false;
+  // CENTROID: running mean of the points averaged into this leaf during this call, and the arrival position
+  // of the last point of this leaf that was processed
+  float mx = 0.f, my = 0.f, mz = 0.f;
+  uint32_t mcount = 0, last_t = 0;
+  const uint32_t T = (sampling == LSB_SAMPLING_CENTROID) ? tpos[n - 1] + eff[n - 1] : 0u;
   for (int j = i; j < n && skey[j] == k; ++j) {
     const PointRaw p = load_raw(cloud + sidx[j]);
+    if (sampling == LSB_SAMPLING_CENTROID && mcount && eff[sidx[j]]) {
+      // the effective points of OTHER leaves that arrived since this leaf's previous one
+      centroid_passes(cur, mx, my, mz, count, tpos[sidx[j]] - last_t - 1u);
+    }
     if (!exists) { cur = p; exists = true; updated = true; }
     else {
       if (raw_label(cur) == 1) continue;
-      if (sampling == LSB_SAMPLING_LAST) { cur = p; updated = true; }
+      if (sampling == LSB_SAMPLING_CENTROID) {
+        const float c = (float)mcount, c1 = (float)(mcount + 1u);
+        mx = (mx * c + __uint_as_float(p.a.x)) / c1;
+        my = (my * c + __uint_as_float(p.a.y)) / c1;
+        mz = (mz * c + __uint_as_float(p.a.z)) / c1;
+        ++mcount;
+      }
+      else if (sampling == LSB_SAMPLING_LAST) { cur = p; updated = true; }
       else if (sampling == LSB_SAMPLING_MAX_INTENSITY) {
         if (raw_intensity(p) > raw_intensity(cur)) { cur = p; updated = true; }
       } else if (sampling == LSB_SAMPLING_CENTER_POINT) {
@@ -146,9 +209,14 @@ __global__ void k_apply_segments(const unsigned long long* __restrict__ skey, co
       }
       // LSB_SAMPLING_FIRST: keep the stored point
     }
+    if (sampling == LSB_SAMPLING_CENTROID) {
+      if (mcount) centroid_passes(cur, mx, my, mz, count, 1u);   // this point's own pass, with the count before its increment
+      last_t = tpos[sidx[j]];
+    }
     raw_set_time_label(cur, currentTime, fixed);
     if (!seen) { ++count; seen = true; }
   }
+  if (sampling == LSB_SAMPLING_CENTROID && mcount) centroid_passes(cur, mx, my, mz, count, T - last_t - 1u);
   if (existed) { store_raw(map_pts + pos, cur); map_counts[pos] = count; }
   else { flags[i] = 1; store_raw(seg_pts + i, cur); seg_counts[i] = count; }
   if (updated) atomicOr(info, 1u);
@@ -367,7 +435,6 @@ void RollingGridGpu::Roll(const float mn[3], const float mx[3], cudaStream_t s, 
 void RollingGridGpu::AddBegin(const lsb_point* d_cloud, size_t n, bool roll, cudaStream_t s, LaunchCounter& lc)
 {
   if (n == 0) return;
-  if (Sampling == LSB_SAMPLING_CENTROID) throw CudaError(LSB_E_INVALID, "SamplingMode::CENTROID is not implemented on the GPU map");
   if (roll) cloud_bbox_async(d_cloud, n, d_bbox, h_bbox, s, lc);
 }
 
@@ -395,8 +462,15 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   const int end_bit = std::min(64, 32 + outer_bits);
   LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, nk_a.p, nk_b.p, ni_a.p, ni_b.p, N, 0, end_bit, s)); lc.add(2 + (end_bit + 7) / 8);
   LSB_CUDA(cudaMemsetAsync(d_info.p, 0, 8 * sizeof(uint32_t), s));
+  if (Sampling == LSB_SAMPLING_CENTROID) {
+    c_eff.reserve(n, s); c_tpos.reserve(n, s);
+    LSB_CUDA(cudaMemsetAsync(c_eff.p, 0, n * sizeof(uint32_t), s));
+    k_centroid_effective<<<G, TPB, 0, s>>>(nk_b.p, ni_b.p, N, keys.p, pts.p, (int)n_entries, fixed ? 1u : 0u, c_eff.p); LSB_LAUNCH_CHECK(); lc.add();
+    tb = cub_tmp.cap;
+    LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, c_eff.p, c_tpos.p, N, s)); lc.add(2);
+  }
   k_apply_segments<<<G, TPB, 0, s>>>(nk_b.p, ni_b.p, N, d_cloud, keys.p, pts.p, counts.p, (int)n_entries, g, Sampling, fixed ? 1u : 0u,
-                                     currentTime, flags.p, pts_b.p, counts_b.p, d_info.p);
+                                     currentTime, flags.p, pts_b.p, counts_b.p, d_info.p, c_eff.p, c_tpos.p);
   LSB_LAUNCH_CHECK(); lc.add();
   tb = cub_tmp.cap;
   LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, N, s)); lc.add(2);

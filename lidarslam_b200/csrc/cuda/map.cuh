@@ -37,6 +37,7 @@ struct RollingGridGpu {
   DevBuf<unsigned long long> nk_a, nk_b, ins_keys;
   DevBuf<uint32_t> ni_a, ni_b, flags, scan, ins_counts;
   DevBuf<lsb_point> ins_pts;
+  DevBuf<uint32_t> c_eff, c_tpos;        // SamplingMode::CENTROID: effective-point flags and their arrival positions
   DevBuf<uint32_t> d_info;               // [8]
   DevBuf<unsigned char> cub_tmp;
   PinnedBuf<uint32_t> h_info;

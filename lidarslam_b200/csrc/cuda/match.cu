@@ -310,8 +310,7 @@ __device__ __forceinline__ void lm_propose_warp(LmState& s)
     if (!ok) {
       num_invalid += 1;
       if (num_invalid >= 5) { done = 1; term = LSB_LM_FAIL_INVALID; break; }
-      radius = radius / dec;
-      dec *= 2.0;
+      radius = radius * 0.5;              // StepIsInvalid (see lm_propose)
       continue;
     }
     num_invalid = 0;

@@ -18,7 +18,9 @@ static int guarded(F&& f)
 {
   try { return f(); }
   catch (const CudaError& e) { g_last_error = e.what(); return e.code; }
+  catch (const std::bad_alloc&) { g_last_error = "out of host memory"; return LSB_E_CAPACITY; }
   catch (const std::exception& e) { g_last_error = e.what(); return LSB_E_INVALID; }
+  catch (...) { g_last_error = "unknown exception"; return LSB_E_INVALID; }
 }
 
 static Iso3d FromRowMajor(const double* T)
@@ -76,7 +78,22 @@ int lsb_reset(lsb_slam* h, int reset_log) { return guarded([&] { h->Reset(reset_
 
 int lsb_set_params(lsb_slam* h, const lsb_params* p) { h->P = *p; return LSB_OK; }
 int lsb_get_params(const lsb_slam* h, lsb_params* p) { *p = h->P; return LSB_OK; }
-int lsb_set_extractor_params(lsb_slam* h, int device_id, const lsb_ke_params* p) { return guarded([&] { h->Extractor(device_id).P = *p; return LSB_OK; }); }
+int lsb_set_extractor_params(lsb_slam* h, int device_id, const lsb_ke_params* p)
+{
+  return guarded([&] {
+    ExtractorGpu& ke = h->Extractor(device_id);
+    // An azimuthal resolution outside the usable range [1e-6, pi/4] means "estimate it from the first frame"
+    // (SpinningSensorKeypointExtractor.cxx:165-170).  A caller that pushes its whole parameter block again (the
+    // C++ mirror does so before every frame) must not throw the estimate away: the reference keeps it for the
+    // life of the extractor (:169), so an out-of-range incoming value leaves a usable stored one in place.
+    const float est = ke.P.azimuthal_resolution;
+    ke.P = *p;
+    const bool incoming_unset = !(p->azimuthal_resolution >= 1e-6f && p->azimuthal_resolution <= 0.78539816339744830962f);
+    const bool stored_usable = est >= 1e-6f && est <= 0.78539816339744830962f;
+    if (incoming_unset && stored_usable) ke.P.azimuthal_resolution = est;
+    return LSB_OK;
+  });
+}
 int lsb_get_extractor_params(const lsb_slam* h, int device_id, lsb_ke_params* p)
 {
   auto it = h->KeyPointsExtractors.find(device_id);
@@ -98,6 +115,7 @@ int lsb_set_voxel_grid_decaying_threshold(lsb_slam* h, double s) { for (auto& m 
 int lsb_set_voxel_grid_sampling_mode(lsb_slam* h, int k, int mode)
 {
   if (k < 0 || k > 2) return LSB_E_INVALID;
+  if (mode < LSB_SAMPLING_FIRST || mode > LSB_SAMPLING_CENTROID) { g_last_error = "unknown SamplingMode"; return LSB_E_INVALID; }   // rejected here, not in the middle of a frame
   h->LocalMaps[k].Sampling = mode;
   return LSB_OK;
 }

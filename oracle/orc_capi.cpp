@@ -40,7 +40,16 @@ ORC_API void orc_destroy(Slam* h) { delete h; }
 ORC_API int orc_reset(Slam* h, int resetLog) { h->Reset(resetLog != 0); return 0; }
 ORC_API int orc_set_params(Slam* h, const lsb_params* p) { h->P = *p; return 0; }
 ORC_API int orc_get_params(const Slam* h, lsb_params* p) { *p = h->P; return 0; }
-ORC_API int orc_set_extractor_params(Slam* h, int dev, const lsb_ke_params* p) { h->KeyPointsExtractors[dev].P = *p; return 0; }
+ORC_API int orc_set_extractor_params(Slam* h, int dev, const lsb_ke_params* p)
+{
+  // same rule as lsb_set_extractor_params: an out-of-range incoming resolution keeps a usable estimate (SSKE.cxx:165-170)
+  lsb_ke_params& P = h->KeyPointsExtractors[dev].P;
+  const float est = P.azimuthal_resolution;
+  P = *p;
+  const bool unset = !(p->azimuthal_resolution >= 1e-6f && p->azimuthal_resolution <= 0.78539816339744830962f);
+  if (unset && est >= 1e-6f && est <= 0.78539816339744830962f) P.azimuthal_resolution = est;
+  return 0;
+}
 ORC_API int orc_get_extractor_params(Slam* h, int dev, lsb_ke_params* p)
 {
   if (!h->KeyPointsExtractors.count(dev)) return LSB_E_INVALID;
@@ -307,6 +316,40 @@ ORC_API int orc_lm_solve_sensors(const double* A9, const double* P3, const doubl
   *accepted_out = opt.State.num_successful;
   *term_out = opt.State.term;
   return opt.State.iter;
+}
+// the same with the per-evaluation trace (rows of 5 doubles, see Optimizer::Trace) and the normal matrix at the solution
+ORC_API int orc_lm_solve_trace(const double* A9, const double* P3, const double* X3, const double* w, long n, const double* x0, double sat,
+                               int max_iter, int two_d, int threads, double* x_out, double* cost_out, int* accepted_out, int* term_out,
+                               double* trace_out, int trace_cap, int* trace_rows, double* H21_out)
+{
+  Optimizer opt;
+  opt.TwoDMode = two_d != 0;
+  opt.LMMaxIter = (unsigned)max_iter;
+  opt.NbThreads = threads > 0 ? threads : 1;
+  opt.Sat = sat;
+  for (int i = 0; i < 6; ++i) opt.PoseArray[i] = x0[i];
+  for (long i = 0; i < n; ++i) {
+    lsb::LmRecord r;
+    lsb::lm_record_set(r, A9 + 9 * i, P3 + 3 * i, X3 + 3 * i, w[i]);
+    opt.Records.push_back(r);
+  }
+  opt.Solve();
+  for (int i = 0; i < 6; ++i) x_out[i] = opt.State.x[i];
+  *cost_out = opt.State.cost;
+  *accepted_out = opt.State.num_successful;
+  *term_out = opt.State.term;
+  const int rows = std::min<int>((int)opt.Trace.size(), trace_cap);
+  for (int r = 0; r < rows; ++r)
+    for (int c = 0; c < 5; ++c) trace_out[5 * r + c] = opt.Trace[r][c];
+  *trace_rows = (int)opt.Trace.size();
+  if (H21_out) for (int i = 0; i < 21; ++i) H21_out[i] = opt.State.H[i];
+  return opt.State.iter;
+}
+// LocalOptimizer::EstimateRegistrationError on a given normal matrix (upper triangle, row-major, 21 entries)
+ORC_API int orc_registration_error(const double* H21, int two_d, lsb_registration_error* out)
+{
+  lsb::registration_error_from_normal_matrix(H21, two_d, out);
+  return 0;
 }
 ORC_API int orc_lm_solve(const double* A9, const double* P3, const double* X3, const double* w, long n, const double* x0, double sat,
                          int max_iter, int two_d, int threads, double* x_out, double* cost_out, int* accepted_out, int* term_out)

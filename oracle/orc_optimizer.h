@@ -4,8 +4,10 @@
 // restatement of Ceres, shared with the GPU on purpose); this file provides the
 // sequential CPU evaluation in the canonical reduction order.
 #pragma once
+#include <array>
 #include <cstdio>
 #include <cstdlib>
+#include <vector>
 #include "orc_matcher.h"
 #include "../lidarslam_b200/csrc/common/lm_core.h"
 #include "../lidarslam_b200/csrc/common/lm_covariance.h"
@@ -21,6 +23,9 @@ struct Optimizer {
   std::vector<lsb::LmRecord> Records;   // index-aligned with the matcher output, w < 0 = no residual
   lsb::LmState State;
   int NumEvaluations = 0;
+  // one row per candidate evaluation: {iteration, cost at x, cost at the candidate, radius used for the step, accepted (1/0)}
+  // (tests compare the accept / reject sequence with an independent numpy restatement of the trust-region loop)
+  std::vector<std::array<double, 5>> Trace;
   lsb::LmSensorTerms SensorTerms;        // wheel-odometer / IMU gravity blocks (Slam.cxx:1123-1131), none by default
   Optimizer() { lsb::lm_sensor_terms_clear(SensorTerms); }
 
@@ -89,10 +94,14 @@ struct Optimizer {
     Evaluate(State.x, E);
     lsb::lm_first_eval(State, E);
     const bool trace = std::getenv("ORC_LM_TRACE") != nullptr;   // debugging aid: one line per evaluation on stderr
+    Trace.clear();
     while (!State.done) {
       Evaluate(State.xc, E);
+      Trace.push_back({(double)State.iter, State.cost, E[27], State.radius, 0.0});
       if (trace) std::fprintf(stderr, "[orc lm] iter %d cost %.12g -> %.12g radius %.3g step %.3g\n", State.iter, State.cost, E[27], State.radius, State.step_norm);
+      const int accepted_before = State.num_successful;
       lsb::lm_next_eval(State, E);
+      Trace.back()[4] = (State.num_successful > accepted_before) ? 1.0 : 0.0;
     }
     if (trace) std::fprintf(stderr, "[orc lm] done: iter %d accepted %d term %d n %zu\n", State.iter, State.num_successful, State.term, Records.size());
     for (int i = 0; i < 6; ++i) PoseArray[i] = State.x[i];

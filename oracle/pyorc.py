@@ -99,3 +99,28 @@ def lm_solve(A, P, X, w, x0, sat, max_iter=15, two_d=False, threads=1, wheel=Non
                                      C.c_double(sat), C.c_int(max_iter), C.c_int(1 if two_d else 0), C.c_int(threads), capi._ptr(sensor),
                                      capi._ptr(x), C.byref(cost), C.byref(acc), C.byref(term))
     return dict(x=x, cost=cost.value, iterations=it, accepted=acc.value, term=term.value)
+
+
+def lm_solve_trace(A, P, X, w, x0, sat, max_iter=15, two_d=False, threads=1):
+    """lm_solve plus the per-evaluation trace (rows: iteration, cost at x, cost at the candidate, radius, accepted) and the
+    upper triangle of the normal matrix at the solution."""
+    A = np.ascontiguousarray(A, dtype=np.float64).reshape(-1, 9)
+    P = np.ascontiguousarray(P, dtype=np.float64).reshape(-1, 3)
+    X = np.ascontiguousarray(X, dtype=np.float64).reshape(-1, 3)
+    w = np.ascontiguousarray(w, dtype=np.float64)
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    x, H = np.zeros(6), np.zeros(21)
+    trace = np.zeros((max_iter + 8, 5))
+    cost, acc, term, rows = C.c_double(), C.c_int(), C.c_int(), C.c_int()
+    it = load().orc_lm_solve_trace(capi._ptr(A), capi._ptr(P), capi._ptr(X), capi._ptr(w), C.c_long(len(A)), capi._ptr(x0), C.c_double(sat),
+                                   C.c_int(max_iter), C.c_int(1 if two_d else 0), C.c_int(threads), capi._ptr(x), C.byref(cost),
+                                   C.byref(acc), C.byref(term), capi._ptr(trace), C.c_int(len(trace)), C.byref(rows), capi._ptr(H))
+    return dict(x=x, cost=cost.value, iterations=it, accepted=acc.value, term=term.value, trace=trace[:rows.value], H=H)
+
+
+def registration_error(H21, two_d=False):
+    """LocalOptimizer::EstimateRegistrationError on a given 6x6 normal matrix (21 upper-triangle entries, row-major)."""
+    H = np.ascontiguousarray(H21, dtype=np.float64)
+    err = capi.RegistrationError()
+    load().orc_registration_error(capi._ptr(H), C.c_int(1 if two_d else 0), C.byref(err))
+    return err

@@ -14,7 +14,7 @@ def _frame(synth, sensor="tiny", idx=0, seed=1234):
     return seq.frame(synth.sensor(sensor), idx)
 
 
-@pytest.mark.parametrize("sensor", ["tiny", "vlp16", "hdl64"])
+@pytest.mark.parametrize("sensor", ["tiny", "vlp16", "hdl64", "os128", "vls128", "pandar64"])
 def test_extractor_bit_exact(gpu, oracle_lib, synth, sensor):
     pts, _, _ = _frame(synth, sensor)
     g, o = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
@@ -145,7 +145,7 @@ def test_undistort_bit_exact(gpu, oracle_lib, synth):
     assert a.tobytes() != pts.tobytes()
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
 def test_map_add_bit_exact(gpu, oracle_lib, synth, mode):
     g, o = gpu(), oracle_lib.Oracle()
     for s in (g, o):
@@ -164,6 +164,38 @@ def test_map_add_bit_exact(gpu, oracle_lib, synth, mode):
             a, b = g.GetMap(k), o.GetMap(k)
             assert len(a) == len(b) and len(a) > 1000
             assert a.tobytes() == b.tobytes(), "map %d differs after add %d" % (k, i)
+
+
+def test_map_centroid_sampling(gpu, oracle_lib):
+    """SamplingMode::CENTROID (RollingGrid.cxx:266-297): the per-point re-averaging couples the leaves of one Add call
+    through the arrival order.  Dense clusters (many points per leaf), leaves touched over several calls (count > 1),
+    fixed points (later points of a fixed leaf are skipped and do not advance the re-averaging), out-of-grid points."""
+    rng = np.random.default_rng(5)
+
+    def cloud(n, spread, centres):
+        p = np.zeros(n, dtype=capi.POINT_DTYPE)
+        c = np.asarray(centres, np.float64)[rng.integers(0, len(centres), n)]
+        xyz = (c + rng.normal(0, spread, (n, 3))).astype(np.float32)
+        p["x"], p["y"], p["z"], p["w"] = xyz[:, 0], xyz[:, 1], xyz[:, 2], 1.0
+        p["intensity"] = rng.uniform(0, 255, n).astype(np.float32)
+        p["laser_id"] = rng.integers(0, 16, n)
+        return p
+
+    g, o = gpu(), oracle_lib.Oracle()
+    for s in (g, o):
+        s.SetVoxelGridSamplingMode(1, 4)
+    centres = rng.uniform(-30, 30, (40, 3))
+    steps = [(4000, 0.4, False), (4000, 0.4, False), (3000, 0.8, True), (5000, 0.5, False), (2000, 300.0, False), (4000, 0.3, False)]
+    for i, (n, spread, fixed) in enumerate(steps):
+        c = cloud(n, spread, centres)
+        g.MapAdd(1, c, fixed, 0.1 * i)
+        o.MapAdd(1, c, fixed, 0.1 * i)
+        a, b = g.GetMap(1), o.GetMap(1)
+        assert len(a) == len(b) and len(a) > 500
+        assert a.tobytes() == b.tobytes(), "centroid map differs after add %d" % i
+    assert (a["label"] == 1).any() and (a["label"] == 0).any()
+    # the stored points are averages, not input points
+    assert g.GetMap(1, True).tobytes() == o.GetMap(1, True).tobytes()
 
 
 def test_map_roll_drops_voxels(gpu, oracle_lib):
