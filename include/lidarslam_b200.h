@@ -239,6 +239,9 @@ LSB_API int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s);
  * otherwise run on their own streams, are serialised on the handle's stream so that the
  * durations are those of the kernels alone (slower frames: not for throughput runs). */
 LSB_API int lsb_set_profiling(lsb_slam* h, int on);
+/* how many times the extractor of device_id estimated its azimuthal resolution from a frame (SSKE.cxx:165-170, 593-637):
+ * 1 after the first frame unless the caller set a usable value (then 0) or reset it */
+LSB_API unsigned int lsb_get_azimuth_estimations(const lsb_slam* h, int device_id);
 LSB_API float lsb_get_overlap(const lsb_slam* h);                                              /* Slam::GetOverlapEstimation */
 LSB_API int lsb_get_comply_motion_limits(const lsb_slam* h);                                   /* Slam::GetComplyMotionLimits (Slam.h:394) */
 LSB_API unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h);                       /* Slam.h TotalMatchedKeypoints */

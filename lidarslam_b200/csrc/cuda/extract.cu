@@ -473,6 +473,7 @@ void ExtractorGpu::compute(const lsb_point* d_pts, size_t n_, cudaStream_t s, La
   // azimuthal resolution (:169): estimated when outside [1e-6, pi/4]
   float az = P.azimuthal_resolution;
   if (az < 1e-6 || M_PI / 4. < az) {
+    ++az_estimations;
     az_angles.reserve(n, s); az_sorted.reserve(n, s);
     k_az_angles<<<G, TPB, 0, s>>>(p4.p, key_b.p, N, az_angles.p); LSB_LAUNCH_CHECK(); lc.add();
     tb = cub_tmp.cap;

@@ -14,6 +14,7 @@ struct ExtractorGpu {
   size_t n = 0;                    // points of the last frame
   unsigned nb_rings = 0;           // max laser_id + 1 (never shrinks, SSKE.cxx:156-164)
   uint32_t counts[3] = {0, 0, 0};  // keypoints per type of the last frame
+  unsigned az_estimations = 0;     // times the azimuthal resolution was estimated (once per extractor unless reset, SSKE.cxx:169)
   double time_min[3] = {0, 0, 0}, time_max[3] = {0, 0, 0};   // range of their `time` field (valid where counts[k] > 0)
 
   // ring-major ("scan line") order: position j <-> (ring, index in ring)

@@ -162,13 +162,23 @@ struct QueryCell {
   bool finite;
 };
 
+// The pose that moves the keypoints to the target's frame: a kernel argument, or (device-resident ICP loop, cuda/icp.cuh)
+// the pose the previous solve left in device memory.  `done` set = the loop is over, the kernel returns at once.
+struct KnnPose {
+  Iso3d value;
+  const Iso3d* dev;
+  const int* done;
+};
+__device__ __forceinline__ bool knn_off(const KnnPose& kp) { return kp.done && *kp.done; }
+
 template <bool FROM_POINTS>
-__device__ __forceinline__ QueryCell make_query(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, const Iso3d& prior, int i,
+__device__ __forceinline__ QueryCell make_query(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, const KnnPose& pose, int i,
                                                 const KnnGridParams& gp)
 {
   QueryCell q;
   if (FROM_POINTS) {
     const float4 p = reinterpret_cast<const float4*>(kp)[2 * (size_t)i];
+    const Iso3d prior = pose.dev ? *pose.dev : pose.value;
     const Vec3d w = apply(prior, Vec3d((double)p.x, (double)p.y, (double)p.z));
     q.qx = (float)w.x; q.qy = (float)w.y; q.qz = (float)w.z;
   } else {
@@ -223,11 +233,12 @@ __constant__ unsigned char c_cube_order[28] = {13, 12, 14, 10, 16, 4, 22, 9, 11,
 // is what the warp kernel below starts from.
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
-k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
+k_knn(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, KnnPose prior, int nq, KnnGridParams gp,
       const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, size_t qs, size_t ts, int32_t* __restrict__ idx_out,
       float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
 {
   constexpr unsigned FULL = 0xffffffffu;
+  if (knn_off(prior)) return;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int sub = t & 3;
   const bool live = (t >> 2) < nq;
@@ -300,7 +311,7 @@ __constant__ unsigned char c_row_order[9] = {4, 1, 7, 3, 5, 0, 2, 6, 8};   // (d
 
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
-k_knn_stream(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, int nq, KnnGridParams gp,
+k_knn_stream(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, KnnPose prior, int nq, KnnGridParams gp,
              const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int k, size_t qs, size_t ts,
              int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out, int32_t* __restrict__ unres_list,
              unsigned* __restrict__ unres_count)
@@ -308,6 +319,7 @@ k_knn_stream(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, 
   constexpr unsigned FULL = 0xffffffffu;
   __shared__ uint32_t s_rb[9][128], s_re[9][128];
   __shared__ float s_rl[9][128];
+  if (knn_off(prior)) return;
   const int tid = threadIdx.x;
   const int i0 = blockIdx.x * blockDim.x + tid;
   const bool live = i0 < nq;
@@ -464,13 +476,14 @@ constexpr int WARP_BUF = 128;
 
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
-k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
+k_knn_warp(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, KnnPose prior, KnnGridParams gp,
            const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, int m, int k, int rcap, int capped, float cap2,
            size_t qs, size_t ts, int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
            const int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count, int32_t* __restrict__ bf_list, unsigned bf_cap)
 {
   __shared__ Key s_keys[4][WARP_BUF];
   __shared__ int s_cnt[4];
+  if (knn_off(prior)) return;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const unsigned count = unres_count[0];
   while (true) {
@@ -580,12 +593,13 @@ constexpr int BF_SEGS = 16;
 
 template <int KMAX, bool FROM_POINTS>
 __global__ void __launch_bounds__(128)
-k_knn_brute(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, Iso3d prior, KnnGridParams gp,
+k_knn_brute(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, KnnPose prior, KnnGridParams gp,
             const float4* __restrict__ sorted, int m, int k, size_t qs, size_t ts, int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
             int32_t* __restrict__ nfound_out, const int32_t* __restrict__ bf_list, unsigned* __restrict__ unres_count,
             Key* __restrict__ partial, unsigned* __restrict__ tickets, unsigned bf_cap)
 {
   constexpr unsigned FULL = 0xffffffffu;
+  if (knn_off(prior)) return;
   const int lane = threadIdx.x & 31;
   const unsigned nbf = min(unres_count[2], bf_cap);
   const unsigned nitems = nbf * BF_SEGS;
@@ -640,9 +654,13 @@ k_knn_brute(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, I
 }
 
 template <bool FROM_POINTS>
-void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso3d& prior, size_t nq, int k, float cap_dist, int32_t* idx,
-                float* d2, int32_t* nf, bool entry_major, cudaStream_t s, LaunchCounter& lc)
+void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso3d& prior_host, size_t nq, int k, float cap_dist, int32_t* idx,
+                float* d2, int32_t* nf, bool entry_major, cudaStream_t s, LaunchCounter& lc, const KnnDeviceArgs* da)
 {
+  KnnPose prior;
+  prior.value = prior_host;
+  prior.dev = da ? da->prior : nullptr;
+  prior.done = da ? da->done : nullptr;
   const size_t qs = entry_major ? 1 : (size_t)k, ts = entry_major ? nq : 1;
   const unsigned G = div_up(nq * 4, 128);   // four lanes per query
   const int NQ = (int)nq, M = (int)g.m;
@@ -775,11 +793,11 @@ void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t
     k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
-  launch_knn<false>(*this, d_q, nullptr, Iso3d::identity(), nq, k, cap_dist, d_idx, d_d2, d_nf, entry_major, s, lc);
+  launch_knn<false>(*this, d_q, nullptr, Iso3d::identity(), nq, k, cap_dist, d_idx, d_d2, d_nf, entry_major, s, lc, nullptr);
 }
 
 void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, float cap_dist, int32_t* d_idx, float* d_d2,
-                            int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc) const
+                            int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc, const KnnDeviceArgs* da) const
 {
   if (nq == 0) return;
   if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
@@ -787,7 +805,7 @@ void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior
     k_fill_empty<<<div_up(nq * k, TPB), TPB, 0, s>>>(d_idx, d_d2, d_nf, nq * k, nq); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
-  launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, cap_dist, d_idx, d_d2, d_nf, entry_major, s, lc);
+  launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, cap_dist, d_idx, d_d2, d_nf, entry_major, s, lc, da);
 }
 
 }  // namespace lsb

@@ -18,6 +18,14 @@ struct KnnGridParams {
   int nx, ny, nz;
 };
 
+// Device-side inputs of a search inside the device-resident ICP loop (cuda/icp.cuh), all nullable
+struct KnnDeviceArgs {
+  const Iso3d* prior = nullptr;   // pose in device memory that moves the keypoints (overrides the host `prior`)
+  const int* done = nullptr;      // when *done != 0 the search kernels return at once (outputs untouched)
+  bool reuse = false;             // idx_out / d2_out / nfound_out still hold the lists of the same queries against the same
+                                  // target at a slightly different pose: they bound the search
+};
+
 struct KnnGrid {
   const lsb_point* cloud = nullptr;   // device, not owned; indices refer to this order
   size_t m = 0;
@@ -53,7 +61,7 @@ struct KnnGrid {
   // kNN of the keypoints kp[0..nq) moved by `prior` in double then cast to float
   // (KeypointsMatcher.cxx:118 + KDTreePCLAdaptor.h:96-101).
   void search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior, int k, float cap_dist, int32_t* d_idx_out, float* d_d2_out,
-                     int32_t* d_nfound_out, bool entry_major, cudaStream_t s, LaunchCounter& lc) const;
+                     int32_t* d_nfound_out, bool entry_major, cudaStream_t s, LaunchCounter& lc, const KnnDeviceArgs* da = nullptr) const;
 };
 
 }  // namespace lsb

@@ -74,8 +74,9 @@ template <int TYPE>
 __global__ void __launch_bounds__(FIT_TPB)
 k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cloud, const int32_t* __restrict__ nn_idx,
       const float* __restrict__ nn_d2, const int32_t* __restrict__ nn_found, int k, FitParams fp, double* __restrict__ records, size_t rec_stride,
-      uint8_t* __restrict__ status, double* __restrict__ weight, int* __restrict__ hist)
+      uint8_t* __restrict__ status, double* __restrict__ weight, int* __restrict__ hist, const int* __restrict__ done)
 {
+  if (done && *done) return;   // device-resident ICP loop: the loop ended in an earlier iteration (cuda/icp.cuh)
   __shared__ int s_hist[LSB_MATCH_N_STATUS];
   if (threadIdx.x < LSB_MATCH_N_STATUS) s_hist[threadIdx.x] = 0;
   __syncthreads();
@@ -192,8 +193,10 @@ k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cl
 }
 
 // target empty: MatchingResults::Reset values (KeypointsMatcher.h:108-118)
-__global__ void k_fit_empty(int nq, double* __restrict__ records, size_t rec_stride, uint8_t* __restrict__ status, double* __restrict__ weight)
+__global__ void k_fit_empty(int nq, double* __restrict__ records, size_t rec_stride, uint8_t* __restrict__ status, double* __restrict__ weight,
+                            const int* __restrict__ done)
 {
+  if (done && *done) return;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nq) return;
   records[REC_W * rec_stride + i] = -1.0;
@@ -462,7 +465,8 @@ __device__ unsigned long long g_lm_probe[64 * 5];
 __global__ void __launch_bounds__(LM_THREADS, 1)
 k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nchunks, int pstride, double sat, LmStart start, int max_iter,
            int two_d, const int* __restrict__ hist, unsigned min_matches, LmState* __restrict__ state_out, double* __restrict__ part,
-           unsigned* __restrict__ bar, const LmSensorTerms terms, MatchWorkspace::LmHostBlock* host_out, unsigned host_seq)
+           unsigned* __restrict__ bar, const LmSensorTerms terms, MatchWorkspace::LmHostBlock* host_out, unsigned host_seq,
+           IcpState* __restrict__ icp, const IcpCtl ctl)
 {
   constexpr int NW = (int)(sizeof(LmState) / 8), NP = (int)(sizeof(LmPoint) / 8);
   static_assert(sizeof(LmState) % 8 == 0 && sizeof(LmPoint) % 8 == 0, "copied as 64-bit words");
@@ -474,13 +478,32 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
   LmState& s_state = *reinterpret_cast<LmState*>(s_state_raw);
   const LmPoint& s_pt = *reinterpret_cast<const LmPoint*>(s_pt_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ int s_off;
+  __shared__ unsigned s_matched;
+
+  // Device-resident ICP loop: when an earlier iteration ended the loop this launch does nothing.  The flag is read by one
+  // thread per CTA (CTA 0 raises it at its tail; a CTA still in its prologue then can only be one whose solve never
+  // starts, see below), and a CTA that stands aside still takes part in the exit count that re-arms the barrier.
+  if (threadIdx.x == 0) s_off = (icp && icp->done) ? 1 : 0;
+  __syncthreads();
+  if (s_off) {
+    if (threadIdx.x == 0) {
+      const unsigned t = atomicAdd(bar + 1, 1u);
+      if (t == gridDim.x - 1) { bar[0] = 0u; bar[1] = 0u; __threadfence(); }
+    }
+    return;
+  }
 
   // prologue: initial state (lm_begin + the "enough matches" gate of the caller) and first chunk
   if (warp == 0) {
     if (lane == 0) {
-      lm_begin(s_state, start.x, max_iter, two_d);
+      double x0[6];
+      if (icp) iso_to_xyzrpy(ctl.stage == ICP_STAGE_LOC ? icp->Tworld : icp->Trelative, x0);   // LocalOptimizer::SetPosePrior (:44-48)
+      else for (int q = 0; q < 6; ++q) x0[q] = start.x[q];
+      lm_begin(s_state, x0, max_iter, two_d);
       unsigned matched = 0;
       for (int t = 0; t < 3; ++t) matched += (unsigned)hist[t * LSB_MATCH_N_STATUS + LSB_MATCH_SUCCESS];
+      s_matched = matched;
       if (matched < min_matches) { s_state.done = 1; s_state.term = LSB_LM_SKIPPED; }
     }
     __syncwarp();
@@ -564,9 +587,25 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
   }
   if (blockIdx.x == 0) {
     if (threadIdx.x < NW) reinterpret_cast<unsigned long long*>(state_out)[threadIdx.x] = s_state_raw[threadIdx.x];
-    if (host_out) {     // every CTA holds the final state: CTA 0 hands it (and the histograms) to the host, then raises the flag
+    // between two ICP iterations: pose update, undistortion refinement, the break tests (cuda/icp.cuh), by one thread
+    __shared__ int s_hand_over;
+    if (threadIdx.x == 0) {
+      s_hand_over = 1;
+      if (icp) {
+        IcpState st = *icp;
+        icp_control(st, ctl, s_state, s_matched);
+        *icp = st;
+        s_hand_over = st.done;
+      }
+    }
+    __syncthreads();
+    if (host_out && s_hand_over) {     // the loop is over: CTA 0 hands the results to the host, then raises the flag
+      constexpr int NI = (int)(sizeof(IcpState) / 8);
+      static_assert(sizeof(IcpState) % 8 == 0, "copied as 64-bit words");
       if (threadIdx.x < NW) reinterpret_cast<volatile unsigned long long*>(&host_out->state)[threadIdx.x] = s_state_raw[threadIdx.x];
       if (threadIdx.x < 3 * LSB_MATCH_N_STATUS) reinterpret_cast<volatile int*>(host_out->hist)[threadIdx.x] = hist[threadIdx.x];
+      if (icp) for (int j = threadIdx.x; j < NI; j += LM_THREADS)
+        reinterpret_cast<volatile unsigned long long*>(&host_out->icp)[j] = reinterpret_cast<const unsigned long long*>(icp)[j];
       __threadfence_system();
       __syncthreads();
       if (threadIdx.x == 0) { *reinterpret_cast<volatile unsigned*>(&host_out->seq) = host_seq; __threadfence_system(); }
@@ -582,7 +621,7 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
 }  // namespace
 
 // ============================================================== host side ====
-void MatchWorkspace::begin_iteration(const size_t nk[3], cudaStream_t s)
+void MatchWorkspace::begin_frame(const size_t nk[3], int n_iters, cudaStream_t s)
 {
   off[0] = 0;
   for (int k = 0; k < 3; ++k) off[k + 1] = off[k] + nk[k];
@@ -593,22 +632,25 @@ void MatchWorkspace::begin_iteration(const size_t nk[3], cudaStream_t s)
   }
   rec_stride = (total + 31) / 32 * 32;
   records.reserve(std::max<size_t>(REC_PLANES * rec_stride, REC_PLANES), s); status.reserve(total, s); weight.reserve(total, s);
-  hist.reserve(3 * LSB_MATCH_N_STATUS, s);
-  h_hist.reserve(3 * LSB_MATCH_N_STATUS);
-  LSB_CUDA(cudaMemsetAsync(hist.p, 0, 3 * LSB_MATCH_N_STATUS * sizeof(int), s));
+  // one histogram block per ICP iteration: an iteration that comes after the loop's break leaves everything untouched
+  hist_iters = std::max(n_iters, 1);
+  hist.reserve((size_t)hist_iters * kHistBlock, s);
+  h_hist.reserve(kHistBlock);
+  LSB_CUDA(cudaMemsetAsync(hist.p, 0, (size_t)hist_iters * kHistBlock * sizeof(int), s));
 }
 
 void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, const KnnGrid& target, const Iso3d& prior,
-                                const lsb_match_params& mp, cudaStream_t s, LaunchCounter& lc)
+                                const lsb_match_params& mp, cudaStream_t s, LaunchCounter& lc, int icp_iter, const IcpState* icp, bool reuse)
 {
   if (nk == 0) return;
   double* rec = records.p + off[type];
   uint8_t* st = status.p + off[type];
   double* wt = weight.p + off[type];
-  int* h = hist.p + type * LSB_MATCH_N_STATUS;
+  int* h = hist.p + (size_t)icp_iter * kHistBlock + type * LSB_MATCH_N_STATUS;
+  const int* done = icp ? &icp->done : nullptr;
   const unsigned G = div_up(nk, FIT_TPB);
   if (target.empty()) {
-    k_fit_empty<<<G, FIT_TPB, 0, s>>>((int)nk, rec, rec_stride, st, wt); LSB_LAUNCH_CHECK(); lc.add();
+    k_fit_empty<<<G, FIT_TPB, 0, s>>>((int)nk, rec, rec_stride, st, wt, done); LSB_LAUNCH_CHECK(); lc.add();
     return;
   }
   FitParams fp;
@@ -629,13 +671,18 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
   // planes / blobs only need neighbours within MaxNeighborsDistance (else NEIGHBORS_TOO_FAR);
   // the line neighbourhood selection needs the exact k nearest whatever their distance
   const float cap = (type == LSB_EDGE) ? -1.f : (float)mp.max_neighbors_distance * 1.0001f + 1e-3f;
-  target.search_points(d_kp, nk, prior, k, cap, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, /*entry_major=*/true, s, lc);
+  KnnDeviceArgs da;
+  // the pose the queries are moved by: of the device-resident loop (Tworld for the localization, Trelative for the ego-motion), or `prior`
+  da.prior = icp ? (icp_stage == ICP_STAGE_LOC ? &icp->Tworld : &icp->Trelative) : nullptr;
+  da.done = done;
+  da.reuse = reuse;
+  target.search_points(d_kp, nk, prior, k, cap, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, /*entry_major=*/true, s, lc, &da);
   t_knn.end(s);
   const int NQ = (int)nk;
   t_fit.begin(s);
-  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h);
-  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h);
-  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h);
+  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done);
+  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done);
+  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done);
   LSB_LAUNCH_CHECK(); lc.add();
   t_fit.end(s);
 }
@@ -643,14 +690,14 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
 void MatchWorkspace::read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s)
 {
   d2h_bytes += 3 * LSB_MATCH_N_STATUS * sizeof(int);
-  LSB_CUDA(cudaMemcpyAsync(h_hist.p, hist.p, 3 * LSB_MATCH_N_STATUS * sizeof(int), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaMemcpyAsync(h_hist.p, hist.p, 3 * LSB_MATCH_N_STATUS * sizeof(int), cudaMemcpyDeviceToHost, s));   // block of iteration 0
   LSB_CUDA(cudaStreamSynchronize(s));
   for (int t = 0; t < 3; ++t)
     for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) hist_out[t][q] = h_hist.p[t * LSB_MATCH_N_STATUS + q];
 }
 
-LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches,
-                              int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc, const LmSensorTerms* sensor_terms)
+void MatchWorkspace::enqueue_solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches, cudaStream_t s,
+                                   LaunchCounter& lc, const LmSensorTerms* sensor_terms, IcpState* icp, const IcpCtl* ctl)
 {
   const int n = (int)total;
   LmSensorTerms terms;
@@ -670,13 +717,15 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   part_a.reserve((size_t)2 * pstride * LSB_LM_NSUM, s);
   lm_state.reserve(1, s); h_lm.reserve(1);
   if (!h_block.p) { h_block.reserve(1); h_block.p->seq = 0; }
-  const unsigned seq = ++solve_seq ? solve_seq : ++solve_seq;   // never 0 (the initial value of the flag)
   if (!lm_counter.p) {           // [arrivals, exits] of the grid barrier: zero between solves
     lm_counter.reserve(2, s);
     LSB_CUDA(cudaMemsetAsync(lm_counter.p, 0, 2 * sizeof(unsigned), s));
   }
   LmStart start;
-  for (int i = 0; i < 6; ++i) start.x[i] = x0[i];
+  for (int i = 0; i < 6; ++i) start.x[i] = x0 ? x0[i] : 0.0;
+  IcpCtl c{};
+  if (ctl) c = *ctl;
+  const int iter = ctl ? ctl->icp_iter : 0;
   t_lm.begin(s);
   // one cooperative launch = the whole LM loop (co-residency of the grid is what the barrier needs)
   cudaLaunchAttribute attr;
@@ -690,12 +739,24 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
   LSB_CUDA(cudaLaunchKernelEx(&cfg, k_lm_solve, (const double*)records.p, rec_stride, n, nchunks, pstride, saturation, start, max_iter, two_d,
-                              (const int*)hist.p, min_matches, lm_state.p, part_a.p, lm_counter.p, terms, h_block.p, seq));
+                              (const int*)(hist.p + (size_t)iter * kHistBlock), min_matches, lm_state.p, part_a.p, lm_counter.p, terms, h_block.p,
+                              solve_seq, icp, c));
   lc.add();
   t_lm.end(s);
-  d2h_bytes += sizeof(LmState) + 3 * LSB_MATCH_N_STATUS * sizeof(int);
+}
+
+unsigned MatchWorkspace::next_solve_seq()
+{
+  if (!h_block.p) { h_block.reserve(1); h_block.p->seq = 0; }
+  return solve_seq = (++solve_seq ? solve_seq : ++solve_seq);   // never 0 (the initial value of the flag)
+}
+
+const MatchWorkspace::LmHostBlock& MatchWorkspace::wait_result(cudaStream_t s)
+{
+  d2h_bytes += sizeof(LmHostBlock);
   // wait for the kernel's own hand-off (no copy, no stream synchronisation); the stream is queried now and then so that a
   // failed launch surfaces as an error instead of an endless wait
+  const unsigned seq = solve_seq;
   volatile unsigned* flag = &h_block.p->seq;
   for (unsigned spins = 1; *flag != seq; ++spins) {
     if ((spins & 4095u) == 0) {
@@ -705,7 +766,15 @@ LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, doubl
     }
   }
   std::atomic_thread_fence(std::memory_order_acquire);
-  const LmHostBlock& blk = *h_block.p;
+  return *h_block.p;
+}
+
+LmState MatchWorkspace::solve(const double x0[6], int max_iter, int two_d, double saturation, unsigned min_matches,
+                              int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s, LaunchCounter& lc, const LmSensorTerms* sensor_terms)
+{
+  next_solve_seq();
+  enqueue_solve(x0, max_iter, two_d, saturation, min_matches, s, lc, sensor_terms, nullptr, nullptr);
+  const LmHostBlock& blk = wait_result(s);
   for (int t = 0; t < 3; ++t)
     for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) hist_out[t][q] = blk.hist[t * LSB_MATCH_N_STATUS + q];
   LmState st;

@@ -60,6 +60,23 @@ __global__ void k_undistort(lsb_point* __restrict__ pts, int n, Interpolator it,
   store_xyz(pts + i, x, y, z);
 }
 
+// Undistortion refinement of the device-resident ICP loop (cuda/icp.cuh): the interpolator is the one icp_control left in
+// device memory.  mode 0 = head of an ICP iteration (applies unless the loop is over), mode 1 = after the loop (applies
+// when the last iteration asked for a final, non-deferred refinement).
+__global__ void k_undistort_state(lsb_point* __restrict__ pts, int n, const IcpState* __restrict__ st, int mode)
+{
+  if (mode == 0 ? st->done != 0 : st->final_refine == 0) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const Iso3d T = st->Pending.at(pts[i].time);
+  float x, y, z;
+  load_xyz(pts + i, x, y, z);
+  transform_point_f(T, x, y, z);
+  store_xyz(pts + i, x, y, z);
+}
+
+__global__ void k_icp_init(IcpState* st, IcpState init) { *st = init; }
+
 // order-preserving map double -> uint64 for atomicMin/atomicMax
 __host__ __device__ __forceinline__ unsigned long long d2ord(double d)
 {
@@ -141,6 +158,17 @@ void dev_undistort(lsb_point* d_pts, size_t n, const Interpolator& it, double ti
 {
   if (!n) return;
   k_undistort<<<div_up(n, TPB), TPB, 0, s>>>(d_pts, (int)n, it, timeOffset); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void dev_undistort_state(lsb_point* d_pts, size_t n, const IcpState* st, int mode, cudaStream_t s, LaunchCounter& lc)
+{
+  if (!n) return;
+  k_undistort_state<<<div_up(n, TPB), TPB, 0, s>>>(d_pts, (int)n, st, mode); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void dev_icp_init(IcpState* d_state, const IcpState& init, cudaStream_t s, LaunchCounter& lc)
+{
+  k_icp_init<<<1, 1, 0, s>>>(d_state, init); LSB_LAUNCH_CHECK(); lc.add();
 }
 
 void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc)

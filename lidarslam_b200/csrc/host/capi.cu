@@ -268,6 +268,11 @@ int lsb_set_profiling(lsb_slam* h, int on)
   h->serial_types = (on != 0);   // kernel durations are taken without overlap between the keypoint types
   return LSB_OK;
 }
+unsigned int lsb_get_azimuth_estimations(const lsb_slam* h, int device_id)
+{
+  auto it = h->KeyPointsExtractors.find(device_id);
+  return (it == h->KeyPointsExtractors.end() || !it->second) ? 0u : it->second->az_estimations;
+}
 float lsb_get_overlap(const lsb_slam* h) { return h->OverlapEstimation; }
 int lsb_get_comply_motion_limits(const lsb_slam* h) { return h->MotionLimits.Comply ? 1 : 0; }
 unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h) { return h->TotalMatchedKeypoints; }

@@ -435,30 +435,18 @@ void lsb_slam::ComputeEgoMotion()
       else EgoGrids[k].clear();
     }
     TotalMatchedKeypoints = 0;
-    lsb_match_params mp = EgoParams(P);
-    const size_t nk[3] = {CurrentKeypoints[0].n, CurrentKeypoints[1].n, 0};
-    for (unsigned icpIter = 0; icpIter < P.ego_motion_icp_max_iter; ++icpIter) {
-      const double iterRatio = icpIter / static_cast<double>(P.ego_motion_icp_max_iter - 1);
-      mp.saturation_distance = (1 - iterRatio) * P.ego_motion_init_saturation_distance + iterRatio * P.ego_motion_final_saturation_distance;
-      mw.begin_iteration(nk, stream);
-      Fork();
-      for (int k = 0; k < 2; ++k) {
-        mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], EgoGrids[k], Trelative, mp, TypeStream(k), lc);
-        Stats.knn_queries += (uint32_t)nk[k];
-      }
-      Join();
-      // the "enough matches" test (:919-923) is taken on the device as well: one read-back per ICP iteration
-      double x0[6];
-      iso_to_xyzrpy(Trelative, x0);
-      const LmState st = mw.solve(x0, (int)P.ego_motion_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance,
-                                  P.min_nb_matched_keypoints, EgoDebug.hist, stream, lc);
-      Stats.ego_icp_iters++;
-      TotalMatchedKeypoints = 0;
-      for (int k = 0; k < 2; ++k) TotalMatchedKeypoints += (unsigned)EgoDebug.hist[k][LSB_MATCH_SUCCESS];
-      if (TotalMatchedKeypoints < P.min_nb_matched_keypoints) { Warnings |= LSB_W_EGO_SKIPPED; break; }   // :919-923
-      Stats.ego_lm_iters += (uint32_t)st.iter;
-      Trelative = xyzrpy_to_iso(st.x);
-      if (st.num_successful + 1 == 1) break;   // summary.num_successful_steps == 1 (:950)
+    if (P.ego_motion_icp_max_iter > 0) {
+      const MatchWorkspace::LmHostBlock& blk = RunIcpLoop(ICP_STAGE_EGO, EgoParams(P), P.ego_motion_icp_max_iter, P.ego_motion_lm_max_iter,
+                                                          P.ego_motion_init_saturation_distance, P.ego_motion_final_saturation_distance, nullptr);
+      const IcpState& st = blk.icp;
+      for (int t = 0; t < 3; ++t)
+        for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) EgoDebug.hist[t][q] = blk.hist[t * LSB_MATCH_N_STATUS + q];
+      Stats.ego_icp_iters = (uint32_t)st.icp_iters;
+      Stats.ego_lm_iters = (uint32_t)st.lm_iters;
+      Stats.knn_queries += (uint32_t)st.icp_iters * (uint32_t)(CurrentKeypoints[0].n + CurrentKeypoints[1].n);
+      TotalMatchedKeypoints = st.total_matched;
+      Warnings |= st.warnings;
+      Trelative = st.Trelative;
     }
     SaveDebug(EgoDebug);
   }
@@ -496,53 +484,79 @@ void lsb_slam::Localization()
   HasPendingRefinement = false;
   trace.mark("submap+grid", stream);
 
-  // ICP - LM loop (:1051-1156)
+  // ICP - LM loop (:1051-1156), device-resident: every iteration enqueued, one hand-over when the loop ends
   TotalMatchedKeypoints = 0;
-  lsb_match_params mp = LocParams(P);
-  const size_t nk[3] = {CurrentKeypoints[0].n, CurrentKeypoints[1].n, CurrentKeypoints[2].n};
-  for (unsigned icpIter = 0; icpIter < P.localization_icp_max_iter; ++icpIter) {
-    const double iterRatio = icpIter / static_cast<double>(P.localization_icp_max_iter - 1);
-    mp.saturation_distance = (1 - iterRatio) * P.localization_init_saturation_distance + iterRatio * P.localization_final_saturation_distance;
-    mw.begin_iteration(nk, stream);
+  if (P.localization_icp_max_iter == 0) return;
+  // wheel-odometer / gravity blocks, if the managers built one for this frame (:1123-1131)
+  const LmSensorTerms sensorTerms = MakeSensorTerms(WheelOdomManager, ImuManager);
+  const MatchWorkspace::LmHostBlock& blk = RunIcpLoop(ICP_STAGE_LOC, LocParams(P), P.localization_icp_max_iter, P.localization_lm_max_iter,
+                                                      P.localization_init_saturation_distance, P.localization_final_saturation_distance, &sensorTerms);
+  trace.mark("icp", stream);
+  const IcpState& st = blk.icp;
+  for (int t = 0; t < 3; ++t)
+    for (int q = 0; q < LSB_MATCH_N_STATUS; ++q) LocDebug.hist[t][q] = blk.hist[t * LSB_MATCH_N_STATUS + q];
+  SaveDebug(LocDebug);
+  Stats.loc_icp_iters = (uint32_t)st.icp_iters;
+  Stats.loc_lm_iters = (uint32_t)st.lm_iters;
+  Stats.knn_queries += (uint32_t)st.icp_iters * (uint32_t)(CurrentKeypoints[0].n + CurrentKeypoints[1].n + CurrentKeypoints[2].n);
+  TotalMatchedKeypoints = st.total_matched;
+  Warnings |= st.warnings;
+  Tworld = st.Tworld;
+  Trelative = st.Trelative;
+  WithinFrameMotion = st.Within;
+  for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
+  if (st.lm_valid) registration_error_from_normal_matrix(blk.state.H, P.two_d_mode != 0, &LocalizationUncertainty);   // :1151-1155
+}
+
+//-----------------------------------------------------------------------------
+// One ICP - LM loop of the frame without a host round trip between its iterations (cuda/icp.cuh): the pose, the within-frame
+// motion and the loop's break tests live in device memory; iteration i + 1 is enqueued behind iteration i and stands aside
+// if the loop ended before it.  Per iteration and keypoint type (own streams): undistortion refinement of the previous solve,
+// kNN (from the second iteration on bounded by the previous neighbour lists), model fit; then one persistent LM kernel whose
+// tail (icp_control) moves the pose on.  The kernel that ends the loop hands the result block to the host.
+const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_match_params& base, unsigned max_iter, unsigned lm_max_iter,
+                                                        double sat_init, double sat_final, const LmSensorTerms* terms)
+{
+  const bool loc = stage == ICP_STAGE_LOC;
+  const int ntypes = loc ? 3 : 2;                                   // ego-motion never uses blobs (:848, :910)
+  size_t nk[3] = {CurrentKeypoints[0].n, CurrentKeypoints[1].n, loc ? CurrentKeypoints[2].n : 0};
+  IcpState init;
+  std::memset(&init, 0, sizeof(init));
+  init.Tworld = Tworld; init.PreviousTworld = PreviousTworld; init.Trelative = Trelative;
+  init.Within = WithinFrameMotion;
+  init.Pending = WithinFrameMotion;
+  init.log_empty = LogTrajectory.empty() ? 1 : 0;
+  init.prev_pose_time = LogTrajectory.empty() ? 0. : LogTrajectory.back().time;
+  init.curr_pose_time = StampToSec(CurrentStamp);
+  init.max_extrapolation_ratio = P.max_extrapolation_ratio;
+  init.undistortion = loc ? P.undistortion : 0;
+  d_icp.reserve(1, stream);
+  dev_icp_init(d_icp.p, init, stream, lc);
+  mw.icp_stage = stage;
+  mw.begin_frame(nk, (int)max_iter, stream);
+  mw.next_solve_seq();
+  const bool refined = loc && P.undistortion == LSB_UNDISTORTION_REFINED;
+  lsb_match_params mp = base;
+  for (unsigned icpIter = 0; icpIter < max_iter; ++icpIter) {
+    const double iterRatio = icpIter / static_cast<double>(max_iter - 1);
+    mp.saturation_distance = (1 - iterRatio) * sat_init + iterRatio * sat_final;          // :905-906, :1084-1085
     Fork();
     for (int k : kTypeOrder) {
+      if (k >= ntypes) continue;
       // the undistortion refinement of the previous iteration (:1146-1147): three independent clouds, one per type stream
-      if (HasPendingRefinement) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, PendingRefinement, 0.0, TypeStream(k), lc);
-      mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], LocalMaps[k].grid, Tworld, mp, TypeStream(k), lc);
-      Stats.knn_queries += (uint32_t)nk[k];
+      if (refined && icpIter > 0) dev_undistort_state(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_icp.p, 0, TypeStream(k), lc);
+      mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], loc ? LocalMaps[k].grid : EgoGrids[k], Iso3d::identity(), mp, TypeStream(k), lc,
+                    (int)icpIter, d_icp.p, /*reuse=*/icpIter > 0);
     }
-    HasPendingRefinement = false;
     Join();
-    trace.mark("match", stream);
-    // the "enough matches" test (:1098-1107) is taken on the device as well: one read-back per ICP iteration
-    double x0[6];
-    iso_to_xyzrpy(Tworld, x0);
-    // wheel-odometer / gravity blocks, if the managers built one for this frame (:1123-1131)
-    const LmSensorTerms sensorTerms = MakeSensorTerms(WheelOdomManager, ImuManager);
-    const LmState st = mw.solve(x0, (int)P.localization_lm_max_iter, P.two_d_mode != 0, mp.saturation_distance,
-                                P.min_nb_matched_keypoints, LocDebug.hist, stream, lc, &sensorTerms);
-    trace.mark("lm", stream);
-    SaveDebug(LocDebug);
-    Stats.loc_icp_iters++;
-    TotalMatchedKeypoints = 0;
-    for (int k = 0; k < 3; ++k) TotalMatchedKeypoints += (unsigned)LocDebug.hist[k][LSB_MATCH_SUCCESS];
-    if (TotalMatchedKeypoints < P.min_nb_matched_keypoints) {   // :1098-1107
-      Trelative = Iso3d::identity();
-      Tworld = PreviousTworld;
-      if (P.undistortion) WithinFrameMotion.set_transforms(Iso3d::identity(), Iso3d::identity());
-      Warnings |= LSB_W_LOC_SKIPPED;
-      break;
-    }
-    Stats.loc_lm_iters += (uint32_t)st.iter;
-    Tworld = xyzrpy_to_iso(st.x);
-    Trelative = inverse(PreviousTworld) * Tworld;
-    const bool lastIter = st.num_successful + 1 == 1 || icpIter == P.localization_icp_max_iter - 1;
-    if (P.undistortion == LSB_UNDISTORTION_REFINED) RefineUndistortion(/*defer=*/!lastIter);
-    if (lastIter) {   // :1151-1155
-      registration_error_from_normal_matrix(st.H, P.two_d_mode != 0, &LocalizationUncertainty);
-      break;
-    }
+    IcpCtl ctl;
+    ctl.stage = stage; ctl.icp_iter = (int)icpIter; ctl.icp_max_iter = (int)max_iter; ctl.min_matches = P.min_nb_matched_keypoints;
+    mw.enqueue_solve(nullptr, (int)lm_max_iter, P.two_d_mode != 0, mp.saturation_distance, P.min_nb_matched_keypoints, stream, lc, terms,
+                     d_icp.p, &ctl);
   }
+  // the refinement of the iteration that ended the loop is applied at once (RefineUndistortion of the last iteration, :1146-1147)
+  if (refined) for (int k = 0; k < 3; ++k) dev_undistort_state(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_icp.p, 1, stream, lc);
+  return mw.wait_result(stream);
 }
 
 //-----------------------------------------------------------------------------

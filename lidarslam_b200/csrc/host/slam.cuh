@@ -71,6 +71,10 @@ struct lsb_slam {
   size_t NbCurrentFrames = 0;
 
   lsb::MatchWorkspace mw;
+  lsb::DevBuf<lsb::IcpState> d_icp;   // state of the device-resident ICP loop (cuda/icp.cuh)
+  // enqueues every iteration of an ICP - LM loop, waits for the hand-over of the iteration that ends it
+  const lsb::MatchWorkspace::LmHostBlock& RunIcpLoop(int stage, const lsb_match_params& base, unsigned max_iter, unsigned lm_max_iter,
+                                                     double sat_init, double sat_final, const lsb::LmSensorTerms* terms);
   lsb::KnnGrid EgoGrids[2];
   // match results kept for GetDebugArray (Slam.cxx:635-657)
   struct StageDebug { lsb::DevBuf<uint8_t> status; lsb::DevBuf<double> weight; size_t off[4] = {0, 0, 0, 0}; int hist[3][LSB_MATCH_N_STATUS] = {}; };
@@ -144,6 +148,9 @@ namespace lsb {
 void dev_transform(lsb_point* d_pts, size_t n, const Iso3d& T, cudaStream_t s, LaunchCounter& lc);                     // Utils::TransformPoint
 void dev_aggregate(lsb_point* d_pts, size_t n, double timeOffset, const Iso3d& T, bool applyT, cudaStream_t s, LaunchCounter& lc);
 void dev_undistort(lsb_point* d_pts, size_t n, const Interpolator& it, double timeOffset, cudaStream_t s, LaunchCounter& lc);   // Slam.cxx:1345-1350
+// the same with the interpolator the device-resident ICP loop holds (cuda/icp.cuh); mode 0: head of an iteration, 1: after the loop
+void dev_undistort_state(lsb_point* d_pts, size_t n, const IcpState* st, int mode, cudaStream_t s, LaunchCounter& lc);
+void dev_icp_init(IcpState* d_state, const IcpState& init, cudaStream_t s, LaunchCounter& lc);
 void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
 void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
 void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx);

@@ -51,6 +51,8 @@ int main(int argc, char** argv)
   std::printf("overlap %a planes_used %.0f maps %zu %zu %zu frames %u\n", (double)slam->GetOverlapEstimation(), info.at("Localization: planes used"),
               slam->GetMap(LidarSlam::EDGE)->size(), slam->GetMap(LidarSlam::PLANE)->size(), slam->GetMap(LidarSlam::BLOB)->size(),
               slam->GetNbrFrameProcessed());
+  // the estimate made on the first frame lives in the extractor object from then on (SSKE.cxx:169)
+  std::printf("azimuth %a estimations %u\n", (double)ke->GetAzimuthalResolution(), lsb_get_azimuth_estimations(slam->GetHandle(), 0));
   if (argc > 4) slam->SaveMapsToPCD(argv[4], LidarSlam::PCDFormat::BINARY_COMPRESSED, true);
   std::fclose(f);
   return 0;

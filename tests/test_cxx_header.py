@@ -58,7 +58,7 @@ def test_header_covers_the_reference_interface():
 def test_header_caller_reproduces_the_ctypes_trajectory(gpu, synth, tmp_path):
     exe = _build(tmp_path)
     seq, sens = synth.Sequence(scene_seed=1234), synth.sensor("vlp16")
-    n = 6
+    n = 50
     g = gpu()
     p = g.GetParams()
     p.use_keypoints[2] = 1
@@ -77,7 +77,10 @@ def test_header_caller_reproduces_the_ctypes_trajectory(gpu, synth, tmp_path):
     r = subprocess.run([exe, path, str(n), str(len(pts)), str(tmp_path / "cxx_")], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     lines = r.stdout.strip().splitlines()
-    assert len(lines) == n + 1
+    assert len(lines) == n + 2
+    az = lines.pop().split()
+    assert az[0] == "azimuth" and int(az[3]) == 1                                     # estimated once, on the first frame
+    assert float.fromhex(az[1]) == float(g.GetExtractorParams().azimuthal_resolution) > 0
     for i, line in enumerate(lines[:n]):
         tok = line.split()
         rc, ne, np_, nb = (int(v) for v in tok[1:5])

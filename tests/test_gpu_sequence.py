@@ -382,3 +382,149 @@ def test_soft_failures_and_state_control(gpu, oracle_lib, synth):
         same("2-D mode frame %d" % i)
     Tg, _ = g.GetWorldTransform()
     assert Tg[2, 3] == 0.0 and abs(Tg[2, 2] - 1.0) < 1e-15                          # z, roll and pitch held (LocalOptimizer.cxx:89-90)
+
+
+# ---- BASELINE.json configs at their stated lengths -------------------------------------------------------------------
+# The reference's own regression replays whole bags pose by pose (ros_wrapping/tests/src/LidarSlamTestNode.cxx:243-325).
+# Here: >= 300 frames per configuration, every frame's keypoints / match statuses bit-exact, pose <= 1e-6 m / rad, maps
+# bit-exact every 25 frames, the whole logged trajectory <= 1e-6 (drift bar: 1 mm), through a 250 m rolling grid so that
+# the maps roll and drop voxels on the way (about 190 m travelled).
+LONG_FRAMES = 300
+
+
+def _long_checks(g, o, n_frames, min_travel=150.0):
+    n, Tg, tg = g.GetTrajectory()
+    m, To, to = o.GetTrajectory()
+    assert n == m == n_frames and np.array_equal(tg, to)
+    assert np.abs(Tg - To).max() <= 1e-6
+    assert np.linalg.norm(Tg[-1][:3, 3]) > min_travel
+    for k in capi.KEYPOINT_TYPES:
+        a = g.GetMap(k)
+        if len(a) == 0:
+            continue
+        # the grid is 250 m across and the sequence saw 190 m + twice the sensor range: it can only hold that if it rolled
+        for ax in ("x", "y", "z"):
+            assert a[ax].max() - a[ax].min() <= 250.0 + 10.0 + 1e-3
+    return Tg
+
+
+def test_config1_hdl64_ego_registration_300_frames(gpu, oracle_lib, synth):
+    """BASELINE configs[1]: HDL-64, ego-motion ICP (MOTION_EXTRAPOLATION_AND_REGISTRATION) + localization ICP."""
+    def cfg(s):
+        p = s.GetParams()
+        p.ego_motion = 3
+        p.logging_timeout = 1e3
+        s.SetParams(p)
+        s.SetVoxelGridSize(25)
+    g, o = _run(gpu, oracle_lib, synth, [synth.sensor("hdl64")], LONG_FRAMES, cfg, check_maps_every=25)
+    _long_checks(g, o, LONG_FRAMES)
+    sg, so = g.GetFrameStats(), o.GetFrameStats()
+    assert sg.ego_icp_iters == so.ego_icp_iters > 0 and list(sg.ego_n_matches) == list(so.ego_n_matches)
+
+
+def test_config2_os128_blobs_undistortion_300_frames(gpu, oracle_lib, synth):
+    """BASELINE configs[2], the headline: OS-128 2048 columns, blobs, refined undistortion, overlap estimator on."""
+    def cfg(s):
+        p = s.GetParams()
+        p.use_keypoints[2] = 1
+        p.overlap_sampling_ratio = 0.33
+        p.logging_timeout = 1e3
+        s.SetParams(p)
+        s.SetVoxelGridSize(25)
+    g, o = _run(gpu, oracle_lib, synth, [synth.sensor("os128")], LONG_FRAMES, cfg, check_maps_every=25)
+    Tg = _long_checks(g, o, LONG_FRAMES)
+    seq = synth.Sequence(scene_seed=1234)
+    sens = synth.sensor("os128")
+    rel = np.linalg.inv(seq.frame(sens, 0)[1]) @ seq.frame(sens, LONG_FRAMES - 1)[1]
+    assert np.linalg.norm(Tg[-1][:3, 3] - rel[:3, 3]) < 1.0      # tracks the ground truth over 190 m
+
+
+def test_config3_vls128_pandar64_rig_300_frames(gpu, oracle_lib, synth):
+    """BASELINE configs[3]: VLS-128 + Pandar64 merged frames (345.6 k points), every frame a key frame, dense leaves."""
+    c, s_ = np.cos(np.pi / 2), np.sin(np.pi / 2)
+    cy, sy = np.cos(np.deg2rad(20)), np.sin(np.deg2rad(20))
+    T = np.eye(4)
+    T[:3, :3] = np.array([[c, -s_, 0], [s_, c, 0], [0, 0, 1.]]) @ np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    T[:3, 3] = [0.6, 0, -0.35]
+
+    def cfg(s):
+        p = s.GetParams()
+        p.use_keypoints[2] = 1
+        p.kf_distance_threshold = 0.0
+        p.logging_timeout = 1e3
+        s.SetParams(p)
+        s.SetVoxelGridSize(25)
+        for k, leaf in enumerate((0.2, 0.3, 0.2)):
+            s.SetVoxelGridLeafSize(k, leaf)
+        s.SetExtractorParams(s.GetExtractorParams(0), 1)
+        s.SetBaseToLidarOffset(T, 1)
+    main = synth.sensor("vls128", device_id=0)
+    sec = synth.sensor("pandar64", device_id=1, mount_xyz=(0.6, 0, -0.35), mount_rpy=(0, np.deg2rad(20), np.pi / 2))
+    g, o = _run(gpu, oracle_lib, synth, [main, sec], LONG_FRAMES, cfg, check_maps_every=25)
+    _long_checks(g, o, LONG_FRAMES)
+    assert g.GetFrameStats().is_keyframe == 1
+
+
+def test_pose_accessors_through_the_c_abi(gpu, oracle_lib, synth):
+    """C-ABI entries beside lsb_get_world_transform: lsb_get_relative_transform (Slam.h Trelative), the registration
+    error with its directions (LocalOptimizer.cxx:112-140) against the oracle AND against numpy on the covariance it
+    returns, and lsb_get_latency_compensated_world_transform (Slam.cxx:555-588) against a scipy slerp restatement."""
+    from scipy.spatial.transform import Rotation, Slerp
+    g, o = gpu(), oracle_lib.Oracle(nb_threads=oracle_lib.max_threads())
+    for s in (g, o):
+        p = s.GetParams()
+        p.use_keypoints[2] = 1
+        p.logging_timeout = 1e3
+        s.SetParams(p)
+    seq, sens = synth.Sequence(scene_seed=1234), synth.sensor("vlp16")
+    lat = g._f("get_latency_compensated_world_transform")
+    import ctypes as C
+    for i in range(6):
+        pts, _, stamp = seq.frame(sens, i)
+        assert g.AddFrame(pts, stamp, i + 1) == o.AddFrame(pts, stamp, i + 1)
+        # relative transform: identical to the oracle, and consistent with the logged poses
+        Rg, Ro = g.GetRelativeTransform(), o.GetRelativeTransform()
+        assert np.abs(Rg - Ro).max() <= 1e-9
+        n, traj, times = g.GetTrajectory()
+        if n >= 2:
+            assert np.abs(np.linalg.inv(traj[-2]) @ traj[-1] - Rg).max() <= 1e-9
+        # registration error: GPU == oracle, and the directions are the top eigenvectors of the covariance blocks
+        eg, eo = g.GetRegistrationError(), o.GetRegistrationError()
+        cov = np.array(eg.covariance).reshape(6, 6)
+        assert np.array_equal(cov, np.array(eo.covariance).reshape(6, 6))
+        assert np.array_equal(g.GetTransformCovariance(), cov.reshape(-1))
+        if i >= 1:
+            assert eg.position_error == eo.position_error and eg.orientation_error == eo.orientation_error
+            assert list(eg.position_error_direction) == list(eo.position_error_direction)
+            assert list(eg.orientation_error_direction) == list(eo.orientation_error_direction)
+            for blk, val, d, deg in ((slice(0, 3), eg.position_error, np.array(eg.position_error_direction), False),
+                                     (slice(3, 6), eg.orientation_error, np.array(eg.orientation_error_direction), True)):
+                lv, lV = np.linalg.eigh(cov[blk, blk])
+                exp = np.sqrt(lv[2]) * (180.0 / np.pi if deg else 1.0)
+                assert abs(val - exp) <= 1e-9 * exp and abs(abs(d @ lV[:, 2]) - 1) < 1e-7 and val > 0
+        # latency-compensated pose: extrapolation of the last two logged poses by the measured latency
+        T = np.zeros(16)
+        t = C.c_double()
+        rc = lat(g.h, T.ctypes.data_as(C.c_void_p), C.byref(t))
+        T = T.reshape(4, 4)
+        latency = g.GetFrameStats().ms_total * 1e-3
+        if n < 2:
+            assert rc == 0 and np.array_equal(T, traj[-1])
+            continue
+        assert t.value == times[-1]
+        dt = times[-1] - times[-2]
+        assert rc == 0 and abs(latency / dt) < 3.0
+        u = (times[-1] + latency - times[-2]) / dt                   # > 1: extrapolation
+        R0, R1 = Rotation.from_matrix(traj[-2][:3, :3]), Rotation.from_matrix(traj[-1][:3, :3])
+        rel = (R0.inv() * R1).as_rotvec()
+        Rexp = (R0 * Rotation.from_rotvec(u * rel)).as_matrix()       # slerp continued past t = 1
+        texp = traj[-2][:3, 3] + u * (traj[-1][:3, 3] - traj[-2][:3, 3])
+        assert np.abs(T[:3, :3] - Rexp).max() <= 1e-9 and np.abs(T[:3, 3] - texp).max() <= 1e-9
+        assert np.linalg.norm(T[:3, 3] - traj[-1][:3, 3]) > 0        # it did move ahead of the last pose
+    # an extrapolation ratio the latency exceeds: the current pose comes back with the warning flag
+    p = g.GetParams()
+    p.max_extrapolation_ratio = 1e-9
+    g.SetParams(p)
+    T = np.zeros(16)
+    rc = lat(g.h, T.ctypes.data_as(C.c_void_p), C.byref(t))
+    assert rc == 8 and np.array_equal(T.reshape(4, 4), g.GetWorldTransform()[0])     # LSB_W_EXTRAPOLATION
