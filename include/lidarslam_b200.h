@@ -320,6 +320,20 @@ LSB_API long lsb_get_extracted_keypoints(lsb_slam* h, int type, lsb_point* out, 
 LSB_API int lsb_knn_search(lsb_slam* h, const lsb_point* cloud, size_t m, const float* queries_xyz, size_t nq, int k,
                            int32_t* idx_out, float* d2_out);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Same result as lsb_knn_search
+ * (exact, ascending (d2, index), -1 / +inf beyond the number found), but ALLOCATES NOTHING: cloud, queries and outputs
+ * are DEVICE pointers on `cuda_device` supplied by the caller, the work is enqueued on `cuda_stream` (a cudaStream_t;
+ * NULL = the default stream) and NOT synchronised, and the kernel's scratch (per-segment partial lists + tickets) is a
+ * file-scope static __device__ array of 4 MiB + 8 KiB that every GPU loading the library holds until the process exits.
+ * Limits (beyond them: LSB_E_CAPACITY with a message in lsb_last_error): nq <= LSB_NOALLOC_MAX_QUERIES, k <= LSB_NOALLOC_MAX_K.
+ * All calls on a device share that array: calls that overlap on the GPU (different streams without a dependency) RACE.
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress): make it before starting a capture. */
+#define LSB_NOALLOC_MAX_QUERIES 2048
+#define LSB_NOALLOC_MAX_K 16
+LSB_API int lsb_knn_search_noalloc(int cuda_device, const lsb_point* d_cloud, size_t m, const float* d_queries_xyz, size_t nq, int k,
+                                   int32_t* d_idx_out, float* d_d2_out, void* cuda_stream);
+
 /* KeypointsMatcher::BuildMatchResiduals x3 + LocalOptimizer::Solve
  * (KeypointsMatcher.cxx:33-74, LocalOptimizer.cxx:74-102) for ONE ICP iteration:
  * keypoints[t] (BASE frame) matched against target[t] with the pose prior, then LM.

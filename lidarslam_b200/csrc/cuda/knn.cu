@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <atomic>
 
 namespace lsb {
 
@@ -806,6 +807,119 @@ void KnnGrid::search_points(const lsb_point* d_kp, size_t nq, const Iso3d& prior
     return;
   }
   launch_knn<true>(*this, nullptr, d_kp, prior, nq, k, cap_dist, d_idx, d_d2, d_nf, entry_major, s, lc, da);
+}
+
+}  // namespace lsb
+
+// ====================================================================================================
+// Exact kNN that allocates nothing (lsb_knn_search_noalloc, include/lidarslam_b200.h).  No counterpart in the
+// reference: added for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  It is the brute-force kernel of the exact search above
+// (k_knn_brute: a work item = (query, segment of the cloud), per-lane lists, warp merge, partial sorted lists, the
+// warp that completes a query's last segment merges them) reading the caller's cloud directly, with its scratch —
+// the partial lists and the per-query tickets — in ONE file-scope __device__ array instead of DevBufs:
+//   * every GPU that loads the library holds NOALLOC_SCRATCH_BYTES (4 MiB + 8 KiB) until the process exits;
+//   * the limits that size it: nq <= LSB_NOALLOC_MAX_QUERIES (2048), k <= LSB_NOALLOC_MAX_K (16); larger -> LSB_E_CAPACITY;
+//   * every call on a device shares the array and finds the previous call's contents in it: the tickets are cleared by
+//     a memset node at the head of each call (the partial lists are fully rewritten before they are read);
+//   * two calls that overlap on the GPU (different streams, no dependency) race on it.
+// Host code must not pass the array's name to a kernel (on the host it is a stand-in, not a device address): the
+// address is fetched once per device with cudaGetSymbolAddress, with that device current.
+namespace lsb {
+
+namespace {
+
+constexpr int NOALLOC_SEGS = BF_SEGS;
+constexpr size_t NOALLOC_PARTIAL_KEYS = (size_t)LSB_NOALLOC_MAX_QUERIES * NOALLOC_SEGS * LSB_NOALLOC_MAX_K;
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_PARTIAL_KEYS * sizeof(Key) + (size_t)LSB_NOALLOC_MAX_QUERIES * sizeof(unsigned);
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+__global__ void __launch_bounds__(128)
+k_knn_brute_static(const lsb_point* __restrict__ cloud, int m, const float* __restrict__ q_xyz, int nq, int k, int32_t* __restrict__ idx_out,
+                   float* __restrict__ d2_out, Key* __restrict__ partial, unsigned* __restrict__ tickets)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int KMAX = LSB_NOALLOC_MAX_K;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int seg_len = (m + NOALLOC_SEGS - 1) / NOALLOC_SEGS;
+  const int nitems = nq * NOALLOC_SEGS;
+  for (int item = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; item < nitems; item += warps) {
+    const int i = item / NOALLOC_SEGS, seg = item % NOALLOC_SEGS;
+    const float qx = q_xyz[3 * (size_t)i], qy = q_xyz[3 * (size_t)i + 1], qz = q_xyz[3 * (size_t)i + 2];
+    TopK<KMAX> tk;
+    tk.init();
+    const int p0 = seg * seg_len, p1 = min(m, p0 + seg_len);
+    for (int p = p0 + lane; p < p1; p += 32) {
+      const float4 s = __ldg(reinterpret_cast<const float4*>(cloud) + 2 * (size_t)p);
+      const float dx = qx - s.x, dy = qy - s.y, dz = qz - s.z;
+      tk.offer(make_key((dx * dx + dy * dy) + dz * dz, p));      // same arithmetic and tie order as the grid search
+    }
+    Key* out = partial + ((size_t)i * NOALLOC_SEGS + seg) * k;
+    for (int t = 0; t < k; ++t) {          // warp merge of the per-lane lists -> sorted partial list
+      const unsigned hi = (unsigned)(tk.key[0] >> 32), lo = (unsigned)tk.key[0];
+      const unsigned mhi = __reduce_min_sync(FULL, hi);
+      const unsigned mlo = __reduce_min_sync(FULL, (hi == mhi) ? lo : 0xffffffffu);
+      const Key mk = ((Key)mhi << 32) | mlo;
+      if (tk.key[0] == mk && mk != KEY_NONE) tk.pop();
+      if (lane == 0) out[t] = mk;
+    }
+    __threadfence();
+    unsigned done = 0;
+    if (lane == 0) done = atomicAdd(tickets + i, 1u);
+    done = __shfl_sync(FULL, done, 0);
+    if (done != NOALLOC_SEGS - 1) continue;
+    __threadfence();
+    // last segment of this query: merge the sorted lists (lane s < NOALLOC_SEGS walks list s)
+    const Key* lists = partial + (size_t)i * NOALLOC_SEGS * k;
+    int pos = 0;
+    for (int t = 0; t < k; ++t) {
+      const Key head = (lane < NOALLOC_SEGS && pos < k) ? __ldcg(lists + (size_t)lane * k + pos) : KEY_NONE;
+      const unsigned hi = (unsigned)(head >> 32), lo = (unsigned)head;
+      const unsigned mhi = __reduce_min_sync(FULL, hi);
+      const unsigned mlo = __reduce_min_sync(FULL, (hi == mhi) ? lo : 0xffffffffu);
+      const Key mk = ((Key)mhi << 32) | mlo;
+      if (head == mk && mk != KEY_NONE) ++pos;
+      const bool ok = key_d2(mk) < INFINITY;
+      if (lane == 0) { idx_out[(size_t)i * k + t] = ok ? key_id(mk) : -1; d2_out[(size_t)i * k + t] = ok ? key_d2(mk) : INFINITY; }
+    }
+  }
+}
+
+// device address of g_noalloc_scratch, fetched once per device (index = CUDA device ordinal)
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::atomic<unsigned char*> g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+
+}  // namespace
+
+void knn_search_noalloc(int device, const lsb_point* d_cloud, size_t m, const float* d_queries_xyz, size_t nq, int k, int32_t* d_idx_out,
+                        float* d_d2_out, cudaStream_t s)
+{
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) throw CudaError(LSB_E_INVALID, "lsb_knn_search_noalloc: invalid CUDA device index");
+  if (k < 1 || k > LSB_NOALLOC_MAX_K) throw CudaError(LSB_E_CAPACITY, "lsb_knn_search_noalloc: k must be in [1, 16] (LSB_NOALLOC_MAX_K)");
+  if (nq > (size_t)LSB_NOALLOC_MAX_QUERIES)
+    throw CudaError(LSB_E_CAPACITY, "lsb_knn_search_noalloc: more than 2048 queries (LSB_NOALLOC_MAX_QUERIES): the static scratch array is sized for that many");
+  if (m > (size_t)INT_MAX) throw CudaError(LSB_E_CAPACITY, "lsb_knn_search_noalloc: cloud larger than 2^31 - 1 points");
+  if (nq == 0) return;
+  if (!d_queries_xyz || !d_idx_out || !d_d2_out || (m && !d_cloud)) throw CudaError(LSB_E_INVALID, "lsb_knn_search_noalloc: null device pointer");
+  LSB_CUDA(cudaSetDevice(device));
+  unsigned char* base = g_noalloc_ptr[device].load(std::memory_order_acquire);
+  if (!base) {      // set-up, once per device, with that device current
+    void* sym = nullptr;
+    LSB_CUDA(cudaGetSymbolAddress(&sym, g_noalloc_scratch));
+    if (!sym) throw CudaError(LSB_E_CUDA, "lsb_knn_search_noalloc: cudaGetSymbolAddress returned no address");
+    base = static_cast<unsigned char*>(sym);
+    g_noalloc_ptr[device].store(base, std::memory_order_release);
+  }
+  Key* partial = reinterpret_cast<Key*>(base);
+  unsigned* tickets = reinterpret_cast<unsigned*>(base + NOALLOC_PARTIAL_KEYS * sizeof(Key));
+  // the array keeps the previous call's contents: the tickets must start at zero
+  LSB_CUDA(cudaMemsetAsync(tickets, 0, nq * sizeof(unsigned), s));
+  const unsigned warps = (unsigned)(nq * NOALLOC_SEGS);
+  const unsigned G = std::min<unsigned>(div_up((size_t)warps * 32, 128), 148u * 16u);
+  k_knn_brute_static<<<G, 128, 0, s>>>(d_cloud, (int)m, d_queries_xyz, (int)nq, k, d_idx_out, d_d2_out, partial, tickets);
+  LSB_LAUNCH_CHECK();
 }
 
 }  // namespace lsb

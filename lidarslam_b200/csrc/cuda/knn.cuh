@@ -64,4 +64,8 @@ struct KnnGrid {
                      int32_t* d_nfound_out, bool entry_major, cudaStream_t s, LaunchCounter& lc, const KnnDeviceArgs* da = nullptr) const;
 };
 
+// Exact kNN of nq DEVICE queries in a DEVICE cloud without any allocation (static __device__ scratch, see knn.cu); enqueued on s.
+void knn_search_noalloc(int device, const lsb_point* d_cloud, size_t m, const float* d_queries_xyz, size_t nq, int k, int32_t* d_idx_out,
+                        float* d_d2_out, cudaStream_t s);
+
 }  // namespace lsb

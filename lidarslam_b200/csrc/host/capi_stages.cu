@@ -161,6 +161,16 @@ int lsb_knn_search(lsb_slam* h, const lsb_point* cloud, size_t m, const float* q
   });
 }
 
+// no allocation, no handle, no synchronisation: see the declaration (no reference counterpart)
+int lsb_knn_search_noalloc(int cuda_device, const lsb_point* d_cloud, size_t m, const float* d_queries_xyz, size_t nq, int k, int32_t* d_idx_out,
+                           float* d_d2_out, void* cuda_stream)
+{
+  return guarded([&] {
+    knn_search_noalloc(cuda_device, d_cloud, m, d_queries_xyz, nq, k, d_idx_out, d_d2_out, static_cast<cudaStream_t>(cuda_stream));
+    return LSB_OK;
+  });
+}
+
 int lsb_match_and_solve(lsb_slam* h, const lsb_point* const keypoints[3], const size_t nk[3], const lsb_point* const target[3],
                         const size_t nt[3], const lsb_match_params* mp, int lm_max_iter, const double prior_rowmajor[16],
                         uint8_t* status_out, double* weight_out, double pose_out_rowmajor[16], int* lm_accepted_steps,
