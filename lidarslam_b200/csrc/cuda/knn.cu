@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <atomic>
 
 namespace lsb {
@@ -407,6 +408,120 @@ k_knn_stream(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, 
   if (!done) unres_list[atomicAdd(unres_count, 1u)] = i;
 }
 
+__device__ __forceinline__ void axis_cells(float lo, float hi, float o, float cell, int n, int& c0, int& c1);
+
+// Cube pass of the LATER ICP iterations of a frame (KnnDeviceArgs::reuse): the target grid has not changed and the query
+// has moved by millimetres, so the k neighbours found in the previous iteration, re-evaluated at the new query position,
+// give an exact upper bound T of the new k-th distance before anything is searched.  With T known up front
+//   * only the rows of the box of the sphere of radius sqrt(T) are visited (typically 2 x 2 rows of 2 cells instead of the
+//     9 rows of 3 cells of the cube), rows whose lower bound exceeds T are dropped;
+//   * no top-k list is kept while scanning: a candidate with d2 <= T is appended to a per-thread buffer in shared memory
+//     (about k of them: T is the k-th distance up to the motion of the query), a predicated store instead of a sorted
+//     insertion, and the k smallest are then placed by rank;
+//   * the answer is exact by construction (every point within T was seen), so no query is left to the warp pass, except
+//     the ones without a usable previous list (fewer than k found, "too far" results), a box of more than 9 rows or a
+//     buffer overflow (many points at equal distance): those go to k_knn_warp with T as their threshold.
+// One thread per query, trips taken by the 32 lanes together as in k_knn_stream.
+template <int KMAX, bool FROM_POINTS>
+__global__ void __launch_bounds__(128)
+k_knn_reuse(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, KnnPose prior, int nq, KnnGridParams gp,
+            const float4* __restrict__ sorted, const uint32_t* __restrict__ cell_start, const lsb_point* __restrict__ cloud, int k, size_t qs,
+            size_t ts, int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ nfound_out,
+            int32_t* __restrict__ unres_list, unsigned* __restrict__ unres_count)
+{
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int CAP = (KMAX >= 32) ? KMAX + 6 : KMAX + 8;   // 48 KB of static shared memory at most
+  __shared__ Key s_buf[CAP][128];
+  __shared__ uint32_t s_rb[9][128], s_re[9][128];
+  if (knn_off(prior)) return;
+  const int tid = threadIdx.x;
+  const int i0 = blockIdx.x * blockDim.x + tid;
+  const bool live = i0 < nq;
+  const int i = live ? i0 : nq - 1;
+  const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
+  // the bound: largest distance from the moved query to its previous k neighbours
+  bool ok = live && q.finite && (!nfound_out || nfound_out[i] >= k);
+  float T = 0.f;
+#pragma unroll
+  for (int t = 0; t < KMAX; ++t) {
+    if (t < k) {
+      const int id = idx_out[(size_t)i * qs + t * ts];
+      ok = ok && id >= 0;
+      const float4 p = __ldg(reinterpret_cast<const float4*>(cloud) + 2 * (size_t)max(id, 0));
+      const float ax = q.qx - p.x, ay = q.qy - p.y, az = q.qz - p.z;
+      T = fmaxf(T, (ax * ax + ay * ay) + az * az);
+    }
+  }
+  ok = ok && T < INFINITY;
+  int x0 = 0, x1 = 0, y0 = 0, y1 = -1, z0 = 0, z1 = -1;
+  if (ok) {
+    const float r = sqrtf(T);
+    const float rr = r + (1.0e-3f + 1.0e-4f * (r + gp.cell));
+    axis_cells(q.qx - rr, q.qx + rr, gp.ox, gp.cell, gp.nx, x0, x1);
+    axis_cells(q.qy - rr, q.qy + rr, gp.oy, gp.cell, gp.ny, y0, y1);
+    axis_cells(q.qz - rr, q.qz + rr, gp.oz, gp.cell, gp.nz, z0, z1);
+  }
+  const int nyr = y1 - y0 + 1, rows = (z1 - z0 + 1) * nyr;
+  const bool fits = ok && rows <= 9;
+  int nrow = 0;
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    if (fits && t < rows) {
+      const int z = z0 + t / nyr, y = y0 + t % nyr;
+      const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
+      if (gy * gy + gz * gz <= T) {
+        const int base = (z * gp.ny + y) * gp.nx;
+        const uint32_t b = __ldg(cell_start + base + x0), e = __ldg(cell_start + base + x1 + 1);
+        if (b < e) { s_rb[nrow][tid] = b; s_re[nrow][tid] = e; ++nrow; }
+      }
+    }
+  }
+  int cnt = 0, o = 0;
+  uint32_t p = 0, e = 0;
+  while (true) {
+    const bool adv = p >= e && o < nrow;
+    const int oo = adv ? o : 0;
+    p = adv ? s_rb[oo][tid] : p;
+    e = adv ? s_re[oo][tid] : e;
+    o += adv ? 1 : 0;
+    float4 sv[STREAM_TRIPS];
+#pragma unroll
+    for (int j = 0; j < STREAM_TRIPS; ++j) sv[j] = __ldg(sorted + ((p + j < e) ? p + j : 0u));
+#pragma unroll
+    for (int j = 0; j < STREAM_TRIPS; ++j) {
+      const float ax = q.qx - sv[j].x, ay = q.qy - sv[j].y, az = q.qz - sv[j].z;
+      const float d2 = (ax * ax + ay * ay) + az * az;
+      if (p + j < e && d2 <= T) {
+        if (cnt < CAP) s_buf[cnt][tid] = make_key(d2, __float_as_int(sv[j].w));
+        ++cnt;
+      }
+    }
+    p = min(p + (uint32_t)STREAM_TRIPS, max(p, e));
+    if (!__any_sync(FULL, p < e || o < nrow)) break;
+  }
+  if (!live) return;
+  if (!fits || cnt > CAP || cnt < k) {
+    // handed to the warp pass: it reads its threshold from the k-th distance slot (an upper bound, or +inf for "none")
+    if (q.finite) {
+      // a large box (isolated query: the k-th neighbour is many cells away) is not worth one warp's scan: without a threshold
+      // the warp pass takes its usual route for such queries (cube of the cap, then the shared brute-force kernel)
+      d2_out[(size_t)i * qs + (size_t)(k - 1) * ts] = (ok && rows <= 64) ? T : INFINITY;
+      unres_list[atomicAdd(unres_count, 1u)] = i;
+    } else {
+      for (int t = 0; t < k; ++t) { idx_out[(size_t)i * qs + t * ts] = -1; d2_out[(size_t)i * qs + t * ts] = INFINITY; }
+      if (nfound_out) nfound_out[i] = 0;
+    }
+    return;
+  }
+  for (int j = 0; j < cnt; ++j) {
+    const Key mine = s_buf[j][tid];
+    int rank = 0;
+    for (int u = 0; u < cnt; ++u) rank += (s_buf[u][tid] < mine) ? 1 : 0;
+    if (rank < k) { idx_out[(size_t)i * qs + rank * ts] = key_id(mine); d2_out[(size_t)i * qs + rank * ts] = key_d2(mine); }
+  }
+  if (nfound_out) nfound_out[i] = k;
+}
+
 // merges the 32 per-lane sorted lists: round t yields the t-th smallest key of the warp
 // (two warp-wide integer min reductions per round).  Writes the first k; returns the number
 // found and the k-th distance.
@@ -685,9 +800,14 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   static const long quad_max = [] { const char* e = std::getenv("LSB_KNN_QUAD_MAX"); return e ? std::atol(e) : 148L * 64; }();   // tuning hook
   const bool quad = (long)nq <= quad_max;
   const unsigned G1 = div_up(nq, 128);
+  static const bool reuse_on = [] { const char* e = std::getenv("LSB_KNN_REUSE"); return !e || e[0] != '0'; }();   // tuning / A-B hook
+  const bool reuse = da && da->reuse && reuse_on && nf != nullptr;
 #define LSB_KNN_CASE(KM)                                                                                                                   \
   do {                                                                                                                                     \
-    if (quad)                                                                                                                              \
+    if (reuse)                                                                                                                             \
+      k_knn_reuse<KM, FROM_POINTS><<<G1, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, g.cloud, k, qs, ts, idx, d2, nf,   \
+                                                      g.unres_list.p, g.unres_count.p);                                                    \
+    else if (quad)                                                                                                                         \
       k_knn<KM, FROM_POINTS><<<G, 128, 0, s>>>(q, kp, prior, NQ, g.gp, g.sorted.p, g.cell_start.p, k, qs, ts, idx, d2, nf, g.unres_list.p,  \
                                                g.unres_count.p);                                                                           \
     else                                                                                                                                   \
@@ -703,6 +823,7 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
       LSB_LAUNCH_CHECK(); lc.add();                                                                                                        \
     }                                                                                                                                      \
   } while (0)
+  static const bool dbg = std::getenv("LSB_KNN_DEBUG") != nullptr;
   if (k <= 1) LSB_KNN_CASE(1);
   else if (k <= 5) LSB_KNN_CASE(5);
   else if (k <= 8) LSB_KNN_CASE(8);
@@ -710,6 +831,12 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   else if (k <= 16) LSB_KNN_CASE(16);
   else LSB_KNN_CASE(32);
 #undef LSB_KNN_CASE
+  if (dbg) {      // diagnostic only (synchronises): how many queries the first kernel left to the warp pass / brute force
+    unsigned h[4];
+    LSB_CUDA(cudaMemcpyAsync(h, g.unres_count.p, sizeof(h), cudaMemcpyDeviceToHost, s));
+    LSB_CUDA(cudaStreamSynchronize(s));
+    std::fprintf(stderr, "[lsb knn] nq %zu k %d m %zu cell %.2f %s unresolved %u brute %u\n", nq, k, g.m, g.gp.cell, reuse ? "reuse" : (quad ? "quad" : "stream"), h[0], h[2]);
+  }
 }
 
 

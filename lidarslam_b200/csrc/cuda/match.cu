@@ -376,6 +376,19 @@ __device__ __noinline__ void lm_control(unsigned long long* s_state_raw, unsigne
   lm_point_warp(s.xc, s_pt_raw);
 }
 
+// Device-resident ICP loop (cuda/icp.cuh): the steps between two ICP iterations, out of line so that their FP64 pose
+// arithmetic (quaternions, slerp, trig) does not weigh on the registers of the evaluating threads (inlined they cost
+// k_lm_solve 2.7 KB of spills).  One thread; the state lives in shared memory, staged by the whole CTA.
+__device__ __noinline__ void icp_control_dev(unsigned long long* s_icp_raw, IcpCtl ctl, const unsigned long long* s_state_raw, unsigned matched)
+{
+  icp_control(*reinterpret_cast<IcpState*>(s_icp_raw), ctl, *reinterpret_cast<const LmState*>(s_state_raw), matched);
+}
+// LocalOptimizer::SetPosePrior (:44-48) on the pose the previous iteration left in device memory
+__device__ __noinline__ void icp_prior_dev(const IcpState* icp, int stage, double* x0)
+{
+  iso_to_xyzrpy(stage == ICP_STAGE_LOC ? icp->Tworld : icp->Trelative, x0);
+}
+
 constexpr int LM_THREADS = 512;   // 16 warps; each warp evaluates 2 groups of 32 records of the CTA's chunk
 constexpr int LM_WARPS = LM_THREADS / 32;
 constexpr int LM_GROUPS = LSB_LM_CHUNK / 32;
@@ -498,7 +511,7 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
   if (warp == 0) {
     if (lane == 0) {
       double x0[6];
-      if (icp) iso_to_xyzrpy(ctl.stage == ICP_STAGE_LOC ? icp->Tworld : icp->Trelative, x0);   // LocalOptimizer::SetPosePrior (:44-48)
+      if (icp) icp_prior_dev(icp, ctl.stage, x0);
       else for (int q = 0; q < 6; ++q) x0[q] = start.x[q];
       lm_begin(s_state, x0, max_iter, two_d);
       unsigned matched = 0;
@@ -587,25 +600,28 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
   }
   if (blockIdx.x == 0) {
     if (threadIdx.x < NW) reinterpret_cast<unsigned long long*>(state_out)[threadIdx.x] = s_state_raw[threadIdx.x];
-    // between two ICP iterations: pose update, undistortion refinement, the break tests (cuda/icp.cuh), by one thread
+    // between two ICP iterations: pose update, undistortion refinement, the break tests (cuda/icp.cuh), by one thread on a
+    // copy of the state in shared memory (s_group is free by now: every evaluation is over)
+    constexpr int NI = (int)(sizeof(IcpState) / 8);
+    static_assert(sizeof(IcpState) % 8 == 0, "copied as 64-bit words");
+    static_assert(NI <= LSB_LM_NSUM * LM_GROUPS, "the ICP state is staged in s_group");
+    unsigned long long* s_icp_raw = reinterpret_cast<unsigned long long*>(&s_group[0][0]);
     __shared__ int s_hand_over;
+    if (icp) for (int j = threadIdx.x; j < NI; j += LM_THREADS) s_icp_raw[j] = reinterpret_cast<const unsigned long long*>(icp)[j];
+    __syncthreads();
     if (threadIdx.x == 0) {
       s_hand_over = 1;
       if (icp) {
-        IcpState st = *icp;
-        icp_control(st, ctl, s_state, s_matched);
-        *icp = st;
-        s_hand_over = st.done;
+        icp_control_dev(s_icp_raw, ctl, s_state_raw, s_matched);
+        s_hand_over = reinterpret_cast<const IcpState*>(s_icp_raw)->done;
       }
     }
     __syncthreads();
+    if (icp) for (int j = threadIdx.x; j < NI; j += LM_THREADS) reinterpret_cast<unsigned long long*>(icp)[j] = s_icp_raw[j];
     if (host_out && s_hand_over) {     // the loop is over: CTA 0 hands the results to the host, then raises the flag
-      constexpr int NI = (int)(sizeof(IcpState) / 8);
-      static_assert(sizeof(IcpState) % 8 == 0, "copied as 64-bit words");
       if (threadIdx.x < NW) reinterpret_cast<volatile unsigned long long*>(&host_out->state)[threadIdx.x] = s_state_raw[threadIdx.x];
       if (threadIdx.x < 3 * LSB_MATCH_N_STATUS) reinterpret_cast<volatile int*>(host_out->hist)[threadIdx.x] = hist[threadIdx.x];
-      if (icp) for (int j = threadIdx.x; j < NI; j += LM_THREADS)
-        reinterpret_cast<volatile unsigned long long*>(&host_out->icp)[j] = reinterpret_cast<const unsigned long long*>(icp)[j];
+      if (icp) for (int j = threadIdx.x; j < NI; j += LM_THREADS) reinterpret_cast<volatile unsigned long long*>(&host_out->icp)[j] = s_icp_raw[j];
       __threadfence_system();
       __syncthreads();
       if (threadIdx.x == 0) { *reinterpret_cast<volatile unsigned*>(&host_out->seq) = host_seq; __threadfence_system(); }
