@@ -23,6 +23,9 @@ import sys
 import threading
 import time
 
+# before anything initialises CUDA (torch does under torchrun): see RequestWorkQueues in lidarslam_b200/csrc/host/capi.cu
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -43,7 +46,9 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=8, help="frames of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
-    ap.add_argument("--multi-seq", type=int, default=4, help="extra pass: that many independent sequences sharing ONE GPU (0 = skip)")
+    ap.add_argument("--batch", type=int, default=8, help="BASELINE configs[4]: that many independent sequences over the job's GPUs, "
+                                                         "batch / gpus handles per GPU (0 = skip)")
+    ap.add_argument("--deep-start", type=int, default=300, help="second timed window starting at this frame, maps saturated (0 = skip; N = 1 only)")
     return ap.parse_args()
 
 
@@ -52,6 +57,18 @@ def configure(s):
     p.use_keypoints[2] = 1           # blobs
     p.undistortion = 2               # REFINED
     s.SetParams(p)
+
+
+def config_dict(a, world):
+    """the same dictionary on both arms (ours / --impl reference): the driver compares them key by key"""
+    return {"workload": WORKLOAD, "sensor": a.sensor, "sequences": world, "parallelism": "replicas x%d" % world,
+            "l2": "flushed between timed iterations" if not a.no_flush else "not flushed",
+            "timing": "ours: CUDA events on the handle's stream around each lsb_add_frames_dev call, kernel durations (roofline, *_kernels) "
+                      "from a separate pass with lsb_set_profiling(1); reference arm: wall clock around each AddFrame of the CPU port"}
+
+
+def pct(values, q):
+    return float(np.percentile(np.asarray(values, dtype=np.float64), q))
 
 
 def make_frames(sensor, n, seed):
@@ -147,13 +164,15 @@ def _pool_stats():
     return out
 
 
-def run_multi_sequence(n_seq, sensor, warm, steps, device, first):
-    """several handles per GPU (one host thread + streams each) fill the SMs a single latency-bound
-    trajectory leaves idle.  Wall clock around `steps` frames of every sequence, frames resident in HBM, no L2 flush
-    (the sequences evict each other).  `first` = the frames of sequence 0 (already generated)."""
+def run_batch(seq_ids, sensor, warm, steps, device, own=None):
+    """BASELINE configs[4] / SURVEY 8(e): a fixed batch of independent sequences (scene seeds 1234 + id) over the job's GPUs;
+    this rank runs `seq_ids`, one handle + host thread each, sharing its GPU (they fill the SMs a single latency-bound
+    trajectory leaves idle).  Wall clock around `steps` frames of every sequence, frames resident in HBM, no L2 flush (the
+    sequences evict each other).  Returns (seconds, per-frame latencies in ms per sequence, pose of the first sequence)."""
     from lidarslam_b200.slam import Slam
-    seqs = [first] + [make_frames(sensor, warm + steps, 1234 + 100 * (s + 1)) for s in range(n_seq - 1)]
-    npts = len(first[0][0])
+    # own = (sequence id, frames) already generated by the caller
+    seqs = [own[1] if (own is not None and sid == own[0]) else make_frames(sensor, warm + steps, 1234 + sid) for sid in seq_ids]
+    npts = len(seqs[0][0][0])
     hs, dptrs = [], []
     for frames in seqs:
         h = Slam(device=device)
@@ -163,14 +182,17 @@ def run_multi_sequence(n_seq, sensor, warm, steps, device, first):
             h.AddFramesDev([dp[i]], [npts], [frames[i][1]], [i + 1])
         hs.append(h)
         dptrs.append(dp)
-    go = threading.Barrier(n_seq + 1)
+    go = threading.Barrier(len(seqs) + 1)
+    lat = [[] for _ in seqs]
 
-    def work(h, frames, dp):
+    def work(j, h, frames, dp):
         go.wait()
         for i in range(warm, warm + steps):
+            t0 = time.perf_counter()
             h.AddFramesDev([dp[i]], [npts], [frames[i][1]], [i + 1])
+            lat[j].append(1e3 * (time.perf_counter() - t0))
 
-    ts = [threading.Thread(target=work, args=(h, f, d)) for h, f, d in zip(hs, seqs, dptrs)]
+    ts = [threading.Thread(target=work, args=(j, h, f, d)) for j, (h, f, d) in enumerate(zip(hs, seqs, dptrs))]
     for t in ts:
         t.start()
     go.wait()
@@ -181,8 +203,38 @@ def run_multi_sequence(n_seq, sensor, warm, steps, device, first):
     pose0 = hs[0].GetWorldTransform()[0]
     for h in hs:
         h.close()
-    return {"sequences": n_seq, "frames_per_s": n_seq * steps / dt, "ms_per_frame_and_sequence": 1e3 * dt / steps,
-            "timing": "wall clock around %d frames of each sequence, one handle + host thread per sequence on one GPU" % steps}, pose0
+    return dt, lat, pose0
+
+
+def run_deep_window(sensor, start, steps, device, flush):
+    """A second timed window deep in the sequence (BASELINE quotes the metric on a 500-frame sequence): frames 0 .. start - 1
+    go through lsb_add_frames from the host untimed, frames start .. start + steps - 1 are timed like `value` (resident in
+    HBM, CUDA events per call, L2 flushed between calls).  By then the maps are saturated and the grid has rolled."""
+    from lidarslam_b200.slam import Slam
+    from tools.synth import synth
+    seq, sens = synth.Sequence(scene_seed=1234), synth.sensor(sensor)
+    h = Slam(device=device)
+    configure(h)
+    for i in range(start):
+        pts, _, stamp = seq.frame(sens, i)
+        h.AddFrame(pts, stamp, i + 1)
+    window = [seq.frame(sens, i) for i in range(start, start + steps)]
+    npts = len(window[0][0])
+    dp = [h.DevUpload(w[0]) for w in window]
+    ms, kf = [], 0
+    for j, (pts, _, stamp) in enumerate(window):
+        if flush:
+            h.FlushL2()
+        h.AddFramesDev([dp[j]], [npts], [stamp], [start + j + 1])
+        st = h.GetFrameStats()
+        ms.append(st.ms_total)
+        kf += st.is_keyframe
+    out = {"frames": "%d-%d" % (start, start + steps - 1), "value": steps / (sum(ms) * 1e-3), "unit": UNIT,
+           "p50_ms_per_frame": pct(ms, 50), "p95_ms_per_frame": pct(ms, 95), "max_ms_per_frame": max(ms), "key_frames": int(kf),
+           "n_map": list(st.n_map), "n_submap": list(st.n_submap), "n_matches": list(st.n_matches),
+           "timing": "as `value`: CUDA events per call, frames resident in HBM, L2 %s" % ("flushed between calls" if flush else "not flushed")}
+    h.close()
+    return out
 
 
 def main():
@@ -202,7 +254,8 @@ def main():
         line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": K, "warmup": W,
                 "ms_per_step": 1e3 * total / K, "p50_ms_per_frame": 1e3 * statistics.median(times), "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "sensor": a.sensor, "sequences": 1},
+                "p95_ms_per_frame": 1e3 * pct(times, 95),
+                "config": config_dict(a, 1),
                 "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
                                  "sample": "%d frames after %d warm-up frames, CPU/OpenMP restatement of the reference (oracle/)" % (K, W)},
                 "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -321,8 +374,22 @@ def main():
     if world > 1:
         print("[bench rank %d] device %.3f ms/frame, e2e %.3f ms/frame (p50 %.3f, max %.3f)" % (
             rank, total_ms / K, 1e3 * e2e_s / K, 1e3 * statistics.median(e2e_steps), 1e3 * max(e2e_steps)), file=sys.stderr, flush=True)
+    # ---------------- BASELINE configs[4]: a fixed batch of sequences over the job's GPUs ----
+    batch_dt = batch_p95 = 0.0
+    batch_lat, batch_ids, batch_same = [], [], True
+    if a.batch >= world and a.batch % world == 0:
+        for h_ in (g, e, pr):            # give the single-sequence handles' memory back to the pool first
+            h_.close()
+        batch_ids = shard.assign_sequences(a.batch, world)[rank]
+        barrier()
+        batch_dt, batch_lat, pose0 = run_batch(batch_ids, a.sensor, W, K, local, own=(rank, frames))
+        barrier()
+        batch_p95 = max(pct(l, 95) for l in batch_lat)
+        if rank in batch_ids:
+            batch_same = bool(np.array_equal(pose0, Tg)) if batch_ids[0] == rank else True
     # ---------------- max over ranks ------------------------------------------------------
-    (max_ms, max_e2e_ms), (n_launches,) = shard.reduce_job([total_ms, e2e_s * 1e3], [launches], device="cuda:%d" % local)
+    (max_ms, max_e2e_ms, max_batch_ms, max_batch_p95), (n_launches,) = shard.reduce_job(
+        [total_ms, e2e_s * 1e3, batch_dt * 1e3, batch_p95], [launches], device="cuda:%d" % local)
     value = shard.job_throughput(K, world, max_ms * 1e-3)
     e2e_value = shard.job_throughput(K, world, max_e2e_ms * 1e-3)
 
@@ -345,16 +412,13 @@ def main():
         per_launch_s = knn_ms * 1e-3 / max(knn_launches, 1)
         achieved = per_launch_bytes / per_launch_s / 1e9 if per_launch_s > 0 else 0.0
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-                "ms_per_step": max_ms / K, "p50_ms_per_frame": statistics.median(step_ms), "max_ms_per_frame": max(step_ms),
+                "ms_per_step": max_ms / K, "p50_ms_per_frame": statistics.median(step_ms), "p95_ms_per_frame": pct(step_ms, 95), "max_ms_per_frame": max(step_ms),
                 "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64", "data": "synthetic",
                 "points_per_sec": value * npts, "knn_queries_per_sec": knn_queries / (knn_ms * 1e-3) if knn_ms > 0 else None,
-                "config": {"workload": WORKLOAD, "sensor": a.sensor, "sequences": world, "parallelism": "replicas x%d" % world,
-                           "l2": "flushed between timed iterations" if not a.no_flush else "not flushed",
-                           "timing": "CUDA events on the handle's stream around each lsb_add_frames_dev call; kernel durations "
-                                     "(roofline, *_kernels) from a separate pass with lsb_set_profiling(1)"},
+                "config": config_dict(a, world),
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d // K, "d2h_bytes_per_step": d2h // K,
-                        "same_pose_as_device_arm": same_pose, "p50_ms_per_frame": 1e3 * statistics.median(e2e_steps),
+                        "same_pose_as_device_arm": same_pose, "p50_ms_per_frame": 1e3 * statistics.median(e2e_steps), "p95_ms_per_frame": 1e3 * pct(e2e_steps, 95),
                         "max_ms_per_frame": 1e3 * max(e2e_steps)},
                 "gpu_launches": int(n_launches),
                 "clocks": sampler.result(),
@@ -374,19 +438,36 @@ def main():
         lm_launches = max(last.loc_icp_iters, 1) * K
         lm_us = lm_ms * 1e3 / max(lm_launches, 1)
         lm_flops = 300.0 * n_match * evals                                      # ~300 FP64 flops per record and evaluation
+        import ctypes
+        fp = (ctypes.c_double * 4)()
+        from lidarslam_b200 import capi as _capi
+        rc_fp = _capi.load_library().lsb_measure_fp_peaks(ctypes.c_int(local), fp)
+        fp64_peak = fp[1] if rc_fp == 0 and fp[1] > 0 else None       # multiply + add, not fused: what this library issues
+        lm_tflops = lm_flops / (lm_us * 1e-6) / 1e12 if lm_us > 0 else None
+        line["measured_fp_peaks_tflops"] = {"fp64_fma": fp[0], "fp64_mul_add": fp[1], "fp32_fma": fp[2], "fp32_mul_add": fp[3],
+                                            "how": "lsb_measure_fp_peaks: 8 dependent chains per thread, 8 CTAs of 256 threads per SM, best of 5 launches, CUDA events"}
         line["roofline_other"] = [{
             "kernel": "k_lm_solve (residual/Jacobian + J^T J reduction + LM step, one launch per solve)", "bound": "fp64",
-            "achieved": lm_flops / (lm_us * 1e-6) / 1e12 if lm_us > 0 else None, "peak": 37.2, "unit": "TFLOP/s",
-            "frac": (lm_flops / (lm_us * 1e-6) / 1e12 / 37.2) if lm_us > 0 else None,
-            "peak_source": "nominal FP64 vector peak 148 SM x 64 FMA/clk x 2 x 1.965 GHz (not in MEASURED_PEAKS.json); the kernel is built "
-                           "without FMA contraction (bit parity with the CPU oracle), i.e. against an 18.6 Tflop/s ceiling",
+            "achieved": lm_tflops, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": (lm_tflops / fp64_peak) if (lm_tflops and fp64_peak) else None,
+            "peak_source": "measured on this GPU in this run (lsb_measure_fp_peaks): FP64 multiply + add without contraction, the instruction mix "
+                           "the kernel is built with (bit parity with the CPU oracle); the fused-FMA figure is in measured_fp_peaks_tflops",
             "flops_per_launch": lm_flops, "us_per_launch": lm_us, "evaluations_per_launch": evals, "records": n_match,
-            "algorithmic_bytes_per_launch": 104 * n_match, "note": "latency-bound: 4.5 us evaluate + 1.3 us grid barrier + 1.8 us final fold + "
-            "3.6 us trust-region step per evaluation (tools/probes/lm_eval_probe.cu, profiles/r01_lm_probe.txt)"}]
-        if world == 1 and a.multi_seq > 1:
-            ms, pose0 = run_multi_sequence(a.multi_seq, a.sensor, W, K, local, frames)
-            ms["sequence0_same_pose_as_solo_run"] = bool(np.array_equal(pose0, Tg))
-            line["multi_sequence"] = ms
+            "algorithmic_bytes_per_launch": 104 * n_match, "note": "latency-bound: evaluate + grid barrier + final fold + trust-region step per evaluation, phase times in "
+                                                           "profiles/r02_lm_probe.txt (tools/probes/lm_eval_probe.cu)"}]
+        if batch_ids:
+            pooled = [v for l in batch_lat for v in l]
+            line["batch8"] = {"sequences": a.batch, "sequences_per_gpu": a.batch // world, "n_gpus": world,
+                              "frames_per_s": a.batch * K / (max_batch_ms * 1e-3), "unit": UNIT,
+                              "p50_ms_per_frame": pct(pooled, 50), "p95_ms_per_frame": pct(pooled, 95),
+                              "p95_ms_per_frame_worst_sequence_any_rank": max_batch_p95,
+                              "per_sequence_p50_ms": [pct(l, 50) for l in batch_lat],
+                              "sequence_same_pose_as_solo_run": batch_same,
+                              "timing": "wall clock (max over ranks) around %d frames of every sequence, one handle + host thread per sequence, "
+                                        "%d sequences sharing each GPU, frames resident in HBM, no L2 flush; p50 / p95 = wall clock per "
+                                        "lsb_add_frames_dev call, rank 0's sequences pooled" % (K, a.batch // world)}
+        if world == 1 and a.deep_start > 0:
+            line["deep_window"] = run_deep_window(a.sensor, a.deep_start, K, local, not a.no_flush)
         if world == 1 and not a.no_cpu_baseline:
             n_s = min(a.cpu_sample, K)
             times, threads = run_cpu(frames, W, n_s)

@@ -234,6 +234,10 @@ LSB_API long lsb_get_match_debug(lsb_slam* h, int stage, int type, uint8_t* stat
  * field: 0 sin_angle 1 saliency 2 depth_gap 3 intensity_gap 4-6 {edge,plane,blob}_keypoint 7-9 {edge,plane,blob}_validity */
 LSB_API long lsb_get_ke_debug(lsb_slam* h, int device_id, int field, float* out, long cap);
 LSB_API int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s);
+/* Measurement aid (no reference counterpart): arithmetic peaks of the device from a dependent-chain microbenchmark, in
+ * TFLOP/s: [0] FP64 FMA, [1] FP64 multiply + add not fused (what this library issues: it is built without FMA contraction),
+ * [2] FP32 FMA, [3] FP32 multiply + add not fused.  bench.py divides by these instead of nominal figures. */
+LSB_API int lsb_measure_fp_peaks(int cuda_device, double out_tflops[4]);
 /* When on, CUDA events bracket every kNN / fit / LM kernel launch and
  * lsb_frame_stats.ms_knn / ms_fit / ms_lm are filled; the three keypoint types, which
  * otherwise run on their own streams, are serialised on the handle's stream so that the

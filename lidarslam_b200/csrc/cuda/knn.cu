@@ -1,5 +1,5 @@
 // Exact kNN on a uniform grid — see knn.cuh and DESIGN.md §3 K8.  Hand-written search kernels;
-// CUB is used only for the radix sort that orders the target points by cell.
+// CUB is used only for the exclusive scan of the cell histogram.
 //
 // Cells of one (z, y) row are contiguous in the cell-major point array, so a row of cells is ONE
 // index range (two cell_start loads), which makes empty space cheap.  After the cube of Chebyshev
@@ -12,7 +12,6 @@
 // sphere of the tentative k-th distance).
 #include "knn.cuh"
 #include <cub/cub.cuh>
-#include <thrust/iterator/reverse_iterator.h>
 #include <cfloat>
 #include <climits>
 #include <algorithm>
@@ -65,38 +64,30 @@ __device__ __forceinline__ int cell_coord(float v, float o, float cell, int n)
   return (int)f;
 }
 
-__global__ void k_cell_keys(const lsb_point* __restrict__ pts, int m, KnnGridParams gp, uint32_t* __restrict__ key, uint32_t* __restrict__ idx)
+// Cell ordering as a counting sort (no radix sort): the histogram of the cell keys IS the cell_start table once scanned.
+// Pass 1: cell key of every point, its arrival rank inside the cell (atomic counter per cell).  Pass 2 (after an exclusive
+// scan of the counters): the point goes to cell_start[key] + rank.  The order of the points INSIDE a cell follows the
+// atomics and is not reproducible; no result depends on it (every search orders its candidates by (d2, cloud index)).
+__global__ void k_cell_count(const lsb_point* __restrict__ pts, int m, KnnGridParams gp, uint32_t* __restrict__ key, uint32_t* __restrict__ rank,
+                             uint32_t* __restrict__ count)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   const float4 p = reinterpret_cast<const float4*>(pts)[2 * i];
   const int cx = cell_coord(p.x, gp.ox, gp.cell, gp.nx), cy = cell_coord(p.y, gp.oy, gp.cell, gp.ny), cz = cell_coord(p.z, gp.oz, gp.cell, gp.nz);
-  key[i] = (uint32_t)((cz * gp.ny + cy) * gp.nx + cx);
-  idx[i] = (uint32_t)i;
+  const uint32_t k = (uint32_t)((cz * gp.ny + cy) * gp.nx + cx);
+  key[i] = k;
+  rank[i] = atomicAdd(count + k, 1u);
 }
 
-__global__ void k_cell_gather(const lsb_point* __restrict__ pts, int m, const uint32_t* __restrict__ idx, float4* __restrict__ sorted)
+__global__ void k_cell_scatter(const lsb_point* __restrict__ pts, int m, const uint32_t* __restrict__ key, const uint32_t* __restrict__ rank,
+                               const uint32_t* __restrict__ cell_start, float4* __restrict__ sorted)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
-  const uint32_t o = idx[i];
-  const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)o];
-  sorted[i] = make_float4(p.x, p.y, p.z, __int_as_float((int)o));
+  const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)i];
+  sorted[__ldg(cell_start + key[i]) + rank[i]] = make_float4(p.x, p.y, p.z, __int_as_float(i));
 }
-
-// cell_start[c] = number of points whose cell key is < c  (c in [0, ncells]) = the position of the first
-// point of the first non-empty cell >= c.  Two steps instead of a binary search per cell (85 % of the
-// 2.5 M cells of an OS-128 sub-map are empty): every first point of a run of equal keys marks its cell,
-// then a suffix-min scan fills the empty cells with the start of the next non-empty one.
-__global__ void k_cell_mark(const uint32_t* __restrict__ key_sorted, int m, int ncells, uint32_t* __restrict__ mark)
-{
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) mark[ncells] = (uint32_t)m;
-  if (i >= m) return;
-  const uint32_t k = key_sorted[i];
-  if (i == 0 || key_sorted[i - 1] != k) mark[k] = (uint32_t)i;
-}
-struct MinU32 { __host__ __device__ __forceinline__ uint32_t operator()(uint32_t a, uint32_t b) const { return a < b ? a : b; } };
 
 // ------------------------------------------------------------------ search ---
 // A candidate is one 64-bit key: (bits of d2) << 32 | cloud index.  d2 >= +0, so the unsigned
@@ -886,31 +877,18 @@ void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float
   gp.ox = bmin[0] - c; gp.oy = bmin[1] - c; gp.oz = bmin[2] - c;
   gp.nx = (int)nx; gp.ny = (int)ny; gp.nz = (int)nz;
   const int ncells = gp.nx * gp.ny * gp.nz;
-  key_a.reserve(m, s); key_b.reserve(m, s); idx_a.reserve(m, s); idx_b.reserve(m, s);
-  sorted.reserve(m, s); cell_start.reserve((size_t)ncells + 1, s);
+  key_a.reserve(m, s); idx_a.reserve(m, s);
+  const int nc1 = ncells + 1;
+  sorted.reserve(m, s); cell_start.reserve((size_t)nc1, s); cell_count.reserve((size_t)nc1, s);
   const unsigned G = div_up(m, TPB);
-  k_cell_keys<<<G, TPB, 0, s>>>(d_cloud, M, gp, key_a.p, idx_a.p); LSB_LAUNCH_CHECK(); lc.add();
-  int bits = 1;
-  while ((1ll << bits) < ncells) ++bits;
-  size_t tmp = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tmp, key_a.p, key_b.p, idx_a.p, idx_b.p, M, 0, bits, s);
-  cub_tmp.reserve(tmp + 256, s);
-  size_t tb = cub_tmp.cap;
-  LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, key_a.p, key_b.p, idx_a.p, idx_b.p, M, 0, bits, s)); lc.add(3);
-  k_cell_gather<<<G, TPB, 0, s>>>(d_cloud, M, idx_b.p, sorted.p); LSB_LAUNCH_CHECK(); lc.add();
-  {
-    const int nc1 = ncells + 1;
-    cell_mark.reserve((size_t)nc1, s);
-    LSB_CUDA(cudaMemsetAsync(cell_mark.p, 0xff, (size_t)nc1 * sizeof(uint32_t), s));
-    k_cell_mark<<<G, TPB, 0, s>>>(key_b.p, M, ncells, cell_mark.p); LSB_LAUNCH_CHECK(); lc.add();
-    auto in = thrust::make_reverse_iterator(cell_mark.p + nc1);
-    auto out = thrust::make_reverse_iterator(cell_start.p + nc1);
-    size_t tb2 = 0;
-    cub::DeviceScan::InclusiveScan(nullptr, tb2, in, out, MinU32(), nc1, s);
-    cub_tmp.reserve(tb2 + 256, s);
-    tb2 = cub_tmp.cap;
-    LSB_CUDA(cub::DeviceScan::InclusiveScan(cub_tmp.p, tb2, in, out, MinU32(), nc1, s)); lc.add(2);
-  }
+  LSB_CUDA(cudaMemsetAsync(cell_count.p, 0, (size_t)nc1 * sizeof(uint32_t), s));
+  k_cell_count<<<G, TPB, 0, s>>>(d_cloud, M, gp, key_a.p, idx_a.p, cell_count.p); LSB_LAUNCH_CHECK(); lc.add();
+  size_t tb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tb, cell_count.p, cell_start.p, nc1, s);
+  cub_tmp.reserve(tb + 256, s);
+  tb = cub_tmp.cap;
+  LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, cell_count.p, cell_start.p, nc1, s)); lc.add(2);   // cell_start[ncells] = m
+  k_cell_scatter<<<G, TPB, 0, s>>>(d_cloud, M, key_a.p, idx_a.p, cell_start.p, sorted.p); LSB_LAUNCH_CHECK(); lc.add();
 }
 
 void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t* d_idx, float* d_d2, int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc) const

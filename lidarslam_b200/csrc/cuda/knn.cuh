@@ -30,10 +30,10 @@ struct KnnGrid {
   const lsb_point* cloud = nullptr;   // device, not owned; indices refer to this order
   size_t m = 0;
   KnnGridParams gp{};
-  DevBuf<uint32_t> key_a, key_b, idx_a, idx_b;
+  DevBuf<uint32_t> key_a, idx_a;   // cell key and arrival rank inside the cell of every target point
   DevBuf<float4> sorted;          // cell-major points: (x, y, z, bits of the cloud index)
   DevBuf<uint32_t> cell_start;    // [ncells + 1] prefix offsets into sorted
-  DevBuf<uint32_t> cell_mark;     // [ncells + 1] first point of each non-empty cell, UINT_MAX elsewhere (input of the suffix-min scan)
+  DevBuf<uint32_t> cell_count;    // [ncells + 1] points per cell (histogram; its exclusive scan is cell_start)
   DevBuf<unsigned char> cub_tmp;
   mutable DevBuf<int32_t> unres_list;    // queries handed to the brute-force kernel
   mutable DevBuf<unsigned> unres_count;  // [4]: unsettled count, cursor, brute-force count, cursor

@@ -556,36 +556,59 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
         if (q >= 0) s_group[q][g] = r;
       }
       __syncthreads();
+      {
+        const int q1 = warp + LM_WARPS;
+        double v0 = s_group[warp][lane], v1 = (q1 < LSB_LM_NSUM) ? s_group[q1 < LSB_LM_NSUM ? q1 : 0][lane] : 0.0;
 #pragma unroll
-      for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
-        const double v = warp_fold32(s_group[q][lane]);
-        if (lane == 0) my_part[(size_t)q * pstride + c] = v;
+        for (int off = 16; off >= 1; off >>= 1) {
+          v0 += __shfl_down_sync(0xffffffffu, v0, off);
+          v1 += __shfl_down_sync(0xffffffffu, v1, off);
+        }
+        if (lane == 0) {
+          my_part[(size_t)warp * pstride + c] = v0;
+          if (q1 < LSB_LM_NSUM) my_part[(size_t)q1 * pstride + c] = v1;
+        }
       }
       __syncthreads();
     }
     LM_PROBE_STAMP(e, 1);
     lm_grid_barrier(bar, (unsigned)(e + 1) * gridDim.x);
     LM_PROBE_STAMP(e, 2);
-#pragma unroll
-    for (int q = warp; q < LSB_LM_NSUM; q += LM_WARPS) {
-      const double* src = my_part + (size_t)q * pstride;
-      double acc = 0.0;
+    {
+      // warp w folds the quantities w and w + 16: the (up to) eight block folds of a pass are independent chains, loaded
+      // together and folded in lock step (same pairwise tree and the same in-order sum of the block sums as before)
+      constexpr unsigned FULL = 0xffffffffu;
+      double acc[2] = {0.0, 0.0};
       for (int b0 = 0; b0 < nblocks; b0 += 4) {
-        double v[4];
+        double v[2][4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int c = (b0 + u) * 32 + lane;
-          v[u] = (b0 + u < nblocks && c < nchunks) ? __ldcg(src + c) : 0.0;
-        }
+        for (int qi = 0; qi < 2; ++qi) {
+          const int q = warp + LM_WARPS * qi;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (b0 + u < nblocks) {
-            const double f = warp_fold32(v[u]);
-            acc = (b0 + u == 0) ? f : acc + f;
+          for (int u = 0; u < 4; ++u) {
+            const int c = (b0 + u) * 32 + lane;
+            v[qi][u] = (q < LSB_LM_NSUM && b0 + u < nblocks && c < nchunks) ? __ldcg(my_part + (size_t)q * pstride + c) : 0.0;
           }
         }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+#pragma unroll
+          for (int qi = 0; qi < 2; ++qi) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[qi][u] += __shfl_down_sync(FULL, v[qi][u], off);
+          }
+        }
+#pragma unroll
+        for (int qi = 0; qi < 2; ++qi) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (b0 + u < nblocks) acc[qi] = (b0 + u == 0) ? v[qi][u] : acc[qi] + v[qi][u];
+        }
       }
-      if (lane == 0) s_E[q] = acc;
+      if (lane == 0) {
+        s_E[warp] = acc[0];
+        if (warp + LM_WARPS < LSB_LM_NSUM) s_E[warp + LM_WARPS] = acc[1];
+      }
     }
     __syncthreads();
     LM_PROBE_STAMP(e, 3);
@@ -748,7 +771,7 @@ void MatchWorkspace::enqueue_solve(const double x0[6], int max_iter, int two_d, 
   attr.id = cudaLaunchAttributeCooperative;
   attr.val.cooperative = 1;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)std::min(nchunks, lm_grid_limit));
+  cfg.gridDim = dim3((unsigned)std::min(nchunks, std::max(lm_grid_limit / std::max(lm_grid_share, 1), 8)));
   cfg.blockDim = dim3(LM_THREADS);
   cfg.dynamicSmemBytes = kSmem;
   cfg.stream = s;

@@ -26,6 +26,8 @@ struct MatchWorkspace {
   DevBuf<LmState> lm_state;         // [1] final state of the last solve
   DevBuf<unsigned> lm_counter;      // [2] grid barrier of the persistent LM kernel
   int lm_grid_limit = 0;            // co-resident CTAs of that kernel on this device
+  int lm_grid_share = 1;            // handles in flight on this device: a solve takes lm_grid_limit / share CTAs, so that the
+                                    // cooperative launches of several sequences run side by side instead of one after the other
   PinnedBuf<int> h_hist;
   PinnedBuf<LmState> h_lm;
   // result block of a solve in pinned (device-visible) host memory: k_lm_solve stores the final state and the match

@@ -4,6 +4,7 @@
 #include "slam.cuh"
 #include "pcd_io.h"
 #include <cstring>
+#include <cstdlib>
 #include <ctime>
 #include <string>
 
@@ -50,10 +51,22 @@ static long CopyOut(lsb_slam* h, const lsb_point* d, size_t n, lsb_point* out, l
   return (long)n;
 }
 
+// A handle drives four streams (one per keypoint type + its own).  The CUDA default of 8 hardware work queues makes the
+// streams of several handles share queues, which serialises independent sequences (8 OS-128 sequences on one B200: 731
+// frames/s with 8 queues, 1201 with 32, tools/probes/batch_probe.py).  The variable is read when the CUDA context is created,
+// so it is set (never overriding the user's value) before the library's first CUDA call; a process that initialised CUDA
+// earlier has to export it itself.
+static void RequestWorkQueues()
+{
+  static const bool once = [] { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", /*overwrite=*/0); return true; }();
+  (void)once;
+}
+
 extern "C" {
 
 int lsb_device_count(void)
 {
+  RequestWorkQueues();
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
   return n;
@@ -64,6 +77,7 @@ int lsb_create(lsb_slam** out, int cuda_device)
 {
   if (!out) return LSB_E_INVALID;
   *out = nullptr;
+  RequestWorkQueues();
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
     cudaGetLastError();

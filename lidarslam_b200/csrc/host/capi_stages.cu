@@ -161,6 +161,11 @@ int lsb_knn_search(lsb_slam* h, const lsb_point* cloud, size_t m, const float* q
   });
 }
 
+int lsb_measure_fp_peaks(int cuda_device, double out_tflops[4])
+{
+  return guarded([&] { measure_fp_peaks(cuda_device, out_tflops); return LSB_OK; });
+}
+
 // no allocation, no handle, no synchronisation: see the declaration (no reference counterpart)
 int lsb_knn_search_noalloc(int cuda_device, const lsb_point* d_cloud, size_t m, const float* d_queries_xyz, size_t nq, int k, int32_t* d_idx_out,
                            float* d_d2_out, void* cuda_stream)

@@ -533,6 +533,9 @@ const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_mat
   d_icp.reserve(1, stream);
   dev_icp_init(d_icp.p, init, stream, lc);
   mw.icp_stage = stage;
+  // several sequences sharing the GPU: each solve takes its share of the SMs (at most a quarter is given up)
+  static const int share_max = [] { const char* e = std::getenv("LSB_LM_GRID_SHARE_MAX"); return e ? std::max(1, std::atoi(e)) : 4; }();   // tuning hook
+  mw.lm_grid_share = std::min(std::max(g_handles_in_flight.load(std::memory_order_relaxed), 1), share_max);
   mw.begin_frame(nk, (int)max_iter, stream);
   mw.next_solve_seq();
   const bool refined = loc && P.undistortion == LSB_UNDISTORTION_REFINED;

@@ -151,6 +151,8 @@ void dev_undistort(lsb_point* d_pts, size_t n, const Interpolator& it, double ti
 // the same with the interpolator the device-resident ICP loop holds (cuda/icp.cuh); mode 0: head of an iteration, 1: after the loop
 void dev_undistort_state(lsb_point* d_pts, size_t n, const IcpState* st, int mode, cudaStream_t s, LaunchCounter& lc);
 void dev_icp_init(IcpState* d_state, const IcpState& init, cudaStream_t s, LaunchCounter& lc);
+// measured FP64 / FP32 peaks of the device (cuda/peaks.cu)
+void measure_fp_peaks(int device, double out_tflops[4]);
 void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
 void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
 void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx);

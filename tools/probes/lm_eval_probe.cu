@@ -60,7 +60,8 @@ int main(int argc, char** argv)
   int per_sm = 0, sms = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_lm_solve, LM_THREADS, kSmem);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
-  const int grid = std::min(nchunks, per_sm * sms);
+  const int share = argc > 2 ? atoi(argv[2]) : 1;      // > 1: the grid a handle gets when that many share the GPU
+  const int grid = std::min(nchunks, std::max(per_sm * sms / share, 1));
   LmStart start = {{0.01, 0.02, 0.03, 0.001, 0.002, 0.003}};
   LmSensorTerms terms;
   lm_sensor_terms_clear(terms);
@@ -71,7 +72,7 @@ int main(int argc, char** argv)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(LM_THREADS); cfg.dynamicSmemBytes = kSmem; cfg.attrs = &attr; cfg.numAttrs = 1;
     cudaLaunchKernelEx(&cfg, k_lm_solve, (const double*)d_rec, stride, n, nchunks, pstride, 1.0, start, max_iter, 0, (const int*)d_hist, 100u,
-                       d_state, d_part, d_bar, terms, (MatchWorkspace::LmHostBlock*)nullptr, 0u);
+                       d_state, d_part, d_bar, terms, (MatchWorkspace::LmHostBlock*)nullptr, 0u, (IcpState*)nullptr, IcpCtl{});
   };
   printf("n = %d records, %d chunks of %d, grid %d x %d threads (%d CTA/SM)\n", n, nchunks, LSB_LM_CHUNK, grid, LM_THREADS, per_sm);
   printf("empty launch   %7.2f us\n", time_launches(200, [&] { k_empty<<<grid, LM_THREADS>>>(0); }));
