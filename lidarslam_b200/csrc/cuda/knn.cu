@@ -161,6 +161,7 @@ struct KnnPose {
   Iso3d value;
   const Iso3d* dev;
   const int* done;
+  const Interpolator* refine;   // k_knn_reuse only: undistortion refinement applied to the keypoint before it is searched
 };
 __device__ __forceinline__ bool knn_off(const KnnPose& kp) { return kp.done && *kp.done; }
 
@@ -410,7 +411,7 @@ __device__ __forceinline__ void axis_cells(float lo, float hi, float o, float ce
 //     (about k of them: T is the k-th distance up to the motion of the query), a predicated store instead of a sorted
 //     insertion, and the k smallest are then placed by rank;
 //   * the answer is exact by construction (every point within T was seen), so no query is left to the warp pass, except
-//     the ones without a usable previous list (fewer than k found, "too far" results), a box of more than 9 rows or a
+//     the ones without a usable previous list (fewer than k found, "too far" results), a box of more than 16 rows or a
 //     buffer overflow (many points at equal distance): those go to k_knn_warp with T as their threshold.
 // One thread per query, trips taken by the 32 lanes together as in k_knn_stream.
 template <int KMAX, bool FROM_POINTS>
@@ -423,12 +424,22 @@ k_knn_reuse(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, K
   constexpr unsigned FULL = 0xffffffffu;
   constexpr int CAP = (KMAX >= 32) ? KMAX + 6 : KMAX + 8;   // 48 KB of static shared memory at most
   __shared__ Key s_buf[CAP][128];
-  __shared__ uint32_t s_rb[9][128], s_re[9][128];
+  constexpr int MAXROWS = (KMAX >= 32) ? 9 : 16;          // rows of the sphere's box a thread takes on itself (shared memory budget)
+  __shared__ uint32_t s_rb[MAXROWS][128], s_re[MAXROWS][128];
   if (knn_off(prior)) return;
   const int tid = threadIdx.x;
   const int i0 = blockIdx.x * blockDim.x + tid;
   const bool live = i0 < nq;
   const int i = live ? i0 : nq - 1;
+  if (FROM_POINTS && prior.refine && live) {
+    // Slam::RefineUndistortion of the previous ICP iteration (Slam.cxx:1345-1350) on this keypoint, in place: the same
+    // arithmetic as k_undistort_state (one thread per keypoint there too), fused here to save a launch per type
+    lsb_point* pt = const_cast<lsb_point*>(kp) + i;
+    float4 v = reinterpret_cast<float4*>(pt)[0];
+    const Iso3d H = prior.refine->at(pt->time);
+    transform_point_f(H, v.x, v.y, v.z);
+    reinterpret_cast<float4*>(pt)[0] = v;
+  }
   const QueryCell q = make_query<FROM_POINTS>(q_xyz, kp, prior, i, gp);
   // the bound: largest distance from the moved query to its previous k neighbours
   bool ok = live && q.finite && (!nfound_out || nfound_out[i] >= k);
@@ -453,10 +464,10 @@ k_knn_reuse(const float* __restrict__ q_xyz, const lsb_point* __restrict__ kp, K
     axis_cells(q.qz - rr, q.qz + rr, gp.oz, gp.cell, gp.nz, z0, z1);
   }
   const int nyr = y1 - y0 + 1, rows = (z1 - z0 + 1) * nyr;
-  const bool fits = ok && rows <= 9;
+  const bool fits = ok && rows <= MAXROWS;
   int nrow = 0;
 #pragma unroll
-  for (int t = 0; t < 9; ++t) {
+  for (int t = 0; t < MAXROWS; ++t) {
     if (fits && t < rows) {
       const int z = z0 + t / nyr, y = y0 + t % nyr;
       const float gy = axis_gap(y - q.cy, q.oy, gp.cell), gz = axis_gap(z - q.cz, q.oz, gp.cell);
@@ -768,6 +779,7 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   prior.value = prior_host;
   prior.dev = da ? da->prior : nullptr;
   prior.done = da ? da->done : nullptr;
+  prior.refine = (da && da->reuse) ? da->refine : nullptr;
   const size_t qs = entry_major ? 1 : (size_t)k, ts = entry_major ? nq : 1;
   const unsigned G = div_up(nq * 4, 128);   // four lanes per query
   const int NQ = (int)nq, M = (int)g.m;
@@ -791,8 +803,7 @@ void launch_knn(const KnnGrid& g, const float* q, const lsb_point* kp, const Iso
   static const long quad_max = [] { const char* e = std::getenv("LSB_KNN_QUAD_MAX"); return e ? std::atol(e) : 148L * 64; }();   // tuning hook
   const bool quad = (long)nq <= quad_max;
   const unsigned G1 = div_up(nq, 128);
-  static const bool reuse_on = [] { const char* e = std::getenv("LSB_KNN_REUSE"); return !e || e[0] != '0'; }();   // tuning / A-B hook
-  const bool reuse = da && da->reuse && reuse_on && nf != nullptr;
+  const bool reuse = da && da->reuse && knn_reuse_enabled() && nf != nullptr;
 #define LSB_KNN_CASE(KM)                                                                                                                   \
   do {                                                                                                                                     \
     if (reuse)                                                                                                                             \
@@ -839,6 +850,12 @@ __global__ void k_fill_empty(int32_t* idx, float* d2, int32_t* nf, size_t total,
 }
 
 }  // namespace
+
+bool knn_reuse_enabled()
+{
+  static const bool on = [] { const char* e = std::getenv("LSB_KNN_REUSE"); return !e || e[0] != '0'; }();   // tuning / A-B hook
+  return on;
+}
 
 void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc)
 {

@@ -22,9 +22,12 @@ struct KnnGridParams {
 struct KnnDeviceArgs {
   const Iso3d* prior = nullptr;   // pose in device memory that moves the keypoints (overrides the host `prior`)
   const int* done = nullptr;      // when *done != 0 the search kernels return at once (outputs untouched)
+  const Interpolator* refine = nullptr;   // with reuse: undistortion refinement (device memory) applied IN PLACE to the keypoints first
   bool reuse = false;             // idx_out / d2_out / nfound_out still hold the lists of the same queries against the same
                                   // target at a slightly different pose: they bound the search
 };
+
+bool knn_reuse_enabled();   // LSB_KNN_REUSE != 0 (A/B hook)
 
 struct KnnGrid {
   const lsb_point* cloud = nullptr;   // device, not owned; indices refer to this order

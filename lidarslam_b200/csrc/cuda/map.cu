@@ -42,6 +42,7 @@ __device__ __forceinline__ unsigned long long make_key(int idxOut, int idxIn)
 }
 
 __device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return (i >= 0) ? i : (i ^ 0x7fffffff); }
+__device__ __forceinline__ float ord2f_dev(int i) { return __int_as_float((i >= 0) ? i : (i ^ 0x7fffffff)); }
 
 __global__ void k_bbox_init(int* bb) { if (threadIdx.x < 3) bb[threadIdx.x] = INT_MAX; else if (threadIdx.x < 6) bb[threadIdx.x] = INT_MIN; }
 __global__ void k_bbox(const lsb_point* __restrict__ pts, int n, int* __restrict__ bb)
@@ -288,11 +289,19 @@ __global__ void k_compact(const uint32_t* __restrict__ flags, const uint32_t* __
 
 // submap / Get flags.  mode 0: inside bbox; 1: inside && (count >= minFrames || label == 1);
 // 2: inside && (count < minFrames && label != 1); 3: all; 4: count > minFrames
+// bb != nullptr: the voxel bounds come from a bounding box in device memory (ordered-int encoding of k_bbox /
+// k_transformed_bbox), converted exactly as the host does in SubMapSelect, so the host need not read the box back first
 __global__ void k_flag_entries(const unsigned long long* __restrict__ keys, const lsb_point* __restrict__ pts, const uint32_t* __restrict__ counts,
-                               int n, int G, int lx, int ly, int lz, int hx, int hy, int hz, int mode, unsigned minFrames, uint32_t* __restrict__ flags)
+                               int n, int G, int lx, int ly, int lz, int hx, int hy, int hz, int mode, unsigned minFrames, uint32_t* __restrict__ flags,
+                               const int* __restrict__ bb = nullptr, GridGeom g = GridGeom())
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  if (bb) {
+    lx = max(pos2vox(ord2f_dev(bb[0]), g.ox, g.res), 0); hx = min(pos2vox(ord2f_dev(bb[3]), g.ox, g.res), G - 1);
+    ly = max(pos2vox(ord2f_dev(bb[1]), g.oy, g.res), 0); hy = min(pos2vox(ord2f_dev(bb[4]), g.oy, g.res), G - 1);
+    lz = max(pos2vox(ord2f_dev(bb[2]), g.oz, g.res), 0); hz = min(pos2vox(ord2f_dev(bb[5]), g.oz, g.res), G - 1);
+  }
   bool f = true;
   if (mode <= 2) {
     int x, y, z;
@@ -551,11 +560,11 @@ void RollingGridGpu::BuildSubMapKdTree(cudaStream_t s, LaunchCounter& lc)
 // BuildSubMapKdTree(mn, mx, minNbPoints) (:362-442) in two host phases (SubMapSelect enqueues the
 // first selection pass and its count read-back, SubMapFinish consumes it and builds the kNN grid)
 // so that the three maps overlap their read-backs on their own streams.
-void RollingGridGpu::submap_pass(int mode, size_t offset, cudaStream_t s, LaunchCounter& lc)
+void RollingGridGpu::submap_pass(int mode, size_t offset, cudaStream_t s, LaunchCounter& lc, const int* d_bb)
 {
   const int n = (int)n_entries;
   k_flag_entries<<<div_up(n_entries, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, sub_lo[0], sub_lo[1], sub_lo[2],
-                                                        sub_hi[0], sub_hi[1], sub_hi[2], mode, MinFramesPerVoxel, flags.p);
+                                                        sub_hi[0], sub_hi[1], sub_hi[2], mode, MinFramesPerVoxel, flags.p, d_bb, make_geom(*this));
   LSB_LAUNCH_CHECK(); lc.add();
   size_t tb = cub_tmp.cap;
   LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, n, s)); lc.add(2);
@@ -575,6 +584,7 @@ void RollingGridGpu::SubMapSelect(const float mn[3], const float mx[3], int minN
   n_submap = 0;
   sub_min_nb = minNbPoints;
   sub_filter = !(minNbPoints < 0 || MinFramesPerVoxel <= 1);
+  sub_from_device = false;
   submap.reserve(std::max<size_t>(n_entries, 1), s);
   if (n_entries) {
     ensure_scratch(n_entries, s);
@@ -582,10 +592,36 @@ void RollingGridGpu::SubMapSelect(const float mn[3], const float mx[3], int minN
   }
 }
 
+// The same with the bounding box still in device memory (d_bbox, its copy to h_bbox already enqueued by the caller): the
+// selection runs without the host knowing the bounds; SubMapFinish reads box and count back with ONE synchronisation.
+void RollingGridGpu::SubMapSelectDevice(int minNbPoints, cudaStream_t s, LaunchCounter& lc)
+{
+  n_submap = 0;
+  sub_min_nb = minNbPoints;
+  sub_filter = !(minNbPoints < 0 || MinFramesPerVoxel <= 1);
+  sub_from_device = true;
+  submap.reserve(std::max<size_t>(n_entries, 1), s);
+  if (n_entries) {
+    ensure_scratch(n_entries, s);
+    submap_pass(sub_filter ? 1 : 0, 0, s, lc, reinterpret_cast<const int*>(d_bbox.p));
+  }
+}
+
 void RollingGridGpu::SubMapFinish(cudaStream_t s, LaunchCounter& lc)
 {
+  if (sub_from_device) {
+    LSB_CUDA(cudaStreamSynchronize(s));      // the box (copy enqueued by the caller) and, if there are entries, the count
+    float mn[3], mx[3];
+    bbox_decode(h_bbox.p, mn, mx);
+    const GridGeom g = make_geom(*this);
+    const float o[3] = {g.ox, g.oy, g.oz};
+    for (int a = 0; a < 3; ++a) {
+      sub_lo[a] = std::max(pos2vox(mn[a], o[a], g.res), 0);
+      sub_hi[a] = std::min(pos2vox(mx[a], o[a], g.res), GridSize - 1);
+    }
+  }
   if (n_entries) {
-    LSB_CUDA(cudaStreamSynchronize(s));
+    if (!sub_from_device) LSB_CUDA(cudaStreamSynchronize(s));
     n_submap = h_info.p[2];
     if (sub_filter && (int)n_submap < sub_min_nb) {
       submap_pass(2, n_submap, s, lc);

@@ -62,6 +62,7 @@ struct RollingGridGpu {
   void BuildSubMapKdTree(cudaStream_t s, LaunchCounter& lc);                             // :353-359
   void BuildSubMapKdTree(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc);   // :362-442
   void SubMapSelect(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc);
+  void SubMapSelectDevice(int minNbPoints, cudaStream_t s, LaunchCounter& lc);   // bounds from d_bbox (device), no read-back first
   void SubMapFinish(cudaStream_t s, LaunchCounter& lc);
   bool IsSubMapKdTreeValid() const { return tree_valid && n_submap > 0; }               // RollingGrid.h:132-135
   bool IsTimeThreshold() const { return DecayingThreshold > 0; }
@@ -72,7 +73,8 @@ struct RollingGridGpu {
   void build_grid(const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc);
   size_t compact_entries(cudaStream_t s, LaunchCounter& lc);   // keeps entries with flags[i] != 0
   void ensure_scratch(size_t n, cudaStream_t s);
-  void submap_pass(int mode, size_t offset, cudaStream_t s, LaunchCounter& lc);
+  void submap_pass(int mode, size_t offset, cudaStream_t s, LaunchCounter& lc, const int* d_bb = nullptr);
+  bool sub_from_device = false;
   int sub_lo[3] = {0, 0, 0}, sub_hi[3] = {-1, -1, -1}, sub_min_nb = -1;
   bool sub_filter = false;
 };

@@ -679,7 +679,7 @@ void MatchWorkspace::begin_frame(const size_t nk[3], int n_iters, cudaStream_t s
 }
 
 void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, const KnnGrid& target, const Iso3d& prior,
-                                const lsb_match_params& mp, cudaStream_t s, LaunchCounter& lc, int icp_iter, const IcpState* icp, bool reuse)
+                                const lsb_match_params& mp, cudaStream_t s, LaunchCounter& lc, int icp_iter, const IcpState* icp, bool reuse, bool refine)
 {
   if (nk == 0) return;
   double* rec = records.p + off[type];
@@ -715,6 +715,7 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
   da.prior = icp ? (icp_stage == ICP_STAGE_LOC ? &icp->Tworld : &icp->Trelative) : nullptr;
   da.done = done;
   da.reuse = reuse;
+  da.refine = (reuse && icp && refine) ? &icp->Pending : nullptr;
   target.search_points(d_kp, nk, prior, k, cap, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, /*entry_major=*/true, s, lc, &da);
   t_knn.end(s);
   const int NQ = (int)nk;

@@ -43,12 +43,15 @@ struct MatchWorkspace {
   // buffers and zeroed match histograms for up to n_iters ICP iterations on nk keypoints per type
   void begin_frame(const size_t nk[3], int n_iters, cudaStream_t s);
   void begin_iteration(const size_t nk[3], cudaStream_t s) { begin_frame(nk, 1, s); }
+  // the reuse search kernel visits every keypoint exactly once only when it runs at all (non-empty target, reuse enabled)
+  static bool can_fuse_refinement(const KnnGrid& target, size_t nk) { return nk > 0 && !target.empty() && knn_reuse_enabled(); }
   // KeypointsMatcher::BuildMatchResiduals for one keypoint type (kNN + model fit) in ICP iteration icp_iter.
   // icp != nullptr: device-resident loop - the queries are moved by the pose held in *icp (`prior` is ignored) and the
   // kernels return at once when icp->done is set.  reuse: the neighbour lists of the previous iteration (same keypoints,
-  // same target) are still in the workspace and bound the search.
+  // same target) are still in the workspace and bound the search.  refine (with reuse): the undistortion refinement the previous
+  // iteration left in icp->Pending is applied to the keypoints inside the search kernel (else the caller applies it first).
   void match_type(int type, const lsb_point* d_kp, size_t nk, const KnnGrid& target, const Iso3d& prior, const lsb_match_params& mp,
-                  cudaStream_t s, LaunchCounter& lc, int icp_iter = 0, const IcpState* icp = nullptr, bool reuse = false);
+                  cudaStream_t s, LaunchCounter& lc, int icp_iter = 0, const IcpState* icp = nullptr, bool reuse = false, bool refine = false);
   // reads the status histograms back (one stream sync); hist_out[3][LSB_MATCH_N_STATUS]
   void read_histograms(int hist_out[3][LSB_MATCH_N_STATUS], cudaStream_t s);
   // LocalOptimizer::Solve on the current records; returns the final state and the match histograms

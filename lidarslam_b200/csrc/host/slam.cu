@@ -472,13 +472,14 @@ void lsb_slam::Localization()
     if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) return;
     if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(ts, lc); return; }
     if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, ts, lc);
-    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     if (CurrentKeypoints[k].n) {
+      // the box stays on the device for the selection; box and sub-map size come back with one synchronisation
       dev_transformed_bbox_async(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, map.d_bbox, map.h_bbox, ts, lc);
-      LSB_CUDA(cudaStreamSynchronize(ts));
-      bbox_decode(map.h_bbox.p, mn, mx);
+      map.SubMapSelectDevice((int)(CurrentKeypoints[k].n / 2), ts, lc);
+    } else {
+      const float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+      map.SubMapSelect(mn, mx, 0, ts, lc);
     }
-    map.SubMapSelect(mn, mx, (int)(CurrentKeypoints[k].n / 2), ts, lc);
     map.SubMapFinish(ts, lc);
   });
   HasPendingRefinement = false;
@@ -533,8 +534,8 @@ const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_mat
   d_icp.reserve(1, stream);
   dev_icp_init(d_icp.p, init, stream, lc);
   mw.icp_stage = stage;
-  // several sequences sharing the GPU: each solve takes its share of the SMs (at most a quarter is given up)
-  static const int share_max = [] { const char* e = std::getenv("LSB_LM_GRID_SHARE_MAX"); return e ? std::max(1, std::atoi(e)) : 4; }();   // tuning hook
+  // several sequences sharing the GPU: each solve takes its share of the SMs (never less than a sixth)
+  static const int share_max = [] { const char* e = std::getenv("LSB_LM_GRID_SHARE_MAX"); return e ? std::max(1, std::atoi(e)) : 6; }();   // tuning hook (6: best of 1 / 2 / 4 / 6 / 8 for 8 OS-128 sequences on one B200)
   mw.lm_grid_share = std::min(std::max(g_handles_in_flight.load(std::memory_order_relaxed), 1), share_max);
   mw.begin_frame(nk, (int)max_iter, stream);
   mw.next_solve_seq();
@@ -547,9 +548,12 @@ const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_mat
     for (int k : kTypeOrder) {
       if (k >= ntypes) continue;
       // the undistortion refinement of the previous iteration (:1146-1147): three independent clouds, one per type stream
-      if (refined && icpIter > 0) dev_undistort_state(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_icp.p, 0, TypeStream(k), lc);
-      mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], loc ? LocalMaps[k].grid : EgoGrids[k], Iso3d::identity(), mp, TypeStream(k), lc,
-                    (int)icpIter, d_icp.p, /*reuse=*/icpIter > 0);
+      // (fused into the search kernel when that one runs per keypoint: reuse pass on a non-empty target)
+      const KnnGrid& target = loc ? LocalMaps[k].grid : EgoGrids[k];
+      const bool fuse = refined && icpIter > 0 && mw.can_fuse_refinement(target, nk[k]);
+      if (refined && icpIter > 0 && !fuse) dev_undistort_state(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_icp.p, 0, TypeStream(k), lc);
+      mw.match_type(k, CurrentKeypoints[k].buf.p, nk[k], target, Iso3d::identity(), mp, TypeStream(k), lc, (int)icpIter, d_icp.p,
+                    /*reuse=*/icpIter > 0, /*refine=*/fuse);
     }
     Join();
     IcpCtl ctl;
