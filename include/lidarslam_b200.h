@@ -3,7 +3,7 @@
  * Drop-in boundary: a reference maintainer keeps LidarSlam::Slam's public C++
  * API (reference slam_lib/include/LidarSlam/Slam.h:98-394) and forwards its
  * bodies to these entry points (see INTEGRATION.md and
- * lidarslam_b200/csrc/shim/LidarSlam/Slam.h).  Every entry point cites the
+ * include/LidarSlam/Slam.h, the header-only C++ mirror of that class).  Every entry point cites the
  * reference interface it replaces.  Plain pointers and sizes only; all buffers
  * passed in and out are HOST memory unless the name says `_dev`.
  *
@@ -101,7 +101,7 @@ typedef struct lsb_params {
   int32_t use_keypoints[3];            /* {1,1,0} */
   int32_t ego_motion;                  /* LSB_EGO_MOTION_EXTRAPOLATION */
   int32_t undistortion;                /* LSB_UNDISTORTION_REFINED */
-  int32_t verbosity;
+  int32_t verbosity;                   /* accepted and IGNORED (the reference prints phase timers, Slam.cxx:246-295): phase times are in lsb_frame_stats */
   double logging_timeout;              /* 0 */
   int32_t two_d_mode;                  /* 0 */
   uint32_t ego_motion_icp_max_iter;    /* 4 */
