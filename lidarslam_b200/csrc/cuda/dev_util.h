@@ -109,10 +109,11 @@ struct KernelTimer {
     LSB_CUDA(cudaEventRecord(ev[used + 1], s));
     used += 2;
   }
-  // call after the stream is synchronised; returns ms and resets
-  float collect(unsigned* n_launches)
+  // call after the stream is synchronised; returns ms and resets (each: the individual durations in us, in launch order)
+  float collect(unsigned* n_launches, std::vector<float>* each = nullptr)
   {
     float total = 0.f;
+    if (each) for (size_t i = 0; i + 1 < used; i += 2) { float ms = 0.f; cudaEventElapsedTime(&ms, ev[i], ev[i + 1]); each->push_back(ms * 1e3f); }
     for (size_t i = 0; i + 1 < used; i += 2) { float ms = 0.f; cudaEventElapsedTime(&ms, ev[i], ev[i + 1]); total += ms; }
     used = 0;
     if (n_launches) *n_launches = launches;

@@ -9,6 +9,7 @@
 #include <climits>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 
 namespace lsb {
@@ -79,6 +80,50 @@ __global__ void k_point_keys(const lsb_point* __restrict__ pts, int n, GridGeom 
   }
   key[i] = k;
   idx[i] = (uint32_t)i;
+}
+
+// Compact 32-bit form of the leaf key for the sort of one incoming cloud: the outer voxel index RELATIVE to the voxel box of
+// the cloud (same z-major / y / x-minor nesting as to1d, so the order is that of the canonical key) above the inner leaf index
+// biased to be non-negative.  Fits 31 bits for the usual geometries (OS-128: 14 + 17), which takes the radix sort from seven
+// 8-bit passes over 64-bit keys to four over 32-bit ones; the canonical 64-bit keys are rebuilt after the sort.
+struct CompactKey {
+  int x0, y0, z0, dx, dy, dz;   // voxel box of the cloud
+  int bits_in;                  // bits of the biased inner index
+  int bias;                     // added to the (signed) inner 1-D index
+};
+constexpr uint32_t INVALID_KEY32 = 0xffffffffu;
+
+__global__ void k_point_keys32(const lsb_point* __restrict__ pts, int n, GridGeom g, CompactKey ck, uint32_t* __restrict__ key, uint32_t* __restrict__ idx,
+                               uint32_t* __restrict__ info)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)i];
+  const int vx = pos2vox(p.x, g.ox, g.res), vy = pos2vox(p.y, g.oy, g.res), vz = pos2vox(p.z, g.oz, g.res);
+  uint32_t k = INVALID_KEY32;
+  if (vx >= 0 && vx < g.G && vy >= 0 && vy < g.G && vz >= 0 && vz < g.G) {
+    const float cx = (float)vx * g.res + g.ox, cy = (float)vy * g.res + g.oy, cz = (float)vz * g.res + g.oz;
+    const int ix = pos2vox(p.x, cx, g.leaf), iy = pos2vox(p.y, cy, g.leaf), iz = pos2vox(p.z, cz, g.leaf);
+    const int rx = vx - ck.x0, ry = vy - ck.y0, rz = vz - ck.z0;
+    const long long in = (long long)to1d(ix, iy, iz, g.G) + ck.bias;
+    if (rx < 0 || rx >= ck.dx || ry < 0 || ry >= ck.dy || rz < 0 || rz >= ck.dz || in < 0 || in >= (1ll << ck.bits_in)) atomicOr(info + 7, 1u);   // the host's bounds were wrong: reported, never silent
+    else k = ((uint32_t)((rz * ck.dy + ry) * ck.dx + rx) << ck.bits_in) | (uint32_t)in;
+  }
+  key[i] = k;
+  idx[i] = (uint32_t)i;
+}
+
+__global__ void k_expand_keys(const uint32_t* __restrict__ key32, int n, int G, CompactKey ck, unsigned long long* __restrict__ key64)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t c = key32[i];
+  if (c == INVALID_KEY32) { key64[i] = INVALID_KEY; return; }
+  const int in = (int)(c & ((1u << ck.bits_in) - 1u)) - ck.bias;
+  int rel = (int)(c >> ck.bits_in);
+  const int rx = rel % ck.dx; rel /= ck.dx;
+  const int ry = rel % ck.dy, rz = rel / ck.dy;
+  key64[i] = make_key(to1d(rx + ck.x0, ry + ck.y0, rz + ck.z0, G), in);
 }
 
 __device__ __forceinline__ int lower_bound_key(const unsigned long long* __restrict__ keys, int n, unsigned long long k)
@@ -450,27 +495,58 @@ void RollingGridGpu::AddBegin(const lsb_point* d_cloud, size_t n, bool roll, cud
 void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, double currentTime, bool roll, cudaStream_t s, LaunchCounter& lc)
 {
   if (n == 0) return;
+  float mn[3], mx[3];
   if (roll) {
-    float mn[3], mx[3];
     LSB_CUDA(cudaStreamSynchronize(s));
     bbox_decode(h_bbox.p, mn, mx);
     Roll(mn, mx, s, lc);
   }
   const GridGeom g = make_geom(*this);
   const int N = (int)n;
+  // compact 32-bit sort keys when the cloud's voxel box and the inner index range fit (see CompactKey)
+  CompactKey ck{};
+  bool compact = false;
+  static const bool compact_on = [] { const char* e = std::getenv("LSB_MAP_COMPACT_KEYS"); return !e || e[0] != '0'; }();   // A/B hook
+  if (roll && compact_on && LeafSize > 0. && VoxelResolution > 0.) {
+    const float o[3] = {g.ox, g.oy, g.oz};
+    int lo[3], hi[3];
+    bool any = true;
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = std::max(pos2vox(mn[a], o[a], g.res), 0);
+      hi[a] = std::min(pos2vox(mx[a], o[a], g.res), g.G - 1);
+      any = any && lo[a] <= hi[a];
+    }
+    if (any) {
+      ck.x0 = lo[0]; ck.y0 = lo[1]; ck.z0 = lo[2];
+      ck.dx = hi[0] - lo[0] + 1; ck.dy = hi[1] - lo[1] + 1; ck.dz = hi[2] - lo[2] + 1;
+      const long long imax = (long long)std::ceil(VoxelResolution / (2. * LeafSize)) + 2;       // |inner coordinate| along one axis
+      const long long B = imax * ((long long)g.G * g.G + g.G + 1);
+      int bits_in = 1, bits_out = 0;
+      while ((1ll << bits_in) <= 2 * B) ++bits_in;
+      while ((1ll << bits_out) < (long long)ck.dx * ck.dy * ck.dz) ++bits_out;
+      if (bits_in + bits_out <= 31 && B < (1ll << 30)) { ck.bits_in = bits_in; ck.bias = (int)B; compact = true; }
+    }
+  }
   nk_a.reserve(n, s); nk_b.reserve(n, s); ni_a.reserve(n, s); ni_b.reserve(n, s);
   ins_keys.reserve(n, s); ins_pts.reserve(n, s); ins_counts.reserve(n, s);
   pts_b.reserve(n, s); counts_b.reserve(n, s);      // per-segment scratch (seg_pts / seg_counts)
   ensure_scratch(std::max(n, n_entries), s);
   const unsigned G = div_up(n, TPB);
-  k_point_keys<<<G, TPB, 0, s>>>(d_cloud, N, g, nk_a.p, ni_a.p); LSB_LAUNCH_CHECK(); lc.add();
-  size_t tb = cub_tmp.cap;
-  // significant bits only: the outer index is < G^3 and INVALID_KEY (all ones) still sorts last as long as 2^bits > G^3
-  int outer_bits = 1;
-  while ((1ll << outer_bits) <= (long long)g.G * g.G * g.G) ++outer_bits;
-  const int end_bit = std::min(64, 32 + outer_bits);
-  LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, nk_a.p, nk_b.p, ni_a.p, ni_b.p, N, 0, end_bit, s)); lc.add(2 + (end_bit + 7) / 8);
   LSB_CUDA(cudaMemsetAsync(d_info.p, 0, 8 * sizeof(uint32_t), s));
+  size_t tb = cub_tmp.cap;
+  if (compact) {
+    // flags / scan are free until the segment replay: they hold the 32-bit keys before and after the sort
+    k_point_keys32<<<G, TPB, 0, s>>>(d_cloud, N, g, ck, flags.p, ni_a.p, d_info.p); LSB_LAUNCH_CHECK(); lc.add();
+    LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, flags.p, scan.p, ni_a.p, ni_b.p, N, 0, 32, s)); lc.add(2 + 4);
+    k_expand_keys<<<G, TPB, 0, s>>>(scan.p, N, g.G, ck, nk_b.p); LSB_LAUNCH_CHECK(); lc.add();
+  } else {
+    k_point_keys<<<G, TPB, 0, s>>>(d_cloud, N, g, nk_a.p, ni_a.p); LSB_LAUNCH_CHECK(); lc.add();
+    // significant bits only: the outer index is < G^3 and INVALID_KEY (all ones) still sorts last as long as 2^bits > G^3
+    int outer_bits = 1;
+    while ((1ll << outer_bits) <= (long long)g.G * g.G * g.G) ++outer_bits;
+    const int end_bit = std::min(64, 32 + outer_bits);
+    LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, nk_a.p, nk_b.p, ni_a.p, ni_b.p, N, 0, end_bit, s)); lc.add(2 + (end_bit + 7) / 8);
+  }
   if (Sampling == LSB_SAMPLING_CENTROID) {
     c_eff.reserve(n, s); c_tpos.reserve(n, s);
     LSB_CUDA(cudaMemsetAsync(c_eff.p, 0, n * sizeof(uint32_t), s));
@@ -485,13 +561,14 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, N, s)); lc.add(2);
   k_gather_inserts<<<G, TPB, 0, s>>>(flags.p, scan.p, N, nk_b.p, pts_b.p, counts_b.p, ins_keys.p, ins_pts.p, ins_counts.p, d_info.p);
   LSB_LAUNCH_CHECK(); lc.add();
-  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
 }
 
 void RollingGridGpu::AddMerge(size_t n, cudaStream_t s, LaunchCounter& lc)
 {
   if (n == 0) return;
   LSB_CUDA(cudaStreamSynchronize(s));
+  if (h_info.p[7]) throw CudaError(LSB_E_CUDA, "RollingGrid::Add: a leaf key fell outside the compact key range (internal bound error)");
   const bool updated = h_info.p[0] != 0;
   const size_t n_ins = h_info.p[1];
   if (n_ins) {

@@ -24,6 +24,8 @@ __device__ __forceinline__ void store_xyz(lsb_point* p, float x, float y, float 
   reinterpret_cast<float4*>(p)[0] = v;
 }
 
+__device__ __forceinline__ int f2ord_k(float f) { const int i = __float_as_int(f); return (i >= 0) ? i : (i ^ 0x7fffffff); }
+
 __global__ void k_transform(lsb_point* __restrict__ pts, int n, Iso3d T)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -32,6 +34,30 @@ __global__ void k_transform(lsb_point* __restrict__ pts, int n, Iso3d T)
   load_xyz(pts + i, x, y, z);
   transform_point_f(T, x, y, z);
   store_xyz(pts + i, x, y, z);
+}
+
+// k_transform with the bounding box of the transformed cloud (pcl::getMinMax3D of RollingGrid::Add, RollingGrid.cxx:171-172)
+// reduced on the way: the box is that of the floats just stored, i.e. what a separate pass over the cloud would find
+__global__ void k_transform_bbox(lsb_point* __restrict__ pts, int n, Iso3d T, int* __restrict__ bb)
+{
+  int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    float x, y, z;
+    load_xyz(pts + i, x, y, z);
+    transform_point_f(T, x, y, z);
+    store_xyz(pts + i, x, y, z);
+    const int v[3] = {f2ord_k(x), f2ord_k(y), f2ord_k(z)};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = min(mn[a], v[a]); mx[a] = max(mx[a], v[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    for (int off = 16; off; off >>= 1) {
+      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], off));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], off));
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(bb + a, mn[a]); atomicMax(bb + 3 + a, mx[a]); }
+  }
 }
 
 __global__ void k_aggregate(lsb_point* __restrict__ pts, int n, double timeOffset, Iso3d T, int applyT)
@@ -146,6 +172,15 @@ void dev_transform(lsb_point* d_pts, size_t n, const Iso3d& T, cudaStream_t s, L
 {
   if (!n) return;
   k_transform<<<div_up(n, TPB), TPB, 0, s>>>(d_pts, (int)n, T); LSB_LAUNCH_CHECK(); lc.add();
+}
+
+void dev_transform_bbox_async(lsb_point* d_pts, size_t n, const Iso3d& T, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, cudaStream_t s,
+                              LaunchCounter& lc)
+{
+  d_bbox.reserve(8, s); h_bbox.reserve(8);
+  k_bbox_init<<<1, 32, 0, s>>>((int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
+  if (n) { k_transform_bbox<<<std::min(div_up(n, TPB), 1184u), TPB, 0, s>>>(d_pts, (int)n, T, (int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add(); }
+  LSB_CUDA(cudaMemcpyAsync(h_bbox.p, d_bbox.p, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
 }
 
 void dev_aggregate(lsb_point* d_pts, size_t n, double timeOffset, const Iso3d& T, bool applyT, cudaStream_t s, LaunchCounter& lc)

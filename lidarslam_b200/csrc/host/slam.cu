@@ -55,7 +55,12 @@ lsb_slam::lsb_slam(int dev) : device(dev)
     }
   }
   for (auto& e : ev) LSB_CUDA(cudaEventCreate(&e));
-  for (auto& t : tstream) LSB_CUDA(cudaStreamCreateWithFlags(&t, cudaStreamNonBlocking));
+  {
+    // LSB_TYPE_PRIORITIES="e,p,b": CUDA stream priority of the three type streams (0 = default, negative = higher); tuning hook
+    int prio[3] = {0, 0, 0};
+    if (const char* e = std::getenv("LSB_TYPE_PRIORITIES")) std::sscanf(e, "%d,%d,%d", &prio[0], &prio[1], &prio[2]);
+    for (int k = 0; k < 3; ++k) LSB_CUDA(cudaStreamCreateWithPriority(&tstream[k], cudaStreamNonBlocking, prio[k]));
+  }
   LSB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   for (auto& e : ev_join) LSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   lsb_default_params(&P);
@@ -297,9 +302,23 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   cudaEventElapsedTime(&Stats.ms_map_update, ev[3], ev[4]);
   cudaEventElapsedTime(&Stats.ms_total, ev[0], ev[4]);
   Stats.kernel_launches = lc.n - launches0;
-  Stats.ms_knn = mw.t_knn.collect(&Stats.knn_launches);
-  Stats.ms_fit = mw.t_fit.collect(nullptr);
-  Stats.ms_lm = mw.t_lm.collect(&Stats.lm_launches);
+  if (trace.on && mw.t_knn.enabled) {      // LSB_TRACE=1 with lsb_set_profiling(1): the individual brackets, in enqueue order
+    std::vector<float> a, b, c;
+    Stats.ms_knn = mw.t_knn.collect(&Stats.knn_launches, &a);
+    Stats.ms_fit = mw.t_fit.collect(nullptr, &b);
+    Stats.ms_lm = mw.t_lm.collect(&Stats.lm_launches, &c);
+    std::fprintf(stderr, "[lsb trace] knn us:");
+    for (float v : a) std::fprintf(stderr, " %.0f", v);
+    std::fprintf(stderr, " | fit us:");
+    for (float v : b) std::fprintf(stderr, " %.0f", v);
+    std::fprintf(stderr, " | lm us:");
+    for (float v : c) std::fprintf(stderr, " %.0f", v);
+    std::fprintf(stderr, "  (per ICP iteration: types in the order blob, plane, edge)\n");
+  } else {
+    Stats.ms_knn = mw.t_knn.collect(&Stats.knn_launches);
+    Stats.ms_fit = mw.t_fit.collect(nullptr);
+    Stats.ms_lm = mw.t_lm.collect(&Stats.lm_launches);
+  }
   // device->host: match histograms + LM states (counted by the workspace) and the small per-stage
   // counters (keypoint counts, time range, bboxes, map counters: < 64 B each, bounded here)
   Stats.d2h_bytes = mw.d2h_bytes + 64 * 16;
@@ -594,23 +613,28 @@ void lsb_slam::UpdateMapsUsingTworld()
   ForEachType([&](int k) {
     if (!P.use_keypoints[k]) return;
     cudaStream_t ts = TypeStream(k);
-    const DCloud& w = WorldKeypoints(k, ts);
-    LocalMaps[k].Add(w.buf.p, w.n, false, CurrentTime, true, ts, lc);
+    bool boxed = false;
+    const DCloud& w = WorldKeypoints(k, ts, &LocalMaps[k], &boxed);      // the box RollingGrid::Add rolls by comes with the transform
+    if (!boxed) LocalMaps[k].AddBegin(w.buf.p, w.n, true, ts, lc);
+    LocalMaps[k].AddSort(w.buf.p, w.n, false, CurrentTime, true, ts, lc);
+    LocalMaps[k].AddMerge(w.n, ts, lc);
   });
 }
 
 // GetKeypoints(k, true) -> TransformPointCloud (:690-702, :1491-1509), cached per frame
-const DCloud& lsb_slam::WorldKeypoints(int k, cudaStream_t s)
+const DCloud& lsb_slam::WorldKeypoints(int k, cudaStream_t s, RollingGridGpu* box, bool* boxed)
 {
   cudaStream_t stream = s ? s : this->stream;
   DCloud& w = CurrentWorldKeypoints[k];
+  if (boxed) *boxed = false;
   if (!WorldKeypointsValid[k]) {
     const DCloud& c = CurrentKeypoints[k];
     w.buf.reserve(std::max<size_t>(c.n, 1), stream);
     w.n = c.n;
     if (c.n) {
       LSB_CUDA(cudaMemcpyAsync(w.buf.p, c.buf.p, c.n * sizeof(lsb_point), cudaMemcpyDeviceToDevice, stream));
-      dev_transform(w.buf.p, w.n, Tworld, stream, lc);
+      if (box) { dev_transform_bbox_async(w.buf.p, w.n, Tworld, box->d_bbox, box->h_bbox, stream, lc); if (boxed) *boxed = true; }
+      else dev_transform(w.buf.p, w.n, Tworld, stream, lc);
     }
     WorldKeypointsValid[k] = true;
   }

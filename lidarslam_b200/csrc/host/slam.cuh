@@ -118,7 +118,9 @@ struct lsb_slam {
   lsb::Iso3d GetBaseToLidarOffset(int dev) const;
   lsb::ExtractorGpu& Extractor(int dev);
   // device clouds produced on demand
-  const DCloud& WorldKeypoints(int k, cudaStream_t s = nullptr);
+  // box != nullptr: the bounding box of the cloud is reduced into box->d_bbox / h_bbox while it is transformed (*boxed = true);
+  // a cloud that was already cached comes back without a box (*boxed = false)
+  const DCloud& WorldKeypoints(int k, cudaStream_t s = nullptr, lsb::RollingGridGpu* box = nullptr, bool* boxed = nullptr);
   size_t RegisteredFrame(lsb::DevBuf<lsb_point>& out);
 
  private:
@@ -146,6 +148,9 @@ struct lsb_slam {
 namespace lsb {
 // device helpers implemented in slam_kernels.cu
 void dev_transform(lsb_point* d_pts, size_t n, const Iso3d& T, cudaStream_t s, LaunchCounter& lc);                     // Utils::TransformPoint
+// dev_transform + the bounding box of the result (ordered-int encoding in d_bbox, copy to h_bbox enqueued): no second pass
+void dev_transform_bbox_async(lsb_point* d_pts, size_t n, const Iso3d& T, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, cudaStream_t s,
+                              LaunchCounter& lc);
 void dev_aggregate(lsb_point* d_pts, size_t n, double timeOffset, const Iso3d& T, bool applyT, cudaStream_t s, LaunchCounter& lc);
 void dev_undistort(lsb_point* d_pts, size_t n, const Interpolator& it, double timeOffset, cudaStream_t s, LaunchCounter& lc);   // Slam.cxx:1345-1350
 // the same with the interpolator the device-resident ICP loop holds (cuda/icp.cuh); mode 0: head of an iteration, 1: after the loop
