@@ -355,13 +355,22 @@ __device__ __noinline__ void lm_point_warp(const double* x, unsigned long long* 
   if (lane == 0) lm_make_point_from_trig(xl, trig, *reinterpret_cast<LmPoint*>(s_pt_raw));
 }
 
+// tools/probes/lm_eval_probe.cu defines LSB_LM_PROBE to time the phases of one evaluation (CTA 0)
+#ifdef LSB_LM_PROBE
+__device__ unsigned long long g_lm_probe[64 * 8];
+#define LM_PROBE_STAMP(e, k) do { if (blockIdx.x == 0 && threadIdx.x == 0 && (e) < 64) { unsigned long long t_; \
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_lm_probe[(e) * 8 + (k)] = t_; } } while (0)
+#else
+#define LM_PROBE_STAMP(e, k) do { } while (0)
+#endif
+
 // The trust-region step, run by warp 0 of every CTA on the CTA's own copy of the state (shared
 // memory) and kept out of line so that its registers do not weigh on the evaluating threads.
 // Every CTA holds the same state and the same 28 sums, and every operation below is
 // deterministic, so the copies stay bit-identical without any exchange.  Lane 0 takes the accept /
 // reject decision (scalar), the warp proposes the next step, and the six sin/cos of the next
 // evaluation point are computed by six lanes in parallel.
-__device__ __noinline__ void lm_control(unsigned long long* s_state_raw, unsigned long long* s_pt_raw, const double* sE, int first)
+__device__ __noinline__ void lm_control(unsigned long long* s_state_raw, unsigned long long* s_pt_raw, const double* sE, int first, int e = 0)
 {
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -370,8 +379,10 @@ __device__ __noinline__ void lm_control(unsigned long long* s_state_raw, unsigne
   if (lane == 0) propose = (first ? lm_first_update(s, sE) : lm_next_update(s, sE)) ? 1 : 0;
   __syncwarp();
   propose = __shfl_sync(FULL, propose, 0);
+  LM_PROBE_STAMP(e, 5);
   if (propose) lm_propose_warp(s);
   __syncwarp();
+  LM_PROBE_STAMP(e, 6);
   if (s.done) return;
   lm_point_warp(s.xc, s_pt_raw);
 }
@@ -454,15 +465,6 @@ __device__ __forceinline__ void lm_grid_barrier(unsigned* bar, unsigned target)
 }
 
 struct LmStart { double x[6]; };
-
-// tools/probes/lm_eval_probe.cu defines LSB_LM_PROBE to time the phases of one evaluation (CTA 0)
-#ifdef LSB_LM_PROBE
-__device__ unsigned long long g_lm_probe[64 * 5];
-#define LM_PROBE_STAMP(e, k) do { if (blockIdx.x == 0 && threadIdx.x == 0 && (e) < 64) { unsigned long long t_; \
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_lm_probe[(e) * 5 + (k)] = t_; } } while (0)
-#else
-#define LM_PROBE_STAMP(e, k) do { } while (0)
-#endif
 
 // LocalOptimizer::Solve as ONE persistent kernel: the whole trust-region loop (common/lm_core.h)
 // with a grid barrier per cost/Jacobian evaluation instead of a launch.  CTA b owns the chunks
@@ -616,7 +618,7 @@ k_lm_solve(const double* __restrict__ records, size_t rec_stride, int n, int nch
       // wheel-odometer / IMU gravity blocks (Slam.cxx:1123-1131): added to the reduced sums at the evaluation point
       if ((terms.use_wheel | terms.use_gravity) && lane == 0) lm_add_sensor_terms(terms, s_pt, s_E);
       __syncwarp();
-      lm_control(s_state_raw, s_pt_raw, s_E, e == 0);
+      lm_control(s_state_raw, s_pt_raw, s_E, e == 0, e);
     }
     __syncthreads();
     LM_PROBE_STAMP(e, 4);

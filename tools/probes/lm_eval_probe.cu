@@ -86,10 +86,12 @@ int main(int argc, char** argv)
   }
   // phases of each evaluation on CTA 0 (globaltimer, ns)
   solve(3); cudaDeviceSynchronize();
-  unsigned long long st[64 * 5];
+  unsigned long long st[64 * 8];
   cudaMemcpyFromSymbol(st, g_lm_probe, sizeof(st));
   for (int e = 0; e < 4; ++e)
-    printf("eval %d: evaluate+chunk fold %5.2f us | barrier %5.2f | final fold %5.2f | control %5.2f\n", e, (st[e * 5 + 1] - st[e * 5]) * 1e-3,
-           (st[e * 5 + 2] - st[e * 5 + 1]) * 1e-3, (st[e * 5 + 3] - st[e * 5 + 2]) * 1e-3, (st[e * 5 + 4] - st[e * 5 + 3]) * 1e-3);
+    printf("eval %d: evaluate+chunk fold %5.2f us | barrier %5.2f | final fold %5.2f | control %5.2f (update %4.2f, propose %4.2f, next point %4.2f)\n", e,
+           (st[e * 8 + 1] - st[e * 8]) * 1e-3, (st[e * 8 + 2] - st[e * 8 + 1]) * 1e-3, (st[e * 8 + 3] - st[e * 8 + 2]) * 1e-3,
+           (st[e * 8 + 4] - st[e * 8 + 3]) * 1e-3, (st[e * 8 + 5] - st[e * 8 + 3]) * 1e-3, (st[e * 8 + 6] - st[e * 8 + 5]) * 1e-3,
+           (st[e * 8 + 4] - st[e * 8 + 6]) * 1e-3);
   return 0;
 }
