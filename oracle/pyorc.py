@@ -1,4 +1,4 @@
-"""CPU ORACLE (test infrastructure) — ctypes front-end of oracle/_ref/liborc.so.
+"""CPU ORACLE (test infrastructure) — ctypes front-end of oracle/_build/liborc.so (the restatement; no compiled reference exists).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
 legs may import this module.  It reuses the product's generic ctypes wrapper
@@ -23,7 +23,7 @@ def build():
 def load():
     global _LIB
     if _LIB is None:
-        p = os.path.join(_HERE, "_ref", "liborc.so")
+        p = os.path.join(_HERE, "_build", "liborc.so")
         if not os.path.exists(p):
             build()
         _LIB = C.CDLL(p)
