@@ -8,12 +8,20 @@ A step = one AddFrames call on the next frame of the sequence.  Ranks run indepe
 sequences (replicas only: no collective on the frame path), so the whole-job
 value is ranks x frames / max-over-ranks time ("weak" scaling).
 
-  value  : frames already resident in HBM (lsb_add_frames_dev), CUDA-event time per step.
-  e2e    : the same frames through lsb_add_frames with pinned HOST buffers (H2D inside),
-           wall clock around the call, pose read back on the host every step.
+  value  : frames already resident in HBM, K steps bracketed as ONE region by CUDA events on the
+           handle's stream (lsb_timer_begin / lsb_timer_end, a synchronisation on both sides).  The
+           loop is the pipelined use of the C ABI: step i hands frame i + 1 to lsb_prefetch_frames_dev
+           (its keypoint extraction overlaps frame i's ICP) and calls lsb_add_frames_dev(frame i), whose
+           map update is deferred behind the returned pose; the region holds K extractions, K ICP
+           loops and K map updates.  Inputs larger than L2: K + 1 distinct frames, each read once.
+  e2e    : the same loop through lsb_prefetch_frames / lsb_add_frames with pinned HOST buffers
+           (every frame's H2D copy inside the region), wall clock around the K steps and the final
+           lsb_synchronize, pose read back on the host every step.
+  sync_api : the round-1/2 method for continuity - one fully synchronous call per step (no
+           prefetch, map update inside the call), CUDA events per call (device) / wall clock per
+           call (host buffers), L2 flushed between calls.
   --impl reference : the CPU/OpenMP restatement of the reference (oracle/, all host
            threads) on the same frames, rank 0 only.
-L2 is flushed between timed iterations (the frame + submaps fit the 126 MB L2).
 """
 import argparse
 import json
@@ -62,9 +70,11 @@ def configure(s):
 def config_dict(a, world):
     """the same dictionary on both arms (ours / --impl reference): the driver compares them key by key"""
     return {"workload": WORKLOAD, "sensor": a.sensor, "sequences": world, "parallelism": "replicas x%d" % world,
-            "l2": "flushed between timed iterations" if not a.no_flush else "not flushed",
-            "timing": "ours: CUDA events on the handle's stream around each lsb_add_frames_dev call, kernel durations (roofline, *_kernels) "
-                      "from a separate pass with lsb_set_profiling(1); reference arm: wall clock around each AddFrame of the CPU port"}
+            "l2": "value / e2e: inputs larger than L2 (steps + 1 distinct frames of 8.4 MB, each read once, no flush inside the bracketed region); "
+                  "sync_api and kernel passes: flushed between calls" if not a.no_flush else "not flushed",
+            "timing": "ours: ONE CUDA-event bracket on the handle's stream around the K pipelined steps (lsb_prefetch_frames_dev(i + 1) + "
+                      "lsb_add_frames_dev(i), deferred map updates joined inside the bracket); kernel durations (roofline, *_kernels) from a "
+                      "separate pass with lsb_set_profiling(1); reference arm: wall clock around each AddFrame of the CPU port"}
 
 
 def pct(values, q):
@@ -191,6 +201,7 @@ def run_batch(seq_ids, sensor, warm, steps, device, own=None):
             t0 = time.perf_counter()
             h.AddFramesDev([dp[i]], [npts], [frames[i][1]], [i + 1])
             lat[j].append(1e3 * (time.perf_counter() - t0))
+        h.Synchronize()            # a deferred map update of the last frame ends inside the timed region
 
     ts = [threading.Thread(target=work, args=(j, h, f, d)) for j, (h, f, d) in enumerate(zip(hs, seqs, dptrs))]
     for t in ts:
@@ -208,8 +219,9 @@ def run_batch(seq_ids, sensor, warm, steps, device, own=None):
 
 def run_deep_window(sensor, start, steps, device, flush):
     """A second timed window deep in the sequence (BASELINE quotes the metric on a 500-frame sequence): frames 0 .. start - 1
-    go through lsb_add_frames from the host untimed, frames start .. start + steps - 1 are timed like `value` (resident in
-    HBM, CUDA events per call, L2 flushed between calls).  By then the maps are saturated and the grid has rolled."""
+    go through lsb_add_frames from the host untimed; by then the maps are saturated and the grid has rolled.  Frames
+    start .. start + steps - 1 are timed the round-1/2 way (synchronous calls, CUDA events per call, L2 flushed between calls),
+    the next `steps` frames like `value` (pipelined loop, one bracketed region)."""
     from lidarslam_b200.slam import Slam
     from tools.synth import synth
     seq, sens = synth.Sequence(scene_seed=1234), synth.sensor(sensor)
@@ -218,21 +230,35 @@ def run_deep_window(sensor, start, steps, device, flush):
     for i in range(start):
         pts, _, stamp = seq.frame(sens, i)
         h.AddFrame(pts, stamp, i + 1)
-    window = [seq.frame(sens, i) for i in range(start, start + steps)]
+    window = [seq.frame(sens, i) for i in range(start, start + 2 * steps + 1)]
     npts = len(window[0][0])
     dp = [h.DevUpload(w[0]) for w in window]
+    h.SetPipelining(False)
     ms, kf = [], 0
-    for j, (pts, _, stamp) in enumerate(window):
+    for j in range(steps):
         if flush:
             h.FlushL2()
-        h.AddFramesDev([dp[j]], [npts], [stamp], [start + j + 1])
+        h.AddFramesDev([dp[j]], [npts], [window[j][2]], [start + j + 1])
         st = h.GetFrameStats()
         ms.append(st.ms_total)
         kf += st.is_keyframe
-    out = {"frames": "%d-%d" % (start, start + steps - 1), "value": steps / (sum(ms) * 1e-3), "unit": UNIT,
-           "p50_ms_per_frame": pct(ms, 50), "p95_ms_per_frame": pct(ms, 95), "max_ms_per_frame": max(ms), "key_frames": int(kf),
+    h.SetPipelining(True)
+    h.PrefetchFramesDev([dp[steps]], [npts], [window[steps][2]], [start + steps + 1])
+    h.TimerBegin()
+    lat = []
+    for j in range(steps, 2 * steps):
+        h.PrefetchFramesDev([dp[j + 1]], [npts], [window[j + 1][2]], [start + j + 2])
+        t0 = time.perf_counter()
+        h.AddFramesDev([dp[j]], [npts], [window[j][2]], [start + j + 1])
+        lat.append(1e3 * (time.perf_counter() - t0))
+    total = h.TimerEnd()
+    out = {"frames": "%d-%d" % (start + steps, start + 2 * steps - 1), "value": steps / (total * 1e-3), "unit": UNIT,
+           "p50_ms_per_frame": pct(lat, 50), "p95_ms_per_frame": pct(lat, 95), "max_ms_per_frame": max(lat),
            "n_map": list(st.n_map), "n_submap": list(st.n_submap), "n_matches": list(st.n_matches),
-           "timing": "as `value`: CUDA events per call, frames resident in HBM, L2 %s" % ("flushed between calls" if flush else "not flushed")}
+           "timing": "as `value`: pipelined loop, one CUDA-event bracket, frames resident in HBM",
+           "sync_api": {"frames": "%d-%d" % (start, start + steps - 1), "value": steps / (sum(ms) * 1e-3), "p50_ms_per_frame": pct(ms, 50),
+                        "p95_ms_per_frame": pct(ms, 95), "key_frames": int(kf),
+                        "timing": "synchronous calls, CUDA events per call, L2 %s" % ("flushed between calls" if flush else "not flushed")}}
     h.close()
     return out
 
@@ -288,7 +314,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    frames = make_frames(a.sensor, W + K, shard.sequence_seed(rank))   # one independent sequence per rank
+    frames = make_frames(a.sensor, W + K + 1, shard.sequence_seed(rank))   # one independent sequence per rank (+ 1: the last step prefetches too)
     npts = len(frames[0][0])
 
     # ---------------- kernel pass: per-kernel durations (not the throughput number) ------
@@ -316,60 +342,105 @@ def main():
         knn_queries += st.knn_queries
     Tp, _ = pr.GetWorldTransform()
 
-    # ---------------- value: frames resident in HBM -------------------------------------
+    # ---------------- sync_api, device: one synchronous call per step, events per call, L2 flushed ----
+    sy = Slam(device=local)
+    configure(sy)
+    sy.SetPipelining(False)
+    for i in range(W):
+        sy.AddFramesDev([dptrs[i]], [npts], [frames[i][1]], [i + 1])
+    barrier()
+    sync_ms = []
+    phase = np.zeros(4)
+    for i in range(W, W + K):
+        if not a.no_flush:
+            sy.FlushL2()
+        sy.AddFramesDev([dptrs[i]], [npts], [frames[i][1]], [i + 1])
+        st = sy.GetFrameStats()
+        sync_ms.append(st.ms_total)
+        phase += [st.ms_extract, st.ms_ego, st.ms_localization, st.ms_map_update]
+    last = st
+    Ts, _ = sy.GetWorldTransform()
+    barrier()
+
+    # ---------------- value: frames resident in HBM, the pipelined loop as one bracketed region -------
     g = Slam(device=local)
     configure(g)
     for i in range(W):
         g.AddFramesDev([dptrs[i]], [npts], [frames[i][1]], [i + 1])
+    launches0 = g.GetFrameStats().launches_total
+    g.PrefetchFramesDev([dptrs[W]], [npts], [frames[W][1]], [W + 1])
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
-    step_ms, launches = [], 0
-    phase = np.zeros(4)
+    g.TimerBegin()                     # everything so far (frame W's extraction included) is over
+    step_ms = []
     t_wall0 = time.perf_counter()
     for i in range(W, W + K):
-        if not a.no_flush:
-            g.FlushL2()
+        g.PrefetchFramesDev([dptrs[i + 1]], [npts], [frames[i + 1][1]], [i + 2])
+        t0 = time.perf_counter()
         g.AddFramesDev([dptrs[i]], [npts], [frames[i][1]], [i + 1])
-        st = g.GetFrameStats()
-        step_ms.append(st.ms_total)
-        launches += st.kernel_launches
-        phase += [st.ms_extract, st.ms_ego, st.ms_localization, st.ms_map_update]
+        step_ms.append(1e3 * (time.perf_counter() - t0))
+    total_ms = g.TimerEnd()            # joins the last map update and the last staged extraction
     barrier()
     wall = time.perf_counter() - t_wall0
     sampler.stop_flag = True
     sampler.join()
-    last = st
-    total_ms = float(sum(step_ms))
-    # ---------------- e2e: host buffers through lsb_add_frames ---------------------------
+    launches = g.GetFrameStats().launches_total - launches0
+    # ---------------- e2e: host buffers, the same pipelined loop, wall clock -----------------------
     e = Slam(device=local)
     configure(e)
+    pins = [pinned_points(npts) for _ in range(K + 1)]     # the sensor driver's ring of pinned buffers, filled outside the timed region
+    for j in range(K + 1):
+        pins[j][0][:] = frames[W + j][0]
+    for i in range(W):
+        e.AddFrame(frames[i][0], frames[i][1], i + 1)
+    e.PrefetchFrames([pins[0][0]], [frames[W][1]], [W + 1])
+    e.Synchronize()
+    barrier()
+    e2e_steps, d2h, h2d = [], 0, 0
+    t_e0 = time.perf_counter()
+    for j in range(K):
+        i = W + j
+        e.PrefetchFrames([pins[j + 1][0]], [frames[i + 1][1]], [i + 2])     # H2D of the next frame + its extraction, behind this call
+        t0 = time.perf_counter()
+        e.AddFrames([pins[j][0]], [frames[i][1]], [i + 1])                  # pose of frame i (its H2D was enqueued one step earlier, inside the region)
+        T, _ = e.GetWorldTransform()                                        # the step's result on the host
+        e2e_steps.append(time.perf_counter() - t0)
+        h2d += pins[j + 1][0].nbytes
+    e.Synchronize()
+    e2e_s = time.perf_counter() - t_e0
+    barrier()
+    d2h = K * (e.GetFrameStats().d2h_bytes + 128)
+    # ---------------- sync_api, host buffers: one synchronous call per step, wall clock per call -----
+    es = Slam(device=local)
+    configure(es)
+    es.SetPipelining(False)
     pin, pin_ptr = pinned_points(npts)
     for i in range(W):
         pin[:] = frames[i][0]
-        e.AddFrame(pin, frames[i][1], i + 1)
+        es.AddFrame(pin, frames[i][1], i + 1)
     barrier()
-    e2e_s, d2h, h2d, e2e_steps = 0.0, 0, 0, []
+    sync_e2e = []
     for i in range(W, W + K):
         if not a.no_flush:
-            e.FlushL2()
+            es.FlushL2()
         pin[:] = frames[i][0]                       # the sensor driver's buffer (pinned), filled outside the timed region
         t0 = time.perf_counter()
-        e.AddFrame(pin, frames[i][1], i + 1)        # H2D + whole path + readbacks
-        T, _ = e.GetWorldTransform()                # the step's result on the host
-        e2e_steps.append(time.perf_counter() - t0)
-        e2e_s += e2e_steps[-1]
-        se = e.GetFrameStats()
-        d2h += se.d2h_bytes + 128
-        h2d += se.h2d_bytes
+        es.AddFrame(pin, frames[i][1], i + 1)       # H2D + whole path + readbacks
+        Te, _ = es.GetWorldTransform()
+        sync_e2e.append(time.perf_counter() - t0)
     barrier()
     if max(e2e_steps) > 2 * statistics.median(e2e_steps):
         print("[bench rank %d] e2e outlier steps (ms): %s" % (rank, " ".join("%.2f" % (1e3 * t) for t in e2e_steps)), file=sys.stderr, flush=True)
     if os.environ.get("LSB_TRACE") == "1":
         print("[bench rank %d] device memory pool (MiB): %s" % (rank, _pool_stats()), file=sys.stderr, flush=True)
     Tg, _ = g.GetWorldTransform()
-    same_pose = bool(np.abs(Tg - T).max() < 1e-9 and np.abs(Tg - Tp).max() < 1e-9)
+    same_pose = bool(max(np.abs(Tg - X).max() for X in (T, Tp, Ts, Te)) < 1e-9)
     pinned_free(pin_ptr)
+    es.close()
+    e.close()
+    for _, ptr in pins:
+        pinned_free(ptr)
 
     if world > 1:
         print("[bench rank %d] device %.3f ms/frame, e2e %.3f ms/frame (p50 %.3f, max %.3f)" % (
@@ -378,7 +449,7 @@ def main():
     batch_dt = batch_p95 = 0.0
     batch_lat, batch_ids, batch_same = [], [], True
     if a.batch >= world and a.batch % world == 0:
-        for h_ in (g, e, pr):            # give the single-sequence handles' memory back to the pool first
+        for h_ in (g, sy, pr):           # give the single-sequence handles' memory back to the pool first
             h_.close()
         batch_ids = shard.assign_sequences(a.batch, world)[rank]
         barrier()
@@ -413,6 +484,7 @@ def main():
         achieved = per_launch_bytes / per_launch_s / 1e9 if per_launch_s > 0 else 0.0
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
                 "ms_per_step": max_ms / K, "p50_ms_per_frame": statistics.median(step_ms), "p95_ms_per_frame": pct(step_ms, 95), "max_ms_per_frame": max(step_ms),
+                "latency_note": "p50 / p95 / max: wall clock of the lsb_add_frames_dev call (input staged -> pose on the host); ms_per_step: bracketed region / steps",
                 "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32/f64", "data": "synthetic",
                 "points_per_sec": value * npts, "knn_queries_per_sec": knn_queries / (knn_ms * 1e-3) if knn_ms > 0 else None,
@@ -426,11 +498,15 @@ def main():
                              "frac": achieved / peak if peak else None, "traffic": traffic,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                              "bytes_per_launch": per_launch_bytes, "us_per_launch": per_launch_s * 1e6, "launches": knn_launches},
-                "phase_ms_per_frame": {"extract": phase[0] / K, "ego_motion": phase[1] / K, "localization": phase[2] / K,
+                "phase_ms_per_frame": {"from": "the sync_api pass (one synchronous call per step)", "extract": phase[0] / K, "ego_motion": phase[1] / K, "localization": phase[2] / K,
                                        "map_update": phase[3] / K, "knn_kernels": knn_ms / K, "fit_kernels": fit_ms / K, "lm_kernels": lm_ms / K},
                 "frame": {"n_keypoints": list(last.n_keypoints), "n_submap": list(last.n_submap), "n_matches": list(last.n_matches),
                           "loc_icp_iters": last.loc_icp_iters, "loc_lm_iters": last.loc_lm_iters, "launches_per_frame": last.kernel_launches},
-                "wall_s_timed_region": wall}
+                "wall_s_timed_region": wall,
+                "sync_api": {"value": K * world / (sum(sync_ms) * 1e-3), "unit": UNIT, "p50_ms_per_frame": statistics.median(sync_ms), "p95_ms_per_frame": pct(sync_ms, 95),
+                             "e2e": K * world / sum(sync_e2e), "e2e_p50_ms_per_frame": 1e3 * statistics.median(sync_e2e), "e2e_p95_ms_per_frame": 1e3 * pct(sync_e2e, 95),
+                             "how": "rank 0's sequence x ranks; no prefetch, map update inside the call (lsb_set_pipelining(h, 0)), CUDA events per call "
+                                    "(device) / wall clock per call incl. H2D (host buffers), L2 flushed between calls: the method of rounds 1-2"}}
         # secondary evidence the north star asks for: FP64 pipe use of the Jacobian / normal-equation stage.  k_lm_solve is the
         # largest single kernel of a frame since the LM loop became one persistent launch per solve.
         n_match = sum(last.n_matches)

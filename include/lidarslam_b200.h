@@ -167,6 +167,10 @@ typedef struct lsb_frame_stats {
   float ms_fit, ms_lm;                 /* model-fit kernels / LM evaluation kernels (needs lsb_set_profiling) */
   uint32_t lm_launches;
   uint64_t d2h_bytes, h2d_bytes;       /* bytes copied device->host / host->device inside the call */
+  uint32_t map_update_deferred;        /* 1: the call returned with the pose while the map update went on (ms_total ends where it starts;
+                                          ms_map_update and n_map are completed by lsb_get_frame_stats, which waits for it) */
+  uint32_t prefetched;                 /* 1: the input had been staged by lsb_prefetch_frames (ms_extract ~ 0) */
+  uint32_t launches_total;             /* our kernels launched by this handle since it was created (staged and deferred work included) */
 } lsb_frame_stats;
 
 typedef struct lsb_slam lsb_slam;      /* opaque: one CUDA stream + all device buffers of one sequence */
@@ -206,6 +210,30 @@ LSB_API int lsb_add_frames(lsb_slam* h, int n_frames, const lsb_point* const* fr
  * inputs in HBM. */
 LSB_API int lsb_add_frames_dev(lsb_slam* h, int n_frames, const lsb_point* const* dev_frames, const size_t* n,
                                const uint64_t* stamp_us, const uint32_t* seq);
+
+/* ---- pipelining (no counterpart in the reference: Slam::AddFrames is synchronous, Slam.cxx:230-344) ----------------------------
+ * A trajectory is sequential, but two pieces of a frame do not depend on its neighbours' results and are taken off the caller's
+ * critical path:
+ *  - the map update of frame t (Slam::UpdateMapsUsingTworld, Slam.cxx:1178-1222) is deferred: lsb_add_frames returns once the
+ *    pose is known, the update runs behind it and is joined before the next frame's sub-maps are selected or by the first entry
+ *    point that looks at the maps / keypoints / statistics.  Results are identical; lsb_set_pipelining(h, 0) restores the
+ *    fully synchronous call.
+ *  - lsb_prefetch_frames hands the NEXT input in ahead of time (a bag replay, a driver queue): its upload and keypoint extraction
+ *    (Slam::ExtractKeypoints, Slam.cxx:746-810, which reads nothing but the frame and the extractor parameters) run on an ingest
+ *    stream while the current frame is in its ICP loop.  lsb_add_frames / lsb_add_frames_dev called later with the same buffer
+ *    pointers, sizes and stamps picks the staged keypoints up; any other input drops what is staged.  At most two inputs are
+ *    staged at a time (LSB_E_CAPACITY beyond).  The buffers must stay valid and unchanged until the matching add call returns.
+ *    Parameter setters drop staged inputs (they were extracted with the old parameters). */
+LSB_API int lsb_prefetch_frames(lsb_slam* h, int n_frames, const lsb_point* const* frames, const size_t* n,
+                                const uint64_t* stamp_us, const uint32_t* seq);
+LSB_API int lsb_prefetch_frames_dev(lsb_slam* h, int n_frames, const lsb_point* const* dev_frames, const size_t* n,
+                                    const uint64_t* stamp_us, const uint32_t* seq);
+LSB_API int lsb_set_pipelining(lsb_slam* h, int defer_map_update);
+LSB_API int lsb_synchronize(lsb_slam* h);            /* every deferred / staged job over, every stream of the handle idle */
+/* Whole-loop timing with CUDA events on the handle's stream: begin = lsb_synchronize + event; end = deferred and staged work
+ * joined into the stream + event + wait; *ms = time between the two (benchmarks: K calls bracketed as one region). */
+LSB_API int lsb_timer_begin(lsb_slam* h);
+LSB_API int lsb_timer_end(lsb_slam* h, float* ms);
 
 /* Memory helpers for callers without their own CUDA allocator: pinned host
  * buffers (fast H2D for lsb_add_frames) and device buffers (lsb_add_frames_dev). */

@@ -90,7 +90,8 @@ class FrameStats(C.Structure):
                 ("ms_extract", C.c_float), ("ms_ego", C.c_float), ("ms_localization", C.c_float),
                 ("ms_map_update", C.c_float), ("ms_total", C.c_float), ("ms_knn", C.c_float),
                 ("knn_launches", C.c_uint32), ("ms_fit", C.c_float), ("ms_lm", C.c_float), ("lm_launches", C.c_uint32),
-                ("d2h_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64)]
+                ("d2h_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64),
+                ("map_update_deferred", C.c_uint32), ("prefetched", C.c_uint32), ("launches_total", C.c_uint32)]
 
 
 def _ptr(a):

@@ -123,7 +123,7 @@ struct KernelTimer {
 };
 
 // Launch counter of one handle (lsb_frame_stats.kernel_launches).
-struct LaunchCounter {   // bumped from the host lanes (host/lanes.h) as well
+struct LaunchCounter {   // bumped from the helper threads (host/worker.h) as well
   std::atomic<unsigned> n{0};
   void add(unsigned k = 1) { n.fetch_add(k, std::memory_order_relaxed); }
 };

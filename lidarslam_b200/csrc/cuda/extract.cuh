@@ -33,6 +33,9 @@ struct ExtractorGpu {
   PinnedBuf<float> h_az;
 
   ExtractorGpu();
+  // parameters and the state that outlives a frame (azimuth estimate, ring count): handed from one instance to the next when
+  // several instances take turns (lsb_prefetch_frames)
+  void adopt_scalars(const ExtractorGpu& o) { P = o.P; nb_rings = o.nb_rings; az_estimations = o.az_estimations; }
   // SpinningSensorKeypointExtractor::ComputeKeyPoints on a DEVICE cloud.
   // Synchronises the stream once (keypoint counts).
   void compute(const lsb_point* d_pts, size_t n, cudaStream_t s, LaunchCounter& lc);

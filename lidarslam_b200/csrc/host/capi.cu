@@ -87,14 +87,21 @@ int lsb_create(lsb_slam** out, int cuda_device)
   if (cuda_device < 0 || cuda_device >= n) { g_last_error = "invalid CUDA device index"; return LSB_E_INVALID; }
   return guarded([&] { *out = new lsb_slam(cuda_device); return LSB_OK; });
 }
-void lsb_destroy(lsb_slam* h) { delete h; }
-int lsb_reset(lsb_slam* h, int reset_log) { return guarded([&] { h->Reset(reset_log != 0); return LSB_OK; }); }
+void lsb_destroy(lsb_slam* h)
+{
+  if (h) guarded([&] { h->Quiesce(true); return LSB_OK; });   // an error of a job nobody waited for dies with the handle
+  delete h;
+}
+int lsb_reset(lsb_slam* h, int reset_log) { return guarded([&] { h->Quiesce(true); h->Reset(reset_log != 0); return LSB_OK; }); }
 
-int lsb_set_params(lsb_slam* h, const lsb_params* p) { h->P = *p; return LSB_OK; }
+// Entry points that read or change what the helper thread works on (maps, keypoints, extractors, statistics) wait for it
+// first; setters also drop inputs staged with the old parameters.
+int lsb_set_params(lsb_slam* h, const lsb_params* p) { return guarded([&] { h->Quiesce(true); h->P = *p; return LSB_OK; }); }
 int lsb_get_params(const lsb_slam* h, lsb_params* p) { *p = h->P; return LSB_OK; }
 int lsb_set_extractor_params(lsb_slam* h, int device_id, const lsb_ke_params* p)
 {
   return guarded([&] {
+    h->Quiesce(true);
     ExtractorGpu& ke = h->Extractor(device_id);
     // An azimuthal resolution outside the usable range [1e-6, pi/4] means "estimate it from the first frame"
     // (SpinningSensorKeypointExtractor.cxx:165-170).  A caller that pushes its whole parameter block again (the
@@ -110,28 +117,40 @@ int lsb_set_extractor_params(lsb_slam* h, int device_id, const lsb_ke_params* p)
 }
 int lsb_get_extractor_params(const lsb_slam* h, int device_id, lsb_ke_params* p)
 {
+  { const int rc = guarded([&] { const_cast<lsb_slam*>(h)->Quiesce(false); return LSB_OK; }); if (rc < 0) return rc; }
   auto it = h->KeyPointsExtractors.find(device_id);
   if (it == h->KeyPointsExtractors.end() || !it->second) { g_last_error = "no extractor for this device_id"; return LSB_E_INVALID; }
   *p = it->second->P;
   return LSB_OK;
 }
-int lsb_set_base_to_lidar(lsb_slam* h, int device_id, const double T[16]) { h->BaseToLidarOffsets[device_id] = FromRowMajor(T); return LSB_OK; }
+int lsb_set_base_to_lidar(lsb_slam* h, int device_id, const double T[16])
+{
+  return guarded([&] { h->Quiesce(true); h->BaseToLidarOffsets[device_id] = FromRowMajor(T); return LSB_OK; });
+}
 int lsb_set_voxel_grid_leaf_size(lsb_slam* h, int k, double size)
 {
   if (k < 0 || k > 2) return LSB_E_INVALID;
-  h->LocalMaps[k].LeafSize = size;   // RollingGrid::SetLeafSize is a plain SetMacro (RollingGrid.h:106)
-  return LSB_OK;
+  return guarded([&] {
+    h->Quiesce(false);
+    h->LocalMaps[k].LeafSize = size;   // RollingGrid::SetLeafSize is a plain SetMacro (RollingGrid.h:106)
+    return LSB_OK;
+  });
 }
-int lsb_set_voxel_grid_size(lsb_slam* h, int size) { return guarded([&] { for (auto& m : h->LocalMaps) m.SetGridSize(size, h->stream, h->lc); return LSB_OK; }); }
-int lsb_set_voxel_grid_resolution(lsb_slam* h, double r) { return guarded([&] { for (auto& m : h->LocalMaps) m.SetVoxelResolution(r, h->stream, h->lc); return LSB_OK; }); }
-int lsb_set_voxel_grid_min_frames_per_voxel(lsb_slam* h, unsigned n) { for (auto& m : h->LocalMaps) m.MinFramesPerVoxel = n; return LSB_OK; }
-int lsb_set_voxel_grid_decaying_threshold(lsb_slam* h, double s) { for (auto& m : h->LocalMaps) m.DecayingThreshold = s; return LSB_OK; }
+int lsb_set_voxel_grid_size(lsb_slam* h, int size) { return guarded([&] { h->Quiesce(false); for (auto& m : h->LocalMaps) m.SetGridSize(size, h->stream, h->lc); return LSB_OK; }); }
+int lsb_set_voxel_grid_resolution(lsb_slam* h, double r) { return guarded([&] { h->Quiesce(false); for (auto& m : h->LocalMaps) m.SetVoxelResolution(r, h->stream, h->lc); return LSB_OK; }); }
+int lsb_set_voxel_grid_min_frames_per_voxel(lsb_slam* h, unsigned n)
+{
+  return guarded([&] { h->Quiesce(false); for (auto& m : h->LocalMaps) m.MinFramesPerVoxel = n; return LSB_OK; });
+}
+int lsb_set_voxel_grid_decaying_threshold(lsb_slam* h, double s)
+{
+  return guarded([&] { h->Quiesce(false); for (auto& m : h->LocalMaps) m.DecayingThreshold = s; return LSB_OK; });
+}
 int lsb_set_voxel_grid_sampling_mode(lsb_slam* h, int k, int mode)
 {
   if (k < 0 || k > 2) return LSB_E_INVALID;
   if (mode < LSB_SAMPLING_FIRST || mode > LSB_SAMPLING_CENTROID) { g_last_error = "unknown SamplingMode"; return LSB_E_INVALID; }   // rejected here, not in the middle of a frame
-  h->LocalMaps[k].Sampling = mode;
-  return LSB_OK;
+  return guarded([&] { h->Quiesce(false); h->LocalMaps[k].Sampling = mode; return LSB_OK; });
 }
 
 int lsb_add_frames(lsb_slam* h, int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq)
@@ -141,6 +160,40 @@ int lsb_add_frames(lsb_slam* h, int n_frames, const lsb_point* const* frames, co
 int lsb_add_frames_dev(lsb_slam* h, int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq)
 {
   return guarded([&] { return h->AddFrames(n_frames, frames, n, stamp_us, seq, true); });
+}
+int lsb_prefetch_frames(lsb_slam* h, int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq)
+{
+  return guarded([&] { return h->PrefetchFrames(n_frames, frames, n, stamp_us, seq, false); });
+}
+int lsb_prefetch_frames_dev(lsb_slam* h, int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq)
+{
+  return guarded([&] { return h->PrefetchFrames(n_frames, frames, n, stamp_us, seq, true); });
+}
+int lsb_set_pipelining(lsb_slam* h, int defer_map_update)
+{
+  return guarded([&] { h->Quiesce(false); h->defer_map_update = defer_map_update != 0; return LSB_OK; });
+}
+int lsb_synchronize(lsb_slam* h) { return guarded([&] { h->SynchronizeAll(); return LSB_OK; }); }
+int lsb_timer_begin(lsb_slam* h)
+{
+  return guarded([&] {
+    h->SynchronizeAll();
+    LSB_CUDA(cudaEventRecord(h->ev_timer[0], h->stream));
+    return LSB_OK;
+  });
+}
+int lsb_timer_end(lsb_slam* h, float* ms)
+{
+  return guarded([&] {
+    h->Quiesce(false);                                   // helper jobs over; `stream` already waits for a deferred map update
+    for (auto& sl : h->staged) if (sl.valid) LSB_CUDA(cudaStreamWaitEvent(h->stream, sl.ready, 0));
+    LSB_CUDA(cudaEventRecord(h->ev_timer[1], h->stream));
+    LSB_CUDA(cudaEventSynchronize(h->ev_timer[1]));
+    float t = 0.f;
+    LSB_CUDA(cudaEventElapsedTime(&t, h->ev_timer[0], h->ev_timer[1]));
+    if (ms) *ms = t;
+    return LSB_OK;
+  });
 }
 
 void* lsb_host_alloc(size_t bytes) { void* p = nullptr; if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; } return p; }
@@ -165,7 +218,7 @@ int lsb_dev_upload(lsb_slam* h, void* dst, const void* src, size_t bytes)
 int lsb_dev_flush_l2(lsb_slam* h)
 {
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     const size_t bytes = 256u << 20;
     h->tmp_u8.reserve(bytes, h->stream);
     LSB_CUDA(cudaMemsetAsync(h->tmp_u8.p, (int)(h->NbrFrameProcessed & 0xff), bytes, h->stream));
@@ -212,7 +265,7 @@ long lsb_get_keypoints(lsb_slam* h, int type, int world, lsb_point* out, long ca
 {
   if (type < 0 || type > 2) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     if (!world) return (int)CopyOut(h, h->CurrentKeypoints[type].buf.p, h->CurrentKeypoints[type].n, out, cap);
     const DCloud& w = h->WorldKeypoints(type);
     return (int)CopyOut(h, w.buf.p, w.n, out, cap);
@@ -222,7 +275,7 @@ long lsb_get_map(lsb_slam* h, int type, int clean, lsb_point* out, long cap)
 {
   if (type < 0 || type > 2) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     RollingGridGpu& m = h->LocalMaps[type];
     if (!clean) return (int)CopyOut(h, m.pts.p, m.n_entries, out, cap);
     h->tmp_cloud.reserve(std::max<size_t>(m.n_entries, 1), h->stream);
@@ -233,12 +286,12 @@ long lsb_get_map(lsb_slam* h, int type, int clean, lsb_point* out, long cap)
 long lsb_get_submap(lsb_slam* h, int type, lsb_point* out, long cap)
 {
   if (type < 0 || type > 2) return LSB_E_INVALID;
-  return guarded([&] { LSB_CUDA(cudaSetDevice(h->device)); return (int)CopyOut(h, h->LocalMaps[type].submap.p, h->LocalMaps[type].n_submap, out, cap); });
+  return guarded([&] { h->Quiesce(false); return (int)CopyOut(h, h->LocalMaps[type].submap.p, h->LocalMaps[type].n_submap, out, cap); });
 }
 long lsb_get_registered_frame(lsb_slam* h, lsb_point* out, long cap)
 {
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     const size_t n = h->RegisteredFrame(h->tmp_cloud);
     return (int)CopyOut(h, h->tmp_cloud.p, n, out, cap);
   });
@@ -247,7 +300,7 @@ long lsb_get_match_debug(lsb_slam* h, int stage, int type, uint8_t* status, doub
 {
   if (type < 0 || type > 2 || stage < 0 || stage > 1) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     lsb_slam::StageDebug& d = stage == 0 ? h->EgoDebug : h->LocDebug;
     const uint8_t* st = stage == 0 ? d.status.p : h->mw.status.p;
     const double* wt = stage == 0 ? d.weight.p : h->mw.weight.p;
@@ -261,6 +314,7 @@ long lsb_get_match_debug(lsb_slam* h, int stage, int type, uint8_t* status, doub
 }
 long lsb_get_ke_debug(lsb_slam* h, int device_id, int field, float* out, long cap)
 {
+  { const int rc = guarded([&] { h->Quiesce(false); return LSB_OK; }); if (rc < 0) return rc; }
   auto it = h->KeyPointsExtractors.find(device_id);
   if (it == h->KeyPointsExtractors.end() || !it->second) { g_last_error = "no extractor for this device_id"; return LSB_E_INVALID; }
   return guarded([&] {
@@ -275,15 +329,20 @@ long lsb_get_ke_debug(lsb_slam* h, int device_id, int field, float* out, long ca
     return (int)ke.n;
   });
 }
-int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s) { *s = h->Stats; return LSB_OK; }
+int lsb_get_frame_stats(const lsb_slam* h, lsb_frame_stats* s)
+{
+  return guarded([&] { const_cast<lsb_slam*>(h)->Quiesce(false); *s = h->Stats; s->launches_total = h->lc.n; return LSB_OK; });   // a deferred map update completes ms_map_update / n_map
+}
 int lsb_set_profiling(lsb_slam* h, int on)
 {
+  { const int rc = guarded([&] { h->Quiesce(false); return LSB_OK; }); if (rc < 0) return rc; }
   h->mw.t_knn.enabled = h->mw.t_fit.enabled = h->mw.t_lm.enabled = (on != 0);
   h->serial_types = (on != 0);   // kernel durations are taken without overlap between the keypoint types
   return LSB_OK;
 }
 unsigned int lsb_get_azimuth_estimations(const lsb_slam* h, int device_id)
 {
+  guarded([&] { const_cast<lsb_slam*>(h)->Quiesce(false); return LSB_OK; });
   auto it = h->KeyPointsExtractors.find(device_id);
   return (it == h->KeyPointsExtractors.end() || !it->second) ? 0u : it->second->az_estimations;
 }
@@ -291,8 +350,11 @@ float lsb_get_overlap(const lsb_slam* h) { return h->OverlapEstimation; }
 int lsb_get_comply_motion_limits(const lsb_slam* h) { return h->MotionLimits.Comply ? 1 : 0; }
 unsigned int lsb_get_total_matched_keypoints(const lsb_slam* h) { return h->TotalMatchedKeypoints; }
 
-int lsb_set_world_transform_from_guess(lsb_slam* h, const double T[16]) { h->SetWorldTransformFromGuess(FromRowMajor(T)); return LSB_OK; }
-int lsb_clear_maps(lsb_slam* h) { return guarded([&] { h->ClearMaps(); return LSB_OK; }); }
+int lsb_set_world_transform_from_guess(lsb_slam* h, const double T[16])
+{
+  return guarded([&] { h->Quiesce(false); h->SetWorldTransformFromGuess(FromRowMajor(T)); return LSB_OK; });
+}
+int lsb_clear_maps(lsb_slam* h) { return guarded([&] { h->Quiesce(false); h->ClearMaps(); return LSB_OK; }); }
 
 /* ---- external sensor constraints ------------------------------------ */
 int lsb_add_wheel_odom_measurement(lsb_slam* h, const lsb_wheel_odom_measurement* m)
@@ -347,7 +409,7 @@ int lsb_save_maps_to_pcd(lsb_slam* h, const char* file_prefix, int pcd_format, i
 {
   if (!file_prefix || pcd_format < 0 || pcd_format > 2) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     int worst = LSB_OK;
     std::vector<lsb_point> host;
     for (int k = 0; k < 3; ++k) {
@@ -373,7 +435,7 @@ int lsb_load_maps_from_pcd(lsb_slam* h, const char* file_prefix, int reset_maps)
 {
   if (!file_prefix) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     if (reset_maps) h->ClearMaps();                               // Slam.cxx:526-527
     int loaded = 0;
     std::vector<lsb_point> host;

@@ -47,7 +47,7 @@ int lsb_map_load_points(lsb_slam* h, int type, const lsb_point* pts, long n, int
 {
   if (type < 0 || type > 2 || n < 0) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     Upload(h, h->tmp_cloud, pts, (size_t)n);
     h->LocalMaps[type].Add(h->tmp_cloud.p, (size_t)n, fixed != 0, 0., true, h->stream, h->lc);   // Slam.cxx:537
     LSB_CUDA(cudaStreamSynchronize(h->stream));
@@ -75,7 +75,7 @@ long lsb_convert_velodyne(lsb_slam* h, const lsb_velodyne_point* pts, size_t n, 
   if (!(cp.rpm > 0.)) return LSB_E_INVALID;
   long r = 0;
   const int rc = guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     h->conv.velodyne(pts, n, cp, h->stream, h->lc);
     r = ConvertedOut(h, out, cap);
     return LSB_OK;
@@ -89,7 +89,7 @@ long lsb_convert_robosense(lsb_slam* h, const lsb_xyzi_point* pts, uint32_t widt
   if (!(cp.rpm > 0.)) return LSB_E_INVALID;
   long r = 0;
   const int rc = guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     h->conv.robosense(pts, width, height, cp, h->stream, h->lc);
     r = ConvertedOut(h, out, cap);
     return LSB_OK;
@@ -99,6 +99,7 @@ long lsb_convert_robosense(lsb_slam* h, const lsb_xyzi_point* pts, uint32_t widt
 int lsb_add_converted_frame(lsb_slam* h, uint64_t stamp_us, uint32_t seq)
 {
   return guarded([&] {
+    h->Quiesce(true);
     const lsb_point* frame = h->conv.out.p;
     const size_t n = h->conv.n_out;
     return h->AddFrames(1, &frame, &n, &stamp_us, &seq, true);
@@ -108,7 +109,7 @@ int lsb_add_converted_frame(lsb_slam* h, uint64_t stamp_us, uint32_t seq)
 int lsb_extract_keypoints(lsb_slam* h, const lsb_point* pts, size_t n, uint8_t* label_out, uint32_t counts[3])
 {
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     Upload(h, h->tmp_cloud, pts, n);
     ExtractorGpu& ke = h->Extractor(0);
     ke.compute(h->tmp_cloud.p, n, h->stream, h->lc);
@@ -128,7 +129,7 @@ long lsb_get_extracted_keypoints(lsb_slam* h, int type, lsb_point* out, long cap
 {
   if (type < 0 || type > 2) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     ExtractorGpu& ke = h->Extractor(0);
     const size_t n = ke.counts[type];
     if (out && n && cap > 0) {
@@ -142,7 +143,7 @@ long lsb_get_extracted_keypoints(lsb_slam* h, int type, lsb_point* out, long cap
 int lsb_knn_search(lsb_slam* h, const lsb_point* cloud, size_t m, const float* queries_xyz, size_t nq, int k, int32_t* idx_out, float* d2_out)
 {
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     if (k < 1 || k > KNN_MAX_K) throw CudaError(LSB_E_INVALID, "k must be in [1, 32]");
     Upload(h, h->tmp_cloud, cloud, m);
     KnnGrid grid;
@@ -182,7 +183,7 @@ int lsb_match_and_solve(lsb_slam* h, const lsb_point* const keypoints[3], const 
                         int* lm_iterations, double* final_cost, lsb_registration_error* err_out)
 {
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     const Iso3d T = FromRowMajor(prior_rowmajor);
     DevBuf<lsb_point> dk[3], dt[3];
     KnnGrid grids[3];
@@ -225,7 +226,7 @@ int lsb_map_add(lsb_slam* h, int type, const lsb_point* pts, size_t n, int fixed
 {
   if (type < 0 || type > 2) return LSB_E_INVALID;
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     Upload(h, h->tmp_cloud, pts, n);
     h->LocalMaps[type].Add(h->tmp_cloud.p, n, fixed != 0, current_time, true, h->stream, h->lc);
     LSB_CUDA(cudaStreamSynchronize(h->stream));
@@ -236,7 +237,7 @@ int lsb_map_add(lsb_slam* h, int type, const lsb_point* pts, size_t n, int fixed
 int lsb_undistort(lsb_slam* h, lsb_point* pts, size_t n, const double H0[16], const double H1[16], double t0, double t1)
 {
   return guarded([&] {
-    LSB_CUDA(cudaSetDevice(h->device));
+    h->Quiesce(false);
     Interpolator it;
     it.t0 = t0; it.t1 = t1;
     it.set_transforms(FromRowMajor(H0), FromRowMajor(H1));

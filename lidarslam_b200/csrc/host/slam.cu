@@ -23,7 +23,14 @@ static inline double StampToSec(uint64_t us) { return us * 1e-6; }   // Utils::P
 lsb_slam::lsb_slam(int dev) : device(dev)
 {
   LSB_CUDA(cudaSetDevice(dev));
-  LSB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  // the frame's own streams run at the highest priority, the ingest stream (prefetched frames) at the lowest: a kernel of
+  // the current frame's ICP chain is scheduled ahead of the next frame's extraction blocks (LSB_MAIN_PRIORITY: tuning hook)
+  int prio_lo = 0, prio_hi = 0;
+  LSB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  int prio_main = prio_hi;
+  if (const char* e = std::getenv("LSB_MAIN_PRIORITY")) prio_main = std::atoi(e);
+  LSB_CUDA(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, prio_main));
+  LSB_CUDA(cudaStreamCreateWithPriority(&istream, cudaStreamNonBlocking, prio_lo));
   {  // keep freed blocks in the device's default pool: buffer growth must not hit the driver again
     cudaMemPool_t pool;
     LSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
@@ -57,12 +64,16 @@ lsb_slam::lsb_slam(int dev) : device(dev)
   for (auto& e : ev) LSB_CUDA(cudaEventCreate(&e));
   {
     // LSB_TYPE_PRIORITIES="e,p,b": CUDA stream priority of the three type streams (0 = default, negative = higher); tuning hook
-    int prio[3] = {0, 0, 0};
+    int prio[3] = {prio_main, prio_main, prio_main};
     if (const char* e = std::getenv("LSB_TYPE_PRIORITIES")) std::sscanf(e, "%d,%d,%d", &prio[0], &prio[1], &prio[2]);
     for (int k = 0; k < 3; ++k) LSB_CUDA(cudaStreamCreateWithPriority(&tstream[k], cudaStreamNonBlocking, prio[k]));
   }
   LSB_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   for (auto& e : ev_join) LSB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (auto& e : ev_map_end) LSB_CUDA(cudaEventCreate(&e));
+  for (auto& e : ev_timer) LSB_CUDA(cudaEventCreate(&e));
+  for (auto& sl : staged) LSB_CUDA(cudaEventCreateWithFlags(&sl.ready, cudaEventDisableTiming));
+  if (const char* e = std::getenv("LSB_DEFER_MAP")) defer_map_update = (e[0] != '0');
   lsb_default_params(&P);
   if (const char* e = std::getenv("LSB_TRACE")) trace.on = (e[0] == '1');
   if (const char* e = std::getenv("LSB_HOST_LANES")) use_lanes = (e[0] != '0');
@@ -88,10 +99,16 @@ lsb_slam::lsb_slam(int dev) : device(dev)
 
 lsb_slam::~lsb_slam()
 {
-  lanes.reset();   // joins the helper threads
+  if (worker) { worker->drain(); worker.reset(); }
+  for (auto& w : tworker) if (w) { w->drain(); w.reset(); }
   cudaSetDevice(device);
   for (auto& t : tstream) if (t) cudaStreamSynchronize(t);
+  if (istream) cudaStreamSynchronize(istream);
   if (stream) cudaStreamSynchronize(stream);
+  for (auto& e : ev_map_end) if (e) cudaEventDestroy(e);
+  for (auto& e : ev_timer) if (e) cudaEventDestroy(e);
+  for (auto& sl : staged) if (sl.ready) cudaEventDestroy(sl.ready);
+  if (istream) cudaStreamDestroy(istream);
   for (auto& e : ev) if (e) cudaEventDestroy(e);
   if (ev_fork) cudaEventDestroy(ev_fork);
   for (auto& e : ev_join) if (e) cudaEventDestroy(e);
@@ -128,7 +145,7 @@ void lsb_slam::Fork()
   for (auto& t : tstream) LSB_CUDA(cudaStreamWaitEvent(t, ev_fork, 0));
 }
 
-// Host lanes cost two extra busy host threads per handle in flight.  They pay while every handle has three cores to
+// The per-type helper threads cost busy host threads per handle in flight.  They pay while every handle has three cores to
 // itself; beyond that (many sequences on one GPU, or many ranks on one host: torchrun exports LOCAL_WORLD_SIZE) the
 // spinning helpers steal the cores the other handles' callers need (8 sequences on 16 cores: 298 frames/s with lanes,
 // 856 without), so the types are then enqueued from the caller's thread.
@@ -151,14 +168,23 @@ struct InFlightGuard {
 
 void lsb_slam::ForEachType(const std::function<void(int)>& fn)
 {
-  Fork();
   const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
   if (serial_types || !use_lanes || crowded) {
+    JoinMapUpdate();             // a deferred update of these maps ends before the caller's thread touches them
+    Fork();
     for (int k : kTypeOrder) fn(k);
-  } else {
-    if (!lanes) lanes.reset(new TypeLanes(device));
-    lanes->run(kTypeOrder, fn);
+    Join();
+    return;
   }
+  Fork();
+  unsigned ticket[3];
+  for (int k : kTypeOrder) ticket[k] = TypeWorker(k).post([&fn, k] { fn(k); });
+  std::exception_ptr first;
+  for (int k : kTypeOrder) {
+    try { TypeWorker(k).wait(ticket[k]); } catch (...) { if (!first) first = std::current_exception(); }
+  }
+  if (first) std::rethrow_exception(first);
+  JoinMapUpdate();               // its jobs ran ahead of these on the same threads: only the bookkeeping (and its errors) is left
   Join();
 }
 
@@ -221,48 +247,167 @@ ExtractorGpu& lsb_slam::Extractor(int dev)
 }
 
 //-----------------------------------------------------------------------------
+lsb_slam::StageCfg lsb_slam::MakeStageCfg() const
+{
+  StageCfg c;
+  for (const auto& kv : KeyPointsExtractors) if (kv.second) c.ke_ids.push_back(kv.first);
+  c.offsets = BaseToLidarOffsets;
+  for (int k = 0; k < 3; ++k) c.use[k] = P.use_keypoints[k] != 0;
+  return c;
+}
+
+// host -> device copy of the input frames (skipped for device-resident input) and the device id of each
+void lsb_slam::UploadFrames(FrameList& pool, int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq,
+                            bool on_device, const StageCfg& cfg, cudaStream_t s)
+{
+  while (pool.size() < (size_t)n_frames) pool.emplace_back(new DFrame());
+  for (int i = 0; i < n_frames; ++i) {
+    DFrame& f = *pool[i];
+    f.n = n[i]; f.stamp_us = stamp_us[i]; f.seq = seq ? seq[i] : 0u;
+    if (on_device) f.d = frames[i];
+    else {
+      f.own.buf.reserve(std::max<size_t>(n[i], 1), s);
+      if (n[i]) LSB_CUDA(cudaMemcpyAsync(f.own.buf.p, frames[i], n[i] * sizeof(lsb_point), cudaMemcpyHostToDevice, s));
+      f.d = f.own.buf.p;
+    }
+    f.device_id = 0;
+    if (n[i]) {
+      if (on_device && cfg.ke_ids.size() == 1 && cfg.offsets.empty()) {
+        // one sensor, no calibration: the device id selects nothing (Slam.cxx:764-780), no read-back
+        f.device_id = cfg.ke_ids[0];
+      } else if (on_device) {
+        lsb_point first;
+        LSB_CUDA(cudaMemcpyAsync(&first, frames[i], sizeof(lsb_point), cudaMemcpyDeviceToHost, s));
+        LSB_CUDA(cudaStreamSynchronize(s));
+        f.device_id = first.device_id;
+      } else f.device_id = frames[i][0].device_id;
+    }
+  }
+}
+
+// lsb_prefetch_frames: the helper thread uploads the frames on the ingest stream and extracts their keypoints into a staging
+// slot; lsb_add_frames of the same buffers / sizes / stamps picks the slot up instead of extracting.
+int lsb_slam::PrefetchFrames(int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq, bool on_device)
+{
+  LSB_CUDA(cudaSetDevice(device));
+  if (n_frames <= 0) return LSB_E_INVALID;
+  StagedInput* slot = nullptr;
+  for (auto& sl : staged) if (!sl.valid) { slot = &sl; break; }
+  if (!slot) throw CudaError(LSB_E_CAPACITY, "lsb_prefetch_frames: two inputs are staged already; add one of them first");
+  slot->valid = true;
+  slot->on_device = on_device;
+  slot->src.assign(frames, frames + n_frames);
+  slot->n.assign(n, n + n_frames);
+  slot->stamp.assign(stamp_us, stamp_us + n_frames);
+  slot->seq.assign((size_t)n_frames, 0u);
+  if (seq) slot->seq.assign(seq, seq + n_frames);
+  const StageCfg cfg = MakeStageCfg();
+  const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
+  slot->ticket = Worker().post([this, slot, cfg] {
+    const int nf = (int)slot->src.size();
+    UploadFrames(slot->frames, nf, slot->src.data(), slot->n.data(), slot->stamp.data(), slot->seq.data(), slot->on_device, cfg, istream);
+    ExtractInto(slot->frames, (size_t)nf, slot->stamp[0], cfg, slot, slot->kp, slot->tmin, slot->tmax, istream);
+    LSB_CUDA(cudaEventRecord(slot->ready, istream));
+  }, !crowded);
+  return LSB_OK;
+}
+
+void lsb_slam::JoinMapUpdate()
+{
+  if (!map_pending) return;
+  map_pending = false;
+  std::exception_ptr first;
+  for (int k = 0; k < 3; ++k) {
+    if (!map_posted[k]) continue;
+    map_posted[k] = false;
+    try { TypeWorker(k).wait(map_ticket[k]); } catch (...) { if (!first) first = std::current_exception(); }
+    LSB_CUDA(cudaStreamWaitEvent(stream, ev_map_end[k], 0));
+  }
+  if (first) std::rethrow_exception(first);     // what the update threw
+}
+
+void lsb_slam::FinishMapStats()
+{
+  JoinMapUpdate();
+  if (!map_stats_pending) return;
+  map_stats_pending = false;
+  float worst = 0.f;
+  for (int k = 0; k < 3; ++k) {
+    Stats.n_map[k] = LocalMaps[k].Size();
+    if (!map_stats_type[k]) continue;
+    LSB_CUDA(cudaEventSynchronize(ev_map_end[k]));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ev[4], ev_map_end[k]) == cudaSuccess) worst = std::max(worst, ms); else cudaGetLastError();
+  }
+  Stats.ms_map_update = worst;
+}
+
+void lsb_slam::Quiesce(bool drop_staged)
+{
+  LSB_CUDA(cudaSetDevice(device));
+  std::exception_ptr first;
+  try { FinishMapStats(); } catch (...) { first = std::current_exception(); }
+  for (auto& sl : staged) {
+    if (!sl.valid) continue;
+    try { Worker().wait(sl.ticket); } catch (...) { if (!first) first = std::current_exception(); sl.valid = false; }
+    if (drop_staged) sl.valid = false;
+  }
+  if (first) std::rethrow_exception(first);
+}
+
+void lsb_slam::SynchronizeAll()
+{
+  Quiesce(false);
+  for (auto& t : tstream) LSB_CUDA(cudaStreamSynchronize(t));
+  LSB_CUDA(cudaStreamSynchronize(istream));
+  LSB_CUDA(cudaStreamSynchronize(stream));
+}
+
+//-----------------------------------------------------------------------------
 int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq, bool on_device)
 {
   LSB_CUDA(cudaSetDevice(device));
   InFlightGuard inflight;
   Warnings = 0;
   if (!CheckFrames(n_frames, n, stamp_us, seq)) return LSB_W_FRAME_IGNORED;
+  // staged ahead of time (lsb_prefetch_frames)?  Same buffers, sizes and stamps; anything else staged is dropped
+  StagedInput* hit = nullptr;
+  for (auto& sl : staged) {
+    if (!sl.valid || hit) continue;
+    bool same = sl.on_device == on_device && (int)sl.src.size() == n_frames;
+    for (int i = 0; same && i < n_frames; ++i) same = sl.src[i] == frames[i] && sl.n[i] == n[i] && sl.stamp[i] == stamp_us[i];
+    if (same) hit = &sl;
+  }
+  if (!hit) {
+    bool any = false;
+    for (auto& sl : staged) any = any || sl.valid;
+    if (any) Quiesce(true);
+  }
+  if (map_stats_pending && !map_pending) map_stats_pending = false;   // nobody asked for the previous frame's statistics
   const unsigned launches0 = lc.n;
   LSB_CUDA(cudaEventRecord(ev[0], stream));
   trace.mark("start", stream);
-  // host -> device copy of the input frames (skipped for device-resident input)
-  while (FramePool.size() < (size_t)n_frames) FramePool.emplace_back(new DFrame());
   NbCurrentFrames = (size_t)n_frames;
-  std::memset(&Stats, 0, sizeof(Stats));
-  for (int i = 0; i < n_frames; ++i) {
-    DFrame& f = *FramePool[i];
-    f.n = n[i]; f.stamp_us = stamp_us[i]; f.seq = seq ? seq[i] : 0u;
-    Stats.n_points += (uint32_t)n[i];
-    if (on_device) f.d = frames[i];
-    else {
-      f.own.buf.reserve(std::max<size_t>(n[i], 1), stream);
-      if (n[i]) LSB_CUDA(cudaMemcpyAsync(f.own.buf.p, frames[i], n[i] * sizeof(lsb_point), cudaMemcpyHostToDevice, stream));
-      f.d = f.own.buf.p;
-    }
-    f.device_id = 0;
-    if (n[i]) {
-      if (on_device && KeyPointsExtractors.size() == 1 && BaseToLidarOffsets.empty()) {
-        // one sensor, no calibration: the device id selects nothing (Slam.cxx:764-780), no read-back
-        f.device_id = KeyPointsExtractors.begin()->first;
-      } else if (on_device) {
-        lsb_point first;
-        LSB_CUDA(cudaMemcpyAsync(&first, frames[i], sizeof(lsb_point), cudaMemcpyDeviceToHost, stream));
-        LSB_CUDA(cudaStreamSynchronize(stream));
-        f.device_id = first.device_id;
-      } else f.device_id = frames[i][0].device_id;
-    }
+  {
+    const bool keep = map_stats_pending;      // the previous frame's map update may still be running: its statistics are gone with this memset
+    std::memset(&Stats, 0, sizeof(Stats));
+    (void)keep;
+  }
+  for (int i = 0; i < n_frames; ++i) Stats.n_points += (uint32_t)n[i];
+  if (hit) {
+    Worker().wait(hit->ticket);               // upload + extraction enqueued and their counts read back (rethrows)
+    FramePool.swap(hit->frames);
+    LSB_CUDA(cudaStreamWaitEvent(stream, hit->ready, 0));
+  } else {
+    UploadFrames(FramePool, n_frames, frames, n, stamp_us, seq, on_device, MakeStageCfg(), stream);
   }
   CurrentStamp = stamp_us[0];
   CurrentTime = StampToSec(CurrentStamp);
   for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
 
   trace.mark("h2d", stream);
-  ExtractKeypoints();
+  ExtractKeypoints(hit);
+  if (hit) hit->valid = false;
   trace.mark("extract", stream);
   LSB_CUDA(cudaEventRecord(ev[1], stream));
   ComputeEgoMotion();
@@ -281,10 +426,15 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   }
   uint32_t n_submap[3];
   for (int k = 0; k < 3; ++k) n_submap[k] = (uint32_t)LocalMaps[k].n_submap;   // sizes of the sub-maps this frame was matched against
-  if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
-  Join();
-  trace.mark("map_update", stream);
+  JoinMapUpdate();                                                             // (frames that skipped the localization)
+  // the frame's end event: with a deferred map update it stands where the pose is known and the update starts
   LSB_CUDA(cudaEventRecord(ev[4], stream));
+  if (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE) UpdateMapsUsingTworld();
+  if (!map_pending) {
+    Join();
+    LSB_CUDA(cudaEventRecord(ev[4], stream));
+  }
+  trace.mark("map_update", stream);
   LSB_CUDA(cudaEventSynchronize(ev[4]));
   if (lcp_pending) { OverlapEstimation = h_lcp.p[0]; lcp_pending = false; }
   trace.dump();
@@ -292,15 +442,18 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   for (int k = 0; k < 3; ++k) {
     Stats.n_keypoints[k] = (uint32_t)CurrentKeypoints[k].n;
     Stats.n_submap[k] = n_submap[k];
-    Stats.n_map[k] = LocalMaps[k].Size();
+    Stats.n_map[k] = LocalMaps[k].Size();          // deferred update: completed by FinishMapStats
     Stats.n_matches[k] = (uint32_t)LocDebug.hist[k][LSB_MATCH_SUCCESS];
     Stats.ego_n_matches[k] = (uint32_t)EgoDebug.hist[k][LSB_MATCH_SUCCESS];
   }
   cudaEventElapsedTime(&Stats.ms_extract, ev[0], ev[1]);
   cudaEventElapsedTime(&Stats.ms_ego, ev[1], ev[2]);
   cudaEventElapsedTime(&Stats.ms_localization, ev[2], ev[3]);
-  cudaEventElapsedTime(&Stats.ms_map_update, ev[3], ev[4]);
+  if (map_pending) { Stats.ms_map_update = 0.f; map_stats_pending = true; }
+  else cudaEventElapsedTime(&Stats.ms_map_update, ev[3], ev[4]);
   cudaEventElapsedTime(&Stats.ms_total, ev[0], ev[4]);
+  Stats.map_update_deferred = map_pending ? 1u : 0u;
+  Stats.prefetched = hit ? 1u : 0u;
   Stats.kernel_launches = lc.n - launches0;
   if (trace.on && mw.t_knn.enabled) {      // LSB_TRACE=1 with lsb_set_profiling(1): the individual brackets, in enqueue order
     std::vector<float> a, b, c;
@@ -347,40 +500,76 @@ bool lsb_slam::CheckFrames(int n_frames, const size_t* n, const uint64_t* stamp_
 }
 
 //-----------------------------------------------------------------------------
-void lsb_slam::ExtractKeypoints()
+void lsb_slam::ExtractKeypoints(StagedInput* hit)
 {
   for (int k = 0; k < 3; ++k) { PreviousKeypoints[k].swap(CurrentKeypoints[k]); CurrentKeypoints[k].n = 0; }   // :751
-  KpTimeMin = std::numeric_limits<double>::max();
-  KpTimeMax = std::numeric_limits<double>::lowest();
+  if (hit) {
+    // extracted ahead of time on the ingest stream: the staged clouds become the current ones, the extractor instances that
+    // ran for them become the handle's (GetDebugArray reads the frame they hold)
+    for (int k = 0; k < 3; ++k) CurrentKeypoints[k].swap(hit->kp[k]);
+    KpTimeMin = hit->tmin; KpTimeMax = hit->tmax;
+    std::lock_guard<std::mutex> g(ke_mu);
+    for (int dev : hit->used_ids) {
+      auto& mine = KeyPointsExtractors[dev];
+      auto& theirs = hit->extractors[dev];
+      if (!mine || !theirs) continue;
+      theirs->adopt_scalars(*mine);
+      mine.swap(theirs);
+    }
+    return;
+  }
+  ExtractInto(FramePool, NbCurrentFrames, CurrentStamp, MakeStageCfg(), nullptr, CurrentKeypoints, KpTimeMin, KpTimeMax, stream);
+}
+
+void lsb_slam::ExtractInto(FrameList& pool, size_t nb, uint64_t stamp0, const StageCfg& cfg, StagedInput* slot, DCloud out[3], double& tmin, double& tmax,
+                           cudaStream_t s)
+{
+  for (int k = 0; k < 3; ++k) out[k].n = 0;
+  tmin = std::numeric_limits<double>::max();
+  tmax = std::numeric_limits<double>::lowest();
+  if (slot) slot->used_ids.clear();
   // With several input frames the extractor buffers are reused, so keypoints are
   // appended to the aggregate right after each extraction.
-  for (size_t fi = 0; fi < NbCurrentFrames; ++fi) {
-    DFrame& f = *FramePool[fi];
+  for (size_t fi = 0; fi < nb; ++fi) {
+    DFrame& f = *pool[fi];
     if (f.n == 0) continue;
     int dev = f.device_id;
-    if (!KeyPointsExtractors.count(dev) || !KeyPointsExtractors[dev]) {   // :764-780
-      if (KeyPointsExtractors.size() == 1) dev = KeyPointsExtractors.begin()->first;
+    if (std::find(cfg.ke_ids.begin(), cfg.ke_ids.end(), dev) == cfg.ke_ids.end()) {   // :764-780
+      if (cfg.ke_ids.size() == 1) dev = cfg.ke_ids[0];
       else continue;
     }
-    ExtractorGpu& ke = *KeyPointsExtractors[dev];
-    ke.compute(f.d, f.n, stream, lc);
+    ExtractorGpu* kep = nullptr;
+    if (slot) {
+      // a staging slot runs its own extractor instance (the handle's holds the frame in flight) on the handle's current
+      // parameters and azimuth estimate, and hands the estimate on
+      auto& se = slot->extractors[dev];
+      if (!se) se.reset(new ExtractorGpu());
+      std::lock_guard<std::mutex> g(ke_mu);
+      se->adopt_scalars(*KeyPointsExtractors[dev]);
+      kep = se.get();
+      if (std::find(slot->used_ids.begin(), slot->used_ids.end(), dev) == slot->used_ids.end()) slot->used_ids.push_back(dev);
+    } else kep = KeyPointsExtractors[dev].get();
+    ExtractorGpu& ke = *kep;
+    ke.compute(f.d, f.n, s, lc);
+    if (slot) { std::lock_guard<std::mutex> g(ke_mu); KeyPointsExtractors[dev]->adopt_scalars(ke); }
     // AggregateFrames(keypoints[k], false)  (:1512-1578)
     for (int k = 0; k < 3; ++k) {
-      if (!P.use_keypoints[k] || ke.counts[k] == 0) continue;
-      DCloud& agg = CurrentKeypoints[k];
+      if (!cfg.use[k] || ke.counts[k] == 0) continue;
+      DCloud& agg = out[k];
       const size_t start = agg.n, cnt = ke.counts[k];
-      agg.buf.reserve(start + cnt, stream, true, start);
-      LSB_CUDA(cudaMemcpyAsync(agg.buf.p + start, ke.kp[k].p, cnt * sizeof(lsb_point), cudaMemcpyDeviceToDevice, stream));
+      agg.buf.reserve(start + cnt, s, true, start);
+      LSB_CUDA(cudaMemcpyAsync(agg.buf.p + start, ke.kp[k].p, cnt * sizeof(lsb_point), cudaMemcpyDeviceToDevice, s));
       agg.n = start + cnt;
-      const double timeOffset = StampToSec(f.stamp_us) - StampToSec(CurrentStamp);
-      const Iso3d tf = GetBaseToLidarOffset(f.device_id);
+      const double timeOffset = StampToSec(f.stamp_us) - StampToSec(stamp0);
+      auto it = cfg.offsets.find(f.device_id);
+      const Iso3d tf = it != cfg.offsets.end() ? it->second : Iso3d::identity();
       const bool ident = iso_is_approx(tf, Iso3d::identity());
-      if (!ident || timeOffset != 0.0) dev_aggregate(agg.buf.p + start, cnt, timeOffset, tf, !ident, stream, lc);
+      if (!ident || timeOffset != 0.0) dev_aggregate(agg.buf.p + start, cnt, timeOffset, tf, !ident, s, lc);
       // time range of the aggregate: t -> t + offset is monotone, so min / max commute with it
       const double lo = (timeOffset != 0.0) ? ke.time_min[k] + timeOffset : ke.time_min[k];
       const double hi = (timeOffset != 0.0) ? ke.time_max[k] + timeOffset : ke.time_max[k];
-      KpTimeMin = std::min(KpTimeMin, lo);
-      KpTimeMax = std::max(KpTimeMax, hi);
+      tmin = std::min(tmin, lo);
+      tmax = std::max(tmax, hi);
     }
   }
 }
@@ -432,6 +621,8 @@ void lsb_slam::SaveDebug(StageDebug& d)
 
 void lsb_slam::ComputeEgoMotion()
 {
+  // the frame-to-frame registration uses the type streams: the previous frame's deferred map update is joined first
+  if (P.ego_motion == LSB_EGO_REGISTRATION || P.ego_motion == LSB_EGO_MOTION_EXTRAPOLATION_AND_REGISTRATION) JoinMapUpdate();
   Trelative = Iso3d::identity();
   std::memset(EgoDebug.hist, 0, sizeof(EgoDebug.hist));
   for (auto& o : EgoDebug.off) o = 0;
@@ -484,7 +675,7 @@ void lsb_slam::Localization()
 
   // Submaps (:1003-1037): the three maps work on their own streams and host lanes; each lane waits
   // for its own read-backs (bbox of the keypoints, size of the submap)
-  ForEachType([&](int k) {
+  ForEachType([&](int k) {                     // (behind the previous frame's map update if that was deferred)
     RollingGridGpu& map = LocalMaps[k];
     cudaStream_t ts = TypeStream(k);
     if (HasPendingRefinement) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, PendingRefinement, 0.0, ts, lc);
@@ -609,6 +800,37 @@ void lsb_slam::UpdateMapsUsingTworld()
   Stats.is_keyframe = 1;
   KfCounter++;
   KfLastPose = Tworld;
+  const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
+  if (defer_map_update && use_lanes && !serial_types && !crowded) {
+    // Deferred: the transform + bounding box of the three clouds is enqueued here (it reads this frame's keypoint buffers,
+    // which the next frame's extraction recycles), the two read-back rounds of RollingGrid::Add are driven by the types' helper
+    // threads on the type streams while the caller returns with the pose.  The next frame's sub-map selection is posted to the
+    // same threads and streams, so it is ordered behind the update on the host and on the device.
+    Fork();
+    struct Job { const lsb_point* p; size_t n; bool use; } job[3];
+    for (int k : kTypeOrder) {
+      job[k].use = P.use_keypoints[k] != 0;
+      job[k].p = nullptr; job[k].n = 0;
+      if (!job[k].use) continue;
+      bool boxed = false;
+      const DCloud& w = WorldKeypoints(k, tstream[k], &LocalMaps[k], &boxed);
+      if (!boxed) LocalMaps[k].AddBegin(w.buf.p, w.n, true, tstream[k], lc);
+      job[k].p = w.buf.p; job[k].n = w.n;
+    }
+    const double now = CurrentTime;
+    for (int k : kTypeOrder) {
+      map_posted[k] = map_stats_type[k] = job[k].use;
+      if (!job[k].use) continue;
+      const Job jb = job[k];
+      map_ticket[k] = TypeWorker(k).post([this, jb, now, k] {
+        LocalMaps[k].AddSort(jb.p, jb.n, false, now, true, tstream[k], lc);
+        LocalMaps[k].AddMerge(jb.n, tstream[k], lc);
+        LSB_CUDA(cudaEventRecord(ev_map_end[k], tstream[k]));
+      });
+    }
+    map_pending = true;
+    return;
+  }
   // RollingGrid::Add of the three types, each on its stream and host lane
   ForEachType([&](int k) {
     if (!P.use_keypoints[k]) return;

@@ -17,7 +17,8 @@
 #include "../common/lm_covariance.h"
 #include "../common/motion_limits.h"
 #include "../common/sensor_constraints.h"
-#include "lanes.h"
+#include "worker.h"
+#include <mutex>
 
 struct DCloud {
   lsb::DevBuf<lsb_point> buf;
@@ -36,8 +37,12 @@ struct lsb_slam {
   cudaStream_t TypeStream(int k) const { return serial_types ? stream : tstream[k]; }
   void Fork();                     // type streams wait for `stream`
   void Join();                     // `stream` waits for the type streams
-  // Fork, fn(k) for the three types (each on its own host lane unless serial_types / LSB_HOST_LANES=0), Join
-  std::unique_ptr<lsb::TypeLanes> lanes;
+  // Fork, fn(k) for the three types, Join.  Each type has its own helper thread (host/worker.h) that enqueues the type's launch
+  // sequences and waits for its small read-backs, so that the three sequences do not queue behind one another on one host
+  // thread; the same thread runs the type's deferred map update, so a type's jobs stay in order without a join in between.
+  // serial_types / LSB_HOST_LANES=0 / many handles sharing the host cores: everything on the caller's thread.
+  std::unique_ptr<lsb::AsyncWorker> tworker[3];
+  lsb::AsyncWorker& TypeWorker(int k) { if (!tworker[k]) tworker[k].reset(new lsb::AsyncWorker(device)); return *tworker[k]; }
   bool use_lanes = true;
   void ForEachType(const std::function<void(int)>& fn);
   lsb::LaunchCounter lc;
@@ -67,8 +72,61 @@ struct lsb_slam {
 
   // device copies of the input frames (the reference retains the input clouds, Slam.cxx:237)
   struct DFrame { DCloud own; const lsb_point* d = nullptr; size_t n = 0; uint64_t stamp_us = 0; uint32_t seq = 0; int device_id = 0; };
-  std::vector<std::unique_ptr<DFrame>> FramePool;
+  typedef std::vector<std::unique_ptr<DFrame>> FrameList;
+  FrameList FramePool;
   size_t NbCurrentFrames = 0;
+
+  // ---- work the caller does not wait for (host/worker.h) --------------------------------------------------------------
+  // (1) Deferred map update: AddFrames returns once the pose is known; RollingGrid::Add of the three maps (two read-back
+  //     rounds each) is driven by the helper thread on the type streams and joined before the next frame's sub-maps are
+  //     selected, or by whatever entry point looks at the maps first.
+  // (2) Prefetch (lsb_prefetch_frames): upload + keypoint extraction of a frame handed in ahead of time run on the ingest
+  //     stream while the current frame is in its ICP loop (which leaves most SMs idle); AddFrames of that frame finds its
+  //     keypoints ready.  Two slots, so that frame t + 2 can be staged before frame t + 1 is consumed.
+  std::unique_ptr<lsb::AsyncWorker> worker;
+  lsb::AsyncWorker& Worker() { if (!worker) worker.reset(new lsb::AsyncWorker(device)); return *worker; }
+  bool defer_map_update = true;          // LSB_DEFER_MAP=0 / lsb_set_pipelining(h, 0): the map update ends inside AddFrames
+  bool map_pending = false;
+  unsigned map_ticket[3] = {0, 0, 0};
+  bool map_posted[3] = {false, false, false};
+  cudaEvent_t ev_map_end[3] = {nullptr, nullptr, nullptr};
+  bool map_stats_pending = false;        // ms_map_update / n_map of the last frame still to be filled in
+  bool map_stats_type[3] = {false, false, false};
+  void JoinMapUpdate();                  // host side of the deferred update over, `stream` ordered behind the type streams
+  void FinishMapStats();                 // waits for the deferred kernels and completes Stats (lsb_get_frame_stats)
+  void Quiesce(bool drop_staged);        // every helper job over (entry points other than AddFrames / prefetch / pose getters)
+  void SynchronizeAll();                 // Quiesce + every stream idle
+
+  struct StageCfg {                      // what the extraction reads from the handle, captured when the job is posted
+    std::vector<int> ke_ids;
+    std::map<int, lsb::Iso3d> offsets;
+    bool use[3] = {true, true, true};
+  };
+  struct StagedInput {
+    bool valid = false, on_device = false;
+    unsigned ticket = 0;
+    std::vector<const lsb_point*> src;
+    std::vector<size_t> n;
+    std::vector<uint64_t> stamp;
+    std::vector<uint32_t> seq;
+    FrameList frames;
+    DCloud kp[3];
+    double tmin = 0., tmax = 0.;
+    std::map<int, std::unique_ptr<lsb::ExtractorGpu>> extractors;
+    std::vector<int> used_ids;           // extractors that ran for this input
+    cudaEvent_t ready = nullptr;         // recorded on the ingest stream behind the last kernel of the job
+  } staged[2];
+  cudaStream_t istream = nullptr;        // ingest stream (lowest priority: the ICP of the current frame goes first)
+  std::mutex ke_mu;                      // extractor instances / their scalar state (parameters, azimuth estimate) change hands
+  int PrefetchFrames(int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq, bool on_device);
+  StageCfg MakeStageCfg() const;
+  void UploadFrames(FrameList& pool, int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq,
+                    bool on_device, const StageCfg& cfg, cudaStream_t s);
+  // SpinningSensorKeypointExtractor per frame + AggregateFrames(keypoints, false) into out[3]; exts == nullptr: the handle's own extractors
+  void ExtractInto(FrameList& pool, size_t nb, uint64_t stamp0, const StageCfg& cfg, StagedInput* slot, DCloud out[3], double& tmin, double& tmax,
+                   cudaStream_t s);
+  // whole-loop timing (lsb_timer_begin / lsb_timer_end)
+  cudaEvent_t ev_timer[2] = {nullptr, nullptr};
 
   lsb::MatchWorkspace mw;
   lsb::DevBuf<lsb::IcpState> d_icp;   // state of the device-resident ICP loop (cuda/icp.cuh)
@@ -125,7 +183,7 @@ struct lsb_slam {
 
  private:
   bool CheckFrames(int n_frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq);   // Slam.cxx:709-743
-  void ExtractKeypoints();                               // :746-810
+  void ExtractKeypoints(StagedInput* hit);               // :746-810
   void ComputeEgoMotion();                               // :813-972
   void ComputeSensorConstraints();                       // :346-352
   void Localization();                                   // :975-1175

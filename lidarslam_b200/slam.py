@@ -37,6 +37,36 @@ class Slam(capi.CApi):
         sq = (C.c_uint32 * n)(*[int(s) for s in (seqs or [0] * n)])
         return self._check(self.lib.lsb_add_frames_dev(self.h, C.c_int(n), ptrs, sz, stamps, sq))
 
+    # ---- pipelining (include/lidarslam_b200.h: no counterpart in the reference) --------
+    def _frame_args(self, ptrs, sizes, stamps_us, seqs):
+        n = len(ptrs)
+        return (C.c_int(n), (C.c_void_p * n)(*ptrs), (C.c_size_t * n)(*[int(s) for s in sizes]),
+                (C.c_uint64 * n)(*[int(s) for s in stamps_us]), (C.c_uint32 * n)(*[int(s) for s in (seqs or [0] * n)]))
+
+    def PrefetchFramesDev(self, dev_ptrs, sizes, stamps_us, seqs=None):
+        return self._check(self.lib.lsb_prefetch_frames_dev(self.h, *self._frame_args(dev_ptrs, sizes, stamps_us, seqs)))
+
+    def PrefetchFrames(self, frames, stamps_us, seqs=None):
+        """frames: numpy point arrays that stay alive and unchanged until the matching AddFrames returns"""
+        frames = [capi.as_points(f) for f in frames]
+        self._staged_keep = getattr(self, "_staged_keep", []) + [frames]
+        self._staged_keep = self._staged_keep[-3:]
+        return self._check(self.lib.lsb_prefetch_frames(self.h, *self._frame_args([f.ctypes.data for f in frames], [len(f) for f in frames], stamps_us, seqs)))
+
+    def SetPipelining(self, defer_map_update):
+        self._check(self.lib.lsb_set_pipelining(self.h, C.c_int(1 if defer_map_update else 0)))
+
+    def Synchronize(self):
+        self._check(self.lib.lsb_synchronize(self.h))
+
+    def TimerBegin(self):
+        self._check(self.lib.lsb_timer_begin(self.h))
+
+    def TimerEnd(self):
+        ms = C.c_float()
+        self._check(self.lib.lsb_timer_end(self.h, C.byref(ms)))
+        return ms.value
+
     def FlushL2(self):
         self._check(self.lib.lsb_dev_flush_l2(self.h))
 
