@@ -43,6 +43,8 @@ struct RollingGridGpu {
   PinnedBuf<uint32_t> h_info;
   PinnedBuf<float> h_bbox;
   DevBuf<float> d_bbox;
+  DevBuf<int> box_partial;               // per-block partial boxes + ticket of the fused box kernels (slam_kernels.cu)
+  DevBuf<unsigned> box_counter;
 
   void Reset(const float position[3], cudaStream_t s);                     // :40-48
   void Clear();                                                            // :51-56

@@ -249,8 +249,8 @@ int lsb_get_latency_compensated_world_transform(const lsb_slam* h, double T[16],
   return LSB_OK;
 }
 int lsb_get_relative_transform(const lsb_slam* h, double T[16]) { ToRowMajor(h->Trelative, T); return LSB_OK; }
-int lsb_get_covariance(const lsb_slam* h, double c[36]) { std::memcpy(c, h->LocalizationUncertainty.covariance, 36 * sizeof(double)); return LSB_OK; }
-int lsb_get_registration_error(const lsb_slam* h, lsb_registration_error* e) { *e = h->LocalizationUncertainty; return LSB_OK; }
+int lsb_get_covariance(const lsb_slam* h, double c[36]) { std::memcpy(c, h->Uncertainty().covariance, 36 * sizeof(double)); return LSB_OK; }
+int lsb_get_registration_error(const lsb_slam* h, lsb_registration_error* e) { *e = h->Uncertainty(); return LSB_OK; }
 long lsb_get_trajectory(const lsb_slam* h, double* Ts, double* times, long cap)
 {
   const long n = (long)h->LogTrajectory.size();

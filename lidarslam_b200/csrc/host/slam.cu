@@ -211,6 +211,7 @@ void lsb_slam::Reset(bool resetLog)
   Tworld = PreviousTworld = Trelative = Iso3d::identity();
   WithinFrameMotion.reset();
   std::memset(&LocalizationUncertainty, 0, sizeof(LocalizationUncertainty));
+  UncertaintyPending = false;
   NbCurrentFrames = 0;
   CurrentStamp = 0;
   for (int k = 0; k < 3; ++k) {
@@ -678,13 +679,18 @@ void lsb_slam::Localization()
   ForEachType([&](int k) {                     // (behind the previous frame's map update if that was deferred)
     RollingGridGpu& map = LocalMaps[k];
     cudaStream_t ts = TypeStream(k);
-    if (HasPendingRefinement) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, PendingRefinement, 0.0, ts, lc);
+    const bool select = P.use_keypoints[k] && !map.IsSubMapKdTreeValid() && P.map_update != LSB_MAP_NONE && CurrentKeypoints[k].n;
+    if (HasPendingRefinement && !select) dev_undistort(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, PendingRefinement, 0.0, ts, lc);
     if (!P.use_keypoints[k] || map.IsSubMapKdTreeValid()) return;
     if (P.map_update == LSB_MAP_NONE) { map.BuildSubMapKdTree(ts, lc); return; }
+    if (CurrentKeypoints[k].n) {
+      // pending undistortion and the box of the cloud under the predicted pose in one launch (before ClearOldPoints, which does
+      // not read the keypoints); the box stays on the device for the selection, box and sub-map size come back with one synchronisation
+      dev_undistort_transformed_bbox(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, HasPendingRefinement ? &PendingRefinement : nullptr, Tworld,
+                                     map.box_partial, map.box_counter, map.d_bbox, map.h_bbox, ts, lc);
+    }
     if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, ts, lc);
     if (CurrentKeypoints[k].n) {
-      // the box stays on the device for the selection; box and sub-map size come back with one synchronisation
-      dev_transformed_bbox_async(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, Tworld, map.d_bbox, map.h_bbox, ts, lc);
       map.SubMapSelectDevice((int)(CurrentKeypoints[k].n / 2), ts, lc);
     } else {
       const float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
@@ -715,8 +721,13 @@ void lsb_slam::Localization()
   Tworld = st.Tworld;
   Trelative = st.Trelative;
   WithinFrameMotion = st.Within;
-  for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = false;
-  if (st.lm_valid) registration_error_from_normal_matrix(blk.state.H, P.two_d_mode != 0, &LocalizationUncertainty);   // :1151-1155
+  for (int k = 0; k < 3; ++k) WorldKeypointsValid[k] = WorldBoxReady[k] = finish_enqueued && CurrentKeypoints[k].n > 0;
+  finish_enqueued = false;
+  if (st.lm_valid) {                                                            // :1151-1155, evaluated on demand (Uncertainty())
+    std::memcpy(UncertaintyH, blk.state.H, sizeof(UncertaintyH));
+    UncertaintyTwoD = P.two_d_mode != 0;
+    UncertaintyPending = true;
+  }
 }
 
 //-----------------------------------------------------------------------------
@@ -771,8 +782,24 @@ const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_mat
     mw.enqueue_solve(nullptr, (int)lm_max_iter, P.two_d_mode != 0, mp.saturation_distance, P.min_nb_matched_keypoints, stream, lc, terms,
                      d_icp.p, &ctl);
   }
-  // the refinement of the iteration that ended the loop is applied at once (RefineUndistortion of the last iteration, :1146-1147)
-  if (refined) for (int k = 0; k < 3; ++k) dev_undistort_state(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_icp.p, 1, stream, lc);
+  // the refinement of the iteration that ended the loop is applied at once (RefineUndistortion of the last iteration, :1146-1147);
+  // when a map update may follow, the same launch leaves the world clouds and their boxes (input of RollingGrid::Add) behind
+  finish_enqueued = false;
+  if (loc && (P.map_update == LSB_MAP_ADD_KPTS_TO_FIXED_MAP || P.map_update == LSB_MAP_UPDATE)) {
+    FinishArgs fa;
+    for (int k = 0; k < 3; ++k) {
+      DCloud& w = CurrentWorldKeypoints[k];
+      w.buf.reserve(std::max<size_t>(nk[k], 1), stream);
+      w.n = nk[k];
+      LocalMaps[k].d_bbox.reserve(8, stream); LocalMaps[k].h_bbox.reserve(8);
+      fa.cur[k] = CurrentKeypoints[k].buf.p; fa.world[k] = w.buf.p; fa.n[k] = (int)nk[k];
+      fa.d_bb[k] = reinterpret_cast<int*>(LocalMaps[k].d_bbox.p); fa.h_bb[k] = reinterpret_cast<int*>(LocalMaps[k].h_bbox.p);
+    }
+    dev_finish_keypoints(fa, d_icp.p, refined, finish_partial, finish_counter, stream, lc);
+    finish_enqueued = true;
+  } else if (refined) {
+    for (int k = 0; k < 3; ++k) dev_undistort_state(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, d_icp.p, 1, stream, lc);
+  }
   return mw.wait_result(stream);
 }
 
@@ -849,6 +876,7 @@ const DCloud& lsb_slam::WorldKeypoints(int k, cudaStream_t s, RollingGridGpu* bo
   cudaStream_t stream = s ? s : this->stream;
   DCloud& w = CurrentWorldKeypoints[k];
   if (boxed) *boxed = false;
+  if (WorldKeypointsValid[k] && WorldBoxReady[k] && box && boxed) { *boxed = true; WorldBoxReady[k] = false; }   // left by the loop's tail
   if (!WorldKeypointsValid[k]) {
     const DCloud& c = CurrentKeypoints[k];
     w.buf.reserve(std::max<size_t>(c.n, 1), stream);

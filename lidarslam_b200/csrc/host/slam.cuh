@@ -68,6 +68,10 @@ struct lsb_slam {
   // reference (Slam.cxx:984): one device storage.
   DCloud CurrentKeypoints[3], PreviousKeypoints[3], CurrentWorldKeypoints[3];
   bool WorldKeypointsValid[3] = {false, false, false};
+  bool WorldBoxReady[3] = {false, false, false};     // LocalMaps[k].h_bbox holds the box of CurrentWorldKeypoints[k] (k_finish_keypoints)
+  bool finish_enqueued = false;                      // the loop's tail produced the world clouds of this frame
+  lsb::DevBuf<int> finish_partial;
+  lsb::DevBuf<unsigned> finish_counter;
   double KpTimeMin = 0., KpTimeMax = 0.;   // `time` range of CurrentKeypoints (read back with the keypoint counts)
 
   // device copies of the input frames (the reference retains the input clouds, Slam.cxx:237)
@@ -137,7 +141,17 @@ struct lsb_slam {
   // match results kept for GetDebugArray (Slam.cxx:635-657)
   struct StageDebug { lsb::DevBuf<uint8_t> status; lsb::DevBuf<double> weight; size_t off[4] = {0, 0, 0, 0}; int hist[3][LSB_MATCH_N_STATUS] = {}; };
   StageDebug EgoDebug, LocDebug;
-  lsb_registration_error LocalizationUncertainty;
+  // LocalOptimizer::EstimateRegistrationError (LocalOptimizer.cxx:112-140) is evaluated when somebody asks for it: the normal
+  // matrix of the last solve is kept, the 6x6 eigen-decompositions stay off the frame's critical path
+  mutable lsb_registration_error LocalizationUncertainty;
+  mutable bool UncertaintyPending = false;
+  double UncertaintyH[21];
+  bool UncertaintyTwoD = false;
+  const lsb_registration_error& Uncertainty() const
+  {
+    if (UncertaintyPending) { lsb::registration_error_from_normal_matrix(UncertaintyH, UncertaintyTwoD, &LocalizationUncertainty); UncertaintyPending = false; }
+    return LocalizationUncertainty;
+  }
   unsigned TotalMatchedKeypoints = 0;
   float OverlapEstimation = -1.f;
   lsb::MotionLimitsState MotionLimits;                                     // Slam.h:660-663
@@ -204,6 +218,21 @@ struct lsb_slam {
 };
 
 namespace lsb {
+// tail of the localization loop for the three keypoint clouds (slam_kernels.cu: k_finish_keypoints)
+struct FinishArgs {
+  lsb_point* cur[3];
+  lsb_point* world[3];
+  int n[3];
+  int b0[4];            // first block of each type (filled by dev_finish_keypoints)
+  int* d_bb[3];         // box of the world cloud, ordered-int encoding: device copy and pinned host copy (RollingGridGpu::d_bbox / h_bbox)
+  int* h_bb[3];
+};
+void dev_finish_keypoints(FinishArgs a, const IcpState* st, bool refine, DevBuf<int>& partial, DevBuf<unsigned>& counter, cudaStream_t s,
+                          LaunchCounter& lc);
+// head of a type's sub-map selection: pending undistortion (nullptr: none) + box of the cloud under T, box published in d_bbox and
+// in h_bbox (pinned, readable after the stream's next synchronisation); one launch
+void dev_undistort_transformed_bbox(lsb_point* d_pts, size_t n, const Interpolator* pending, const Iso3d& T, DevBuf<int>& partial,
+                                    DevBuf<unsigned>& counter, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc);
 // device helpers implemented in slam_kernels.cu
 void dev_transform(lsb_point* d_pts, size_t n, const Iso3d& T, cudaStream_t s, LaunchCounter& lc);                     // Utils::TransformPoint
 // dev_transform + the bounding box of the result (ordered-int encoding in d_bbox, copy to h_bbox enqueued): no second pass
