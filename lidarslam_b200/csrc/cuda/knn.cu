@@ -80,13 +80,17 @@ __global__ void k_cell_count(const lsb_point* __restrict__ pts, int m, KnnGridPa
   rank[i] = atomicAdd(count + k, 1u);
 }
 
+// The histogram is left all zero again (its scan has been taken): the next build starts from a clean table without a
+// memset of the whole grid (10 MB for the 2.5 M cells of a blob sub-map) on the frame's critical chain.
 __global__ void k_cell_scatter(const lsb_point* __restrict__ pts, int m, const uint32_t* __restrict__ key, const uint32_t* __restrict__ rank,
-                               const uint32_t* __restrict__ cell_start, float4* __restrict__ sorted)
+                               const uint32_t* __restrict__ cell_start, float4* __restrict__ sorted, uint32_t* __restrict__ count)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)i];
-  sorted[__ldg(cell_start + key[i]) + rank[i]] = make_float4(p.x, p.y, p.z, __int_as_float(i));
+  const uint32_t k = key[i];
+  sorted[__ldg(cell_start + k) + rank[i]] = make_float4(p.x, p.y, p.z, __int_as_float(i));
+  count[k] = 0u;
 }
 
 // ------------------------------------------------------------------ search ---
@@ -896,16 +900,19 @@ void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float
   const int ncells = gp.nx * gp.ny * gp.nz;
   key_a.reserve(m, s); idx_a.reserve(m, s);
   const int nc1 = ncells + 1;
-  sorted.reserve(m, s); cell_start.reserve((size_t)nc1, s); cell_count.reserve((size_t)nc1, s);
+  sorted.reserve(m, s); cell_start.reserve((size_t)nc1, s);
+  if ((size_t)nc1 > cell_count.cap) {      // invariant: the whole table is zero between builds (k_cell_scatter cleans up behind itself)
+    cell_count.reserve((size_t)nc1, s);
+    LSB_CUDA(cudaMemsetAsync(cell_count.p, 0, cell_count.cap * sizeof(uint32_t), s));
+  }
   const unsigned G = div_up(m, TPB);
-  LSB_CUDA(cudaMemsetAsync(cell_count.p, 0, (size_t)nc1 * sizeof(uint32_t), s));
   k_cell_count<<<G, TPB, 0, s>>>(d_cloud, M, gp, key_a.p, idx_a.p, cell_count.p); LSB_LAUNCH_CHECK(); lc.add();
   size_t tb = 0;
   cub::DeviceScan::ExclusiveSum(nullptr, tb, cell_count.p, cell_start.p, nc1, s);
   cub_tmp.reserve(tb + 256, s);
   tb = cub_tmp.cap;
   LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, cell_count.p, cell_start.p, nc1, s)); lc.add(2);   // cell_start[ncells] = m
-  k_cell_scatter<<<G, TPB, 0, s>>>(d_cloud, M, key_a.p, idx_a.p, cell_start.p, sorted.p); LSB_LAUNCH_CHECK(); lc.add();
+  k_cell_scatter<<<G, TPB, 0, s>>>(d_cloud, M, key_a.p, idx_a.p, cell_start.p, sorted.p, cell_count.p); LSB_LAUNCH_CHECK(); lc.add();
 }
 
 void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t* d_idx, float* d_d2, int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc) const

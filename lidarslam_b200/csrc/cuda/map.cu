@@ -4,6 +4,7 @@
 // rule over its (short, arrival-ordered) segment -> binary-search join with the
 // sorted map: existing leaves are updated in place, new leaves are merged by rank.
 #include "map.cuh"
+#include "select.cuh"
 #include "../common/linalg.h"
 #include <cub/cub.cuh>
 #include <climits>
@@ -365,6 +366,87 @@ __global__ void k_flag_entries(const unsigned long long* __restrict__ keys, cons
   flags[i] = f ? 1u : 0u;
 }
 
+// voxel / frame-count test of k_flag_entries for one entry (same modes)
+__device__ __forceinline__ bool entry_selected(const unsigned long long* __restrict__ keys, const lsb_point* __restrict__ pts,
+                                               const uint32_t* __restrict__ counts, int i, int G, int lx, int ly, int lz, int hx, int hy, int hz,
+                                               int mode, unsigned minFrames)
+{
+  bool f = true;
+  if (mode <= 2) {
+    int x, y, z;
+    to3d((int)(keys[i] >> 32), G, x, y, z);
+    f = lx <= x && x <= hx && ly <= y && y <= hy && lz <= z && z <= hz;
+  }
+  if (f && mode != 0 && mode != 3) {
+    const unsigned c = counts[i];
+    if (mode == 4) f = c > minFrames;
+    else {
+      const unsigned label = reinterpret_cast<const uint4*>(pts)[2 * (size_t)i + 1].w >> 24;
+      const bool keep = c >= minFrames || label == 1;
+      f = (mode == 1) ? keep : !keep;
+    }
+  }
+  return f;
+}
+
+// Sub-map selection in ONE launch: k_flag_entries + exclusive scan + k_compact (points only) by decoupled look-back
+// (select.cuh).  A tile is SEL_ITEMS consecutive entries per thread, so the output keeps the map's order.
+constexpr int SEL_ITEMS = 4;
+__global__ void __launch_bounds__(TPB) k_select_entries(const unsigned long long* __restrict__ keys, const lsb_point* __restrict__ pts,
+                                                        const uint32_t* __restrict__ counts, int n, int G, int lx, int ly, int lz, int hx, int hy,
+                                                        int hz, int mode, unsigned minFrames, const int* __restrict__ bb, GridGeom g,
+                                                        lsb_point* __restrict__ out, unsigned long long* __restrict__ desc,
+                                                        unsigned* __restrict__ ticket, unsigned epoch, unsigned ntiles, uint32_t* __restrict__ info)
+{
+  if (bb) {
+    lx = max(pos2vox(ord2f_dev(bb[0]), g.ox, g.res), 0); hx = min(pos2vox(ord2f_dev(bb[3]), g.ox, g.res), G - 1);
+    ly = max(pos2vox(ord2f_dev(bb[1]), g.oy, g.res), 0); hy = min(pos2vox(ord2f_dev(bb[4]), g.oy, g.res), G - 1);
+    lz = max(pos2vox(ord2f_dev(bb[2]), g.oz, g.res), 0); hz = min(pos2vox(ord2f_dev(bb[5]), g.oz, g.res), G - 1);
+  }
+  unsigned tile = sel::take_ticket(ticket);
+  const int base = (int)tile * (TPB * SEL_ITEMS) + (int)threadIdx.x * SEL_ITEMS;
+  bool f[SEL_ITEMS];
+  unsigned cnt = 0;
+#pragma unroll
+  for (int q = 0; q < SEL_ITEMS; ++q) {
+    const int i = base + q;
+    f[q] = i < n && entry_selected(keys, pts, counts, i, G, lx, ly, lz, hx, hy, hz, mode, minFrames);
+    cnt += f[q] ? 1u : 0u;
+  }
+  unsigned o = sel::tile_offset<TPB>(cnt, desc, ticket, epoch, ntiles, tile, info + 2);
+#pragma unroll
+  for (int q = 0; q < SEL_ITEMS; ++q)
+    if (f[q]) { store_raw(out + o, load_raw(pts + base + q)); ++o; }
+}
+
+// k_gather_inserts with its scan, one launch: flagged segment heads -> the (sorted) insert list; info[1] = their number
+__global__ void __launch_bounds__(TPB) k_select_inserts(const uint32_t* __restrict__ flags, int n, const unsigned long long* __restrict__ skey,
+                                                        const lsb_point* __restrict__ seg_pts, const uint32_t* __restrict__ seg_counts,
+                                                        unsigned long long* __restrict__ ins_keys, lsb_point* __restrict__ ins_pts,
+                                                        uint32_t* __restrict__ ins_counts, unsigned long long* __restrict__ desc,
+                                                        unsigned* __restrict__ ticket, unsigned epoch, unsigned ntiles, uint32_t* __restrict__ info)
+{
+  unsigned tile = sel::take_ticket(ticket);
+  const int base = (int)tile * (TPB * SEL_ITEMS) + (int)threadIdx.x * SEL_ITEMS;
+  bool f[SEL_ITEMS];
+  unsigned cnt = 0;
+#pragma unroll
+  for (int q = 0; q < SEL_ITEMS; ++q) {
+    f[q] = base + q < n && flags[base + q] != 0u;
+    cnt += f[q] ? 1u : 0u;
+  }
+  unsigned o = sel::tile_offset<TPB>(cnt, desc, ticket, epoch, ntiles, tile, info + 1);
+#pragma unroll
+  for (int q = 0; q < SEL_ITEMS; ++q) {
+    if (!f[q]) continue;
+    const int i = base + q;
+    ins_keys[o] = skey[i];
+    store_raw(ins_pts + o, load_raw(seg_pts + i));
+    ins_counts[o] = seg_counts[i];
+    ++o;
+  }
+}
+
 // ClearOldPoints (:325-350)
 __global__ void k_flag_old(const lsb_point* __restrict__ pts, int n, double currentTime, double threshold, uint32_t* __restrict__ flags)
 {
@@ -557,10 +639,13 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   k_apply_segments<<<G, TPB, 0, s>>>(nk_b.p, ni_b.p, N, d_cloud, keys.p, pts.p, counts.p, (int)n_entries, g, Sampling, fixed ? 1u : 0u,
                                      currentTime, flags.p, pts_b.p, counts_b.p, d_info.p, c_eff.p, c_tpos.p);
   LSB_LAUNCH_CHECK(); lc.add();
-  tb = cub_tmp.cap;
-  LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, N, s)); lc.add(2);
-  k_gather_inserts<<<G, TPB, 0, s>>>(flags.p, scan.p, N, nk_b.p, pts_b.p, counts_b.p, ins_keys.p, ins_pts.p, ins_counts.p, d_info.p);
-  LSB_LAUNCH_CHECK(); lc.add();
+  {
+    const unsigned tiles = div_up(n, (size_t)TPB * SEL_ITEMS);
+    const unsigned epoch = sel_state.prepare(tiles, s);
+    k_select_inserts<<<tiles, TPB, 0, s>>>(flags.p, N, nk_b.p, pts_b.p, counts_b.p, ins_keys.p, ins_pts.p, ins_counts.p, sel_state.desc.p,
+                                           sel_state.ticket.p, epoch, tiles, d_info.p);
+    LSB_LAUNCH_CHECK(); lc.add();
+  }
   LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
 }
 
@@ -640,12 +725,11 @@ void RollingGridGpu::BuildSubMapKdTree(cudaStream_t s, LaunchCounter& lc)
 void RollingGridGpu::submap_pass(int mode, size_t offset, cudaStream_t s, LaunchCounter& lc, const int* d_bb)
 {
   const int n = (int)n_entries;
-  k_flag_entries<<<div_up(n_entries, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, sub_lo[0], sub_lo[1], sub_lo[2],
-                                                        sub_hi[0], sub_hi[1], sub_hi[2], mode, MinFramesPerVoxel, flags.p, d_bb, make_geom(*this));
-  LSB_LAUNCH_CHECK(); lc.add();
-  size_t tb = cub_tmp.cap;
-  LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, flags.p, scan.p, n, s)); lc.add(2);
-  k_compact<<<div_up(n_entries, TPB), TPB, 0, s>>>(flags.p, scan.p, n, nullptr, pts.p, nullptr, nullptr, submap.p + offset, nullptr, d_info.p);
+  const unsigned tiles = div_up(n_entries, (size_t)TPB * SEL_ITEMS);
+  const unsigned epoch = sel_state.prepare(tiles, s);
+  k_select_entries<<<tiles, TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, sub_lo[0], sub_lo[1], sub_lo[2], sub_hi[0], sub_hi[1], sub_hi[2],
+                                         mode, MinFramesPerVoxel, d_bb, make_geom(*this), submap.p + offset, sel_state.desc.p,
+                                         sel_state.ticket.p, epoch, tiles, d_info.p);
   LSB_LAUNCH_CHECK(); lc.add();
   LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
 }

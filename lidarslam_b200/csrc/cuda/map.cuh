@@ -6,6 +6,7 @@
 #pragma once
 #include "dev_util.h"
 #include "knn.cuh"
+#include "select.cuh"
 
 namespace lsb {
 
@@ -43,6 +44,7 @@ struct RollingGridGpu {
   PinnedBuf<uint32_t> h_info;
   PinnedBuf<float> h_bbox;
   DevBuf<float> d_bbox;
+  SelectState sel_state;                 // single-pass compaction (select.cuh) of this map's launches, ordered on its stream
   DevBuf<int> box_partial;               // per-block partial boxes + ticket of the fused box kernels (slam_kernels.cu)
   DevBuf<unsigned> box_counter;
 

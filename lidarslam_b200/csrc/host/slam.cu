@@ -17,6 +17,10 @@ using namespace lsb;
 // Enqueue order of the per-type work: the type with the most keypoints first, so that the longest
 // chain of a fork/join section starts first (the results do not depend on the order).
 static const int kTypeOrder[3] = {LSB_BLOB, LSB_PLANE, LSB_EDGE};
+// Matching passes of an ICP iteration are enqueued by one thread: the edge chain (cube pass, warp pass, brute-force tail, RANSAC
+// fit: four dependent latency-bound launches) is the longest after the blobs', so it goes second (CUPTI timeline of a frame:
+// with the planes in between, the edges' first kernel started 54 us after the blobs' and ended the iteration 26 us late).
+static const int kMatchOrder[3] = {LSB_BLOB, LSB_EDGE, LSB_PLANE};
 
 static inline double StampToSec(uint64_t us) { return us * 1e-6; }   // Utils::PclStampToSec
 
@@ -766,7 +770,7 @@ const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_mat
     const double iterRatio = icpIter / static_cast<double>(max_iter - 1);
     mp.saturation_distance = (1 - iterRatio) * sat_init + iterRatio * sat_final;          // :905-906, :1084-1085
     Fork();
-    for (int k : kTypeOrder) {
+    for (int k : kMatchOrder) {
       if (k >= ntypes) continue;
       // the undistortion refinement of the previous iteration (:1146-1147): three independent clouds, one per type stream
       // (fused into the search kernel when that one runs per keypoint: reuse pass on a non-empty target)
