@@ -343,6 +343,10 @@ LSB_API long lsb_pcd_read(const char* path, lsb_point* out, long cap);
 /* SpinningSensorKeypointExtractor::ComputeKeyPoints (SSKE.cxx:118-136) on one frame.
  * label_out[i] (input order): bit0 EDGE, bit1 PLANE, bit2 BLOB.  counts[3] = keypoints per type.
  * Keypoints are then readable with lsb_get_extracted_keypoints. */
+/* Stage entry for tests: the stable single-launch radix sort of (key, value) pairs the map update orders a cloud's leaf keys
+ * with (csrc/cuda/sort32.cu; stands where the reference walks its nested unordered_maps, RollingGrid.cxx:188-313).  Host
+ * arrays, sorted in place by the low key_bits bits of the key; n <= 262144. */
+LSB_API int lsb_sort_pairs32(lsb_slam* h, uint32_t* keys, uint32_t* values, size_t n, int key_bits);
 LSB_API int lsb_extract_keypoints(lsb_slam* h, const lsb_point* pts, size_t n, uint8_t* label_out, uint32_t counts[3]);
 LSB_API long lsb_get_extracted_keypoints(lsb_slam* h, int type, lsb_point* out, long cap);
 

@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "_lib", "liblidarslam_b200.so")
 OBJ = os.path.join(ROOT, "build", "obj")
 
-SOURCES = ["cuda/extract.cu", "cuda/knn.cu", "cuda/match.cu", "cuda/map.cu", "cuda/slam_kernels.cu", "cuda/lcp.cu", "cuda/convert.cu", "cuda/peaks.cu",
+SOURCES = ["cuda/extract.cu", "cuda/knn.cu", "cuda/match.cu", "cuda/map.cu", "cuda/sort32.cu", "cuda/slam_kernels.cu", "cuda/lcp.cu", "cuda/convert.cu", "cuda/peaks.cu",
            "host/slam.cu", "host/capi.cu", "host/capi_stages.cu", "host/defaults.cpp", "host/pcd_io.cpp"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",

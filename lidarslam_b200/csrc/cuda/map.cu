@@ -5,6 +5,7 @@
 // sorted map: existing leaves are updated in place, new leaves are merged by rank.
 #include "map.cuh"
 #include "select.cuh"
+#include "sort32.cuh"
 #include "../common/linalg.h"
 #include <cub/cub.cuh>
 #include <climits>
@@ -588,6 +589,7 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   // compact 32-bit sort keys when the cloud's voxel box and the inner index range fit (see CompactKey)
   CompactKey ck{};
   bool compact = false;
+  int key_bits = 32;
   static const bool compact_on = [] { const char* e = std::getenv("LSB_MAP_COMPACT_KEYS"); return !e || e[0] != '0'; }();   // A/B hook
   if (roll && compact_on && LeafSize > 0. && VoxelResolution > 0.) {
     const float o[3] = {g.ox, g.oy, g.oz};
@@ -606,7 +608,7 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
       int bits_in = 1, bits_out = 0;
       while ((1ll << bits_in) <= 2 * B) ++bits_in;
       while ((1ll << bits_out) < (long long)ck.dx * ck.dy * ck.dz) ++bits_out;
-      if (bits_in + bits_out <= 31 && B < (1ll << 30)) { ck.bits_in = bits_in; ck.bias = (int)B; compact = true; }
+      if (bits_in + bits_out <= 31 && B < (1ll << 30)) { ck.bits_in = bits_in; ck.bias = (int)B; compact = true; key_bits = bits_in + bits_out; }
     }
   }
   nk_a.reserve(n, s); nk_b.reserve(n, s); ni_a.reserve(n, s); ni_b.reserve(n, s);
@@ -616,11 +618,20 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   const unsigned G = div_up(n, TPB);
   LSB_CUDA(cudaMemsetAsync(d_info.p, 0, 8 * sizeof(uint32_t), s));
   size_t tb = cub_tmp.cap;
+  const uint32_t* sorted_idx = ni_b.p;
   if (compact) {
     // flags / scan are free until the segment replay: they hold the 32-bit keys before and after the sort
     k_point_keys32<<<G, TPB, 0, s>>>(d_cloud, N, g, ck, flags.p, ni_a.p, d_info.p); LSB_LAUNCH_CHECK(); lc.add();
-    LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, flags.p, scan.p, ni_a.p, ni_b.p, N, 0, 32, s)); lc.add(2 + 4);
-    k_expand_keys<<<G, TPB, 0, s>>>(scan.p, N, g.G, ck, nk_b.p); LSB_LAUNCH_CHECK(); lc.add();
+    static const bool own_sort = [] { const char* e = std::getenv("LSB_MAP_OWN_SORT"); return !e || e[0] != '0'; }();   // A/B hook
+    if (own_sort && n <= Sort32::max_pairs()) {
+      // one launch (sort32.cu); one bit above the significant ones keeps INVALID_KEY32 (all ones) behind every valid key
+      const bool in_b = sorter.sort(flags.p, ni_a.p, scan.p, ni_b.p, n, std::min(32, key_bits + 1), s, lc);
+      sorted_idx = in_b ? ni_b.p : ni_a.p;
+      k_expand_keys<<<G, TPB, 0, s>>>(in_b ? scan.p : flags.p, N, g.G, ck, nk_b.p); LSB_LAUNCH_CHECK(); lc.add();
+    } else {
+      LSB_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, flags.p, scan.p, ni_a.p, ni_b.p, N, 0, 32, s)); lc.add(2 + 4);
+      k_expand_keys<<<G, TPB, 0, s>>>(scan.p, N, g.G, ck, nk_b.p); LSB_LAUNCH_CHECK(); lc.add();
+    }
   } else {
     k_point_keys<<<G, TPB, 0, s>>>(d_cloud, N, g, nk_a.p, ni_a.p); LSB_LAUNCH_CHECK(); lc.add();
     // significant bits only: the outer index is < G^3 and INVALID_KEY (all ones) still sorts last as long as 2^bits > G^3
@@ -632,11 +643,11 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   if (Sampling == LSB_SAMPLING_CENTROID) {
     c_eff.reserve(n, s); c_tpos.reserve(n, s);
     LSB_CUDA(cudaMemsetAsync(c_eff.p, 0, n * sizeof(uint32_t), s));
-    k_centroid_effective<<<G, TPB, 0, s>>>(nk_b.p, ni_b.p, N, keys.p, pts.p, (int)n_entries, fixed ? 1u : 0u, c_eff.p); LSB_LAUNCH_CHECK(); lc.add();
+    k_centroid_effective<<<G, TPB, 0, s>>>(nk_b.p, sorted_idx, N, keys.p, pts.p, (int)n_entries, fixed ? 1u : 0u, c_eff.p); LSB_LAUNCH_CHECK(); lc.add();
     tb = cub_tmp.cap;
     LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, c_eff.p, c_tpos.p, N, s)); lc.add(2);
   }
-  k_apply_segments<<<G, TPB, 0, s>>>(nk_b.p, ni_b.p, N, d_cloud, keys.p, pts.p, counts.p, (int)n_entries, g, Sampling, fixed ? 1u : 0u,
+  k_apply_segments<<<G, TPB, 0, s>>>(nk_b.p, sorted_idx, N, d_cloud, keys.p, pts.p, counts.p, (int)n_entries, g, Sampling, fixed ? 1u : 0u,
                                      currentTime, flags.p, pts_b.p, counts_b.p, d_info.p, c_eff.p, c_tpos.p);
   LSB_LAUNCH_CHECK(); lc.add();
   {

@@ -7,6 +7,7 @@
 #include "dev_util.h"
 #include "knn.cuh"
 #include "select.cuh"
+#include "sort32.cuh"
 
 namespace lsb {
 
@@ -44,6 +45,7 @@ struct RollingGridGpu {
   PinnedBuf<uint32_t> h_info;
   PinnedBuf<float> h_bbox;
   DevBuf<float> d_bbox;
+  Sort32 sorter;                         // single-launch radix sort of the cloud's compact leaf keys (sort32.cu)
   SelectState sel_state;                 // single-pass compaction (select.cuh) of this map's launches, ordered on its stream
   DevBuf<int> box_partial;               // per-block partial boxes + ticket of the fused box kernels (slam_kernels.cu)
   DevBuf<unsigned> box_counter;

@@ -106,6 +106,24 @@ int lsb_add_converted_frame(lsb_slam* h, uint64_t stamp_us, uint32_t seq)
   });
 }
 
+int lsb_sort_pairs32(lsb_slam* h, uint32_t* keys, uint32_t* values, size_t n, int key_bits)
+{
+  if (n && (!keys || !values)) return LSB_E_INVALID;
+  return guarded([&] {
+    h->Quiesce(false);
+    if (n == 0) return (int)LSB_OK;
+    DevBuf<uint32_t> ka, va, kb, vb;
+    ka.reserve(n, h->stream); va.reserve(n, h->stream); kb.reserve(n, h->stream); vb.reserve(n, h->stream);
+    LSB_CUDA(cudaMemcpyAsync(ka.p, keys, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    LSB_CUDA(cudaMemcpyAsync(va.p, values, n * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    const bool in_b = h->LocalMaps[0].sorter.sort(ka.p, va.p, kb.p, vb.p, n, key_bits, h->stream, h->lc);
+    LSB_CUDA(cudaMemcpyAsync(keys, in_b ? kb.p : ka.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    LSB_CUDA(cudaMemcpyAsync(values, in_b ? vb.p : va.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    LSB_CUDA(cudaStreamSynchronize(h->stream));
+    return (int)LSB_OK;
+  });
+}
+
 int lsb_extract_keypoints(lsb_slam* h, const lsb_point* pts, size_t n, uint8_t* label_out, uint32_t counts[3])
 {
   return guarded([&] {

@@ -562,8 +562,14 @@ void lsb_slam::ExtractInto(FrameList& pool, size_t nb, uint64_t stamp0, const St
       if (!cfg.use[k] || ke.counts[k] == 0) continue;
       DCloud& agg = out[k];
       const size_t start = agg.n, cnt = ke.counts[k];
-      agg.buf.reserve(start + cnt, s, true, start);
-      LSB_CUDA(cudaMemcpyAsync(agg.buf.p + start, ke.kp[k].p, cnt * sizeof(lsb_point), cudaMemcpyDeviceToDevice, s));
+      if (nb == 1) {
+        // one input frame: the extractor's keypoint buffer BECOMES the aggregate (buffers change hands, nothing is copied;
+        // the extractor gets the aggregate's old buffer for its next frame)
+        agg.buf.swap(ke.kp[k]);       // (ExtractorGpu::compute sizes kp[k] before it writes)
+      } else {
+        agg.buf.reserve(start + cnt, s, true, start);
+        LSB_CUDA(cudaMemcpyAsync(agg.buf.p + start, ke.kp[k].p, cnt * sizeof(lsb_point), cudaMemcpyDeviceToDevice, s));
+      }
       agg.n = start + cnt;
       const double timeOffset = StampToSec(f.stamp_us) - StampToSec(stamp0);
       auto it = cfg.offsets.find(f.device_id);

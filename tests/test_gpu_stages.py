@@ -304,3 +304,25 @@ def test_every_handle_tops_up_the_memory_pool(gpu, synth):
     assert u2 > 0 and r2 >= u2
     for h in handles:
         h.close()
+
+
+@pytest.mark.parametrize("n,bits", [(1, 5), (31, 11), (4096, 12), (4097, 22), (5000, 23), (81233, 29), (100000, 32), (262144, 28)])
+def test_sort_pairs32_is_a_stable_sort(gpu, n, bits):
+    """sort32.cu (the map update's key sort): stable order of numpy's argsort(kind="stable") on the low `bits` bits,
+    tiles / passes / partial last tile, keys with few distinct values (long runs) and the all-ones key of rejected points."""
+    import ctypes as C
+    g = gpu()
+    rng = np.random.default_rng(n + bits)
+    mask = (1 << bits) - 1
+    keys = rng.integers(0, 1 << 32, size=n, dtype=np.uint64).astype(np.uint32)
+    if n > 100:
+        keys[rng.integers(0, n, size=n // 3)] = keys[0]                 # runs of equal keys
+        keys[rng.integers(0, n, size=n // 50)] = 0xFFFFFFFF
+        keys[: n // 4] &= 0xFF                                          # small values: empty high digits
+    vals = np.arange(n, dtype=np.uint32)
+    order = np.argsort(keys & np.uint32(mask), kind="stable")
+    k, v = keys.copy(), vals.copy()
+    rc = g.lib.lsb_sort_pairs32(g.h, k.ctypes.data_as(C.c_void_p), v.ctypes.data_as(C.c_void_p), C.c_size_t(n), C.c_int(bits))
+    assert rc == 0, g.last_error()
+    assert np.array_equal(v, vals[order])
+    assert np.array_equal(k, keys[order])
