@@ -191,6 +191,29 @@ public:
     this->PullExtractors();
   }
 
+  // Not part of the reference interface (include/lidarslam_b200.h, "pipelining"): hands the NEXT input in ahead of time, e.g.
+  // from a bag replay or a driver queue.  Its upload and keypoint extraction run while the current frame is in its ICP loop;
+  // AddFrames called later with the same clouds picks the staged keypoints up.  The clouds are retained until then.
+  void PrefetchFrames(const std::vector<PointCloud::Ptr>& frames)
+  {
+    std::vector<const lsb_point*> ptr;
+    std::vector<std::size_t> n;
+    std::vector<std::uint64_t> stamp;
+    std::vector<std::uint32_t> seq;
+    for (const auto& f : frames) {
+      ptr.push_back(f && !f->empty() ? reinterpret_cast<const lsb_point*>(f->points.data()) : nullptr);
+      n.push_back(f ? f->size() : 0);
+      stamp.push_back(f ? (std::uint64_t)f->header.stamp : 0);
+      seq.push_back(f ? (std::uint32_t)f->header.seq : 0);
+    }
+    this->PushExtractors();
+    if (lsb_prefetch_frames(this->Gpu, (int)frames.size(), ptr.data(), n.data(), stamp.data(), seq.data()) < 0) { LSB_PRINT_ERROR(lsb_last_error()); return; }
+    this->StagedFrames.push_back(frames);
+    while (this->StagedFrames.size() > 3) this->StagedFrames.erase(this->StagedFrames.begin());
+  }
+  // 0: every AddFrames ends with its map update (the reference's timing); 1 (default): the map update is joined by the next frame
+  void SetPipelining(bool deferMapUpdate) { lsb_set_pipelining(this->Gpu, deferMapUpdate ? 1 : 0); }
+
   Transform GetWorldTransform() const                                        // Slam.cxx:550-553
   {
     double T[16], t = 0.;
@@ -410,6 +433,7 @@ private:
   unsigned int NbrFrameProcessed = 0;
   std::string BaseFrameId = "base", WorldFrameId = "world";                // Slam.h:456-457
   std::vector<PointCloud::Ptr> CurrentFrames;                                // kept like the reference (Slam.cxx:237)
+  std::vector<std::vector<PointCloud::Ptr>> StagedFrames;                    // inputs handed to PrefetchFrames, alive until they are added
   std::map<std::uint8_t, KeypointExtractorPtr> KeyPointsExtractors;          // Slam.h:500
   std::map<std::uint8_t, Isometry3d> BaseToLidarOffsets;                     // Slam.h:505
   double VoxelGridDecayingThreshold = -1.;

@@ -100,11 +100,15 @@ struct Line { Vec3f dir, pos; };
 
 __device__ __forceinline__ float line_sqdist(const Line& l, const Vec3f& p) { return sqnorm(cross(p - l.pos, l.dir)); }
 
-// LineFitting::FitPCA (:59-84) over q[0..n)
-__device__ bool fit_pca(const Vec3f* q, int n, Line& l)
+// LineFitting::FitPCA (:59-84) over q[0..n).  NT > 0: the count is known at compile time (n == NT), the loops unroll and the
+// caller's neighbour arrays stay in registers (with a run-time count they live in local memory); same operations, same order.
+template <int NT>
+__device__ __forceinline__ bool fit_pca(const Vec3f* q, int n_rt, Line& l)
 {
+  const int n = NT > 0 ? NT : n_rt;
   CovAccum<float> acc;
-  for (int t = 0; t < n; ++t) acc.add(q[t].x, q[t].y, q[t].z);
+#pragma unroll
+  for (int t = 0; t < (NT > 0 ? NT : 2 * KE_MAX_WIDTH); ++t) if (t < n) acc.add(q[t].x, q[t].y, q[t].z);
   Mat3f cov, evecs;
   float evals[3];
   acc.finish(l.pos, cov);
@@ -112,29 +116,42 @@ __device__ bool fit_pca(const Vec3f* q, int n, Line& l)
   l.dir = evecs.col(2);
   const float maxd = 0.02f;
   const float sqMax = maxd * maxd;
-  for (int t = 0; t < n; ++t)
-    if (line_sqdist(l, q[t]) > sqMax) return false;
-  return true;
+  bool ok = true;
+#pragma unroll
+  for (int t = 0; t < (NT > 0 ? NT : 2 * KE_MAX_WIDTH); ++t)
+    if (t < n && line_sqdist(l, q[t]) > sqMax) ok = false;
+  return ok;
 }
 
 // LineFitting::FitPCAAndCheckConsistency (:87-108)
-__device__ bool fit_pca_consistent(const Vec3f* q, int n, Line& l, float maxSinAngle)
+template <int NT>
+__device__ __forceinline__ bool fit_pca_consistent(const Vec3f* q, int n_rt, Line& l, float maxSinAngle)
 {
+  const int n = NT > 0 ? NT : n_rt;
   const Vec3f U = normalized(q[n - 1] - q[0]);
-  for (int t = 0; t < n - 1; ++t) {
-    const Vec3f V = normalized(q[t + 1] - q[t]);
-    const float sinAngle = norm(cross(U, V));
-    if (sinAngle > maxSinAngle) return false;
+  bool ok = true;
+#pragma unroll
+  for (int t = 0; t < (NT > 0 ? NT - 1 : KE_MAX_WIDTH - 1); ++t) {
+    if (t < n - 1) {
+      const Vec3f V = normalized(q[t + 1] - q[t]);
+      const float sinAngle = norm(cross(U, V));
+      if (sinAngle > maxSinAngle) ok = false;
+    }
   }
-  return fit_pca(q, n, l);
+  if (!ok) return false;
+  return fit_pca<NT>(q, n, l);
 }
 
+// WT > 0: neighbour half-width known at compile time (W == WT; the reference's default is 4), WT == 0: any width up to KE_MAX_WIDTH
+template <int WT>
 __global__ void __launch_bounds__(128)
 k_curvature(const float4* __restrict__ p4, const uint32_t* __restrict__ key, int n, const int* __restrict__ ring_start,
             const int* __restrict__ ring_end, const uint8_t* __restrict__ valid, float* __restrict__ angles,
-            float* __restrict__ depth_gap, float* __restrict__ saliency, float* __restrict__ intensity_gap, int W,
+            float* __restrict__ depth_gap, float* __restrict__ saliency, float* __restrict__ intensity_gap, int W_rt,
             float sqDistToLineThreshold, float maxSinAngle)
 {
+  const int W = WT > 0 ? WT : W_rt;
+  constexpr int WMAX = WT > 0 ? WT : KE_MAX_WIDTH;
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
   float oAngle = 0.f, oDepth = 0.f, oSal = 0.f, oInt = 0.f;
@@ -148,19 +165,21 @@ k_curvature(const float4* __restrict__ p4, const uint32_t* __restrict__ key, int
     active = !(Npts < 2 * W + 1) && i >= W && i + W < Npts;
   }
   if (active) {
-    Vec3f left[KE_MAX_WIDTH], right[KE_MAX_WIDTH], far[2 * KE_MAX_WIDTH];
-    float sqn_l[KE_MAX_WIDTH], sqn_r[KE_MAX_WIDTH];
+    Vec3f left[WMAX], right[WMAX];
     const float4 c4 = p4[j];
     const Vec3f central = xyz(c4);
-    for (int t = 0; t < W; ++t) {      // from the centre outward (:363-366)
-      left[t] = xyz(p4[j - 1 - t]);
-      right[t] = xyz(p4[j + 1 + t]);
+#pragma unroll
+    for (int t = 0; t < WMAX; ++t) {      // from the centre outward (:363-366)
+      if (t < W) {
+        left[t] = xyz(p4[j - 1 - t]);
+        right[t] = xyz(p4[j + 1 + t]);
+      }
     }
     const float ig = p4[j + 1].w - p4[j - 1].w;
     oInt = (ig < 0.f) ? -ig : ig;
     Line leftLine, rightLine;
-    const bool leftFlat = fit_pca_consistent(left, W, leftLine, maxSinAngle);
-    const bool rightFlat = fit_pca_consistent(right, W, rightLine, maxSinAngle);
+    const bool leftFlat = fit_pca_consistent<WT>(left, W, leftLine, maxSinAngle);
+    const bool rightFlat = fit_pca_consistent<WT>(right, W, rightLine, maxSinAngle);
     float distLeft = 0.f, distRight = 0.f;
     if (leftFlat && rightFlat) {
       distLeft = line_sqdist(leftLine, central);
@@ -169,31 +188,39 @@ k_curvature(const float4* __restrict__ p4, const uint32_t* __restrict__ key, int
         oAngle = norm(cross(leftLine.dir, rightLine.dir));
     } else if (!leftFlat && rightFlat) {
       distLeft = FLT_MAX;
-      for (int t = 0; t < W; ++t) { const float d = line_sqdist(rightLine, left[t]); distLeft = (d < distLeft) ? d : distLeft; }
+#pragma unroll
+      for (int t = 0; t < WMAX; ++t) if (t < W) { const float d = line_sqdist(rightLine, left[t]); distLeft = (d < distLeft) ? d : distLeft; }
       distLeft *= 0.25f;
     } else if (leftFlat && !rightFlat) {
       distRight = FLT_MAX;
-      for (int t = 0; t < W; ++t) { const float d = line_sqdist(leftLine, right[t]); distRight = (d < distRight) ? d : distRight; }
+#pragma unroll
+      for (int t = 0; t < WMAX; ++t) if (t < W) { const float d = line_sqdist(leftLine, right[t]); distRight = (d < distRight) ? d : distRight; }
       distRight *= 0.25f;
     } else {
       const float sqCurrDepth = sqnorm(central);
       const float minDepthGapDist = 1.5f;
-      for (int t = 0; t < W; ++t) { sqn_l[t] = sqnorm(left[t]); sqn_r[t] = sqnorm(right[t]); }
-      bool gapL = false, gapR = false;
+      Vec3f far[2 * WMAX];
+      bool gapL = false, gapR = false, stopL = false, stopR = false;
       int nfar = 0;
-      for (int t = 0; t < W; ++t) {
-        const float d = sqn_l[t] - sqCurrDepth;
-        if (((d < 0.f) ? -d : d) > minDepthGapDist) { gapL = true; far[nfar++] = left[t]; }
-        else if (gapL) break;
+#pragma unroll
+      for (int t = 0; t < WMAX; ++t) {
+        if (t < W && !stopL) {
+          const float d = sqnorm(left[t]) - sqCurrDepth;
+          if (((d < 0.f) ? -d : d) > minDepthGapDist) { gapL = true; far[nfar++] = left[t]; }
+          else if (gapL) stopL = true;
+        }
       }
-      for (int t = 0; t < W; ++t) {
-        const float d = sqn_r[t] - sqCurrDepth;
-        if (((d < 0.f) ? -d : d) > minDepthGapDist) { gapR = true; far[nfar++] = right[t]; }
-        else if (gapR) break;
+#pragma unroll
+      for (int t = 0; t < WMAX; ++t) {
+        if (t < W && !stopR) {
+          const float d = sqnorm(right[t]) - sqCurrDepth;
+          if (((d < 0.f) ? -d : d) > minDepthGapDist) { gapR = true; far[nfar++] = right[t]; }
+          else if (gapR) stopR = true;
+        }
       }
       if (nfar > W) {
         Line farLine;
-        fit_pca(far, nfar, farLine);
+        fit_pca<0>(far, nfar, farLine);
         oSal = line_sqdist(farLine, central);
       }
     }
@@ -503,8 +530,12 @@ void ExtractorGpu::compute(const lsb_point* d_pts, size_t n_, cudaStream_t s, La
   LSB_LAUNCH_CHECK(); lc.add();
   // K3
   const float maxSinAngle = dm::sinf((float)(40. * 0.017453293));   // LineFitting::MaxAngle (:55)
-  k_curvature<<<div_up(n, 128), 128, 0, s>>>(p4.p, key_b.p, N, ring_start.p, ring_end.p, valid.p, angles.p, depth_gap.p, saliency.p,
-                                             intensity_gap.p, W, P.dist_to_line_threshold * P.dist_to_line_threshold, maxSinAngle);
+  if (W == 4)
+    k_curvature<4><<<div_up(n, 128), 128, 0, s>>>(p4.p, key_b.p, N, ring_start.p, ring_end.p, valid.p, angles.p, depth_gap.p, saliency.p,
+                                                  intensity_gap.p, W, P.dist_to_line_threshold * P.dist_to_line_threshold, maxSinAngle);
+  else
+    k_curvature<0><<<div_up(n, 128), 128, 0, s>>>(p4.p, key_b.p, N, ring_start.p, ring_end.p, valid.p, angles.p, depth_gap.p, saliency.p,
+                                                  intensity_gap.p, W, P.dist_to_line_threshold * P.dist_to_line_threshold, maxSinAngle);
   LSB_LAUNCH_CHECK(); lc.add();
   // K4
   LSB_CUDA(cudaMemsetAsync(label.p, 0, n, s));

@@ -117,7 +117,9 @@ int lsb_set_extractor_params(lsb_slam* h, int device_id, const lsb_ke_params* p)
 }
 int lsb_get_extractor_params(const lsb_slam* h, int device_id, lsb_ke_params* p)
 {
-  { const int rc = guarded([&] { const_cast<lsb_slam*>(h)->Quiesce(false); return LSB_OK; }); if (rc < 0) return rc; }
+  // no join of deferred / staged work (the C++ mirror reads the azimuth estimate back after every frame): the extractor state
+  // changes hands under ke_mu, so the copy is consistent; with an input staged ahead it may already hold that input's estimate
+  std::lock_guard<std::mutex> g(const_cast<lsb_slam*>(h)->ke_mu);
   auto it = h->KeyPointsExtractors.find(device_id);
   if (it == h->KeyPointsExtractors.end() || !it->second) { g_last_error = "no extractor for this device_id"; return LSB_E_INVALID; }
   *p = it->second->P;
@@ -342,7 +344,7 @@ int lsb_set_profiling(lsb_slam* h, int on)
 }
 unsigned int lsb_get_azimuth_estimations(const lsb_slam* h, int device_id)
 {
-  guarded([&] { const_cast<lsb_slam*>(h)->Quiesce(false); return LSB_OK; });
+  std::lock_guard<std::mutex> g(const_cast<lsb_slam*>(h)->ke_mu);
   auto it = h->KeyPointsExtractors.find(device_id);
   return (it == h->KeyPointsExtractors.end() || !it->second) ? 0u : it->second->az_estimations;
 }

@@ -31,15 +31,25 @@ int main(int argc, char** argv)
   slam->SetBaseToLidarOffset(LidarSlam::Isometry3d::Identity(), 0);
   slam->SetVoxelGridLeafSize(LidarSlam::EDGE, 0.30);
 
-  for (int i = 0; i < nFrames; ++i) {
+  // frames are read one ahead; from the middle of the run on the next one is handed in before the current one is added
+  // (PrefetchFrames: same results, its extraction overlaps the current frame)
+  auto readFrame = [&](int i) -> LidarSlam::Slam::PointCloud::Ptr {
     LidarSlam::Slam::PointCloud::Ptr pc(new LidarSlam::Slam::PointCloud);
     std::uint64_t stamp = 0;
-    if (std::fread(&stamp, 8, 1, f) != 1) return 2;
+    if (std::fread(&stamp, 8, 1, f) != 1) return nullptr;
     pc->resize(nPoints);
-    if (std::fread(pc->points.data(), sizeof(LidarSlam::LidarPoint), nPoints, f) != nPoints) return 2;
+    if (std::fread(pc->points.data(), sizeof(LidarSlam::LidarPoint), nPoints, f) != nPoints) return nullptr;
     pc->header.stamp = stamp;
     pc->header.seq = (std::uint32_t)(i + 1);
     pc->header.frame_id = "lidar";
+    return pc;
+  };
+  LidarSlam::Slam::PointCloud::Ptr next = readFrame(0);
+  for (int i = 0; i < nFrames; ++i) {
+    LidarSlam::Slam::PointCloud::Ptr pc = next;
+    if (!pc) return 2;
+    next = (i + 1 < nFrames) ? readFrame(i + 1) : nullptr;
+    if (next && i >= nFrames / 2) slam->PrefetchFrames({next});
     slam->AddFrame(pc);
     const LidarSlam::Transform T = slam->GetWorldTransform();
     std::printf("%d %d %zu %zu %zu", i, slam->GetLastStatus(), slam->GetKeypoints(LidarSlam::EDGE)->size(),
