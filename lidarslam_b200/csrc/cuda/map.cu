@@ -270,23 +270,6 @@ __global__ void k_apply_segments(const unsigned long long* __restrict__ skey, co
   if (updated) atomicOr(info, 1u);
 }
 
-// compaction of flagged segment heads into the (sorted) insert list
-__global__ void k_gather_inserts(const uint32_t* __restrict__ flags, const uint32_t* __restrict__ scan, int n,
-                                 const unsigned long long* __restrict__ skey, const lsb_point* __restrict__ seg_pts,
-                                 const uint32_t* __restrict__ seg_counts, unsigned long long* __restrict__ ins_keys,
-                                 lsb_point* __restrict__ ins_pts, uint32_t* __restrict__ ins_counts, uint32_t* __restrict__ info)
-{
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  if (flags[i]) {
-    const uint32_t o = scan[i];
-    ins_keys[o] = skey[i];
-    store_raw(ins_pts + o, load_raw(seg_pts + i));
-    ins_counts[o] = seg_counts[i];
-  }
-  if (i == n - 1) info[1] = scan[i] + flags[i];
-}
-
 // merge by rank: both key lists are sorted and disjoint
 __global__ void k_merge(const unsigned long long* __restrict__ ka, const lsb_point* __restrict__ pa, const uint32_t* __restrict__ ca, int na,
                         const unsigned long long* __restrict__ kb, const lsb_point* __restrict__ pb, const uint32_t* __restrict__ cb, int nb,
@@ -390,6 +373,19 @@ __device__ __forceinline__ bool entry_selected(const unsigned long long* __restr
   return f;
 }
 
+// The counters a host phase waits for go to pinned host memory straight from the kernel that completes them (the tile that
+// holds the grand total): no device-to-host copy is enqueued and the waiting thread polls a sequence word instead of
+// synchronising the stream (map.cu: wait_info).  info[0..7] were completed by this or earlier kernels of the stream.
+__device__ __forceinline__ void publish_info(const uint32_t* __restrict__ info, volatile uint32_t* __restrict__ h_info, uint32_t seq, bool last_tile)
+{
+  if (!last_tile || threadIdx.x != 0) return;       // thread 0 of warp 0 wrote the total (sel::tile_offset)
+  __threadfence();
+#pragma unroll
+  for (int q = 0; q < 8; ++q) h_info[q] = __ldcg(info + q);
+  __threadfence_system();
+  h_info[8] = seq;
+}
+
 // Sub-map selection in ONE launch: k_flag_entries + exclusive scan + k_compact (points only) by decoupled look-back
 // (select.cuh).  A tile is SEL_ITEMS consecutive entries per thread, so the output keeps the map's order.
 constexpr int SEL_ITEMS = 4;
@@ -397,7 +393,8 @@ __global__ void __launch_bounds__(TPB) k_select_entries(const unsigned long long
                                                         const uint32_t* __restrict__ counts, int n, int G, int lx, int ly, int lz, int hx, int hy,
                                                         int hz, int mode, unsigned minFrames, const int* __restrict__ bb, GridGeom g,
                                                         lsb_point* __restrict__ out, unsigned long long* __restrict__ desc,
-                                                        unsigned* __restrict__ ticket, unsigned epoch, unsigned ntiles, uint32_t* __restrict__ info)
+                                                        unsigned* __restrict__ ticket, unsigned epoch, unsigned ntiles, uint32_t* __restrict__ info,
+                                                        volatile uint32_t* __restrict__ h_info, uint32_t seq)
 {
   if (bb) {
     lx = max(pos2vox(ord2f_dev(bb[0]), g.ox, g.res), 0); hx = min(pos2vox(ord2f_dev(bb[3]), g.ox, g.res), G - 1);
@@ -418,6 +415,7 @@ __global__ void __launch_bounds__(TPB) k_select_entries(const unsigned long long
 #pragma unroll
   for (int q = 0; q < SEL_ITEMS; ++q)
     if (f[q]) { store_raw(out + o, load_raw(pts + base + q)); ++o; }
+  publish_info(info, h_info, seq, tile == ntiles - 1);
 }
 
 // k_gather_inserts with its scan, one launch: flagged segment heads -> the (sorted) insert list; info[1] = their number
@@ -425,7 +423,8 @@ __global__ void __launch_bounds__(TPB) k_select_inserts(const uint32_t* __restri
                                                         const lsb_point* __restrict__ seg_pts, const uint32_t* __restrict__ seg_counts,
                                                         unsigned long long* __restrict__ ins_keys, lsb_point* __restrict__ ins_pts,
                                                         uint32_t* __restrict__ ins_counts, unsigned long long* __restrict__ desc,
-                                                        unsigned* __restrict__ ticket, unsigned epoch, unsigned ntiles, uint32_t* __restrict__ info)
+                                                        unsigned* __restrict__ ticket, unsigned epoch, unsigned ntiles, uint32_t* __restrict__ info,
+                                                        volatile uint32_t* __restrict__ h_info, uint32_t seq)
 {
   unsigned tile = sel::take_ticket(ticket);
   const int base = (int)tile * (TPB * SEL_ITEMS) + (int)threadIdx.x * SEL_ITEMS;
@@ -446,6 +445,7 @@ __global__ void __launch_bounds__(TPB) k_select_inserts(const uint32_t* __restri
     ins_counts[o] = seg_counts[i];
     ++o;
   }
+  publish_info(info, h_info, seq, tile == ntiles - 1);
 }
 
 // ClearOldPoints (:325-350)
@@ -489,6 +489,25 @@ void cloud_bbox(const lsb_point* d_cloud, size_t n, float mn[3], float mx[3], De
   bbox_decode(h_bbox.p, mn, mx);
 }
 
+// waits for the sequence word a kernel of stream s leaves in pinned memory (publish_info); the stream is queried now and then so
+// that a failed launch surfaces as an error instead of an endless wait
+static void wait_info(const uint32_t* h_info, uint32_t seq, cudaStream_t s)
+{
+  const volatile uint32_t* flag = h_info + 8;
+  unsigned spins = 0;
+  while (*flag != seq) {
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+    if ((++spins & 0x3fffu) == 0) {
+      const cudaError_t rc = cudaStreamQuery(s);
+      if (rc == cudaErrorNotReady) continue;
+      LSB_CUDA(rc);
+      if (*flag != seq) throw CudaError(LSB_E_CUDA, "RollingGrid: the stream is idle but its counters never arrived");
+    }
+  }
+}
+
 static GridGeom make_geom(const RollingGridGpu& m)
 {
   GridGeom g;
@@ -503,7 +522,8 @@ static GridGeom make_geom(const RollingGridGpu& m)
 void RollingGridGpu::ensure_scratch(size_t n, cudaStream_t s)
 {
   flags.reserve(n + 1, s); scan.reserve(n + 1, s);
-  d_info.reserve(8, s); h_info.reserve(8);
+  d_info.reserve(8, s);
+  if (!h_info.p) { h_info.reserve(16); std::memset(h_info.p, 0, 16 * sizeof(uint32_t)); }
   size_t tmp = 0, tmp2 = 0;
   cub::DeviceScan::ExclusiveSum(nullptr, tmp, flags.p, scan.p, (int)n, s);
   cub::DeviceRadixSort::SortPairs(nullptr, tmp2, nk_a.p, nk_b.p, ni_a.p, ni_b.p, (int)n, 0, 64, s);
@@ -653,17 +673,17 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   {
     const unsigned tiles = div_up(n, (size_t)TPB * SEL_ITEMS);
     const unsigned epoch = sel_state.prepare(tiles, s);
+    info_seq = info_seq + 1 ? info_seq + 1 : 1;
     k_select_inserts<<<tiles, TPB, 0, s>>>(flags.p, N, nk_b.p, pts_b.p, counts_b.p, ins_keys.p, ins_pts.p, ins_counts.p, sel_state.desc.p,
-                                           sel_state.ticket.p, epoch, tiles, d_info.p);
+                                           sel_state.ticket.p, epoch, tiles, d_info.p, h_info.p, info_seq);
     LSB_LAUNCH_CHECK(); lc.add();
   }
-  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
 }
 
 void RollingGridGpu::AddMerge(size_t n, cudaStream_t s, LaunchCounter& lc)
 {
   if (n == 0) return;
-  LSB_CUDA(cudaStreamSynchronize(s));
+  wait_info(h_info.p, info_seq, s);
   if (h_info.p[7]) throw CudaError(LSB_E_CUDA, "RollingGrid::Add: a leaf key fell outside the compact key range (internal bound error)");
   const bool updated = h_info.p[0] != 0;
   const size_t n_ins = h_info.p[1];
@@ -738,11 +758,11 @@ void RollingGridGpu::submap_pass(int mode, size_t offset, cudaStream_t s, Launch
   const int n = (int)n_entries;
   const unsigned tiles = div_up(n_entries, (size_t)TPB * SEL_ITEMS);
   const unsigned epoch = sel_state.prepare(tiles, s);
+  info_seq = info_seq + 1 ? info_seq + 1 : 1;
   k_select_entries<<<tiles, TPB, 0, s>>>(keys.p, pts.p, counts.p, n, GridSize, sub_lo[0], sub_lo[1], sub_lo[2], sub_hi[0], sub_hi[1], sub_hi[2],
                                          mode, MinFramesPerVoxel, d_bb, make_geom(*this), submap.p + offset, sel_state.desc.p,
-                                         sel_state.ticket.p, epoch, tiles, d_info.p);
+                                         sel_state.ticket.p, epoch, tiles, d_info.p, h_info.p, info_seq);
   LSB_LAUNCH_CHECK(); lc.add();
-  LSB_CUDA(cudaMemcpyAsync(h_info.p, d_info.p, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
 }
 
 void RollingGridGpu::SubMapSelect(const float mn[3], const float mx[3], int minNbPoints, cudaStream_t s, LaunchCounter& lc)
@@ -781,8 +801,10 @@ void RollingGridGpu::SubMapSelectDevice(int minNbPoints, cudaStream_t s, LaunchC
 
 void RollingGridGpu::SubMapFinish(cudaStream_t s, LaunchCounter& lc)
 {
+  // the selection kernel leaves the count in pinned memory (publish_info); the box was published by an earlier kernel of the stream
+  if (n_entries) wait_info(h_info.p, info_seq, s);
+  else if (sub_from_device) LSB_CUDA(cudaStreamSynchronize(s));
   if (sub_from_device) {
-    LSB_CUDA(cudaStreamSynchronize(s));      // the box (copy enqueued by the caller) and, if there are entries, the count
     float mn[3], mx[3];
     bbox_decode(h_bbox.p, mn, mx);
     const GridGeom g = make_geom(*this);
@@ -793,11 +815,10 @@ void RollingGridGpu::SubMapFinish(cudaStream_t s, LaunchCounter& lc)
     }
   }
   if (n_entries) {
-    if (!sub_from_device) LSB_CUDA(cudaStreamSynchronize(s));
     n_submap = h_info.p[2];
     if (sub_filter && (int)n_submap < sub_min_nb) {
       submap_pass(2, n_submap, s, lc);
-      LSB_CUDA(cudaStreamSynchronize(s));
+      wait_info(h_info.p, info_seq, s);
       n_submap += h_info.p[2];
     }
   }

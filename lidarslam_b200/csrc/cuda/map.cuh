@@ -42,7 +42,8 @@ struct RollingGridGpu {
   DevBuf<uint32_t> c_eff, c_tpos;        // SamplingMode::CENTROID: effective-point flags and their arrival positions
   DevBuf<uint32_t> d_info;               // [8]
   DevBuf<unsigned char> cub_tmp;
-  PinnedBuf<uint32_t> h_info;
+  PinnedBuf<uint32_t> h_info;            // [16]: [0..7] counters, [8] sequence word of the kernel that published them
+  uint32_t info_seq = 0;
   PinnedBuf<float> h_bbox;
   DevBuf<float> d_bbox;
   Sort32 sorter;                         // single-launch radix sort of the cloud's compact leaf keys (sort32.cu)

@@ -170,12 +170,13 @@ struct InFlightGuard {
   ~InFlightGuard() { g_handles_in_flight.fetch_sub(1, std::memory_order_relaxed); }
 };
 
-void lsb_slam::ForEachType(const std::function<void(int)>& fn)
+void lsb_slam::ForEachType(const std::function<void(int)>& fn, const std::function<void()>& meanwhile)
 {
   const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
   if (serial_types || !use_lanes || crowded) {
     JoinMapUpdate();             // a deferred update of these maps ends before the caller's thread touches them
     Fork();
+    if (meanwhile) meanwhile();
     for (int k : kTypeOrder) fn(k);
     Join();
     return;
@@ -184,6 +185,7 @@ void lsb_slam::ForEachType(const std::function<void(int)>& fn)
   unsigned ticket[3];
   for (int k : kTypeOrder) ticket[k] = TypeWorker(k).post([&fn, k] { fn(k); });
   std::exception_ptr first;
+  if (meanwhile) { try { meanwhile(); } catch (...) { first = std::current_exception(); } }   // caller's own work on `stream`, beside the helpers
   for (int k : kTypeOrder) {
     try { TypeWorker(k).wait(ticket[k]); } catch (...) { if (!first) first = std::current_exception(); }
   }
@@ -707,7 +709,7 @@ void lsb_slam::Localization()
       map.SubMapSelect(mn, mx, 0, ts, lc);
     }
     map.SubMapFinish(ts, lc);
-  });
+  }, [&] { if (P.localization_icp_max_iter > 0) IcpBegin(ICP_STAGE_LOC, P.localization_icp_max_iter); });
   HasPendingRefinement = false;
   trace.mark("submap+grid", stream);
 
@@ -741,16 +743,11 @@ void lsb_slam::Localization()
 }
 
 //-----------------------------------------------------------------------------
-// One ICP - LM loop of the frame without a host round trip between its iterations (cuda/icp.cuh): the pose, the within-frame
-// motion and the loop's break tests live in device memory; iteration i + 1 is enqueued behind iteration i and stands aside
-// if the loop ended before it.  Per iteration and keypoint type (own streams): undistortion refinement of the previous solve,
-// kNN (from the second iteration on bounded by the previous neighbour lists), model fit; then one persistent LM kernel whose
-// tail (icp_control) moves the pose on.  The kernel that ends the loop hands the result block to the host.
-const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_match_params& base, unsigned max_iter, unsigned lm_max_iter,
-                                                        double sat_init, double sat_final, const LmSensorTerms* terms)
+// Prologue of an ICP - LM loop: the loop's state in device memory and the per-frame reset of the match workspace.  It needs
+// nothing of the sub-maps, so the localization enqueues it on `stream` while the helper threads are still selecting them.
+void lsb_slam::IcpBegin(int stage, unsigned max_iter)
 {
   const bool loc = stage == ICP_STAGE_LOC;
-  const int ntypes = loc ? 3 : 2;                                   // ego-motion never uses blobs (:848, :910)
   size_t nk[3] = {CurrentKeypoints[0].n, CurrentKeypoints[1].n, loc ? CurrentKeypoints[2].n : 0};
   IcpState init;
   std::memset(&init, 0, sizeof(init));
@@ -770,6 +767,23 @@ const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_mat
   mw.lm_grid_share = std::min(std::max(g_handles_in_flight.load(std::memory_order_relaxed), 1), share_max);
   mw.begin_frame(nk, (int)max_iter, stream);
   mw.next_solve_seq();
+  icp_begun = true;
+}
+
+//-----------------------------------------------------------------------------
+// One ICP - LM loop of the frame without a host round trip between its iterations (cuda/icp.cuh): the pose, the within-frame
+// motion and the loop's break tests live in device memory; iteration i + 1 is enqueued behind iteration i and stands aside
+// if the loop ended before it.  Per iteration and keypoint type (own streams): undistortion refinement of the previous solve,
+// kNN (from the second iteration on bounded by the previous neighbour lists), model fit; then one persistent LM kernel whose
+// tail (icp_control) moves the pose on.  The kernel that ends the loop hands the result block to the host.
+const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_match_params& base, unsigned max_iter, unsigned lm_max_iter,
+                                                        double sat_init, double sat_final, const LmSensorTerms* terms)
+{
+  const bool loc = stage == ICP_STAGE_LOC;
+  const int ntypes = loc ? 3 : 2;                                   // ego-motion never uses blobs (:848, :910)
+  size_t nk[3] = {CurrentKeypoints[0].n, CurrentKeypoints[1].n, loc ? CurrentKeypoints[2].n : 0};
+  if (!icp_begun) IcpBegin(stage, max_iter);
+  icp_begun = false;
   const bool refined = loc && P.undistortion == LSB_UNDISTORTION_REFINED;
   lsb_match_params mp = base;
   for (unsigned icpIter = 0; icpIter < max_iter; ++icpIter) {

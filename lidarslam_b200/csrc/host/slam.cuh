@@ -44,7 +44,7 @@ struct lsb_slam {
   std::unique_ptr<lsb::AsyncWorker> tworker[3];
   lsb::AsyncWorker& TypeWorker(int k) { if (!tworker[k]) tworker[k].reset(new lsb::AsyncWorker(device)); return *tworker[k]; }
   bool use_lanes = true;
-  void ForEachType(const std::function<void(int)>& fn);
+  void ForEachType(const std::function<void(int)>& fn, const std::function<void()>& meanwhile = {});   // meanwhile: run by the caller beside the helpers
   lsb::LaunchCounter lc;
   lsb_params P;
 
@@ -137,6 +137,8 @@ struct lsb_slam {
   // enqueues every iteration of an ICP - LM loop, waits for the hand-over of the iteration that ends it
   const lsb::MatchWorkspace::LmHostBlock& RunIcpLoop(int stage, const lsb_match_params& base, unsigned max_iter, unsigned lm_max_iter,
                                                      double sat_init, double sat_final, const lsb::LmSensorTerms* terms);
+  void IcpBegin(int stage, unsigned max_iter);     // the loop's prologue (may be enqueued ahead of RunIcpLoop)
+  bool icp_begun = false;
   lsb::KnnGrid EgoGrids[2];
   // match results kept for GetDebugArray (Slam.cxx:635-657)
   struct StageDebug { lsb::DevBuf<uint8_t> status; lsb::DevBuf<double> weight; size_t off[4] = {0, 0, 0, 0}; int hist[3][LSB_MATCH_N_STATUS] = {}; };
