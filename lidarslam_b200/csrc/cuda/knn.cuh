@@ -40,6 +40,7 @@ struct KnnGrid {
   DevBuf<unsigned char> cub_tmp;
   mutable DevBuf<int32_t> unres_list;    // queries handed to the brute-force kernel
   mutable DevBuf<unsigned> unres_count;  // [4]: unsettled count, cursor, brute-force count, cursor
+  mutable bool counters_clean = false;   // unres_count is known to be zero (the matcher's fit kernel clears it behind a search), else a search memsets it first
   mutable DevBuf<int32_t> bf_list;       // exact search: isolated queries for the brute-force kernel
   mutable DevBuf<unsigned long long> bf_partial;   // their per-segment partial lists
   mutable DevBuf<unsigned> bf_tickets;   // per-query segment counter (self-resetting)

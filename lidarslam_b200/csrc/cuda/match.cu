@@ -74,9 +74,13 @@ template <int TYPE>
 __global__ void __launch_bounds__(FIT_TPB)
 k_fit(const lsb_point* __restrict__ kp, int nq, const lsb_point* __restrict__ cloud, const int32_t* __restrict__ nn_idx,
       const float* __restrict__ nn_d2, const int32_t* __restrict__ nn_found, int k, FitParams fp, double* __restrict__ records, size_t rec_stride,
-      uint8_t* __restrict__ status, double* __restrict__ weight, int* __restrict__ hist, const int* __restrict__ done)
+      uint8_t* __restrict__ status, double* __restrict__ weight, int* __restrict__ hist, const int* __restrict__ done,
+      unsigned* __restrict__ knn_counters)
 {
   if (done && *done) return;   // device-resident ICP loop: the loop ended in an earlier iteration (cuda/icp.cuh)
+  // the search that fed this kernel is over: its work counters (KnnGrid::unres_count) go back to zero here, which saves the next
+  // search of the grid a memset at the head of its chain
+  if (knn_counters && blockIdx.x == 0 && threadIdx.x < 4) knn_counters[threadIdx.x] = 0u;
   __shared__ int s_hist[LSB_MATCH_N_STATUS];
   if (threadIdx.x < LSB_MATCH_N_STATUS) s_hist[threadIdx.x] = 0;
   __syncthreads();
@@ -722,10 +726,11 @@ void MatchWorkspace::match_type(int type, const lsb_point* d_kp, size_t nk, cons
   t_knn.end(s);
   const int NQ = (int)nk;
   t_fit.begin(s);
-  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done);
-  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done);
-  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done);
+  if (type == LSB_EDGE) k_fit<LSB_EDGE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done, target.unres_count.p);
+  else if (type == LSB_PLANE) k_fit<LSB_PLANE><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done, target.unres_count.p);
+  else k_fit<LSB_BLOB><<<G, FIT_TPB, 0, s>>>(d_kp, NQ, target.cloud, nn_idx[type].p, nn_d2[type].p, nn_found[type].p, k, fp, rec, rec_stride, st, wt, h, done, target.unres_count.p);
   LSB_LAUNCH_CHECK(); lc.add();
+  target.counters_clean = target.unres_count.p != nullptr;
   t_fit.end(s);
 }
 

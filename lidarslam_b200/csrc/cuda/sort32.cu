@@ -90,10 +90,12 @@ __global__ void __launch_bounds__(S_TPB) k_sort_pairs32(uint32_t* __restrict__ k
       tot[u] = pre[u] = 0u;
       const int b = (int)threadIdx.x * per + u;
       if (u < per && b < bins) {
-        for (int c = 0; c < ncta; ++c) {
-          const uint32_t v = __ldcg(h + (size_t)c * S_MAX_BINS + b);
-          tot[u] += v;
-          pre[u] += (c < cta) ? v : 0u;
+        for (int c0 = 0; c0 < ncta; c0 += 8) {        // eight independent loads in flight per batch
+          uint32_t v[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[e] = (c0 + e < ncta) ? __ldcg(h + (size_t)(c0 + e) * S_MAX_BINS + b) : 0u;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { tot[u] += v[e]; pre[u] += (c0 + e < cta) ? v[e] : 0u; }
         }
       }
       mine += tot[u];
