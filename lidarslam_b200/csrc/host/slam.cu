@@ -165,6 +165,17 @@ static int HostThreadBudget()
   }();
   return budget;
 }
+// Host cores against busy host threads.  A handle in flight keeps up to five threads busy (the caller, one helper per keypoint
+// type, one for staged inputs).  0 = room for all of them, the helpers spin between jobs (frames arrive back to back);
+// 1 = at least three cores per handle: the helpers are used but sleep when idle (a wake-up costs a few microseconds per job);
+// 2 = fewer: everything on the caller's thread, nothing deferred.
+static int HostMode()
+{
+  const int h = std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)), budget = HostThreadBudget();
+  static const int forced = [] { const char* e = std::getenv("LSB_HOST_MODE"); return e ? std::atoi(e) : -1; }();   // tuning hook
+  if (forced >= 0) return forced;
+  return budget >= 5 * h ? 0 : (budget >= 3 * h ? 1 : 2);
+}
 struct InFlightGuard {
   InFlightGuard() { g_handles_in_flight.fetch_add(1, std::memory_order_relaxed); }
   ~InFlightGuard() { g_handles_in_flight.fetch_sub(1, std::memory_order_relaxed); }
@@ -172,8 +183,8 @@ struct InFlightGuard {
 
 void lsb_slam::ForEachType(const std::function<void(int)>& fn, const std::function<void()>& meanwhile)
 {
-  const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
-  if (serial_types || !use_lanes || crowded) {
+  const int mode = HostMode();
+  if (serial_types || !use_lanes || mode == 2) {
     JoinMapUpdate();             // a deferred update of these maps ends before the caller's thread touches them
     Fork();
     if (meanwhile) meanwhile();
@@ -183,7 +194,7 @@ void lsb_slam::ForEachType(const std::function<void(int)>& fn, const std::functi
   }
   Fork();
   unsigned ticket[3];
-  for (int k : kTypeOrder) ticket[k] = TypeWorker(k).post([&fn, k] { fn(k); });
+  for (int k : kTypeOrder) ticket[k] = TypeWorker(k).post([&fn, k] { fn(k); }, mode == 0);
   std::exception_ptr first;
   if (meanwhile) { try { meanwhile(); } catch (...) { first = std::current_exception(); } }   // caller's own work on `stream`, beside the helpers
   for (int k : kTypeOrder) {
@@ -309,13 +320,13 @@ int lsb_slam::PrefetchFrames(int n_frames, const lsb_point* const* frames, const
   slot->seq.assign((size_t)n_frames, 0u);
   if (seq) slot->seq.assign(seq, seq + n_frames);
   const StageCfg cfg = MakeStageCfg();
-  const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
+  const int mode = HostMode();
   slot->ticket = Worker().post([this, slot, cfg] {
     const int nf = (int)slot->src.size();
     UploadFrames(slot->frames, nf, slot->src.data(), slot->n.data(), slot->stamp.data(), slot->seq.data(), slot->on_device, cfg, istream);
     ExtractInto(slot->frames, (size_t)nf, slot->stamp[0], cfg, slot, slot->kp, slot->tmin, slot->tmax, istream);
     LSB_CUDA(cudaEventRecord(slot->ready, istream));
-  }, !crowded);
+  }, mode == 0);
   return LSB_OK;
 }
 
@@ -851,8 +862,8 @@ void lsb_slam::UpdateMapsUsingTworld()
   Stats.is_keyframe = 1;
   KfCounter++;
   KfLastPose = Tworld;
-  const bool crowded = 3 * std::max(1, g_handles_in_flight.load(std::memory_order_relaxed)) > HostThreadBudget();
-  if (defer_map_update && use_lanes && !serial_types && !crowded) {
+  const int mode = HostMode();
+  if (defer_map_update && use_lanes && !serial_types && mode != 2) {
     // Deferred: the transform + bounding box of the three clouds is enqueued here (it reads this frame's keypoint buffers,
     // which the next frame's extraction recycles), the two read-back rounds of RollingGrid::Add are driven by the types' helper
     // threads on the type streams while the caller returns with the pose.  The next frame's sub-map selection is posted to the
@@ -877,7 +888,7 @@ void lsb_slam::UpdateMapsUsingTworld()
         LocalMaps[k].AddSort(jb.p, jb.n, false, now, true, tstream[k], lc);
         LocalMaps[k].AddMerge(jb.n, tstream[k], lc);
         LSB_CUDA(cudaEventRecord(ev_map_end[k], tstream[k]));
-      });
+      }, mode == 0);
     }
     map_pending = true;
     return;

@@ -19,8 +19,10 @@ frames = [seq.frame(sens, i) for i in range(n_before + 1)]
 dev = [g.DevUpload(f[0]) for f in frames]
 for i in range(n_before):
     g.AddFramesDev([dev[i]], [len(frames[i][0])], [frames[i][2]], [i + 1])
+g.Synchronize()
 rt.cudaProfilerStart()
 g.AddFramesDev([dev[n_before]], [len(frames[n_before][0])], [frames[n_before][2]], [n_before + 1])
+g.Synchronize()          # the frame's deferred map update is part of the profiled range
 rt.cudaProfilerStop()
 st = g.GetFrameStats()
 print("profiled frame %d: keypoints %s sub-maps %s key frame %d launches %d %.3f ms" % (
