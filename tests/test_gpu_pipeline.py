@@ -171,3 +171,44 @@ def test_setters_drop_staged_inputs_and_whole_loop_timer(gpu, synth):
     _same(want, got, "setter between prefetch and add")
     p.Synchronize()
     p.close()
+
+
+_MODE_SCRIPT = r"""
+import hashlib, sys
+sys.path.insert(0, %r)
+from lidarslam_b200.slam import Slam
+from lidarslam_b200 import capi
+from tools.synth import synth
+seq, sens = synth.Sequence(scene_seed=1234), synth.sensor("vlp16")
+frames = [seq.frame(sens, i) for i in range(10)]
+h = Slam(device=0)
+p = h.GetParams(); p.use_keypoints[2] = 1; h.SetParams(p)
+m = hashlib.sha256()
+h.PrefetchFrames([frames[0][0]], [frames[0][2]], [1])
+for i, (pts, _, stamp) in enumerate(frames):
+    if i + 1 < len(frames):
+        h.PrefetchFrames([frames[i + 1][0]], [frames[i + 1][2]], [i + 2])
+    h.AddFrames([pts], [stamp], [i + 1])
+    m.update(h.GetWorldTransform()[0].tobytes())
+for k in capi.KEYPOINT_TYPES:
+    m.update(h.GetMap(k).tobytes()); m.update(h.GetKeypoints(k).tobytes())
+print("HASH", m.hexdigest())
+"""
+
+
+def test_host_thread_policies_give_the_same_results(gpu):
+    """LSB_HOST_MODE 0 / 1 / 2 (helpers spinning / sleeping / everything on the caller's thread, nothing deferred) and
+    LSB_HOST_LANES=0: the host-side scheduling changes, the results do not (each policy in its own process: read at start-up)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    got = {}
+    for name, env in (("mode0", {"LSB_HOST_MODE": "0"}), ("mode1", {"LSB_HOST_MODE": "1"}), ("mode2", {"LSB_HOST_MODE": "2"}),
+                      ("lanes0", {"LSB_HOST_LANES": "0"}), ("sync", {"LSB_DEFER_MAP": "0"}), ("cubsort", {"LSB_MAP_OWN_SORT": "0"})):
+        e = dict(os.environ)
+        e.update(env)
+        r = subprocess.run([sys.executable, "-c", _MODE_SCRIPT % root], env=e, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, name + ": " + r.stdout + r.stderr
+        got[name] = [l for l in r.stdout.splitlines() if l.startswith("HASH")][0]
+    assert len(set(got.values())) == 1, got
