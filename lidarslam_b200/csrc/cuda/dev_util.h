@@ -7,6 +7,7 @@
 #include <cstdint>
 #include <cstddef>
 #include <cstdio>
+#include <cstring>
 #include <string>
 #include <vector>
 #include <stdexcept>
@@ -83,6 +84,7 @@ struct PinnedBuf {
     if (n <= cap) return;
     if (p) cudaFreeHost(p);
     LSB_CUDA(cudaMallocHost(&p, n * sizeof(T)));
+    std::memset(p, 0, n * sizeof(T));       // sequence words polled by host threads must not start out as garbage
     cap = n;
   }
 };

@@ -68,9 +68,11 @@ __device__ __forceinline__ int cell_coord(float v, float o, float cell, int n)
 // Pass 1: cell key of every point, its arrival rank inside the cell (atomic counter per cell).  Pass 2 (after an exclusive
 // scan of the counters): the point goes to cell_start[key] + rank.  The order of the points INSIDE a cell follows the
 // atomics and is not reproducible; no result depends on it (every search orders its candidates by (d2, cloud index)).
+// d_m != nullptr: the point count comes from device memory (launch sized for an upper bound before the host knew it)
 __global__ void k_cell_count(const lsb_point* __restrict__ pts, int m, KnnGridParams gp, uint32_t* __restrict__ key, uint32_t* __restrict__ rank,
-                             uint32_t* __restrict__ count)
+                             uint32_t* __restrict__ count, const uint32_t* __restrict__ d_m)
 {
+  if (d_m) m = (int)*d_m;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   const float4 p = reinterpret_cast<const float4*>(pts)[2 * i];
@@ -83,8 +85,10 @@ __global__ void k_cell_count(const lsb_point* __restrict__ pts, int m, KnnGridPa
 // The histogram is left all zero again (its scan has been taken): the next build starts from a clean table without a
 // memset of the whole grid (10 MB for the 2.5 M cells of a blob sub-map) on the frame's critical chain.
 __global__ void k_cell_scatter(const lsb_point* __restrict__ pts, int m, const uint32_t* __restrict__ key, const uint32_t* __restrict__ rank,
-                               const uint32_t* __restrict__ cell_start, float4* __restrict__ sorted, uint32_t* __restrict__ count)
+                               const uint32_t* __restrict__ cell_start, float4* __restrict__ sorted, uint32_t* __restrict__ count,
+                               const uint32_t* __restrict__ d_m)
 {
+  if (d_m) m = (int)*d_m;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
   const float4 p = reinterpret_cast<const float4*>(pts)[2 * (size_t)i];
@@ -863,8 +867,10 @@ bool knn_reuse_enabled()
   return on;
 }
 
-void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc)
+void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc,
+                    const uint32_t* d_m)
 {
+  if (d_m && !(lo && hi)) throw CudaError(LSB_E_INVALID, "KnnGrid::build: a device-side count needs host-known bounds");
   cloud = d_cloud;
   m = m_;
   if (m == 0) return;
@@ -908,7 +914,7 @@ void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float
     LSB_CUDA(cudaMemsetAsync(cell_count.p, 0, cell_count.cap * sizeof(uint32_t), s));
   }
   const unsigned G = div_up(m, TPB);
-  k_cell_count<<<G, TPB, 0, s>>>(d_cloud, M, gp, key_a.p, idx_a.p, cell_count.p); LSB_LAUNCH_CHECK(); lc.add();
+  k_cell_count<<<G, TPB, 0, s>>>(d_cloud, M, gp, key_a.p, idx_a.p, cell_count.p, d_m); LSB_LAUNCH_CHECK(); lc.add();
   // (a single-pass scan of our own - select.cuh - was measured here: one launch less, but 26 instead of 15 us for the 2.5 M cells
   //  of a blob sub-map, and 1 - 3 % fewer frames per second)
   size_t tb = 0;
@@ -916,7 +922,7 @@ void KnnGrid::build(const lsb_point* d_cloud, size_t m_, float cell, const float
   cub_tmp.reserve(tb + 256, s);
   tb = cub_tmp.cap;
   LSB_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, cell_count.p, cell_start.p, nc1, s)); lc.add(2);   // cell_start[ncells] = m
-  k_cell_scatter<<<G, TPB, 0, s>>>(d_cloud, M, key_a.p, idx_a.p, cell_start.p, sorted.p, cell_count.p); LSB_LAUNCH_CHECK(); lc.add();
+  k_cell_scatter<<<G, TPB, 0, s>>>(d_cloud, M, key_a.p, idx_a.p, cell_start.p, sorted.p, cell_count.p, d_m); LSB_LAUNCH_CHECK(); lc.add();
 }
 
 void KnnGrid::search(const float* d_q, size_t nq, int k, float cap_dist, int32_t* d_idx, float* d_d2, int32_t* d_nf, bool entry_major, cudaStream_t s, LaunchCounter& lc) const

@@ -51,7 +51,11 @@ struct KnnGrid {
   void clear() { cloud = nullptr; m = 0; }
   // Builds the grid over d_cloud[0..m).  lo/hi: host-known bounds containing every
   // point (nullptr => computed on the device, one stream sync).
-  void build(const lsb_point* d_cloud, size_t m, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc);
+  // d_m != nullptr (needs lo / hi): the number of points is read from device memory, `m` is an upper bound that sizes the
+  // launches; the caller sets the true count with set_count() once it knows it (before any search).
+  void build(const lsb_point* d_cloud, size_t m, float cell, const float* lo, const float* hi, cudaStream_t s, LaunchCounter& lc,
+             const uint32_t* d_m = nullptr);
+  void set_count(size_t true_m) { m = true_m; if (m == 0) cloud = nullptr; }
 
   // kNN of nq float queries (xyz packed).  idx_out/d2_out: [nq * k], missing
   // entries -1 / +inf.  nfound_out may be nullptr.  Layout: query-major [nq][k], or

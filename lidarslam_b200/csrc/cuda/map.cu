@@ -271,10 +271,14 @@ __global__ void k_apply_segments(const unsigned long long* __restrict__ skey, co
 }
 
 // merge by rank: both key lists are sorted and disjoint
+// d_nb != nullptr: the number of inserts is read from device memory (the launch was sized for the worst case before the host knew it)
 __global__ void k_merge(const unsigned long long* __restrict__ ka, const lsb_point* __restrict__ pa, const uint32_t* __restrict__ ca, int na,
                         const unsigned long long* __restrict__ kb, const lsb_point* __restrict__ pb, const uint32_t* __restrict__ cb, int nb,
-                        unsigned long long* __restrict__ ko, lsb_point* __restrict__ po, uint32_t* __restrict__ co)
+                        unsigned long long* __restrict__ ko, lsb_point* __restrict__ po, uint32_t* __restrict__ co,
+                        const uint32_t* __restrict__ d_nb = nullptr)
 {
+  if (d_nb) nb = (int)*d_nb;
+  if (d_nb && nb == 0) return;          // nothing to insert: the map stays where it is
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < na) {
     const unsigned long long k = ka[i];
@@ -508,6 +512,24 @@ static void wait_info(const uint32_t* h_info, uint32_t seq, cudaStream_t s)
   }
 }
 
+// the box a fused box kernel of stream s publishes in pinned memory (slam_kernels.cu: sequence word behind the six bounds)
+static void wait_box(const float* h_bbox, int seq, cudaStream_t s)
+{
+  const volatile int* flag = reinterpret_cast<const volatile int*>(h_bbox) + 6;
+  unsigned spins = 0;
+  while (*flag != seq) {
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+    if ((++spins & 0x3fffu) == 0) {
+      const cudaError_t rc = cudaStreamQuery(s);
+      if (rc == cudaErrorNotReady) continue;
+      LSB_CUDA(rc);
+      if (*flag != seq) throw CudaError(LSB_E_CUDA, "RollingGrid: the stream is idle but the keypoints' box never arrived");
+    }
+  }
+}
+
 static GridGeom make_geom(const RollingGridGpu& m)
 {
   GridGeom g;
@@ -591,6 +613,7 @@ void RollingGridGpu::Roll(const float mn[3], const float mx[3], cudaStream_t s, 
 // key / sort / replay / gather), AddMerge (rank merge of the new leaves).
 void RollingGridGpu::AddBegin(const lsb_point* d_cloud, size_t n, bool roll, cudaStream_t s, LaunchCounter& lc)
 {
+  box_by_kernel = false;
   if (n == 0) return;
   if (roll) cloud_bbox_async(d_cloud, n, d_bbox, h_bbox, s, lc);
 }
@@ -600,7 +623,9 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
   if (n == 0) return;
   float mn[3], mx[3];
   if (roll) {
-    LSB_CUDA(cudaStreamSynchronize(s));
+    if (box_by_kernel) wait_box(h_bbox.p, box_seq, s);     // published by the tail of the ICP loop (k_finish_keypoints)
+    else LSB_CUDA(cudaStreamSynchronize(s));
+    box_by_kernel = false;
     bbox_decode(h_bbox.p, mn, mx);
     Roll(mn, mx, s, lc);
   }
@@ -678,6 +703,16 @@ void RollingGridGpu::AddSort(const lsb_point* d_cloud, size_t n, bool fixed, dou
                                            sel_state.ticket.p, epoch, tiles, d_info.p, h_info.p, info_seq);
     LSB_LAUNCH_CHECK(); lc.add();
   }
+  // The merge by rank is enqueued at once, sized for the worst case (every point a new leaf), and reads the number of inserts
+  // from device memory: it runs while the count is on its way to the host (AddMerge), which only does the bookkeeping.
+  // Output: a second set of map arrays (merge_*: keys_b / pts_b / counts_b are the roll's and the replay's scratch).
+  {
+    const size_t total_max = n_entries + n;
+    merge_keys.reserve(total_max, s); merge_pts.reserve(total_max, s); merge_counts.reserve(total_max, s);
+    k_merge<<<div_up(total_max, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, (int)n_entries, ins_keys.p, ins_pts.p, ins_counts.p, 0,
+                                                   merge_keys.p, merge_pts.p, merge_counts.p, d_info.p + 1);
+    LSB_LAUNCH_CHECK(); lc.add();
+  }
 }
 
 void RollingGridGpu::AddMerge(size_t n, cudaStream_t s, LaunchCounter& lc)
@@ -687,15 +722,9 @@ void RollingGridGpu::AddMerge(size_t n, cudaStream_t s, LaunchCounter& lc)
   if (h_info.p[7]) throw CudaError(LSB_E_CUDA, "RollingGrid::Add: a leaf key fell outside the compact key range (internal bound error)");
   const bool updated = h_info.p[0] != 0;
   const size_t n_ins = h_info.p[1];
-  if (n_ins) {
-    const size_t total = n_entries + n_ins;
-    keys_b.reserve(total, s); pts_b.reserve(total, s); counts_b.reserve(total, s);
-    // pts_b / counts_b were the segment scratch: the inserts were already gathered out of them
-    k_merge<<<div_up(total, TPB), TPB, 0, s>>>(keys.p, pts.p, counts.p, (int)n_entries, ins_keys.p, ins_pts.p, ins_counts.p, (int)n_ins,
-                                               keys_b.p, pts_b.p, counts_b.p);
-    LSB_LAUNCH_CHECK(); lc.add();
-    keys.swap(keys_b); pts.swap(pts_b); counts.swap(counts_b);
-    n_entries = total;
+  if (n_ins) {          // the merged map was written by the launch AddSort enqueued: it becomes the map
+    keys.swap(merge_keys); pts.swap(merge_pts); counts.swap(merge_counts);
+    n_entries += n_ins;
     NbPoints += (unsigned)n_ins;
   }
   if (updated) ResetTree();
@@ -801,19 +830,44 @@ void RollingGridGpu::SubMapSelectDevice(int minNbPoints, cudaStream_t s, LaunchC
 
 void RollingGridGpu::SubMapFinish(cudaStream_t s, LaunchCounter& lc)
 {
-  // the selection kernel leaves the count in pinned memory (publish_info); the box was published by an earlier kernel of the stream
-  if (n_entries) wait_info(h_info.p, info_seq, s);
-  else if (sub_from_device) LSB_CUDA(cudaStreamSynchronize(s));
-  if (sub_from_device) {
+  const GridGeom g = make_geom(*this);
+  const float o[3] = {g.ox, g.oy, g.oz};
+  auto grid_bounds = [&](float blo[3], float bhi[3]) {
+    // every submap point lies in an outer voxel of [lo, hi]: host-known kNN grid bounds (with slack)
+    for (int a = 0; a < 3; ++a) {
+      blo[a] = o[a] + ((float)sub_lo[a] - 0.5f) * g.res - 0.01f * g.res;
+      bhi[a] = o[a] + ((float)sub_hi[a] + 0.5f) * g.res + 0.01f * g.res;
+    }
+    return sub_lo[0] <= sub_hi[0] && sub_lo[1] <= sub_hi[1] && sub_lo[2] <= sub_hi[2];
+  };
+  auto bounds_from_box = [&] {
     float mn[3], mx[3];
     bbox_decode(h_bbox.p, mn, mx);
-    const GridGeom g = make_geom(*this);
-    const float o[3] = {g.ox, g.oy, g.oz};
     for (int a = 0; a < 3; ++a) {
       sub_lo[a] = std::max(pos2vox(mn[a], o[a], g.res), 0);
       sub_hi[a] = std::min(pos2vox(mx[a], o[a], g.res), GridSize - 1);
     }
+  };
+  float blo[3], bhi[3];
+  if (sub_from_device && n_entries && !sub_filter && box_seq > 0) {
+    // The box arrives first (the head kernel of the chain published it): the kNN grid over the sub-map is enqueued at once,
+    // sized for the worst case (the whole map selected) with the sub-map's size read from device memory, and runs while the
+    // size is on its way to the host.
+    wait_box(h_bbox.p, box_seq, s);
+    bounds_from_box();
+    if (grid_bounds(blo, bhi)) {
+      tree_valid = true;
+      grid.build(submap.p, n_entries, knn_cell_factor * (float)LeafSize, blo, bhi, s, lc, d_info.p + 2);
+      wait_info(h_info.p, info_seq, s);
+      n_submap = h_info.p[2];
+      grid.set_count(n_submap);
+      return;
+    }
   }
+  // the selection kernel leaves the count in pinned memory (publish_info); the box was published by an earlier kernel of the stream
+  if (n_entries) wait_info(h_info.p, info_seq, s);
+  else if (sub_from_device) LSB_CUDA(cudaStreamSynchronize(s));
+  if (sub_from_device) bounds_from_box();
   if (n_entries) {
     n_submap = h_info.p[2];
     if (sub_filter && (int)n_submap < sub_min_nb) {
@@ -822,15 +876,7 @@ void RollingGridGpu::SubMapFinish(cudaStream_t s, LaunchCounter& lc)
       n_submap += h_info.p[2];
     }
   }
-  // every submap point lies in an outer voxel of [lo, hi]: host-known kNN grid bounds (with slack)
-  const GridGeom g = make_geom(*this);
-  const float o[3] = {g.ox, g.oy, g.oz};
-  float blo[3], bhi[3];
-  for (int a = 0; a < 3; ++a) {
-    blo[a] = o[a] + ((float)sub_lo[a] - 0.5f) * g.res - 0.01f * g.res;
-    bhi[a] = o[a] + ((float)sub_hi[a] + 0.5f) * g.res + 0.01f * g.res;
-  }
-  const bool bounded = sub_lo[0] <= sub_hi[0] && sub_lo[1] <= sub_hi[1] && sub_lo[2] <= sub_hi[2];
+  const bool bounded = grid_bounds(blo, bhi);
   build_grid(bounded ? blo : nullptr, bounded ? bhi : nullptr, s, lc);
 }
 

@@ -27,6 +27,9 @@ struct RollingGridGpu {
   DevBuf<unsigned long long> keys, keys_b;
   DevBuf<lsb_point> pts, pts_b;
   DevBuf<uint32_t> counts, counts_b;
+  DevBuf<unsigned long long> merge_keys;   // output of the merge launched ahead of the insert count (swapped in when there are inserts)
+  DevBuf<lsb_point> merge_pts;
+  DevBuf<uint32_t> merge_counts;
 
   // submap (target of the localization kNN)
   DevBuf<lsb_point> submap;
@@ -44,6 +47,9 @@ struct RollingGridGpu {
   DevBuf<unsigned char> cub_tmp;
   PinnedBuf<uint32_t> h_info;            // [16]: [0..7] counters, [8] sequence word of the kernel that published them
   uint32_t info_seq = 0;
+  bool box_by_kernel = false;            // h_bbox is being written by a fused box kernel with sequence word box_seq (else: by a copy on the stream)
+  int box_seq = 0;                       // sequence word of the last box published in h_bbox[6] (fused box kernels)
+  int NextBoxSeq() { box_seq = (box_seq + 1 > 0) ? box_seq + 1 : 1; return box_seq; }
   PinnedBuf<float> h_bbox;
   DevBuf<float> d_bbox;
   Sort32 sorter;                         // single-launch radix sort of the cloud's compact leaf keys (sort32.cu)

@@ -64,7 +64,7 @@ __global__ void k_transform_bbox(lsb_point* __restrict__ pts, int n, Iso3d T, in
 // to arrive (ticket counter, reset by that block) folds the `nb` partials from `first` on and publishes the box in device
 // memory and in pinned host memory (UVA: the host reads it after the stream's next synchronisation, no copy enqueued).
 __device__ __forceinline__ void box_reduce_publish(int mn[3], int mx[3], int first, int nb, int* __restrict__ partial,
-                                                   unsigned* __restrict__ counter, int* __restrict__ d_bb, int* __restrict__ h_bb)
+                                                   unsigned* __restrict__ counter, int* __restrict__ d_bb, int* __restrict__ h_bb, int seq)
 {
   __shared__ int sh[TPB / 32][6];
   __shared__ bool is_last;
@@ -115,7 +115,11 @@ __device__ __forceinline__ void box_reduce_publish(int mn[3], int mx[3], int fir
     h_bb[threadIdx.x] = f;
     __threadfence_system();
   }
-  if (threadIdx.x == 0) *counter = 0u;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *counter = 0u;
+    reinterpret_cast<volatile int*>(h_bb)[6] = seq;      // sequence word: a host thread may poll for the box instead of synchronising
+  }
 }
 
 // Tail of the device-resident localization loop, ONE launch for the three keypoint clouds: the last undistortion refinement
@@ -150,7 +154,7 @@ __global__ void __launch_bounds__(TPB) k_finish_keypoints(FinishArgs a, const Ic
     reinterpret_cast<uint4*>(o)[1] = w;
     mn[0] = mx[0] = f2ord_k(x); mn[1] = mx[1] = f2ord_k(y); mn[2] = mx[2] = f2ord_k(z);
   }
-  box_reduce_publish(mn, mx, a.b0[t], nb, partial, counter + t, a.d_bb[t], a.h_bb[t]);
+  box_reduce_publish(mn, mx, a.b0[t], nb, partial, counter + t, a.d_bb[t], a.h_bb[t], a.seq[t]);
 }
 
 // Head of the sub-map selection of one keypoint type, one launch: the undistortion still pending on the cloud (k_undistort)
@@ -158,7 +162,7 @@ __global__ void __launch_bounds__(TPB) k_finish_keypoints(FinishArgs a, const Ic
 // pcl::getMinMax3D (k_transformed_bbox), published like the box above.
 __global__ void __launch_bounds__(TPB) k_undistort_transformed_bbox(lsb_point* __restrict__ pts, int n, Interpolator it, int undistort, Iso3d T,
                                                                     int* __restrict__ partial, unsigned* __restrict__ counter,
-                                                                    int* __restrict__ d_bb, int* __restrict__ h_bb)
+                                                                    int* __restrict__ d_bb, int* __restrict__ h_bb, int seq)
 {
   int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
   const int i = blockIdx.x * TPB + threadIdx.x;
@@ -176,7 +180,7 @@ __global__ void __launch_bounds__(TPB) k_undistort_transformed_bbox(lsb_point* _
     const float wz = (float)(T.R.m[6] * x + T.R.m[7] * y + T.R.m[8] * z + T.t.z);
     mn[0] = mx[0] = f2ord_k(wx); mn[1] = mx[1] = f2ord_k(wy); mn[2] = mx[2] = f2ord_k(wz);
   }
-  box_reduce_publish(mn, mx, 0, (int)gridDim.x, partial, counter, d_bb, h_bb);
+  box_reduce_publish(mn, mx, 0, (int)gridDim.x, partial, counter, d_bb, h_bb, seq);
 }
 
 __global__ void k_aggregate(lsb_point* __restrict__ pts, int n, double timeOffset, Iso3d T, int applyT)
@@ -314,7 +318,8 @@ void dev_finish_keypoints(FinishArgs a, const IcpState* st, bool refine, DevBuf<
 }
 
 void dev_undistort_transformed_bbox(lsb_point* d_pts, size_t n, const Interpolator* pending, const Iso3d& T, DevBuf<int>& partial,
-                                    DevBuf<unsigned>& counter, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc)
+                                    DevBuf<unsigned>& counter, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, int seq, cudaStream_t s,
+                                    LaunchCounter& lc)
 {
   if (!n) return;
   const unsigned nb = div_up(n, TPB);
@@ -324,7 +329,7 @@ void dev_undistort_transformed_bbox(lsb_point* d_pts, size_t n, const Interpolat
   Interpolator none;
   none.reset();
   k_undistort_transformed_bbox<<<nb, TPB, 0, s>>>(d_pts, (int)n, pending ? *pending : none, pending ? 1 : 0, T, partial.p, counter.p,
-                                                  reinterpret_cast<int*>(d_bbox.p), reinterpret_cast<int*>(h_bbox.p));
+                                                  reinterpret_cast<int*>(d_bbox.p), reinterpret_cast<int*>(h_bbox.p), seq);
   LSB_LAUNCH_CHECK(); lc.add();
 }
 

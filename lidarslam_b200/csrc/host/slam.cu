@@ -710,7 +710,7 @@ void lsb_slam::Localization()
       // pending undistortion and the box of the cloud under the predicted pose in one launch (before ClearOldPoints, which does
       // not read the keypoints); the box stays on the device for the selection, box and sub-map size come back with one synchronisation
       dev_undistort_transformed_bbox(CurrentKeypoints[k].buf.p, CurrentKeypoints[k].n, HasPendingRefinement ? &PendingRefinement : nullptr, Tworld,
-                                     map.box_partial, map.box_counter, map.d_bbox, map.h_bbox, ts, lc);
+                                     map.box_partial, map.box_counter, map.d_bbox, map.h_bbox, map.NextBoxSeq(), ts, lc);
     }
     if (map.IsTimeThreshold()) map.ClearOldPoints(CurrentTime, ts, lc);
     if (CurrentKeypoints[k].n) {
@@ -829,6 +829,8 @@ const MatchWorkspace::LmHostBlock& lsb_slam::RunIcpLoop(int stage, const lsb_mat
       LocalMaps[k].d_bbox.reserve(8, stream); LocalMaps[k].h_bbox.reserve(8);
       fa.cur[k] = CurrentKeypoints[k].buf.p; fa.world[k] = w.buf.p; fa.n[k] = (int)nk[k];
       fa.d_bb[k] = reinterpret_cast<int*>(LocalMaps[k].d_bbox.p); fa.h_bb[k] = reinterpret_cast<int*>(LocalMaps[k].h_bbox.p);
+      fa.seq[k] = LocalMaps[k].NextBoxSeq();
+      LocalMaps[k].box_by_kernel = nk[k] > 0;      // RollingGrid::Add polls for this box instead of synchronising its stream
     }
     dev_finish_keypoints(fa, d_icp.p, refined, finish_partial, finish_counter, stream, lc);
     finish_enqueued = true;
@@ -918,7 +920,7 @@ const DCloud& lsb_slam::WorldKeypoints(int k, cudaStream_t s, RollingGridGpu* bo
     w.n = c.n;
     if (c.n) {
       LSB_CUDA(cudaMemcpyAsync(w.buf.p, c.buf.p, c.n * sizeof(lsb_point), cudaMemcpyDeviceToDevice, stream));
-      if (box) { dev_transform_bbox_async(w.buf.p, w.n, Tworld, box->d_bbox, box->h_bbox, stream, lc); if (boxed) *boxed = true; }
+      if (box) { box->box_by_kernel = false; dev_transform_bbox_async(w.buf.p, w.n, Tworld, box->d_bbox, box->h_bbox, stream, lc); if (boxed) *boxed = true; }
       else dev_transform(w.buf.p, w.n, Tworld, stream, lc);
     }
     WorldKeypointsValid[k] = true;

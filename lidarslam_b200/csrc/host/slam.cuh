@@ -228,13 +228,15 @@ struct FinishArgs {
   int b0[4];            // first block of each type (filled by dev_finish_keypoints)
   int* d_bb[3];         // box of the world cloud, ordered-int encoding: device copy and pinned host copy (RollingGridGpu::d_bbox / h_bbox)
   int* h_bb[3];
+  int seq[3];           // sequence word written behind each box (h_bb[k][6])
 };
 void dev_finish_keypoints(FinishArgs a, const IcpState* st, bool refine, DevBuf<int>& partial, DevBuf<unsigned>& counter, cudaStream_t s,
                           LaunchCounter& lc);
 // head of a type's sub-map selection: pending undistortion (nullptr: none) + box of the cloud under T, box published in d_bbox and
 // in h_bbox (pinned, readable after the stream's next synchronisation); one launch
 void dev_undistort_transformed_bbox(lsb_point* d_pts, size_t n, const Interpolator* pending, const Iso3d& T, DevBuf<int>& partial,
-                                    DevBuf<unsigned>& counter, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc);
+                                    DevBuf<unsigned>& counter, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox, int seq, cudaStream_t s,
+                                    LaunchCounter& lc);   // seq: written behind the box in h_bbox[6] (RollingGridGpu::box_seq)
 // device helpers implemented in slam_kernels.cu
 void dev_transform(lsb_point* d_pts, size_t n, const Iso3d& T, cudaStream_t s, LaunchCounter& lc);                     // Utils::TransformPoint
 // dev_transform + the bounding box of the result (ordered-int encoding in d_bbox, copy to h_bbox enqueued): no second pass
