@@ -86,6 +86,10 @@ def main():
     sens = synth.sensor("os128")
     sq = synth.Sequence(scene_seed=1234)
     frames = [sq.frame(sens, i) for i in range(warm + K + 1)]
+    if os.environ.get("PROBE_ONLY") == "both":      # A/B runs: the pipelined loop only, several repetitions
+        for rep in range(int(os.environ.get("PROBE_REPS", "4"))):
+            run(frames, warm, K, True, True, "deferred + prefetch")
+        return
     for rep in range(2):
         run(frames, warm, K, False, False, "synchronous")
         run(frames, warm, K, True, False, "deferred map update")
