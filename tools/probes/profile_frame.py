@@ -7,7 +7,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspa
 from lidarslam_b200.slam import Slam
 from tools.synth import synth
 
-n_before = int(sys.argv[1]) if len(sys.argv) > 1 else 11
+n_before = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 sensor = sys.argv[2] if len(sys.argv) > 2 else "os128"
 rt = ctypes.CDLL("libcudart.so.12")
 g = Slam(device=0)

@@ -34,7 +34,7 @@ def main(raw, out_txt, out_json, searches=9):
     tot = sum(a[1] for a in agg.values())
     lib = sum(a[1] for k, a in agg.items() if k.startswith("cub::"))
     nlib = sum(a[0] for k, a in agg.items() if k.startswith("cub::"))
-    out = ["# per-kernel totals of ONE steady-state OS-128 frame (frame 11 of the sequence, a key frame; tools/probes/profile_frame.py)",
+    out = ["# per-kernel totals of ONE steady-state OS-128 frame (frame 8 of the sequence: a key frame that follows a key frame, so the sub-map selection and the map update are both in it; tools/probes/profile_frame.py)",
            "# from ncu --set full --clock-control none: cold caches, serialised, GPU at idle clocks between replays -> SHARES, not absolutes",
            "# columns: launches, total us, share of kernel time, DRAM MB (read + write), kernel",
            "# %d launches, %.1f us of kernel time; library (CUB) share %.1f %% of kernel time in %d launches" % (len(data), tot, 100 * lib / tot, nlib)]
