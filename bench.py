@@ -14,8 +14,8 @@ value is ranks x frames / max-over-ranks time ("weak" scaling).
            (its keypoint extraction overlaps frame i's ICP) and calls lsb_add_frames_dev(frame i), whose
            map update is deferred behind the returned pose; the region holds K extractions, K ICP
            loops and K map updates.  Inputs larger than L2: K + 1 distinct frames, each read once.
-  e2e    : the same loop through lsb_prefetch_frames / lsb_add_frames with pinned HOST buffers
-           (every frame's H2D copy inside the region), wall clock around the K steps and the final
+  e2e    : the same loop through lsb_prefetch_frames / lsb_add_frames with pinned HOST buffers, inputs handed
+           in two calls ahead (every frame's H2D copy inside the region: K uploads, K extractions), wall clock around the K steps and the final
            lsb_synchronize, pose read back on the host every step.
   sync_api : the round-1/2 method for continuity - one fully synchronous call per step (no
            prefetch, map update inside the call), CUDA events per call (device) / wall clock per
@@ -314,7 +314,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    frames = make_frames(a.sensor, W + K + 1, shard.sequence_seed(rank))   # one independent sequence per rank (+ 1: the last step prefetches too)
+    frames = make_frames(a.sensor, W + K + 2, shard.sequence_seed(rank))   # one independent sequence per rank (+ 2: the last steps prefetch too)
     npts = len(frames[0][0])
 
     # ---------------- kernel pass: per-kernel durations (not the throughput number) ------
@@ -389,24 +389,26 @@ def main():
     # ---------------- e2e: host buffers, the same pipelined loop, wall clock -----------------------
     e = Slam(device=local)
     configure(e)
-    pins = [pinned_points(npts) for _ in range(K + 1)]     # the sensor driver's ring of pinned buffers, filled outside the timed region
-    for j in range(K + 1):
+    pins = [pinned_points(npts) for _ in range(K + 2)]     # the sensor driver's ring of pinned buffers, filled outside the timed region
+    for j in range(K + 2):
         pins[j][0][:] = frames[W + j][0]
     for i in range(W):
         e.AddFrame(frames[i][0], frames[i][1], i + 1)
     e.PrefetchFrames([pins[0][0]], [frames[W][1]], [W + 1])
+    e.PrefetchFrames([pins[1][0]], [frames[W + 1][1]], [W + 2])
     e.Synchronize()
     barrier()
     e2e_steps, d2h, h2d = [], 0, 0
     t_e0 = time.perf_counter()
     for j in range(K):
         i = W + j
-        e.PrefetchFrames([pins[j + 1][0]], [frames[i + 1][1]], [i + 2])     # H2D of the next frame + its extraction, behind this call
+        # two calls ahead: the H2D copy starts now, the extraction when the next call begins (beside that frame's map update)
+        e.PrefetchFrames([pins[j + 2][0]], [frames[i + 2][1]], [i + 3])
         t0 = time.perf_counter()
         e.AddFrames([pins[j][0]], [frames[i][1]], [i + 1])                  # pose of frame i (its H2D was enqueued one step earlier, inside the region)
         T, _ = e.GetWorldTransform()                                        # the step's result on the host
         e2e_steps.append(time.perf_counter() - t0)
-        h2d += pins[j + 1][0].nbytes
+        h2d += pins[j + 2][0].nbytes
     e.Synchronize()
     e2e_s = time.perf_counter() - t_e0
     barrier()

@@ -221,7 +221,7 @@ LSB_API int lsb_add_frames_dev(lsb_slam* h, int n_frames, const lsb_point* const
  *  - lsb_prefetch_frames hands the NEXT input in ahead of time (a bag replay, a driver queue): its upload and keypoint extraction
  *    (Slam::ExtractKeypoints, Slam.cxx:746-810, which reads nothing but the frame and the extractor parameters) run on an ingest
  *    stream while the current frame is in its ICP loop.  lsb_add_frames / lsb_add_frames_dev called later with the same buffer
- *    pointers, sizes and stamps picks the staged keypoints up; any other input drops what is staged.  At most two inputs are
+ *    pointers, sizes and stamps picks the staged keypoints up; any other input drops what is staged.  At most three inputs are
  *    staged at a time (LSB_E_CAPACITY beyond).  The buffers must stay valid and unchanged until the matching add call returns.
  *    Parameter setters drop staged inputs (they were extracted with the old parameters). */
 LSB_API int lsb_prefetch_frames(lsb_slam* h, int n_frames, const lsb_point* const* frames, const size_t* n,

@@ -311,7 +311,7 @@ int lsb_slam::PrefetchFrames(int n_frames, const lsb_point* const* frames, const
   if (n_frames <= 0) return LSB_E_INVALID;
   StagedInput* slot = nullptr;
   for (auto& sl : staged) if (!sl.valid) { slot = &sl; break; }
-  if (!slot) throw CudaError(LSB_E_CAPACITY, "lsb_prefetch_frames: two inputs are staged already; add one of them first");
+  if (!slot) throw CudaError(LSB_E_CAPACITY, "lsb_prefetch_frames: three inputs are staged already; add one of them first");
   slot->valid = true;
   slot->on_device = on_device;
   slot->src.assign(frames, frames + n_frames);
@@ -321,9 +321,20 @@ int lsb_slam::PrefetchFrames(int n_frames, const lsb_point* const* frames, const
   if (seq) slot->seq.assign(seq, seq + n_frames);
   const StageCfg cfg = MakeStageCfg();
   const int mode = HostMode();
-  slot->ticket = Worker().post([this, slot, cfg] {
+  int ahead = 0;                                   // inputs staged and not yet added, this one included
+  for (auto& sl : staged) ahead += sl.valid ? 1 : 0;
+  const unsigned my_seq = ++stage_seq;
+  slot->stage_seq = my_seq;
+  // the call before this input's own: the (ahead - 1)-th AddFrames from now
+  const unsigned gate = frames_started.load(std::memory_order_relaxed) + (unsigned)(ahead - 1);
+  slot->ticket = Worker().post([this, slot, cfg, gate, my_seq] {
     const int nf = (int)slot->src.size();
     UploadFrames(slot->frames, nf, slot->src.data(), slot->n.data(), slot->stamp.data(), slot->seq.data(), slot->on_device, cfg, istream);
+    unsigned spins = 0;
+    while ((int)(frames_started.load(std::memory_order_acquire) - gate) < 0 &&
+           (int)(stage_release.load(std::memory_order_acquire) - my_seq) < 0) {
+      if ((++spins & 63u) == 0) std::this_thread::yield();
+    }
     ExtractInto(slot->frames, (size_t)nf, slot->stamp[0], cfg, slot, slot->kp, slot->tmin, slot->tmax, istream);
     LSB_CUDA(cudaEventRecord(slot->ready, istream));
   }, mode == 0);
@@ -365,6 +376,7 @@ void lsb_slam::Quiesce(bool drop_staged)
   LSB_CUDA(cudaSetDevice(device));
   std::exception_ptr first;
   try { FinishMapStats(); } catch (...) { first = std::current_exception(); }
+  stage_release.store(stage_seq, std::memory_order_release);      // nobody waits behind a gate
   for (auto& sl : staged) {
     if (!sl.valid) continue;
     try { Worker().wait(sl.ticket); } catch (...) { if (!first) first = std::current_exception(); sl.valid = false; }
@@ -401,6 +413,7 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
     for (auto& sl : staged) any = any || sl.valid;
     if (any) Quiesce(true);
   }
+  frames_started.fetch_add(1, std::memory_order_release);
   if (map_stats_pending && !map_pending) map_stats_pending = false;   // nobody asked for the previous frame's statistics
   const unsigned launches0 = lc.n;
   LSB_CUDA(cudaEventRecord(ev[0], stream));
@@ -413,6 +426,7 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   }
   for (int i = 0; i < n_frames; ++i) Stats.n_points += (uint32_t)n[i];
   if (hit) {
+    stage_release.store(hit->stage_seq, std::memory_order_release);   // (added out of turn: its own gate may still be closed)
     Worker().wait(hit->ticket);               // upload + extraction enqueued and their counts read back (rethrows)
     FramePool.swap(hit->frames);
     LSB_CUDA(cudaStreamWaitEvent(stream, hit->ready, 0));

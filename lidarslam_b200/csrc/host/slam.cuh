@@ -86,7 +86,7 @@ struct lsb_slam {
   //     selected, or by whatever entry point looks at the maps first.
   // (2) Prefetch (lsb_prefetch_frames): upload + keypoint extraction of a frame handed in ahead of time run on the ingest
   //     stream while the current frame is in its ICP loop (which leaves most SMs idle); AddFrames of that frame finds its
-  //     keypoints ready.  Two slots, so that frame t + 2 can be staged before frame t + 1 is consumed.
+  //     keypoints ready.  Three slots: frames t + 1 and t + 2 can both be staged before frame t is consumed (the upload of t + 2 then has a whole frame period).
   std::unique_ptr<lsb::AsyncWorker> worker;
   lsb::AsyncWorker& Worker() { if (!worker) worker.reset(new lsb::AsyncWorker(device)); return *worker; }
   bool defer_map_update = true;          // LSB_DEFER_MAP=0 / lsb_set_pipelining(h, 0): the map update ends inside AddFrames
@@ -108,7 +108,7 @@ struct lsb_slam {
   };
   struct StagedInput {
     bool valid = false, on_device = false;
-    unsigned ticket = 0;
+    unsigned ticket = 0, stage_seq = 0;
     std::vector<const lsb_point*> src;
     std::vector<size_t> n;
     std::vector<uint64_t> stamp;
@@ -119,8 +119,14 @@ struct lsb_slam {
     std::map<int, std::unique_ptr<lsb::ExtractorGpu>> extractors;
     std::vector<int> used_ids;           // extractors that ran for this input
     cudaEvent_t ready = nullptr;         // recorded on the ingest stream behind the last kernel of the job
-  } staged[2];
+  } staged[3];
   cudaStream_t istream = nullptr;        // ingest stream (lowest priority: the ICP of the current frame goes first)
+  // An input staged TWO calls ahead is uploaded at once but extracted only when the call before its own begins: its extraction
+  // then runs beside that frame's map update and sub-map selection (short launches that leave the SMs idle), as it does for
+  // device-resident inputs, instead of trailing the upload into the first matching pass.  frames_started counts AddFrames calls;
+  // stage_release forces every staged job up to that sequence number through (set by whoever is about to wait for one).
+  std::atomic<unsigned> frames_started{0}, stage_release{0};
+  unsigned stage_seq = 0;
   std::mutex ke_mu;                      // extractor instances / their scalar state (parameters, azimuth estimate) change hands
   int PrefetchFrames(int n_frames, const lsb_point* const* frames, const size_t* n, const uint64_t* stamp_us, const uint32_t* seq, bool on_device);
   StageCfg MakeStageCfg() const;

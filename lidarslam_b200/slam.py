@@ -50,7 +50,7 @@ class Slam(capi.CApi):
         """frames: numpy point arrays that stay alive and unchanged until the matching AddFrames returns"""
         frames = [capi.as_points(f) for f in frames]
         self._staged_keep = getattr(self, "_staged_keep", []) + [frames]
-        self._staged_keep = self._staged_keep[-3:]
+        self._staged_keep = self._staged_keep[-4:]
         return self._check(self.lib.lsb_prefetch_frames(self.h, *self._frame_args([f.ctypes.data for f in frames], [len(f) for f in frames], stamps_us, seqs)))
 
     def SetPipelining(self, defer_map_update):

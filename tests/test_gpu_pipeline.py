@@ -128,13 +128,15 @@ def test_prefetch_from_device_buffers_dual_sensor_and_mismatch(gpu, synth):
     sizes = [[len(f) for f in fs] for fs, _ in frames]
     p.PrefetchFramesDev(dev[0], sizes[0], frames[0][1], [1, 1])
     for i, (fs, st) in enumerate(frames):
-        if i + 1 < n and i != 3:
+        if i + 1 < n and i not in (3, 5):
             p.PrefetchFramesDev(dev[i + 1], sizes[i + 1], frames[i + 1][1], [i + 2, i + 2])
         if i == 2:
-            # a third staged input is refused, and what is staged survives the refusal
+            # frames 2 and 3 are staged; a third one (two calls ahead: uploaded now, extracted when frame 3's call begins) is
+            # accepted, a fourth is refused, and what is staged survives the refusal
+            p.PrefetchFramesDev(dev[i + 2], sizes[i + 2], frames[i + 2][1], [i + 3, i + 3])
             with pytest.raises(RuntimeError):
-                p.PrefetchFramesDev(dev[i + 2], sizes[i + 2], frames[i + 2][1], [i + 3, i + 3])
-        # frame 4 is never staged: adding it drops the staged frame 5, and every later frame then arrives unstaged as well
+                p.PrefetchFramesDev(dev[i + 3], sizes[i + 3], frames[i + 3][1], [i + 4, i + 4])
+        # frame 6 is never staged: adding it drops the staged frame 7, which then arrives unstaged as well
         p.AddFramesDev(dev[i], sizes[i], st, [i + 1, i + 1])
     got, _ = _snapshot(p, True)
     _same(want, got, "device prefetch")
