@@ -94,3 +94,15 @@ def test_header_caller_reproduces_the_ctypes_trajectory(gpu, synth, tmp_path):
     for k, kind in enumerate(("edges", "planes", "blobs")):
         assert capi.pcd_read(str(tmp_path / ("cxx_" + kind + ".pcd"))).tobytes() == g.GetMap(k, True).tobytes()
     assert "Localization skipped" in r.stderr                 # first frame: the reference's own message on stderr (Slam.cxx:1098-1107)
+
+
+def test_helper_thread_class(built, tmp_path):
+    """lidarslam_b200/csrc/host/worker.h (deferred map update, staged inputs): FIFO order, wait / done / drain, exceptions
+    reach the waiter, sleeping helpers wake up - host logic, no GPU (tests/cxx/worker_test.cpp)."""
+    exe = str(tmp_path / "worker_test")
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-I" + os.path.join(cuda, "include"),
+                           os.path.join(ROOT, "tests", "cxx", "worker_test.cpp"), "-o", exe, "-L" + os.path.join(cuda, "lib64"), "-lcudart",
+                           "-lpthread", "-Wl,-rpath," + os.path.join(cuda, "lib64")])
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "worker ok" in r.stdout, r.stdout + r.stderr
