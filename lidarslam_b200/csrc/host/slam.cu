@@ -331,9 +331,14 @@ int lsb_slam::PrefetchFrames(int n_frames, const lsb_point* const* frames, const
     const int nf = (int)slot->src.size();
     UploadFrames(slot->frames, nf, slot->src.data(), slot->n.data(), slot->stamp.data(), slot->seq.data(), slot->on_device, cfg, istream);
     unsigned spins = 0;
+    bool nap = false;
+    const auto t0 = std::chrono::steady_clock::now();
     while ((int)(frames_started.load(std::memory_order_acquire) - gate) < 0 &&
            (int)(stage_release.load(std::memory_order_acquire) - my_seq) < 0) {
       if ((++spins & 63u) == 0) std::this_thread::yield();
+      // frames arrive back to back: spin; the caller took a break (more than a few frame periods): stop burning a core
+      if ((spins & 1023u) == 0 && !nap) nap = std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(10);
+      if (nap) std::this_thread::sleep_for(std::chrono::microseconds(100));
     }
     ExtractInto(slot->frames, (size_t)nf, slot->stamp[0], cfg, slot, slot->kp, slot->tmin, slot->tmax, istream);
     LSB_CUDA(cudaEventRecord(slot->ready, istream));
@@ -427,7 +432,8 @@ int lsb_slam::AddFrames(int n_frames, const lsb_point* const* frames, const size
   for (int i = 0; i < n_frames; ++i) Stats.n_points += (uint32_t)n[i];
   if (hit) {
     stage_release.store(hit->stage_seq, std::memory_order_release);   // (added out of turn: its own gate may still be closed)
-    Worker().wait(hit->ticket);               // upload + extraction enqueued and their counts read back (rethrows)
+    try { Worker().wait(hit->ticket); }       // upload + extraction enqueued and their counts read back (rethrows)
+    catch (...) { hit->valid = false; throw; }
     FramePool.swap(hit->frames);
     LSB_CUDA(cudaStreamWaitEvent(stream, hit->ready, 0));
   } else {
