@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(TPB) k_finish_keypoints(FinishArgs a, const Ic
 
 // Head of the sub-map selection of one keypoint type, one launch: the undistortion still pending on the cloud (k_undistort)
 // and the box of the cloud under the predicted pose, pcl::transformPointCloud (PCL <= 1.10 explicit form) then
-// pcl::getMinMax3D (k_transformed_bbox), published like the box above.
+// pcl::getMinMax3D, published like the box above.
 __global__ void __launch_bounds__(TPB) k_undistort_transformed_bbox(lsb_point* __restrict__ pts, int n, Interpolator it, int undistort, Iso3d T,
                                                                     int* __restrict__ partial, unsigned* __restrict__ counter,
                                                                     int* __restrict__ d_bb, int* __restrict__ h_bb, int seq)
@@ -226,68 +226,7 @@ __global__ void k_undistort_state(lsb_point* __restrict__ pts, int n, const IcpS
 
 __global__ void k_icp_init(IcpState* st, IcpState init) { *st = init; }
 
-// order-preserving map double -> uint64 for atomicMin/atomicMax
-__host__ __device__ __forceinline__ unsigned long long d2ord(double d)
-{
-  unsigned long long u;
-#ifdef __CUDA_ARCH__
-  u = (unsigned long long)__double_as_longlong(d);
-#else
-  std::memcpy(&u, &d, 8);
-#endif
-  return (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);
-}
-inline double ord2d(unsigned long long u)
-{
-  u = (u & 0x8000000000000000ull) ? (u & 0x7fffffffffffffffull) : ~u;
-  double d;
-  std::memcpy(&d, &u, 8);
-  return d;
-}
-
-__global__ void k_minmax_init(unsigned long long* mm) { mm[0] = ~0ull; mm[1] = 0ull; }
-
-__global__ void k_time_minmax(const lsb_point* __restrict__ pts, int n, unsigned long long* __restrict__ mm)
-{
-  unsigned long long mn = ~0ull, mx = 0ull;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const unsigned long long o = d2ord(pts[i].time);
-    mn = min(mn, o); mx = max(mx, o);
-  }
-  for (int off = 16; off; off >>= 1) {
-    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, off));
-    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-  }
-  if ((threadIdx.x & 31) == 0) { atomicMin(mm, mn); atomicMax(mm + 1, mx); }
-}
-
-__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return (i >= 0) ? i : (i ^ 0x7fffffff); }
 __global__ void k_bbox_init(int* bb) { if (threadIdx.x < 3) bb[threadIdx.x] = INT_MAX; else if (threadIdx.x < 6) bb[threadIdx.x] = INT_MIN; }
-
-// pcl::transformPointCloud (PCL <= 1.10 explicit form) then pcl::getMinMax3D
-__global__ void k_transformed_bbox(const lsb_point* __restrict__ pts, int n, Iso3d T, int* __restrict__ bb)
-{
-  int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    float fx, fy, fz;
-    load_xyz(pts + i, fx, fy, fz);
-    const double x = fx, y = fy, z = fz;
-    const float wx = (float)(T.R.m[0] * x + T.R.m[1] * y + T.R.m[2] * z + T.t.x);
-    const float wy = (float)(T.R.m[3] * x + T.R.m[4] * y + T.R.m[5] * z + T.t.y);
-    const float wz = (float)(T.R.m[6] * x + T.R.m[7] * y + T.R.m[8] * z + T.t.z);
-    const int v[3] = {f2ord(wx), f2ord(wy), f2ord(wz)};
-#pragma unroll
-    for (int a = 0; a < 3; ++a) { mn[a] = min(mn[a], v[a]); mx[a] = max(mx[a], v[a]); }
-  }
-#pragma unroll
-  for (int a = 0; a < 3; ++a) {
-    for (int off = 16; off; off >>= 1) {
-      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], off));
-      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], off));
-    }
-    if ((threadIdx.x & 31) == 0) { atomicMin(bb + a, mn[a]); atomicMax(bb + 3 + a, mx[a]); }
-  }
-}
 
 }  // namespace
 
@@ -354,40 +293,6 @@ void dev_undistort_state(lsb_point* d_pts, size_t n, const IcpState* st, int mod
 void dev_icp_init(IcpState* d_state, const IcpState& init, cudaStream_t s, LaunchCounter& lc)
 {
   k_icp_init<<<1, 1, 0, s>>>(d_state, init); LSB_LAUNCH_CHECK(); lc.add();
-}
-
-void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc)
-{
-  k_minmax_init<<<1, 1, 0, s>>>(d_mm); LSB_LAUNCH_CHECK(); lc.add();
-}
-
-void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc)
-{
-  if (!n) return;
-  k_time_minmax<<<std::min(div_up(n, TPB), 592u), TPB, 0, s>>>(d_pts, (int)n, d_mm); LSB_LAUNCH_CHECK(); lc.add();
-}
-
-void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx)
-{
-  mn = ord2d(h_mm[0]);
-  mx = ord2d(h_mm[1]);
-}
-
-void dev_transformed_bbox_async(const lsb_point* d_pts, size_t n, const Iso3d& T, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
-                                cudaStream_t s, LaunchCounter& lc)
-{
-  d_bbox.reserve(8, s); h_bbox.reserve(8);
-  k_bbox_init<<<1, 32, 0, s>>>((int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add();
-  if (n) { k_transformed_bbox<<<std::min(div_up(n, TPB), 592u), TPB, 0, s>>>(d_pts, (int)n, T, (int*)d_bbox.p); LSB_LAUNCH_CHECK(); lc.add(); }
-  LSB_CUDA(cudaMemcpyAsync(h_bbox.p, d_bbox.p, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
-}
-
-void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,
-                          PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc)
-{
-  dev_transformed_bbox_async(d_pts, n, T, d_bbox, h_bbox, s, lc);
-  LSB_CUDA(cudaStreamSynchronize(s));
-  bbox_decode(h_bbox.p, mn, mx);
 }
 
 }  // namespace lsb

@@ -97,7 +97,6 @@ lsb_slam::lsb_slam(int dev) : device(dev)
     if (std::sscanf(e, "%f,%f,%f", &f[0], &f[1], &f[2]) == 3)
       for (int k = 0; k < 3; ++k) if (f[k] > 0.f) LocalMaps[k].knn_cell_factor = f[k];
   }
-  d_minmax.reserve(2, stream); h_minmax.reserve(2);
   Reset(true);
 }
 

@@ -171,10 +171,6 @@ struct lsb_slam {
   // scratch
   lsb::ConvertWorkspace conv;                                              // driver-cloud adaptors
   lsb::DevBuf<lsb_point> tmp_cloud;
-  lsb::DevBuf<unsigned long long> d_minmax;
-  lsb::PinnedBuf<unsigned long long> h_minmax;
-  lsb::DevBuf<float> d_bbox;
-  lsb::PinnedBuf<float> h_bbox;
   lsb::DevBuf<float> tmp_f;
   lsb::DevBuf<uint8_t> tmp_u8;
   cudaEvent_t ev[6] = {};
@@ -255,16 +251,7 @@ void dev_undistort_state(lsb_point* d_pts, size_t n, const IcpState* st, int mod
 void dev_icp_init(IcpState* d_state, const IcpState& init, cudaStream_t s, LaunchCounter& lc);
 // measured FP64 / FP32 peaks of the device (cuda/peaks.cu)
 void measure_fp_peaks(int device, double out_tflops[4]);
-void dev_time_minmax_begin(unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
-void dev_time_minmax(const lsb_point* d_pts, size_t n, unsigned long long* d_mm, cudaStream_t s, LaunchCounter& lc);
-void time_minmax_decode(const unsigned long long* h_mm, double& mn, double& mx);
-// bbox of (float)(T * p) in the pcl::transformPointCloud arithmetic (Slam.cxx:1026-1029): enqueue only
-// (decode h_bbox with bbox_decode after a sync), or both with one sync
 // LCP overlap estimator (cuda/lcp.cu)
 void dev_lcp_gather(const lsb_point* d_cloud, int nb, float ratio, float* d_q_xyz, cudaStream_t s, LaunchCounter& lc);
 void dev_lcp_reduce(const float* const d2[3], const float thr[3], int nb, DevBuf<float>& chunk_sum, float* d_out, cudaStream_t s, LaunchCounter& lc);
-void dev_transformed_bbox_async(const lsb_point* d_pts, size_t n, const Iso3d& T, DevBuf<float>& d_bbox, PinnedBuf<float>& h_bbox,
-                                cudaStream_t s, LaunchCounter& lc);
-void dev_transformed_bbox(const lsb_point* d_pts, size_t n, const Iso3d& T, float mn[3], float mx[3], DevBuf<float>& d_bbox,
-                          PinnedBuf<float>& h_bbox, cudaStream_t s, LaunchCounter& lc);
 }  // namespace lsb
